@@ -1,0 +1,105 @@
+"""
+oracle/latent.py -- TEST INFRASTRUCTURE (see oracle/__init__.py).
+
+CPU restatement of the latent-distance adjacency model's HMC target and its gradient
+(adjacency.py:209-219, 244-275, 356-421) and of hips-lib's HMC step (not in /root/reference;
+version unpinned; restated from its published code -- "recollection").
+The reference obtains the gradient from autograd (adjacency.py:375-379); here it is hand-derived
+ and pinned by a finite-difference test (tests/test_oracle_latent.py).
+"""
+import numpy as np
+
+
+def logit_matrix(L, mu_0, mu_self):
+    """adjacency.py:209-214 / 252-258:  -||l_i - l_j||^2 + mu_0 + mu_self * I."""
+    N = L.shape[0]
+    D = -((L[:, None, :] - L[None, :, :]) ** 2).sum(2)
+    return D + mu_0 + mu_self * np.eye(N)
+
+
+def hmc_log_probability(L, mu_0, mu_self, A, sigma):
+    """adjacency.py:244-275, literally (P = 1/(1+exp(-eta)); ll = sum A log P + (1-A) log(1-P))."""
+    eta = logit_matrix(L, mu_0, mu_self)
+    P = 1.0 / (1 + np.exp(-eta))
+    ll = np.sum(A * np.log(P) + (1 - A) * np.log(1 - P))
+    lp = -0.5 * np.sum(L * L / sigma)
+    lp += -0.5 * mu_0 ** 2
+    lp += -0.5 * mu_self ** 2
+    return ll + lp
+
+
+def log_probability_stable(L, mu_0, mu_self, A, sigma):
+    """Same value through softplus: A log s(eta) + (1-A) log(1-s(eta)) = A eta - softplus(eta)."""
+    eta = logit_matrix(L, mu_0, mu_self)
+    ll = np.sum(A * eta - np.logaddexp(0.0, eta))
+    return ll - 0.5 * np.sum(L * L) / sigma - 0.5 * mu_0 ** 2 - 0.5 * mu_self ** 2
+
+
+def log_probability_and_grad(L, mu_0, mu_self, A, sigma):
+    """Value and hand-derived gradients (what autograd returns at adjacency.py:375-379,398,415).
+
+    g_ij = A_ij - s(eta_ij);  d/dl_n = -2 sum_j (l_n - l_j)(g_nj + g_jn) - l_n/sigma;
+    d/dmu_0 = sum g - mu_0;  d/dmu_self = sum_i g_ii - mu_self.
+    """
+    eta = logit_matrix(L, mu_0, mu_self)
+    sig = 1.0 / (1.0 + np.exp(-eta))
+    g = A - sig
+    gs = g + g.T
+    lp = np.sum(A * eta - np.logaddexp(0.0, eta)) - 0.5 * np.sum(L * L) / sigma - 0.5 * mu_0 ** 2 - 0.5 * mu_self ** 2
+    gL = -2.0 * (gs.sum(1)[:, None] * L - gs.dot(L)) - L / sigma
+    gmu0 = g.sum() - mu_0
+    gmuself = np.trace(g) - mu_self
+    return lp, gL, gmu0, gmuself
+
+
+def hmc(U, grad_U, step_sz, n_steps, q_curr, draws, negative_log_prob=True,
+        avg_accept_rate=0.9, adaptive_step_sz=False, tgt_accept_rate=0.9,
+        avg_accept_time_const=0.95, min_step_sz=0.00005, max_step_sz=1.0):
+    """hips.inference.hmc.hmc (recollection), Neal's leapfrog HMC.
+
+    ``draws`` = (p0, log_u): injected momentum (standard normal, shape of q) and log-uniform for the
+    accept test.  With negative_log_prob=False, U is a log-probability (the reference's call,
+    adjacency.py:382-385) and is negated internally.
+    Returns q or (q, new_step_sz, new_accept_rate) when adaptive_step_sz.
+    """
+    p0, log_u = draws
+    if negative_log_prob:
+        Uf, dUf = U, grad_U
+    else:
+        Uf, dUf = (lambda q: -1.0 * U(q)), (lambda q: -1.0 * grad_U(q))
+    q = np.array(q_curr, dtype=np.float64, copy=True)
+    p = np.array(p0, dtype=np.float64, copy=True)
+    p_curr = p.copy()
+    p = p - step_sz * dUf(q) / 2.0
+    for i in range(n_steps):
+        q = q + step_sz * p
+        if i < n_steps - 1:
+            p = p - step_sz * dUf(q)
+    p = p - step_sz * dUf(q) / 2.0
+    p = -p
+    U_curr = Uf(q_curr); K_curr = np.sum(p_curr ** 2) / 2.0
+    U_prop = Uf(q); K_prop = np.sum(p ** 2) / 2.0
+    accept = log_u < (U_curr - U_prop + K_curr - K_prop)
+    q_next = q if accept else np.array(q_curr, dtype=np.float64, copy=True)
+    if adaptive_step_sz:
+        new_rate = avg_accept_time_const * avg_accept_rate + (1.0 - avg_accept_time_const) * float(accept)
+        new_step = step_sz * 1.02 if new_rate > tgt_accept_rate else step_sz * 0.98
+        new_step = min(max(new_step, min_step_sz), max_step_sz)
+        return q_next, new_step, new_rate
+    return q_next
+
+
+def resample(L, mu_0, mu_self, A, sigma, step_sz, accept_rate, draws):
+    """adjacency.py:356-421: HMC on L (adaptive, 10 steps), then mu_0 and mu_self (step 0.005, 10 steps).
+    draws = dict(L=(p0[N,D], log_u), mu_0=(p0, log_u), mu_self=(p0, log_u))."""
+    lpL = lambda Lq: log_probability_and_grad(Lq, mu_0, mu_self, A, sigma)[0]
+    dlpL = lambda Lq: log_probability_and_grad(Lq, mu_0, mu_self, A, sigma)[1]
+    L, step_sz, accept_rate = hmc(lpL, dlpL, step_sz, 10, L.copy(), draws["L"], negative_log_prob=False,
+                                  avg_accept_rate=accept_rate, adaptive_step_sz=True)
+    lp0 = lambda m: log_probability_and_grad(L, float(m), mu_self, A, sigma)[0]
+    dlp0 = lambda m: np.array(log_probability_and_grad(L, float(m), mu_self, A, sigma)[2])
+    mu_0 = float(hmc(lp0, dlp0, 0.005, 10, np.array(mu_0), draws["mu_0"], negative_log_prob=False))
+    lps = lambda m: log_probability_and_grad(L, mu_0, float(m), A, sigma)[0]
+    dlps = lambda m: np.array(log_probability_and_grad(L, mu_0, float(m), A, sigma)[3])
+    mu_self = float(hmc(lps, dlps, 0.005, 10, np.array(mu_self), draws["mu_self"], negative_log_prob=False))
+    return L, mu_0, mu_self, step_sz, accept_rate
