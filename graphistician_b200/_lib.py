@@ -1,0 +1,127 @@
+"""ctypes binding of libgk.so (include/gk.h).  There is no CPU fallback: a missing library or a missing
+CUDA device raises, loudly, at first use."""
+import ctypes
+import os
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libgk.so")
+
+GK_F32, GK_F64 = 0, 1
+SELF_SKIP, SELF_ONCE, SELF_TWICE = 0, 1, 2
+SAMPLER_CUMSUM, SAMPLER_LSE = 0, 1
+
+c_int, c_i64, c_dbl, c_vp, c_sz = ctypes.c_int, ctypes.c_int64, ctypes.c_double, ctypes.c_void_p, ctypes.c_size_t
+PI64 = ctypes.POINTER(ctypes.c_int64)
+
+# name -> (restype, argtypes); every symbol include/gk.h declares (tests/test_abi.py checks the two agree)
+SIGNATURES = {
+    "gk_ctx_create": (c_int, [c_int, ctypes.POINTER(c_vp)]),
+    "gk_ctx_destroy": (None, [c_vp]),
+    "gk_last_error": (ctypes.c_char_p, [c_vp]),
+    "gk_ctx_set_stream": (c_int, [c_vp, c_vp]),
+    "gk_ctx_synchronize": (c_int, [c_vp]),
+    "gk_ctx_launch_count": (c_i64, [c_vp]),
+    "gk_ctx_kernel_timing": (c_int, [c_vp, c_int]),
+    "gk_ctx_kernel_timing_read": (c_int, [c_vp, c_int, ctypes.POINTER(c_dbl), PI64, ctypes.POINTER(c_dbl)]),
+    "gk_network_create": (c_int, [c_vp, c_int, c_int, c_int, c_int, c_int, ctypes.POINTER(c_vp)]),
+    "gk_network_upload": (c_int, [c_vp, c_vp, c_vp, c_vp, c_int, c_vp, c_vp]),
+    "gk_network_set_diag": (c_int, [c_vp, c_vp, c_vp, c_vp]),
+    "gk_network_destroy": (c_int, [c_vp, c_vp]),
+    "gk_network_device_bytes": (c_sz, [c_vp]),
+    "gk_block_stats": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
+    "gk_sbm_sweep": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_dbl, c_vp, c_int,
+                             c_vp, PI64]),
+    "gk_sbm_sweep_begin": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_dbl, c_vp]),
+    "gk_sbm_partial_len": (c_sz, [c_vp, c_int]),
+    "gk_sbm_block_partials": (c_int, [c_vp, c_vp, c_int, c_int, c_vp]),
+    "gk_sbm_block_sample": (c_int, [c_vp, c_vp, c_int, c_int, c_vp]),
+    "gk_sbm_get_block": (c_int, [c_vp, c_int, c_int, c_vp]),
+    "gk_sbm_set_block": (c_int, [c_vp, c_int, c_int, c_vp]),
+    "gk_sbm_sweep_end": (c_int, [c_vp, c_vp, c_vp, c_vp, PI64]),
+}
+
+_lib = None
+
+
+class GKError(RuntimeError):
+    pass
+
+
+def load():
+    """dlopen libgk.so and type every entry point.  Raises if the library was not built."""
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise GKError("libgk.so not found at %s: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                          "(there is no CPU fallback)" % LIB_PATH)
+        lib = ctypes.CDLL(LIB_PATH)
+        for name, (res, args) in SIGNATURES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def ptr(a):
+    """Host pointer of a C-contiguous ndarray (None -> NULL)."""
+    if a is None:
+        return None
+    assert a.flags["C_CONTIGUOUS"]
+    return a.ctypes.data
+
+
+class Context:
+    """One gk_ctx: a device, a stream, scratch.  Not thread-safe (as the reference is not)."""
+
+    def __init__(self, device=0):
+        self.lib = load()
+        h = c_vp()
+        rc = self.lib.gk_ctx_create(device, ctypes.byref(h))
+        if rc != 0:
+            raise GKError("gk_ctx_create(device=%d) failed with %d: no usable CUDA device "
+                          "(this engine has no CPU fallback)" % (device, rc))
+        self.h = h
+        self.device = device
+
+    def check(self, rc):
+        if rc != 0:
+            raise GKError("libgk error %d: %s" % (rc, self.lib.gk_last_error(self.h).decode()))
+
+    def set_stream(self, cuda_stream):
+        self.check(self.lib.gk_ctx_set_stream(self.h, c_vp(cuda_stream)))
+
+    def synchronize(self):
+        self.check(self.lib.gk_ctx_synchronize(self.h))
+
+    def launch_count(self):
+        return int(self.lib.gk_ctx_launch_count(self.h))
+
+    def kernel_timing(self, enable):
+        self.check(self.lib.gk_ctx_kernel_timing(self.h, int(enable)))
+
+    def kernel_timing_read(self, family):
+        ms, n, b = c_dbl(), c_i64(), c_dbl()
+        self.check(self.lib.gk_ctx_kernel_timing_read(self.h, family, ctypes.byref(ms), ctypes.byref(n), ctypes.byref(b)))
+        return ms.value, n.value, b.value
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.gk_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+_default_ctx = {}
+
+
+def default_context(device=0):
+    if device not in _default_ctx:
+        _default_ctx[device] = Context(device)
+    return _default_ctx[device]

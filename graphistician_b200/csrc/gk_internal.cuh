@@ -1,0 +1,68 @@
+// gk_internal.cuh -- shared host/device declarations for libgk.so (not part of the C ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string>
+#include <vector>
+#include "../../include/gk.h"
+
+#define GK_PAD 128            // columns of every N x N device array are padded to a multiple of this
+#define GK_NFAMILY 8
+
+struct gk_timing {
+    double ms = 0.0; int64_t launches = 0; double bytes = 0.0;
+    std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending; std::vector<double> pending_bytes;
+};
+
+struct gk_ctx {
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    bool own_stream = false;
+    int num_sms = 148;
+    int64_t launches = 0;
+    bool timing = false;
+    gk_timing fam[GK_NFAMILY];
+    std::string err;
+    // scratch (grown on demand, freed with the ctx)
+    void *scratch[8] = {nullptr}; size_t scratch_bytes[8] = {0};
+    // state of an open sharded sweep
+    struct gk_sweep *sweep = nullptr;
+};
+
+struct gk_net {
+    int N = 0, B = 0, dtype = GK_F32, row0 = 0, nrows = 0;
+    int ld = 0;                       // padded column count (multiple of GK_PAD)
+    uint8_t *A = nullptr, *At = nullptr;   // nrows x ld
+    void *W = nullptr, *Wt = nullptr;      // nrows x ld x B of dtype
+    uint8_t *diagA = nullptr;              // N   (A[n,n]; replicated on every rank)
+    double *diagW = nullptr;               // N x B
+    bool have_diag = false;
+    size_t bytes = 0;
+    // lazily built symmetric forms for the eigenmodel / latent-distance passes
+    uint8_t *Asym = nullptr;               // nrows x ld : A + A^T
+};
+
+int gk_fail(gk_ctx *ctx, int code, const char *fmt, ...);
+void *gk_scratch(gk_ctx *ctx, int slot, size_t bytes);   // returns nullptr (and sets err) on failure
+
+#define GK_CUDA(ctx, call)                                                                     \
+    do {                                                                                       \
+        cudaError_t _e = (call);                                                               \
+        if (_e != cudaSuccess)                                                                 \
+            return gk_fail((ctx), GK_ECUDA, "%s:%d %s: %s", __FILE__, __LINE__, #call,         \
+                           cudaGetErrorString(_e));                                            \
+    } while (0)
+
+#define GK_CHECK_LAUNCH(ctx)                                                                   \
+    do {                                                                                       \
+        (ctx)->launches++;                                                                     \
+        GK_CUDA((ctx), cudaGetLastError());                                                    \
+    } while (0)
+
+// timing brackets around a kernel family (no-ops unless gk_ctx_kernel_timing(ctx, 1))
+void gk_time_begin(gk_ctx *ctx, int family, double bytes);
+void gk_time_end(gk_ctx *ctx, int family);
+
+static inline int gk_pad(int n) { return (n + GK_PAD - 1) / GK_PAD * GK_PAD; }
+static inline size_t gk_esize(int dtype) { return dtype == GK_F64 ? 8 : 4; }

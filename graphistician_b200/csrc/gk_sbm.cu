@@ -1,0 +1,355 @@
+// gk_sbm.cu -- host side of the SBM path: coefficient tables, launch plans, C-ABI entry points.
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+#include "gk_sbm_seq.cuh"
+
+struct gk_sweep {
+    int K = 0, S = 0, N = 0, sampler = 0;
+    // device pointers (carved from ctx scratch)
+    double *tables = nullptr; gk_tables T{};
+    int32_t *c = nullptr; uint8_t *c8 = nullptr; int *sizes = nullptr; unsigned long long *nchanged = nullptr;
+    double *u = nullptr, *out_lp = nullptr, *lp = nullptr, *stats = nullptr;
+    bool want_lp = false;
+};
+
+static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
+
+// sum_edges log N(w; mu, Sigma) = n*c0 + c1.sum_w + sum_{b<=b'} C2s[b,b'] sum_ww[b,b']   (B <= 2, closed form)
+static bool gauss_coef(int B, const double *mu, const double *sg, double *c0, double *c1, double *C2s) {
+    const double LOG2PI = 1.8378770664093453;
+    if (B == 1) {
+        if (!(sg[0] > 0)) return false;
+        double iv = 1.0 / sg[0];
+        c1[0] = iv * mu[0]; *c0 = -0.5 * (LOG2PI + log(sg[0]) + mu[0] * c1[0]); C2s[0] = -0.5 * iv;
+        return true;
+    }
+    double a = sg[0], b = 0.5 * (sg[1] + sg[2]), d = sg[3], det = a * d - b * b;
+    if (!(det > 0) || !(a > 0)) return false;
+    double i00 = d / det, i01 = -b / det, i11 = a / det;
+    c1[0] = i00 * mu[0] + i01 * mu[1]; c1[1] = i01 * mu[0] + i11 * mu[1];
+    *c0 = -0.5 * (2 * LOG2PI + log(det) + mu[0] * c1[0] + mu[1] * c1[1]);
+    C2s[0] = -0.5 * i00; C2s[1] = -i01; C2s[2] = -0.5 * i11;     // packed (0,0),(0,1)x2,(1,1)
+    return true;
+}
+
+// host build of COt / CIt / L1 / selfc / selfa / logm into one contiguous blob
+static int build_tables(gk_ctx *ctx, int K, int B, const double *log_m, const double *p, const double *mu,
+                        const double *sigma, int self_mode, double beta, std::vector<double> &blob, size_t off[6]) {
+    const int S = 1 + B + B * (B + 1) / 2, KS = K * S;
+    off[0] = 0; off[1] = off[0] + (size_t)KS * K; off[2] = off[1] + (size_t)KS * K; off[3] = off[2] + (size_t)K * K;
+    off[4] = off[3] + K; off[5] = off[4] + (size_t)S * K;
+    blob.assign(off[5] + K, 0.0);
+    double *COt = &blob[off[0]], *CIt = &blob[off[1]], *L1 = &blob[off[2]], *selfc = &blob[off[3]],
+           *selfa = &blob[off[4]], *logm = &blob[off[5]];
+    std::vector<double> cell((size_t)K * K * S, 0.0), l1m((size_t)K * K, 0.0);   // cell[(k,k')][s]
+    for (int k = 0; k < K; ++k)
+        for (int k2 = 0; k2 < K; ++k2) {
+            double *cs = &cell[((size_t)k * K + k2) * S];
+            if (p) {
+                double pv = p[k * K + k2];
+                if (!(pv >= 0.0 && pv <= 1.0)) return gk_fail(ctx, GK_EINVAL, "p[%d,%d]=%g outside [0,1]", k, k2, pv);
+                pv = std::min(std::max(pv, 1e-300), 1.0 - 1e-16);
+                double lg = log(pv), l1 = log1p(-pv);
+                cs[0] += beta * (lg - l1);
+                l1m[(size_t)k * K + k2] = beta * l1;
+            }
+            if (mu && B > 0) {
+                double c0, c1[2], C2s[3];
+                if (!gauss_coef(B, mu + ((size_t)k * K + k2) * B, sigma + ((size_t)k * K + k2) * B * B, &c0, c1, C2s))
+                    return gk_fail(ctx, GK_EINVAL, "Sigma[%d,%d] is not positive definite", k, k2);
+                cs[0] += beta * c0;
+                for (int b = 0; b < B; ++b) cs[1 + b] += beta * c1[b];
+                for (int j = 0; j < B * (B + 1) / 2; ++j) cs[1 + B + j] += beta * C2s[j];
+            }
+        }
+    for (int k = 0; k < K; ++k)
+        for (int k2 = 0; k2 < K; ++k2) {
+            for (int s = 0; s < S; ++s) {
+                COt[((size_t)k2 * S + s) * K + k] = cell[((size_t)k * K + k2) * S + s];
+                CIt[((size_t)k2 * S + s) * K + k] = cell[((size_t)k2 * K + k) * S + s];
+            }
+            L1[(size_t)k * K + k2] = l1m[(size_t)k * K + k2] + l1m[(size_t)k2 * K + k];
+        }
+    const double mult = self_mode == GK_SELF_TWICE ? 2.0 : (self_mode == GK_SELF_ONCE ? 1.0 : 0.0);
+    for (int k = 0; k < K; ++k) {
+        logm[k] = log_m[k];
+        if (mult == 0.0) continue;
+        selfc[k] = mult * l1m[(size_t)k * K + k];
+        for (int s = 0; s < S; ++s) selfa[(size_t)s * K + k] = cell[((size_t)k * K + k) * S + s];
+        if (p) {   // the adjacency part of s=0 is doubled in TWICE mode; the Gaussian part is not
+            double pv = std::min(std::max(p[k * K + k], 1e-300), 1.0 - 1e-16);
+            selfa[k] += (mult - 1.0) * beta * (log(pv) - log1p(-pv));
+        }
+    }
+    return GK_OK;
+}
+
+template <typename T, int B>
+static int launch_strip(gk_ctx *ctx, gk_net *net, const uint8_t *c8, int K, int n0, int nb_pad, int dir_first, int ndirs,
+                        void **partial_out, int *nchunks_out) {
+    typedef typename gk_acc<T, B>::type ACC;
+    constexpr int S = gk_sdim<B>::S;
+    int strips = nb_pad / GK_STRIP_COLS;
+    int want = (2 * ctx->num_sms + strips * ndirs - 1) / (strips * ndirs);
+    int chunk_rows = (net->nrows + want - 1) / want;
+    chunk_rows = std::min(std::max(chunk_rows, 64), GK_MAX_CHUNK_ROWS);
+    chunk_rows = (chunk_rows + 3) / 4 * 4;
+    int nchunks = (net->nrows + chunk_rows - 1) / chunk_rows;
+    size_t pbytes = (size_t)ndirs * nchunks * nb_pad * K * S * sizeof(ACC);
+    void *partial = gk_scratch(ctx, 2, pbytes);
+    if (!partial) return GK_ENOMEM;
+    gk_strip_params P;
+    P.Abase[0] = net->At; P.Abase[1] = net->A; P.Wbase[0] = net->Wt; P.Wbase[1] = net->W;
+    P.ld = net->ld; P.row0 = net->row0; P.nrows = net->nrows; P.n0 = n0; P.nb_pad = nb_pad; P.dir_first = dir_first;
+    P.c8 = c8; P.K = K; P.chunk_rows = chunk_rows; P.nchunks = nchunks; P.partial = partial;
+    int U = std::max(K, GK_STRIP_WARPS);
+    size_t smem = (size_t)U * S * GK_SLOT_PITCH * sizeof(ACC) + (size_t)chunk_rows * 3 + 16;
+    static bool attr_set = false;
+    if (!attr_set) {
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_strip_stats<T, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
+        attr_set = true;
+    }
+    double bytes = (double)net->nrows * (double)std::min(nb_pad, net->N - n0) * (1.0 + B * sizeof(T)) * ndirs;
+    gk_time_begin(ctx, 0, bytes);
+    k_strip_stats<T, B><<<dim3(strips, nchunks, ndirs), GK_STRIP_THREADS, smem, ctx->stream>>>(P);
+    gk_time_end(ctx, 0);
+    GK_CHECK_LAUNCH(ctx);
+    *partial_out = partial; *nchunks_out = nchunks;
+    return GK_OK;
+}
+
+template <typename T, int B>
+static int strip_to_stats(gk_ctx *ctx, gk_net *net, const uint8_t *c8, int K, int n0, int nb_pad, int dir_first, int ndirs,
+                          double *stats_dev) {
+    typedef typename gk_acc<T, B>::type ACC;
+    void *partial; int nchunks;
+    int rc = launch_strip<T, B>(ctx, net, c8, K, n0, nb_pad, dir_first, ndirs, &partial, &nchunks);
+    if (rc) return rc;
+    size_t total = (size_t)nb_pad * ndirs * K * gk_sdim<B>::S;
+    int grid = (int)std::min<size_t>((total + 255) / 256, (size_t)ctx->num_sms * 8);
+    k_reduce_partials<ACC><<<grid, 256, 0, ctx->stream>>>((const ACC *)partial, stats_dev, ndirs, nchunks, nb_pad, K * gk_sdim<B>::S);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+#define GK_DISPATCH_TB(net, CALL)                                                      \
+    ((net)->dtype == GK_F32                                                            \
+         ? ((net)->B == 0 ? CALL(float, 0) : (net)->B == 1 ? CALL(float, 1) : CALL(float, 2))   \
+         : ((net)->B == 0 ? CALL(double, 0) : (net)->B == 1 ? CALL(double, 1) : CALL(double, 2)))
+
+// ---------------------------------------------------------------------------------------------
+// K1
+// ---------------------------------------------------------------------------------------------
+extern "C" int gk_block_stats(gk_ctx *ctx, gk_net *net, const int32_t *c, int K, int64_t *n_edge, double *sum_w,
+                              double *sum_ww) {
+    if (!ctx || !net || !c || !n_edge) return GK_EINVAL;
+    if (K < 1 || K > GK_MAX_K) return gk_fail(ctx, GK_EUNSUPPORTED, "K=%d: this build supports 1 <= K <= %d", K, GK_MAX_K);
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int N = net->N, B = net->B, S = 1 + B + B * (B + 1) / 2, KS = K * S;
+    for (int i = 0; i < N; ++i) if (c[i] < 0 || c[i] >= K) return gk_fail(ctx, GK_EINVAL, "c[%d]=%d outside [0,%d)", i, c[i], K);
+    // labels
+    size_t lab_bytes = align_up((size_t)N * 4, 256) + align_up((size_t)N, 256);
+    char *lab = (char *)gk_scratch(ctx, 5, lab_bytes);
+    if (!lab) return GK_ENOMEM;
+    int32_t *c_dev = (int32_t *)lab; uint8_t *c8 = (uint8_t *)(lab + align_up((size_t)N * 4, 256));
+    GK_CUDA(ctx, cudaMemcpyAsync(c_dev, c, (size_t)N * 4, cudaMemcpyHostToDevice, ctx->stream));
+    k_narrow_labels<<<(N + 255) / 256, 256, 0, ctx->stream>>>(c_dev, c8, N);
+    GK_CHECK_LAUNCH(ctx);
+    // cell accumulator
+    const int nparts = 128;
+    size_t cell_bytes = align_up((size_t)K * KS * 8, 256) + (size_t)nparts * K * KS * 8;
+    char *cellbuf = (char *)gk_scratch(ctx, 7, cell_bytes);
+    if (!cellbuf) return GK_ENOMEM;
+    double *cell = (double *)cellbuf, *cellpart = (double *)(cellbuf + align_up((size_t)K * KS * 8, 256));
+    GK_CUDA(ctx, cudaMemsetAsync(cell, 0, (size_t)K * KS * 8, ctx->stream));
+    // node blocks of at most 16384 target nodes per pass (bounds the partial buffers)
+    const int NBMAX = 16384;
+    for (int n0 = 0; n0 < N; n0 += NBMAX) {
+        int nb = std::min(NBMAX, N - n0), nb_pad = (nb + GK_STRIP_COLS - 1) / GK_STRIP_COLS * GK_STRIP_COLS;
+        double *stats = (double *)gk_scratch(ctx, 3, (size_t)nb_pad * KS * 8);
+        if (!stats) return GK_ENOMEM;
+#define CALL_K1(T, BB) strip_to_stats<T, BB>(ctx, net, c8, K, n0, nb_pad, 1, 1, stats)
+        int rc = GK_DISPATCH_TB(net, CALL_K1);
+        if (rc) return rc;
+        k_cell_partial<<<nparts, 128, (size_t)K * KS * 8, ctx->stream>>>(stats, c8, n0, nb, N, K, KS, cellpart);
+        GK_CHECK_LAUNCH(ctx);
+        k_cell_final<<<(K * KS + 127) / 128, 128, 0, ctx->stream>>>(cellpart, nparts, K, S, cell);
+        GK_CHECK_LAUNCH(ctx);
+    }
+    std::vector<double> h((size_t)K * KS);
+    GK_CUDA(ctx, cudaMemcpyAsync(h.data(), cell, (size_t)K * KS * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int a = 0; a < K; ++a)
+        for (int b = 0; b < K; ++b) {
+            const double *cs = &h[((size_t)a * K + b) * S];
+            n_edge[a * K + b] = (int64_t)llround(cs[0]);
+            for (int i = 0; i < B; ++i) {
+                if (sum_w) sum_w[((size_t)a * K + b) * B + i] = cs[1 + i];
+                if (sum_ww)
+                    for (int j = 0; j < B; ++j) {
+                        int lo = std::min(i, j), hi = std::max(i, j);
+                        sum_ww[(((size_t)a * K + b) * B + i) * B + j] = cs[gk_sym_idx(B, lo, hi)];
+                    }
+            }
+        }
+    return GK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K2: sweep = begin -> per node block { partial statistics ; sample } -> end
+// ---------------------------------------------------------------------------------------------
+__global__ void k_set_block(int32_t *c, uint8_t *c8, int *sizes, const int32_t *newc, int n0, int nb) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < nb; i += gridDim.x * blockDim.x) {
+        int n = n0 + i, a = c[n], b = newc[i];
+        if (a != b) { c[n] = b; c8[n] = (uint8_t)b; atomicSub(&sizes[a], 1); atomicAdd(&sizes[b], 1); }
+    }
+}
+
+extern "C" int gk_sbm_sweep_begin(gk_ctx *ctx, gk_net *net, const int32_t *c, int K, const double *log_m, const double *p,
+                                  const double *mu, const double *sigma, int self_mode, int sampler, double beta,
+                                  const double *uniforms) {
+    if (!ctx || !net || !c || !log_m || !uniforms) return GK_EINVAL;
+    if (K < 1 || K > GK_MAX_K) return gk_fail(ctx, GK_EUNSUPPORTED, "K=%d: this build supports 1 <= K <= %d", K, GK_MAX_K);
+    if (self_mode < 0 || self_mode > 2 || sampler < 0 || sampler > 1) return gk_fail(ctx, GK_EINVAL, "bad self_mode/sampler");
+    if ((mu == nullptr) != (sigma == nullptr)) return gk_fail(ctx, GK_EINVAL, "mu and sigma must be given together");
+    if (mu && net->B == 0) return gk_fail(ctx, GK_EINVAL, "weight terms requested but the network has no W");
+    if (self_mode != GK_SELF_SKIP && !net->have_diag) return gk_fail(ctx, GK_EINVAL, "gk_network_set_diag must be called before a sweep with self terms");
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    const int N = net->N;
+    // when the weight term is off the kernels still stream W-less statistics: use B_eff = 0 tables of the net's S
+    const int B = net->B, S = 1 + B + B * (B + 1) / 2;
+    std::vector<int> sizes(K, 0);
+    for (int i = 0; i < N; ++i) {
+        if (c[i] < 0 || c[i] >= K) return gk_fail(ctx, GK_EINVAL, "c[%d]=%d outside [0,%d)", i, c[i], K);
+        sizes[c[i]]++;
+    }
+    std::vector<double> blob; size_t off[6];
+    int rc = build_tables(ctx, K, B, log_m, p, mu, sigma, self_mode, beta, blob, off);
+    if (rc) return rc;
+    delete ctx->sweep;
+    gk_sweep *sw = ctx->sweep = new gk_sweep();
+    sw->K = K; sw->S = S; sw->N = N; sw->sampler = sampler;
+    sw->tables = (double *)gk_scratch(ctx, 1, blob.size() * 8);
+    if (!sw->tables) return GK_ENOMEM;
+    GK_CUDA(ctx, cudaMemcpyAsync(sw->tables, blob.data(), blob.size() * 8, cudaMemcpyHostToDevice, ctx->stream));
+    sw->T.COt = sw->tables + off[0]; sw->T.CIt = sw->tables + off[1]; sw->T.L1 = sw->tables + off[2];
+    sw->T.selfc = sw->tables + off[3]; sw->T.selfa = sw->tables + off[4]; sw->T.logm = sw->tables + off[5];
+    size_t o_c = 0, o_c8 = o_c + align_up((size_t)N * 4, 256), o_sz = o_c8 + align_up((size_t)N, 256),
+           o_nc = o_sz + 256, o_u = o_nc + 256, tot = o_u + align_up((size_t)N * 8, 256);
+    char *st = (char *)gk_scratch(ctx, 5, tot);
+    if (!st) return GK_ENOMEM;
+    sw->c = (int32_t *)(st + o_c); sw->c8 = (uint8_t *)(st + o_c8); sw->sizes = (int *)(st + o_sz);
+    sw->nchanged = (unsigned long long *)(st + o_nc); sw->u = (double *)(st + o_u);
+    GK_CUDA(ctx, cudaMemcpyAsync(sw->c, c, (size_t)N * 4, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(sw->sizes, sizes.data(), (size_t)K * 4, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(sw->u, uniforms, (size_t)N * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemsetAsync(sw->nchanged, 0, 8, ctx->stream));
+    k_narrow_labels<<<(N + 255) / 256, 256, 0, ctx->stream>>>(sw->c, sw->c8, N);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));      // blob/sizes are host temporaries
+    return GK_OK;
+}
+
+extern "C" size_t gk_sbm_partial_len(gk_ctx *ctx, int nb) {
+    if (!ctx || !ctx->sweep || nb <= 0) return 0;
+    size_t nb_pad = (size_t)(nb + GK_STRIP_COLS - 1) / GK_STRIP_COLS * GK_STRIP_COLS;
+    return nb_pad * 2 * ctx->sweep->K * ctx->sweep->S;
+}
+
+extern "C" int gk_sbm_block_partials(gk_ctx *ctx, gk_net *net, int n0, int nb, double *stats_dev) {
+    if (!ctx || !net || !ctx->sweep || !stats_dev) return GK_EINVAL;
+    if (n0 < 0 || nb <= 0 || n0 + nb > net->N || n0 % GK_STRIP_COLS) return gk_fail(ctx, GK_EINVAL, "node block must start on a multiple of %d", GK_STRIP_COLS);
+    gk_sweep *sw = ctx->sweep;
+    int nb_pad = (nb + GK_STRIP_COLS - 1) / GK_STRIP_COLS * GK_STRIP_COLS;
+#define CALL_K2(T, BB) strip_to_stats<T, BB>(ctx, net, sw->c8, sw->K, n0, nb_pad, 0, 2, stats_dev)
+    return GK_DISPATCH_TB(net, CALL_K2);
+}
+
+template <typename T, int B>
+static int launch_sample(gk_ctx *ctx, gk_net *net, gk_sweep *sw, int n0, int nb, const double *stats_dev) {
+    int wpb = 8, grid = std::min((nb + wpb - 1) / wpb, ctx->num_sms * 4);
+    k_lp_from_stats<B><<<grid, wpb * 32, 0, ctx->stream>>>(stats_dev, sw->T, net->diagA, net->diagW, n0, nb, sw->N, sw->K, sw->lp);
+    GK_CHECK_LAUNCH(ctx);
+    gk_seq_params P;
+    P.n0 = n0; P.nb = nb; P.K = sw->K; P.N = sw->N; P.ld = net->ld; P.row0 = net->row0; P.sampler = sw->sampler;
+    P.c = sw->c; P.c8 = sw->c8; P.sizes = sw->sizes; P.lp = sw->lp; P.u = sw->u; P.T = sw->T;
+    P.A = net->A; P.At = net->At; P.W = net->W; P.Wt = net->Wt;
+    P.out_lp = sw->want_lp ? sw->out_lp : nullptr; P.nchanged = sw->nchanged;
+    gk_time_begin(ctx, 1, 0.0);
+    k_sbm_seq<T, B><<<1, GK_SEQ_THREADS, 0, ctx->stream>>>(P);
+    gk_time_end(ctx, 1);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+extern "C" int gk_sbm_block_sample(gk_ctx *ctx, gk_net *net, int n0, int nb, const double *stats_dev) {
+    if (!ctx || !net || !ctx->sweep || !stats_dev) return GK_EINVAL;
+    if (n0 < net->row0 || n0 + nb > net->row0 + net->nrows) return gk_fail(ctx, GK_EINVAL, "the sampling rank must own rows [%d,%d)", n0, n0 + nb);
+    gk_sweep *sw = ctx->sweep;
+    sw->lp = (double *)gk_scratch(ctx, 4, (size_t)nb * sw->K * 8);
+    if (!sw->lp) return GK_ENOMEM;
+#define CALL_SMP(T, BB) launch_sample<T, BB>(ctx, net, sw, n0, nb, stats_dev)
+    return GK_DISPATCH_TB(net, CALL_SMP);
+}
+
+// labels of a node block: read (after the owner sampled) / write (on the other ranks)
+extern "C" int gk_sbm_get_block(gk_ctx *ctx, int n0, int nb, int32_t *c_out) {
+    if (!ctx || !ctx->sweep || !c_out || n0 < 0 || n0 + nb > ctx->sweep->N) return GK_EINVAL;
+    GK_CUDA(ctx, cudaMemcpyAsync(c_out, ctx->sweep->c + n0, (size_t)nb * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}
+extern "C" int gk_sbm_set_block(gk_ctx *ctx, int n0, int nb, const int32_t *c_in) {
+    if (!ctx || !ctx->sweep || !c_in || n0 < 0 || n0 + nb > ctx->sweep->N) return GK_EINVAL;
+    gk_sweep *sw = ctx->sweep;
+    for (int i = 0; i < nb; ++i) if (c_in[i] < 0 || c_in[i] >= sw->K) return gk_fail(ctx, GK_EINVAL, "label out of range");
+    int32_t *tmp = (int32_t *)gk_scratch(ctx, 6, (size_t)nb * 4);
+    if (!tmp) return GK_ENOMEM;
+    GK_CUDA(ctx, cudaMemcpyAsync(tmp, c_in, (size_t)nb * 4, cudaMemcpyHostToDevice, ctx->stream));
+    k_set_block<<<(nb + 255) / 256, 256, 0, ctx->stream>>>(sw->c, sw->c8, sw->sizes, tmp, n0, nb);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}
+
+extern "C" int gk_sbm_sweep_end(gk_ctx *ctx, gk_net *net, int32_t *c_out, double *out_lp, int64_t *out_nchanged) {
+    if (!ctx || !ctx->sweep) return GK_EINVAL;
+    gk_sweep *sw = ctx->sweep;
+    unsigned long long nch = 0;
+    if (c_out) GK_CUDA(ctx, cudaMemcpyAsync(c_out, sw->c, (size_t)sw->N * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_lp && sw->want_lp) GK_CUDA(ctx, cudaMemcpyAsync(out_lp, sw->out_lp, (size_t)sw->N * sw->K * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(&nch, sw->nchanged, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (out_nchanged) *out_nchanged = (int64_t)nch;
+    delete sw; ctx->sweep = nullptr;
+    return GK_OK;
+}
+
+extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, const double *log_m, const double *p,
+                            const double *mu, const double *sigma, int self_mode, int sampler, double beta,
+                            const double *uniforms, int block_nodes, double *out_lp, int64_t *out_nchanged) {
+    if (!ctx || !net || !c_inout) return GK_EINVAL;
+    if (net->row0 != 0 || net->nrows != net->N) return gk_fail(ctx, GK_EINVAL, "gk_sbm_sweep needs an unsharded network; use the begin/partials/sample/end form");
+    if (K == 1) { if (out_nchanged) *out_nchanged = 0; return GK_OK; }      // C == 1: no-op (adjacency.py:657-658)
+    int rc = gk_sbm_sweep_begin(ctx, net, c_inout, K, log_m, p, mu, sigma, self_mode, sampler, beta, uniforms);
+    if (rc) return rc;
+    gk_sweep *sw = ctx->sweep;
+    const int N = net->N;
+    if (out_lp) {
+        sw->out_lp = (double *)gk_scratch(ctx, 6, (size_t)N * K * 8);
+        if (!sw->out_lp) return GK_ENOMEM;
+        sw->want_lp = true;
+    }
+    int bn = block_nodes > 0 ? block_nodes : 1024;
+    bn = std::max(GK_STRIP_COLS, bn / GK_STRIP_COLS * GK_STRIP_COLS);
+    for (int n0 = 0; n0 < N; n0 += bn) {
+        int nb = std::min(bn, N - n0);
+        size_t len = gk_sbm_partial_len(ctx, nb);
+        double *stats = (double *)gk_scratch(ctx, 3, len * 8);
+        if (!stats) return GK_ENOMEM;
+        if ((rc = gk_sbm_block_partials(ctx, net, n0, nb, stats))) return rc;
+        if ((rc = gk_sbm_block_sample(ctx, net, n0, nb, stats))) return rc;
+    }
+    return gk_sbm_sweep_end(ctx, net, c_inout, out_lp, out_nchanged);
+}

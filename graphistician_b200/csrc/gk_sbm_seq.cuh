@@ -1,0 +1,195 @@
+// gk_sbm_seq.cuh -- conditionals from statistics, the exact sequential sampler, and K1 cell reduction.
+#pragma once
+#include "gk_sbm_kernels.cuh"
+
+// Tables (all double, built on the host from p / mu / Sigma, see gk_sbm.cu build_tables):
+//   COt[(k'*S+s)*K + k] : coefficient of out-statistic s of block k' in lp[k]     (cell (k , k'))
+//   CIt[(k'*S+s)*K + k] : coefficient of in-statistic  s of block k' in lp[k]     (cell (k', k ))
+//   L1 [k*K + k']       : beta*(log(1-p[k,k']) + log(1-p[k',k]))  -- multiplies the block sizes
+//   selfc[k], selfa[s*K + k] : diagonal term  selfc + a_nn * sum_s x_s selfa[s]
+struct gk_tables {
+    const double *COt, *CIt, *L1, *selfc, *selfa, *logm;
+};
+
+// lp_base[n][k] = log m[k] + sum_{k',s} out[k'][s] COt + in[k'][s] CIt + self term   (no block-size term)
+// stats: [nb_pad][2][K*S] doubles.  One warp per node, lane = candidate block k.
+template <int B>
+__global__ void k_lp_from_stats(const double *__restrict__ stats, gk_tables Tb, const uint8_t *__restrict__ diagA,
+                                const double *__restrict__ diagW, int n0, int nb, int N, int K, double *__restrict__ lp) {
+    constexpr int S = gk_sdim<B>::S;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
+    const int KS = K * S;
+    for (int i = blockIdx.x * wpb + warp; i < nb; i += gridDim.x * wpb) {
+        const int n = n0 + i;
+        if (n >= N) continue;
+        const double *so = stats + ((size_t)i * 2 + 0) * KS, *si = stats + ((size_t)i * 2 + 1) * KS;
+        double v = 0.0;
+        if (lane < K) {
+            v = Tb.logm[lane] + Tb.selfc[lane];
+            for (int j = 0; j < KS; ++j) v += so[j] * Tb.COt[(size_t)j * K + lane] + si[j] * Tb.CIt[(size_t)j * K + lane];
+            if (diagA[n]) {
+                double x[S]; x[0] = 1.0;
+#pragma unroll
+                for (int b = 0; b < B; ++b) x[1 + b] = diagW[(size_t)n * B + b];
+#pragma unroll
+                for (int b = 0; b < B; ++b)
+#pragma unroll
+                    for (int b2 = b; b2 < B; ++b2) x[gk_sym_idx(B, b, b2)] = x[1 + b] * x[1 + b2];
+#pragma unroll
+                for (int s = 0; s < S; ++s) v += x[s] * Tb.selfa[(size_t)s * K + lane];
+            }
+            lp[(size_t)i * K + lane] = v;
+        }
+    }
+}
+
+struct gk_seq_params {
+    int n0, nb, K, N, ld, row0, sampler;
+    int32_t *c; uint8_t *c8; int *sizes;       // global state (device)
+    double *lp;                                // [nb][K] working conditionals (base, then corrected in place)
+    const double *u;                           // [N] injected uniforms
+    gk_tables T;
+    const uint8_t *A, *At; const void *W, *Wt; // local rows (must contain the block's rows)
+    double *out_lp;                            // optional [N][K]
+    unsigned long long *nchanged;
+};
+
+#define GK_SEQ_THREADS 1024
+#define GK_SEQ_WARPS 32
+
+// Exact serial Gibbs over nodes n0..n0+nb-1, run speculatively: all pending nodes of a window draw from their
+// current conditionals in parallel; everything up to and including the first node whose label changes is
+// committed; that change is pushed (rank-1 correction of lp) to the later nodes of the block; repeat.
+// A committed prefix saw exactly the state the serial loop would have seen, so results are identical.
+template <typename T, int B>
+__global__ void __launch_bounds__(GK_SEQ_THREADS, 1) k_sbm_seq(gk_seq_params P) {
+    constexpr int S = gk_sdim<B>::S;
+    __shared__ double T0[GK_MAX_K], dL1[GK_MAX_K], dCO[S * GK_MAX_K], dCI[S * GK_MAX_K];
+    __shared__ int ssz[GK_MAX_K];
+    __shared__ int s_first;
+    __shared__ unsigned char s_new[4096];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, K = P.K;
+    if (tid < K) ssz[tid] = P.sizes[tid];
+    if (tid == 0) s_first = 0x7fffffff;
+    __syncthreads();
+    if (tid < K) { double t = 0.0; for (int k2 = 0; k2 < K; ++k2) t += (double)ssz[k2] * P.T.L1[tid * K + k2]; T0[tid] = t; }
+    __syncthreads();
+    int cursor = 0, window = 64;
+    unsigned long long changed = 0;
+    while (cursor < P.nb) {
+        const int wend = min(P.nb, cursor + window);
+        for (int i = cursor + warp; i < wend; i += GK_SEQ_WARPS) {
+            const int n = P.n0 + i;
+            if (n >= P.N) { if (lane == 0) s_new[i - cursor] = 255; continue; }
+            const int ci = P.c[n];
+            double v = lane < K ? P.lp[(size_t)i * K + lane] + T0[lane] - P.T.L1[lane * K + ci] : -1e300;
+            double mx = v;
+            for (int o = 16; o; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            double e = lane < K ? exp(v - mx) : 0.0;
+            int newc;
+            if (P.sampler == GK_SAMPLER_CUMSUM) {
+                double cum = e;
+                for (int o = 1; o < 32; o <<= 1) { double t = __shfl_up_sync(0xffffffffu, cum, o); if (lane >= o) cum += t; }
+                double tot = __shfl_sync(0xffffffffu, cum, K - 1);
+                double r = P.u[n] * tot;
+                newc = __popc(__ballot_sync(0xffffffffu, lane < K && r > cum));
+            } else {
+                double tot = e;
+                for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+                double cum = e / tot;
+                for (int o = 1; o < 32; o <<= 1) { double t = __shfl_up_sync(0xffffffffu, cum, o); if (lane >= o) cum += t; }
+                newc = __popc(__ballot_sync(0xffffffffu, lane < K && cum < P.u[n]));
+            }
+            newc = min(newc, K - 1);
+            if (P.out_lp && lane < K) P.out_lp[(size_t)n * K + lane] = v;
+            if (lane == 0) { s_new[i - cursor] = (unsigned char)newc; if (newc != ci) atomicMin(&s_first, i); }
+        }
+        __syncthreads();
+        const int first = s_first;
+        __syncthreads();
+        if (first >= wend) {                       // nothing in the window moved: commit it all
+            cursor = wend; window = min(window * 2, 4096);
+            continue;
+        }
+        // commit nodes cursor..first; node `first` moves a -> b
+        const int ns = P.n0 + first, a = P.c[ns], b = s_new[first - cursor];
+        if (tid < K) {
+            dL1[tid] = P.T.L1[tid * K + b] - P.T.L1[tid * K + a];
+            for (int s = 0; s < S; ++s) {
+                dCO[s * K + tid] = P.T.COt[(size_t)(b * S + s) * K + tid] - P.T.COt[(size_t)(a * S + s) * K + tid];
+                dCI[s * K + tid] = P.T.CIt[(size_t)(b * S + s) * K + tid] - P.T.CIt[(size_t)(a * S + s) * K + tid];
+            }
+        }
+        __syncthreads();
+        const size_t rowoff = (size_t)(ns - P.row0) * P.ld;
+        const int rem = P.nb - first - 1;
+        for (int t = tid; t < rem * K; t += GK_SEQ_THREADS) {
+            const int i = first + 1 + t / K, k = t % K, n = P.n0 + i;
+            if (n >= P.N) continue;
+            // out-edge n -> ns lives in row ns of A^T; in-edge ns -> n lives in row ns of A
+            double xo[S], xi[S];
+            const bool eo = P.At[rowoff + n] != 0, ei = P.A[rowoff + n] != 0;
+            xo[0] = eo ? 1.0 : 0.0; xi[0] = ei ? 1.0 : 0.0;
+            if constexpr (B > 0) {
+                const T *wo = (const T *)P.Wt + (rowoff + n) * B, *wi = (const T *)P.W + (rowoff + n) * B;
+#pragma unroll
+                for (int bb = 0; bb < B; ++bb) { xo[1 + bb] = eo ? (double)wo[bb] : 0.0; xi[1 + bb] = ei ? (double)wi[bb] : 0.0; }
+#pragma unroll
+                for (int bb = 0; bb < B; ++bb)
+#pragma unroll
+                    for (int b2 = bb; b2 < B; ++b2) {
+                        xo[gk_sym_idx(B, bb, b2)] = xo[1 + bb] * xo[1 + b2];
+                        xi[gk_sym_idx(B, bb, b2)] = xi[1 + bb] * xi[1 + b2];
+                    }
+            }
+            double d = dL1[k];
+#pragma unroll
+            for (int s = 0; s < S; ++s) d += xo[s] * dCO[s * K + k] + xi[s] * dCI[s * K + k];
+            P.lp[(size_t)i * K + k] += d;
+        }
+        if (tid == 0) {
+            P.c[ns] = b; P.c8[ns] = (uint8_t)b;
+            P.sizes[a] -= 1; P.sizes[b] += 1;
+            s_first = 0x7fffffff;
+        }
+        changed++;
+        cursor = first + 1; window = max(64, window / 2);
+        __syncthreads();
+    }
+    if (tid == 0 && P.nchanged) atomicAdd(P.nchanged, changed);
+}
+
+// K1: fold per-node in-edge statistics  stats[n1][bin = c[n2]][s]  into cells (c[n2], c[n1]).
+// Each CTA owns a contiguous node range; thread j (< K*S) owns column j of a private [K][K*S] table
+// (no atomics, fixed order).  cellpart: [gridDim.x][K][K*S].
+__global__ void k_cell_partial(const double *__restrict__ stats, const uint8_t *__restrict__ c8, int n0, int nb, int N,
+                               int K, int KS, double *__restrict__ cellpart) {
+    extern __shared__ double tbl[];                  // [K][KS]
+    for (int t = threadIdx.x; t < K * KS; t += blockDim.x) tbl[t] = 0.0;
+    __syncthreads();
+    const int per = (nb + gridDim.x - 1) / gridDim.x;
+    const int lo = blockIdx.x * per, hi = min(nb, lo + per);
+    for (int j = threadIdx.x; j < KS; j += blockDim.x)
+        for (int i = lo; i < hi; ++i) {
+            int n = n0 + i;
+            if (n < N) tbl[c8[n] * KS + j] += stats[(size_t)i * KS + j];
+        }
+    __syncthreads();
+    for (int t = threadIdx.x; t < K * KS; t += blockDim.x) cellpart[(size_t)blockIdx.x * K * KS + t] = tbl[t];
+}
+
+// cell[(k_src*K + k_dst)*S + s] += sum over CTAs  (cellpart index: [cta][k_dst][k_src*S + s])
+__global__ void k_cell_final(const double *__restrict__ cellpart, int nparts, int K, int S, double *__restrict__ cell) {
+    const int KS = K * S;
+    for (int t = blockIdx.x * blockDim.x + threadIdx.x; t < K * KS; t += gridDim.x * blockDim.x) {
+        int kdst = t / KS, j = t - kdst * KS, ksrc = j / S, s = j - ksrc * S;
+        double v = 0.0;
+        for (int p = 0; p < nparts; ++p) v += cellpart[(size_t)p * K * KS + t];
+        cell[((size_t)ksrc * K + kdst) * S + s] += v;
+    }
+}
+
+// c (int32) -> c8 and block sizes are prepared on the host; this just narrows the labels on the device
+__global__ void k_narrow_labels(const int32_t *__restrict__ c, uint8_t *__restrict__ c8, int N) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) c8[i] = (uint8_t)c[i];
+}

@@ -1,0 +1,121 @@
+"""Device-resident network data and the thin numpy-facing wrappers over the C ABI.
+
+A ``DeviceNetwork`` is the engine's view of the reference's ``network`` argument -- the ``(A, W)`` tuple of
+the new API (networks.py:69-71) or the ``network.A / network.W`` object of the old API
+(stochastic_block_model.py:217-218): A (N x N, {0,1}) as uint8, W (N x N x B) as fp32 (default) or fp64
+(parity mode), both also held transposed so that in-edges stream as rows.
+"""
+import ctypes
+import weakref
+
+import numpy as np
+
+from . import _lib
+from ._lib import GK_F32, GK_F64, ptr
+
+
+class DeviceNetwork:
+    def __init__(self, A, W=None, dtype="f32", ctx=None, row0=0, nrows=None, At_rows=None, Wt_rows=None,
+                 diagA=None, diagW=None):
+        self.ctx = ctx or _lib.default_context()
+        A = np.asarray(A)
+        self.N = int(A.shape[1])
+        self.row0 = int(row0)
+        self.nrows = int(A.shape[0] if nrows is None else nrows)
+        assert A.shape == (self.nrows, self.N), "A must be (nrows, N)"
+        self.B = 0 if W is None else int(W.shape[2])
+        self.dtype = GK_F64 if dtype in ("f64", np.float64, "float64") else GK_F32
+        h = ctypes.c_void_p()
+        self.ctx.check(self.ctx.lib.gk_network_create(self.ctx.h, self.N, self.B, self.dtype, self.row0, self.nrows,
+                                                      ctypes.byref(h)))
+        self.h = h
+        self._finalizer = weakref.finalize(self, _destroy, self.ctx, h)
+        self.upload(A, W, At_rows, Wt_rows, diagA, diagW)
+
+    def upload(self, A, W=None, At_rows=None, Wt_rows=None, diagA=None, diagW=None):
+        """Host -> device copy of this rank's shard (and device-side transposes when unsharded)."""
+        A8 = _as_u8(A)
+        Wc, wdt = _as_w(W)
+        At8 = _as_u8(At_rows) if At_rows is not None else None
+        Wtc = _as_w(Wt_rows)[0] if Wt_rows is not None else None
+        self.ctx.check(self.ctx.lib.gk_network_upload(self.ctx.h, self.h, ptr(A8), ptr(Wc), wdt, ptr(At8), ptr(Wtc)))
+        if diagA is None:
+            assert self.nrows == self.N, "row-sharded networks must be given the full diagonal"
+            idx = np.arange(self.N)
+            diagA = A8[idx, idx]
+            diagW = None if W is None else np.asarray(W)[idx, idx]
+        dA = np.ascontiguousarray(diagA, dtype=np.uint8)
+        dW = None if self.B == 0 else np.ascontiguousarray(diagW, dtype=np.float64)
+        self.ctx.check(self.ctx.lib.gk_network_set_diag(self.ctx.h, self.h, ptr(dA), ptr(dW)))
+        self.diagA, self.diagW = dA, dW
+
+    def device_bytes(self):
+        return int(self.ctx.lib.gk_network_device_bytes(self.h))
+
+    # ---- K1 -------------------------------------------------------------------------------------
+    def block_stats(self, c, K):
+        """Off-diagonal block-pair statistics over this rank's rows (exact int64 counts, fp64 sums)."""
+        c32 = np.ascontiguousarray(c, dtype=np.int32)
+        B = self.B
+        n_edge = np.zeros((K, K), np.int64)
+        sum_w = np.zeros((K, K, B))
+        sum_ww = np.zeros((K, K, B, B))
+        self.ctx.check(self.ctx.lib.gk_block_stats(self.ctx.h, self.h, ptr(c32), K, ptr(n_edge),
+                                                   ptr(sum_w) if B else None, ptr(sum_ww) if B else None))
+        return n_edge, sum_w, sum_ww
+
+    def diag_stats(self, c, K):
+        """O(N) host-side diagonal statistics per block (composed with block_stats by the model classes)."""
+        c = np.asarray(c)
+        e = self.diagA != 0
+        out = dict(d_cnt=np.bincount(c, minlength=K).astype(np.int64),
+                   d_edge=np.bincount(c[e], minlength=K).astype(np.int64),
+                   d_sum_w=np.zeros((K, self.B)), d_sum_ww=np.zeros((K, self.B, self.B)))
+        for b in range(self.B):
+            out["d_sum_w"][:, b] = np.bincount(c[e], weights=self.diagW[e, b], minlength=K)
+            for b2 in range(self.B):
+                out["d_sum_ww"][:, b, b2] = np.bincount(c[e], weights=self.diagW[e, b] * self.diagW[e, b2], minlength=K)
+        return out
+
+    # ---- K2 -------------------------------------------------------------------------------------
+    def sbm_sweep(self, c, log_m, p, mu, sigma, uniforms, self_mode=_lib.SELF_ONCE, sampler=_lib.SAMPLER_CUMSUM,
+                  beta=1.0, block_nodes=0, want_lp=False):
+        """Exact sequential block-assignment sweep.  Returns (c_new, lp or None, n_changed)."""
+        K = len(log_m)
+        c32 = np.array(c, dtype=np.int32, copy=True, order="C")
+        lm = np.ascontiguousarray(log_m, dtype=np.float64)
+        pp = None if p is None else np.ascontiguousarray(p, dtype=np.float64)
+        mm = None if mu is None else np.ascontiguousarray(mu, dtype=np.float64)
+        ss = None if sigma is None else np.ascontiguousarray(sigma, dtype=np.float64)
+        u = np.ascontiguousarray(uniforms, dtype=np.float64)
+        assert u.shape == (self.N,)
+        lp = np.zeros((self.N, K)) if want_lp else None
+        nch = ctypes.c_int64(0)
+        self.ctx.check(self.ctx.lib.gk_sbm_sweep(self.ctx.h, self.h, ptr(c32), K, ptr(lm), ptr(pp), ptr(mm), ptr(ss),
+                                                 self_mode, sampler, float(beta), ptr(u), int(block_nodes), ptr(lp),
+                                                 ctypes.byref(nch)))
+        return c32.astype(np.int64), lp, int(nch.value)
+
+    def close(self):
+        self._finalizer()
+
+
+def _destroy(ctx, h):
+    if ctx.h:
+        ctx.lib.gk_network_destroy(ctx.h, h)
+
+
+def _as_u8(A):
+    A = np.asarray(A)
+    if A.dtype != np.uint8:
+        A = (A != 0).astype(np.uint8)
+    return np.ascontiguousarray(A)
+
+
+def _as_w(W):
+    if W is None:
+        return None, GK_F32
+    W = np.asarray(W)
+    if W.dtype == np.float32:
+        return np.ascontiguousarray(W), GK_F32
+    return np.ascontiguousarray(W, dtype=np.float64), GK_F64

@@ -1,0 +1,104 @@
+/*
+ * gk.h -- C ABI of libgk.so, the B200 (sm_100a) Gibbs engine behind graphistician's model classes.
+ *
+ * The reference (slinderman/graphistician) is pure Python and has NO FFI: its hot path is the body
+ * of the model-class methods.  This header is therefore the boundary a maintainer binds with ctypes
+ * (see INTEGRATION.md); each entry point names the reference method body it replaces (file:line
+ * into the upstream tree).
+ *
+ * Conventions: extern "C"; plain pointers and sizes; every call returns 0 on success or a negative
+ * GK_E* code (message via gk_last_error); one gk_ctx per host thread, not thread-safe; all device
+ * work runs on the ctx stream; pointer arguments are HOST pointers unless the name ends in _dev.
+ * Matrices are row-major; W is N x N x B with B innermost, as the reference stores it.
+ */
+#ifndef GK_H
+#define GK_H
+#include <stdint.h>
+#include <stddef.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct gk_ctx gk_ctx;
+typedef struct gk_net gk_net;
+
+enum { GK_OK = 0, GK_EINVAL = -1, GK_ECUDA = -2, GK_ENOMEM = -3, GK_EUNSUPPORTED = -4 };
+enum { GK_F32 = 0, GK_F64 = 1 };
+
+/* diagonal handling of the assignment sweep -- which reference loop is being replaced */
+enum {
+    GK_SELF_SKIP = 0, /* adjacency.py:671-674, weights.py:460-461,466-467 (special_case_self_conns)   */
+    GK_SELF_ONCE = 1, /* stochastic_block_model.py:293-299; adjacency.py:675-677; weights.py:451-470  */
+    GK_SELF_TWICE = 2 /* internals/graph_models.py:275-293 (AIS: diagonal in both directions)        */
+};
+enum {
+    GK_SAMPLER_CUMSUM = 0, /* pybasicbayes sample_discrete_from_log: count(u*cum[-1] > cum)          */
+    GK_SAMPLER_LSE = 1     /* hips log_sum_exp_sample: first index with normalised cdf >= u          */
+};
+
+/* ---- context ------------------------------------------------------------------------------- */
+int gk_ctx_create(int device, gk_ctx **out);
+void gk_ctx_destroy(gk_ctx *ctx);
+const char *gk_last_error(gk_ctx *ctx);
+int gk_ctx_set_stream(gk_ctx *ctx, void *cuda_stream);      /* e.g. torch's current stream handle */
+int gk_ctx_synchronize(gk_ctx *ctx);
+int64_t gk_ctx_launch_count(gk_ctx *ctx);                   /* kernels launched so far by this ctx */
+/* per-kernel CUDA-event timing (bench.py roofline); family: 0 = strip statistics kernel,
+ * 1 = sequential sampler, 2 = Polya-gamma draw, 3 = eigen slab contraction, 4 = latent pairwise */
+int gk_ctx_kernel_timing(gk_ctx *ctx, int enable);
+int gk_ctx_kernel_timing_read(gk_ctx *ctx, int family, double *ms_total, int64_t *launches, double *bytes_total);
+
+/* ---- network data (A: N x N {0,1} uint8, W: N x N x B) --------------------------------------
+ * Replaces the reference's "network" argument ((A, W) tuple, networks.py:69-71; network.A/.W,
+ * stochastic_block_model.py:217-218).  A rank holds the row shard [row0, row0+nrows) of A/W and of
+ * their transposes.  Device layout: see DESIGN.md "HBM layout". */
+int gk_network_create(gk_ctx *ctx, int N, int B, int dev_dtype, int row0, int nrows, gk_net **out);
+/* A_rows: nrows x N; W_rows: nrows x N x B (w_dtype GK_F32/GK_F64) or NULL when B == 0.
+ * At_rows / Wt_rows: rows [row0,row0+nrows) of A^T / W^T, or NULL to transpose on the device
+ * (allowed only when the shard is the whole matrix). */
+int gk_network_upload(gk_ctx *ctx, gk_net *net, const uint8_t *A_rows, const void *W_rows, int w_dtype,
+                      const uint8_t *At_rows, const void *Wt_rows);
+/* diagonal entries A[n,n] (N) and W[n,n,:] (N x B) for ALL N nodes (replicated on every rank);
+ * needed by the sweeps' self terms (stochastic_block_model.py:293-299). */
+int gk_network_set_diag(gk_ctx *ctx, gk_net *net, const uint8_t *diagA, const double *diagW);
+int gk_network_destroy(gk_ctx *ctx, gk_net *net);
+size_t gk_network_device_bytes(gk_net *net);
+
+/* ---- K1: block-pair sufficient statistics -----------------------------------------------------
+ * Replaces adjacency.py:620-648 (resample_p masks), weights.py:399-413, stochastic_block_model.py:
+ * 221-250, internals/weights.py:88-101 (W[A==1] gathers), adjacency.py:153-181 and weights.py:154-162
+ * (K == 1).  Off-diagonal pairs only, over this rank's rows; the O(N) diagonal terms are composed by
+ * the host class.  n_edge[K*K] exact; sum_w[K*K*B]; sum_ww[K*K*B*B] (symmetric, full). */
+int gk_block_stats(gk_ctx *ctx, gk_net *net, const int32_t *c, int K,
+                   int64_t *n_edge, double *sum_w, double *sum_ww);
+
+/* ---- K2: sequential block-assignment sweep ----------------------------------------------------
+ * Replaces stochastic_block_model.py:252-302, adjacency.py:650-695, weights.py:415-488,
+ * internals/graph_models.py:261-297 (beta != 1).  Nodes are resampled in index order with exactly
+ * the serial Gibbs semantics; uniforms[n] is the one uniform the reference draws for node n.
+ * p (K*K) may be NULL (no adjacency term); mu (K*K*B) / sigma (K*K*B*B) may be NULL (no weight term).
+ * out_lp (N*K, optional): un-normalised log conditional of each node at the moment it was drawn.
+ * block_nodes: nodes per parallel statistics phase (0 = auto).  Single-rank networks only; the
+ * sharded path is gk_sbm_block_partials + gk_sbm_block_sample. */
+int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, const double *log_m,
+                 const double *p, const double *mu, const double *sigma, int self_mode, int sampler,
+                 double beta, const double *uniforms, int block_nodes, double *out_lp, int64_t *out_nchanged);
+
+/* Sharded form of the same sweep: per node block, every rank computes the partial
+ * per-node statistics of its own rows, the host all-reduces them, every rank samples redundantly. */
+int gk_sbm_sweep_begin(gk_ctx *ctx, gk_net *net, const int32_t *c, int K, const double *log_m,
+                       const double *p, const double *mu, const double *sigma, int self_mode, int sampler,
+                       double beta, const double *uniforms);
+/* partial statistics for nodes [n0, n0+nb): stats_dev = device buffer of gk_sbm_partial_len() doubles */
+size_t gk_sbm_partial_len(gk_ctx *ctx, int nb);
+int gk_sbm_block_partials(gk_ctx *ctx, gk_net *net, int n0, int nb, double *stats_dev);
+int gk_sbm_block_sample(gk_ctx *ctx, gk_net *net, int n0, int nb, const double *stats_dev);
+/* labels of a node block: read after the owner sampled / overwrite on the other ranks (host arrays) */
+int gk_sbm_get_block(gk_ctx *ctx, int n0, int nb, int32_t *c_out);
+int gk_sbm_set_block(gk_ctx *ctx, int n0, int nb, const int32_t *c_in);
+int gk_sbm_sweep_end(gk_ctx *ctx, gk_net *net, int32_t *c_out, double *out_lp, int64_t *out_nchanged);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* GK_H */

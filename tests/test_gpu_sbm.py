@@ -1,0 +1,122 @@
+"""GPU parity (through the C ABI) of the SBM path against the oracle: K1 block-pair statistics and the
+K2 sequential assignment sweep.  Integer counts and assignments bit-exact; conditionals 1e-5 relative in the
+fp64 data mode, 1e-3 in fp32 (BASELINE.json north_star)."""
+import os
+
+import numpy as np
+import pytest
+
+from oracle import sbm
+
+pytestmark = pytest.mark.gpu
+
+
+def _problem(seed, N, K, B, dens=None):
+    rng = np.random.RandomState(seed)
+    c = rng.randint(0, K, N)
+    m = rng.dirichlet(np.ones(K) * 3) if K > 1 else np.ones(1)
+    p = rng.beta(1, 1, (K, K)) if dens is None else np.full((K, K), dens)
+    mus = rng.randn(K, K, max(B, 1))
+    sig = np.zeros((K, K, max(B, 1), max(B, 1)))
+    for a in range(K):
+        for b in range(K):
+            X = rng.randn(max(B, 1), max(B, 1))
+            sig[a, b] = X.dot(X.T) + 0.5 * np.eye(max(B, 1))
+    A = (rng.rand(N, N) < p[np.ix_(c, c)]).astype(np.uint8)
+    W = (rng.randn(N, N, B) + mus[np.ix_(c, c)][:, :, :B]) if B else None
+    return A, W, c, m, p, mus[:, :, :B], sig[:, :, :B, :B], rng.rand(N)
+
+
+def _net(A, W, dtype):
+    from graphistician_b200 import DeviceNetwork
+    Wd = None if W is None else (W.astype(np.float32) if dtype == "f32" else W)
+    return DeviceNetwork(A, Wd, dtype=dtype), Wd
+
+
+@pytest.mark.parametrize("N,K,B,dtype", [(50, 5, 2, "f64"), (200, 16, 2, "f32"), (333, 7, 1, "f64"),
+                                         (129, 1, 2, "f32"), (64, 32, 0, "f32"), (700, 20, 2, "f64")])
+def test_block_stats(N, K, B, dtype):
+    A, W, c, m, p, mus, sig, u = _problem(N + K, N, K, B)
+    net, Wd = _net(A, W, dtype)
+    n_edge, sw, sww = net.block_stats(c, K)
+    ref = sbm.block_pair_stats(A.astype(float), None if Wd is None else Wd.astype(np.float64), c, K)
+    assert np.array_equal(n_edge, ref["n_edge"])                       # integer counts: bit-exact
+    if B:
+        tol = 1e-10 if dtype == "f64" else 2e-4
+        assert np.allclose(sw, ref["sum_w"], rtol=tol, atol=tol * np.abs(ref["sum_w"]).max())
+        assert np.allclose(sww, ref["sum_ww"], rtol=tol, atol=tol * np.abs(ref["sum_ww"]).max())
+    d = net.diag_stats(c, K)
+    for k in ("d_cnt", "d_edge", "d_sum_w", "d_sum_ww"):
+        assert np.allclose(d[k], ref[k])
+
+
+def _check_sweep(A, W, c, m, p, mus, sig, u, dtype, mode, gmode, beta=1.0, sampler="cumsum", block_nodes=0):
+    from graphistician_b200 import _lib
+    net, Wd = _net(A, W, dtype)
+    W64 = None if Wd is None else Wd.astype(np.float64)
+    c_ref, lp_ref = sbm.sbm_assign_sweep(A.astype(float), W64, c, m, p, mus, sig, u, mode, beta=beta, sampler=sampler)
+    c_gpu, lp_gpu, nch = net.sbm_sweep(c, np.log(m), p, mus, sig, u, self_mode=gmode,
+                                      sampler=_lib.SAMPLER_CUMSUM if sampler == "cumsum" else _lib.SAMPLER_LSE,
+                                      beta=beta, block_nodes=block_nodes, want_lp=True)
+    tol = 1e-5 if dtype == "f64" else 1e-3
+    # conditionals are defined up to the state at draw time, so compare them first, then the assignments
+    scale = np.abs(lp_ref).max()
+    assert np.allclose(lp_gpu, lp_ref, rtol=tol, atol=tol * 1e-2 * scale), np.abs(lp_gpu - lp_ref).max()
+    assert np.array_equal(c_gpu, c_ref)
+    assert nch == int(np.sum(_count_changes(A, W64, c, m, p, mus, sig, u, mode, beta, sampler)))
+
+
+def _count_changes(A, W, c, m, p, mus, sig, u, mode, beta, sampler):
+    # number of nodes whose draw differed from their label at draw time
+    c = np.array(c).copy()
+    logm = np.log(m)
+    gc = sbm.gaussian_coefficients(mus, sig) if mus is not None else None
+    ch = []
+    for n in range(A.shape[0]):
+        lp = sbm.node_conditional(n, A.astype(float), W, c, logm, p, gc, mode, beta)
+        new = sbm.sample_discrete_from_log(lp, u[n]) if sampler == "cumsum" else sbm.log_sum_exp_sample(lp, u[n])
+        ch.append(new != c[n]); c[n] = new
+    return ch
+
+
+@pytest.mark.parametrize("N,K,B,dtype,bn", [(50, 5, 2, "f64", 0), (200, 16, 2, "f64", 64), (333, 7, 1, "f64", 128),
+                                            (200, 16, 2, "f32", 0), (130, 3, 2, "f64", 64), (257, 32, 2, "f64", 0)])
+def test_sweep_old_api_shared_c(N, K, B, dtype, bn):
+    from graphistician_b200 import _lib
+    A, W, c, m, p, mus, sig, u = _problem(7 * N + K, N, K, B)
+    _check_sweep(A, W, c, m, p, mus, sig, u, dtype, sbm.SELF_OLD, _lib.SELF_ONCE, block_nodes=bn)
+
+
+@pytest.mark.parametrize("special", [True, False])
+def test_sweep_new_api(special):
+    from graphistician_b200 import _lib
+    A, W, c, m, p, mus, sig, u = _problem(11, 150, 6, 2)
+    mode, gmode = (sbm.SELF_SKIP, _lib.SELF_SKIP) if special else (sbm.SELF_NEW, _lib.SELF_ONCE)
+    _check_sweep(A, None, c, m, p, None, None, u, "f64", mode, gmode)            # adjacency.py:650-695
+    _check_sweep(A, W, c, m, None, mus, sig, u, "f64", mode, gmode)              # weights.py:415-488
+
+
+def test_sweep_ais_tempered():
+    from graphistician_b200 import _lib
+    A, W, c, m, p, mus, sig, u = _problem(13, 120, 3, 0)
+    _check_sweep(A, None, c, m, p, None, None, u, "f64", sbm.SELF_AIS, _lib.SELF_TWICE, beta=0.37, sampler="lse")
+
+
+def test_golden_fixture(golden_dir):
+    from graphistician_b200 import _lib, DeviceNetwork
+    g = np.load(os.path.join(golden_dir, "sbm_small.npz"))
+    net = DeviceNetwork(g["A"], g["W"], dtype="f64")
+    c1, lp1, _ = net.sbm_sweep(g["c"], np.log(g["m"]), g["p"], g["mus"], g["sigmas"], g["u"], want_lp=True)
+    assert np.array_equal(c1, g["c_old"]) and np.allclose(lp1, g["lp_old"], rtol=1e-9)
+    n_edge, sw, sww = net.block_stats(g["c"], len(g["m"]))
+    assert np.array_equal(n_edge, g["st_n_edge"]) and np.allclose(sww, g["st_sum_ww"], rtol=1e-12, atol=1e-12)
+
+
+def test_peaked_posterior_stationary():
+    # strong block structure: after convergence almost nothing moves; exercises the long speculative windows
+    from graphistician_b200 import _lib
+    A, W, c, m, p, mus, sig, u = _problem(21, 1500, 4, 2)
+    net, Wd = _net(A, W, "f64")
+    c2, _, nch = net.sbm_sweep(c, np.log(m), p, mus, sig, u, want_lp=False)
+    ref, _ = sbm.sbm_assign_sweep(A.astype(float), W, c, m, p, mus, sig, u, sbm.SELF_OLD)
+    assert np.array_equal(c2, ref) and nch < 50
