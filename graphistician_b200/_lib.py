@@ -119,9 +119,18 @@ class Context:
 
 
 _default_ctx = {}
+_default_device = 0
 
 
-def default_context(device=0):
+def set_default_device(device):
+    """Device used by default_context() when none is named (one process per GPU: call with LOCAL_RANK)."""
+    global _default_device
+    _default_device = int(device)
+
+
+def default_context(device=None):
+    if device is None:
+        device = _default_device
     if device not in _default_ctx:
         _default_ctx[device] = Context(device)
     return _default_ctx[device]

@@ -1,0 +1,109 @@
+"""Host-side Normal-inverse-Wishart Gaussian used for the per-cell weight models.
+
+Plays the role of ``pybasicbayes.distributions.Gaussian`` as graphistician uses it
+(internals/weights.py:62-101, weights.py:118-162,403-413): hyper-parameters ``mu_0, sigma_0, kappa_0, nu_0``,
+state ``mu, sigma``, ``resample(data)`` = NIW posterior draw, ``log_likelihood(x)`` = row-wise normal log-pdf.
+The O(N^2) part -- gathering ``W[A==1]`` and reducing it to (n, sum w, sum w w^T) -- is done on the device
+(gk_block_stats); this class consumes those statistics via ``resample_from_stats``.  Draws come from the
+global ``np.random`` stream, as the reference's do (SURVEY.md 8b "Threading / RNG").
+"""
+import numpy as np
+
+_LOG2PI = 1.8378770664093453
+
+
+def _chol_solve_lower(L, Bm):
+    """Solve L X = Bm for lower-triangular L (small matrices; forward substitution)."""
+    n = L.shape[0]
+    X = np.array(Bm, dtype=np.float64, copy=True)
+    for i in range(n):
+        if i:
+            X[i] -= L[i, :i].dot(X[:i])
+        X[i] /= L[i, i]
+    return X
+
+
+def invwishart_draw(S, nu, rng=np.random):
+    """Sigma ~ IW(S, nu) by the Bartlett construction pybasicbayes uses: for small integer nu a (nu x n) normal
+    matrix, otherwise chi-square diagonal + normal upper triangle; R from its QR; T = (R^-T chol(S)^T)^T; T T^T."""
+    n = S.shape[0]
+    chol = np.linalg.cholesky(S)
+    if nu <= 81 + n and nu == round(nu):
+        x = rng.randn(int(nu), n)
+    else:
+        x = np.diag(np.sqrt(np.atleast_1d(rng.chisquare(nu - np.arange(n)))))
+        x[np.triu_indices_from(x, 1)] = rng.randn(n * (n - 1) // 2)
+    R = np.linalg.qr(x, "r")
+    T = _chol_solve_lower(R.T, chol.T).T
+    return T.dot(T.T)
+
+
+class Gaussian(object):
+    """Multivariate normal with a NIW prior on (mu, sigma)."""
+
+    def __init__(self, mu=None, sigma=None, mu_0=None, sigma_0=None, kappa_0=None, nu_0=None):
+        self.mu_0 = None if mu_0 is None else np.array(mu_0, dtype=np.float64)
+        self.sigma_0 = None if sigma_0 is None else np.array(sigma_0, dtype=np.float64)
+        self.kappa_0, self.nu_0 = kappa_0, nu_0
+        self.mu = None if mu is None else np.array(mu, dtype=np.float64)
+        self.sigma = None if sigma is None else np.array(sigma, dtype=np.float64)
+        if self.mu is None and self.mu_0 is not None:
+            self.resample()                       # prior draw, as pybasicbayes does on construction
+
+    @property
+    def D(self):
+        return (self.mu if self.mu is not None else self.mu_0).shape[0]
+
+    @property
+    def sigma_chol(self):
+        return np.linalg.cholesky(self.sigma)
+
+    @property
+    def hypparams(self):
+        return dict(mu_0=self.mu_0, sigma_0=self.sigma_0, kappa_0=self.kappa_0, nu_0=self.nu_0)
+
+    # ---- NIW posterior ---------------------------------------------------------------------------
+    def posterior_hypparams(self, n, sum_x, sum_xxT):
+        """(mu_n, sigma_n, kappa_n, nu_n) from sufficient statistics; the prior when n == 0."""
+        if n <= 0:
+            return self.mu_0, self.sigma_0, self.kappa_0, self.nu_0
+        n = float(n)
+        xbar = np.asarray(sum_x, dtype=np.float64) / n
+        scatter = np.asarray(sum_xxT, dtype=np.float64) - n * np.outer(xbar, xbar)
+        kappa_n = self.kappa_0 + n
+        dev = xbar - self.mu_0
+        mu_n = (self.kappa_0 * self.mu_0 + n * xbar) / kappa_n
+        sigma_n = self.sigma_0 + scatter + (self.kappa_0 * n / kappa_n) * np.outer(dev, dev)
+        return mu_n, 0.5 * (sigma_n + sigma_n.T), kappa_n, self.nu_0 + n
+
+    def resample_from_stats(self, n, sum_x, sum_xxT, rng=np.random):
+        mu_n, sigma_n, kappa_n, nu_n = self.posterior_hypparams(n, sum_x, sum_xxT)
+        self.sigma = invwishart_draw(sigma_n, nu_n, rng)
+        self.mu = rng.multivariate_normal(mu_n, self.sigma / kappa_n)
+        return self
+
+    def resample(self, data=None, rng=np.random):
+        """``Gaussian.resample(data)`` with data an (n, D) array (or empty -> prior draw)."""
+        if data is None or len(data) == 0:
+            return self.resample_from_stats(0, None, None, rng)
+        data = np.asarray(data, dtype=np.float64).reshape(-1, self.D)
+        return self.resample_from_stats(data.shape[0], data.sum(0), data.T.dot(data), rng)
+
+    # ---- likelihood / sampling ---------------------------------------------------------------------
+    def log_likelihood(self, x):
+        x = np.asarray(x, dtype=np.float64).reshape(-1, self.D)
+        L = np.linalg.cholesky(self.sigma)
+        r = _chol_solve_lower(L, (x - self.mu).T)
+        return -0.5 * (r * r).sum(0) - 0.5 * self.D * _LOG2PI - np.log(np.diag(L)).sum()
+
+    def log_likelihood_from_stats(self, n, sum_x, sum_xxT):
+        """sum_i log N(x_i; mu, sigma) from (n, sum x, sum x x^T)."""
+        Sinv = np.linalg.inv(self.sigma)
+        logdet = np.linalg.slogdet(self.sigma)[1]
+        M = sum_xxT - np.outer(self.mu, sum_x) - np.outer(sum_x, self.mu) + n * np.outer(self.mu, self.mu)
+        return -0.5 * (n * (self.D * _LOG2PI + logdet) + np.sum(Sinv * M))
+
+    def rvs(self, size=None):
+        n = 1 if size is None else int(np.prod(size))
+        out = self.mu + np.random.randn(n, self.D).dot(self.sigma_chol.T)
+        return out[0] if size is None else out

@@ -1,0 +1,95 @@
+"""Old-API network objects and base classes.
+
+The reference imports these from ``graphistician.old_abstractions`` (stochastic_block_model.py:12-13,
+eigenmodel.py:1319-1320), a module that is missing from its tree; their contract is reconstructed from the use
+sites: a network exposes ``.A`` (N x N), ``.W`` (N x N x B) and the mean-field expectations
+``.E_A .E_W .E_WWT``.  Here a network additionally owns its device-resident copy (``device()``), uploaded once
+and reused by every ``resample(network)`` call until ``invalidate()``.
+"""
+import numpy as np
+
+from .device import DeviceNetwork
+
+
+class WeightedDirectedNetwork(object):
+    """Abstract network: subclasses provide A, W and their expectations."""
+    A = W = None
+
+    @property
+    def E_A(self):
+        return self.A
+
+    @property
+    def E_W(self):
+        return self.W
+
+    @property
+    def E_WWT(self):
+        return np.einsum("ijb,ijc->ijbc", self.W, self.W)
+
+
+class FixedGaussianNetwork(WeightedDirectedNetwork):
+    """Deterministic data (stochastic_block_model.py:163,224): E_A = A, E_W = W, E_WWT = W W^T per edge."""
+
+    def __init__(self, A, W):
+        A = np.asarray(A)
+        assert A.ndim == 2 and A.shape[0] == A.shape[1], "A must be N x N"
+        self.A = A
+        self.N = A.shape[0]
+        if W is not None:
+            W = np.asarray(W)
+            if W.ndim == 2:
+                W = W[:, :, None]
+            assert W.shape[:2] == A.shape, "W must be N x N x B"
+        self.W = W
+        self.B = 0 if W is None else W.shape[2]
+        self._dev = {}
+
+    def device(self, dtype="f32", ctx=None):
+        """Device-resident copy (uploaded on first use; see SURVEY.md 8b 'Ownership': data is never mutated)."""
+        key = (dtype, id(ctx))
+        if key not in self._dev:
+            self._dev[key] = DeviceNetwork(self.A, self.W, dtype=dtype, ctx=ctx)
+        return self._dev[key]
+
+    def invalidate(self):
+        """Drop device copies (call after mutating A or W in place)."""
+        for d in self._dev.values():
+            d.close()
+        self._dev = {}
+
+    def __deepcopy__(self, memo):
+        return FixedGaussianNetwork(self.A.copy(), None if self.W is None else self.W.copy())
+
+
+def as_network(obj):
+    """Accept what the reference's callers pass: a network object, an (A, W) tuple, or a bare ndarray
+    (test/test_logistic_eigenmodel_geweke.py:41)."""
+    if isinstance(obj, WeightedDirectedNetwork):
+        return obj
+    if isinstance(obj, (tuple, list)) and len(obj) == 2:
+        return FixedGaussianNetwork(obj[0], obj[1])
+    return FixedGaussianNetwork(np.asarray(obj), None)
+
+
+class NetworkDistribution(object):
+    """Old-API base (stochastic_block_model.py:18): log_probability = log_likelihood + log_prior."""
+
+    def log_prior(self):
+        raise NotImplementedError
+
+    def log_likelihood(self, network):
+        raise NotImplementedError
+
+    def log_probability(self, network):
+        return self.log_likelihood(network) + self.log_prior()
+
+    def copy_sample(self):
+        """pybasicbayes ``GibbsSampling.copy_sample`` = deep copy (test/test_logistic_eigenmodel_geweke.py:47)."""
+        import copy
+        return copy.deepcopy(self)
+
+
+class GaussianWeightedNetworkDistribution(object):
+    """Mixin: models exposing P (N x N), Mu (N x N x B), Sigma (N x N x B x B)."""
+    pass

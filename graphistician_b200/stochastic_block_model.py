@@ -1,0 +1,200 @@
+"""Old-API Gaussian stochastic block model with a block vector ``c`` shared by adjacency and weights.
+
+Mirrors ``graphistician.stochastic_block_model.GaussianStochasticBlockModel`` (stochastic_block_model.py:589;
+constructor :39-102, Gibbs :206-309).  Every O(N^2) step of ``resample(network)`` runs in libgk:
+
+  weight models + p   <- gk_block_stats          (replaces the C^2 masks of :221-250)
+  c                   <- gk_sbm_sweep            (replaces the N*C*N loop of :252-302, same serial semantics)
+
+The O(C^2) Beta / NIW / Dirichlet draws stay on the host and consume the global ``np.random`` stream in the
+reference's order: weight models (row-major cells) -> p (row-major) -> N uniforms for c -> m.
+"""
+import copy
+
+import numpy as np
+from scipy.special import gammaln
+
+from . import _lib
+from .internals.weights import GaussianWeights
+from .old_abstractions import (NetworkDistribution, GaussianWeightedNetworkDistribution, FixedGaussianNetwork,
+                               as_network)
+
+
+class _StochasticBlockModelBase(NetworkDistribution):
+    _weight_class = None
+    _default_weight_hypers = {}
+
+    def __init__(self, N, B, C=1, c=None, m=None, pi=1.0, p=None, tau0=1.0, tau1=1.0, weight_hypers={},
+                 allow_self_connections=True, dtype="f32"):
+        self.N, self.B = N, B
+        assert isinstance(C, (int, np.integer)) and C >= 1, "C must be a positive integer number of blocks"
+        self.C = int(C)
+        if isinstance(pi, (int, float)):
+            self.pi = pi * np.ones(C)
+        else:
+            assert isinstance(pi, np.ndarray) and pi.shape == (C,), "pi must be a sclar or a C-vector"
+            self.pi = pi
+        self.tau0, self.tau1 = tau0, tau1
+        self.allow_self_connections = allow_self_connections
+        self.dtype = dtype                       # device storage of W: "f32" (default) or "f64" (parity mode)
+        if m is not None:
+            assert isinstance(m, np.ndarray) and m.shape == (C,) and np.allclose(m.sum(), 1.0) \
+                and np.amin(m) >= 0.0, "m must be a length C probability vector"
+            self.m = m
+        else:
+            self.m = np.random.dirichlet(self.pi)
+        if c is not None:
+            assert isinstance(c, np.ndarray) and c.shape == (self.N,) and np.issubdtype(c.dtype, np.integer) \
+                and np.amin(c) >= 0 and np.amax(c) <= self.C - 1, "c must be a length K-vector of block assignments"
+            self.c = c.copy()
+        else:
+            self.c = np.random.choice(self.C, p=self.m, size=(self.N))
+        if p is not None:
+            if np.isscalar(p):
+                assert p >= 0 and p <= 1, "p must be a probability"
+                self.p = p * np.ones((C, C))
+            else:
+                assert isinstance(p, np.ndarray) and p.shape == (C, C) and np.amin(p) >= 0 \
+                    and np.amax(p) <= 1.0, "p must be a CxC matrix of probabilities"
+                self.p = p
+        else:
+            self.p = np.random.beta(self.tau1, self.tau0, size=(self.C, self.C))
+        self.weight_hypers = copy.deepcopy(self._default_weight_hypers)
+        self.weight_hypers.update(weight_hypers)
+        self.weight_models = [[self._weight_class(self.B, **self.weight_hypers) for _ in range(self.C)]
+                              for _ in range(self.C)]
+
+    # ---- N x N views (stochastic_block_model.py:104-113, 594-628) -------------------------------------
+    @property
+    def P(self):
+        P = self.p[np.ix_(self.c, self.c)]
+        if not self.allow_self_connections:
+            np.fill_diagonal(P, 0.0)
+        return P
+
+    @property
+    def mus(self):
+        return np.array([[wm.mu for wm in row] for row in self.weight_models])
+
+    @property
+    def sigmas(self):
+        return np.array([[wm.sigma for wm in row] for row in self.weight_models])
+
+    @property
+    def Mu(self):
+        return self.mus[np.ix_(self.c, self.c)]
+
+    @property
+    def Sigma(self):
+        return self.sigmas[np.ix_(self.c, self.c)]
+
+    def log_prior(self):
+        """stochastic_block_model.py:115-129: Dirichlet(m) + Beta(p) + sum log m[c]."""
+        lp = gammaln(self.pi.sum()) - gammaln(self.pi).sum() + ((self.pi - 1) * np.log(self.m)).sum()
+        t1, t0 = self.tau1, self.tau0
+        lp += (gammaln(t1 + t0) - gammaln(t1) - gammaln(t0) + (t1 - 1) * np.log(self.p)
+               + (t0 - 1) * np.log(1 - self.p)).sum()
+        lp += np.log(self.m)[self.c].sum()
+        return lp
+
+    def rvs(self, size=[]):
+        """stochastic_block_model.py:152-163 (block-wise draws, row-major cells)."""
+        A = np.zeros((self.N, self.N))
+        W = np.zeros((self.N, self.N, self.B))
+        for c1 in range(self.C):
+            for c2 in range(self.C):
+                blk = (self.c == c1)[:, None] * (self.c == c2)[None, :]
+                A[blk] = np.random.rand(blk.sum()) < self.p[c1, c2]
+                W[blk, :] = self.weight_models[c1][c2].rvs(size=blk.sum())
+        return FixedGaussianNetwork(A, W)
+
+    def invariant_sbm_order(self):
+        """stochastic_block_model.py:165-182."""
+        blocksz = np.bincount(self.c, minlength=self.C)
+        corder = np.argsort(blocksz)
+        newc = np.zeros(self.N)
+        for c in np.arange(self.C):
+            newc[self.c == corder[c]] = c
+        return np.argsort(-newc)
+
+    # ---- device statistics ---------------------------------------------------------------------------
+    def _cell_stats(self, network):
+        """Per-cell (n_edge, n_noedge, sum_w, sum_ww) with the diagonal inside cell (k,k) (old API)."""
+        dev = network.device(self.dtype)
+        n_edge, sw, sww = dev.block_stats(self.c, self.C)
+        d = dev.diag_stats(self.c, self.C)
+        k = np.arange(self.C)
+        n_edge[k, k] += d["d_edge"]
+        sw[k, k] += d["d_sum_w"]
+        sww[k, k] += d["d_sum_ww"]
+        sz = d["d_cnt"]
+        n_pair = np.outer(sz, sz)                 # ordered pairs incl. the diagonal
+        return n_edge, n_pair - n_edge, sw, sww
+
+    def log_likelihood(self, network):
+        """Bernoulli term on A plus Gaussian term on W where A == 1 (successor formulas abstractions.py:111-115,
+        257-274), evaluated from the device block statistics instead of N^2 logpdf calls."""
+        network = as_network(network)
+        n_edge, n_noedge, sw, sww = self._cell_stats(network)
+        p = np.clip(self.p, 1e-300, 1.0)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            ll = np.nansum(n_edge * np.log(p)) + np.nansum(n_noedge * np.log1p(-np.clip(self.p, 0, 1 - 1e-16)))
+        for c1 in range(self.C):
+            for c2 in range(self.C):
+                if n_edge[c1, c2]:
+                    ll += self.weight_models[c1][c2].log_likelihood_from_stats(n_edge[c1, c2], sw[c1, c2], sww[c1, c2])
+        return ll
+
+
+class _GibbsSBM(_StochasticBlockModelBase):
+    def resample(self, networks=[]):
+        """stochastic_block_model.py:206-230."""
+        if not isinstance(networks, list):
+            networks = [networks]
+        assert len(networks) == 1                 # :213 (TODO in the reference)
+        network = as_network(networks[0])
+        n_edge, n_noedge, sw, sww = self._cell_stats(network)
+        for c1 in range(self.C):                  # :221-226
+            for c2 in range(self.C):
+                self.weight_models[c1][c2].resample_from_stats(n_edge[c1, c2], sw[c1, c2], sww[c1, c2])
+        self._resample_p_from_counts(n_edge, n_noedge)
+        self.resample_c(network)
+        self.resample_m()
+
+    def _resample_p_from_counts(self, n_edge, n_noedge):
+        for c1 in range(self.C):                  # :236-250
+            for c2 in range(self.C):
+                self.p[c1, c2] = np.random.beta(self.tau1 + n_edge[c1, c2], self.tau0 + n_noedge[c1, c2])
+
+    def resample_p(self, As):
+        n_edge = np.zeros((self.C, self.C)); n_noedge = np.zeros((self.C, self.C))
+        for A in As:
+            e, ne, _, _ = self._cell_stats(as_network(A))
+            n_edge += e; n_noedge += ne
+        self._resample_p_from_counts(n_edge, n_noedge)
+
+    def resample_c(self, network, uniforms=None, want_lp=False):
+        """stochastic_block_model.py:252-302 -- sequential in n1, one uniform per node (:302)."""
+        if self.C == 1:
+            return None
+        network = as_network(network)
+        u = np.random.random(self.N) if uniforms is None else uniforms
+        dev = network.device(self.dtype)
+        with np.errstate(divide="ignore"):
+            logm = np.log(self.m)
+        has_w = self.B > 0 and network.W is not None
+        c, lp, self._n_changed = dev.sbm_sweep(self.c, logm, self.p, self.mus if has_w else None,
+                                               self.sigmas if has_w else None, u, self_mode=_lib.SELF_ONCE,
+                                               sampler=_lib.SAMPLER_CUMSUM, want_lp=want_lp)
+        self.c = c
+        return lp
+
+    def resample_m(self):
+        """stochastic_block_model.py:304-309."""
+        self.m = np.random.dirichlet(self.pi + np.bincount(self.c, minlength=self.C))
+
+
+class GaussianStochasticBlockModel(_GibbsSBM, GaussianWeightedNetworkDistribution):
+    """stochastic_block_model.py:589-592."""
+    _weight_class = GaussianWeights
+    _default_weight_hypers = {}

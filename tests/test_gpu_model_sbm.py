@@ -1,0 +1,46 @@
+"""GaussianStochasticBlockModel.resample(network) on the GPU against the oracle's full sweep
+(stochastic_block_model.py:206-230), same np.random stream: c bit-exact, (mu, Sigma, p, m) to 1e-5 (fp64 data)."""
+import numpy as np
+import pytest
+
+from oracle import sbm
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.mark.parametrize("N,C,B,dtype", [(50, 5, 2, "f64"), (160, 4, 1, "f64"), (300, 16, 2, "f32")])
+def test_resample_matches_oracle(N, C, B, dtype):
+    from graphistician_b200.stochastic_block_model import GaussianStochasticBlockModel
+    np.random.seed(3)
+    truth = GaussianStochasticBlockModel(N, B, C=C, dtype=dtype)
+    net = truth.rvs()
+    if dtype == "f32":
+        net.W = net.W.astype(np.float32)
+    model = GaussianStochasticBlockModel(N, B, C=C, dtype=dtype)
+    state = dict(c=model.c.copy(), m=model.m.copy(), p=model.p.copy())
+    hyp = dict(pi=model.pi, tau0=model.tau0, tau1=model.tau1,
+               niw=(np.zeros(B), np.eye(B), 1.0, B + 2))
+    A = net.A.astype(float); W = net.W.astype(np.float64)
+    for sweep in range(3):
+        np.random.seed(100 + sweep)
+        model.resample(net)
+        np.random.seed(100 + sweep)
+        st = sbm.block_pair_stats(A, W, state["c"], C)
+        n_edge, n_noedge, sw, sww = sbm.cell_stats_with_diag(st, include_diag=True)
+        mus, sigmas = sbm.resample_gaussians(n_edge, sw, sww, hyp["niw"])
+        p = sbm.resample_p(n_edge, n_noedge, hyp["tau1"], hyp["tau0"])
+        u = np.random.random(N)
+        c, _ = sbm.sbm_assign_sweep(A, W, state["c"], state["m"], p, mus, sigmas, u, sbm.SELF_OLD)
+        m = sbm.resample_m(c, hyp["pi"])
+        state = dict(c=c, m=m, p=p)
+        tol = 1e-5 if dtype == "f64" else 1e-3
+        assert np.allclose(model.mus, mus, rtol=tol, atol=tol)
+        assert np.allclose(model.sigmas, sigmas, rtol=tol, atol=tol)
+        assert np.allclose(model.p, p, rtol=1e-12)
+        assert np.array_equal(model.c, c)
+        assert np.allclose(model.m, m, rtol=1e-12)
+    ll = model.log_likelihood(net)
+    Ps = np.clip(model.P, 1e-300, 1 - 1e-16)
+    ll_ref = np.sum(A * np.log(Ps) + (1 - A) * np.log1p(-Ps)) + sbm.gaussian_edge_log_likelihood_loops(A, W, model.Mu, model.Sigma)
+    assert np.isclose(ll, ll_ref, rtol=1e-5 if dtype == "f64" else 1e-3)
+    assert np.isfinite(model.log_probability(net))
