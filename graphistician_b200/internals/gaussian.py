@@ -107,3 +107,55 @@ class Gaussian(object):
         n = 1 if size is None else int(np.prod(size))
         out = self.mu + np.random.randn(n, self.D).dot(self.sigma_chol.T)
         return out[0] if size is None else out
+
+
+# ------------------------------------------------------------------------------------------------------
+# batched NIW draws for the K x K weight models of an SBM (one vectorised call instead of K^2 object calls)
+# ------------------------------------------------------------------------------------------------------
+def niw_posterior_batched(mu_0, sigma_0, kappa_0, nu_0, n, sum_x, sum_xxT):
+    """Posterior hyper-parameters for a stack of cells.  n [...], sum_x [..., B], sum_xxT [..., B, B];
+    cells with n == 0 keep the prior.  Same formulas as ``Gaussian.posterior_hypparams``."""
+    n = np.asarray(n, dtype=np.float64)
+    nn = np.maximum(n, 1.0)[..., None]
+    xbar = np.where(n[..., None] > 0, sum_x / nn, 0.0)
+    scatter = sum_xxT - n[..., None, None] * xbar[..., :, None] * xbar[..., None, :]
+    kappa_n = kappa_0 + n
+    dev = xbar - mu_0
+    mu_n = (kappa_0 * mu_0 + n[..., None] * xbar) / kappa_n[..., None]
+    sigma_n = sigma_0 + np.where(n[..., None, None] > 0, scatter, 0.0) \
+        + (kappa_0 * n / kappa_n)[..., None, None] * dev[..., :, None] * dev[..., None, :]
+    return mu_n, 0.5 * (sigma_n + np.swapaxes(sigma_n, -1, -2)), kappa_n, nu_0 + n
+
+
+def niw_draw_batched(mu_n, sigma_n, kappa_n, nu_n, chi2, z_off, z_mu):
+    """(mu, Sigma) for a stack of cells from injected draws.
+
+    Bartlett construction (the chi-square branch of pybasicbayes ``sample_invwishart``): X upper triangular with
+    X[i,i] = sqrt(chi2[..., i]), chi2[..., i] ~ chi^2(nu_n - i), strict upper triangle = z_off (row-major);
+    T = chol(sigma_n) X^-1;  Sigma = T T^T;  mu = mu_n + chol(Sigma / kappa_n) z_mu.
+    """
+    B = mu_n.shape[-1]
+    X = np.zeros(sigma_n.shape)
+    idx = np.arange(B)
+    X[..., idx, idx] = np.sqrt(chi2)
+    iu = np.triu_indices(B, 1)
+    if len(iu[0]):
+        X[..., iu[0], iu[1]] = z_off
+    chol = np.linalg.cholesky(sigma_n)
+    T = np.swapaxes(np.linalg.solve(np.swapaxes(X, -1, -2), np.swapaxes(chol, -1, -2)), -1, -2)
+    sigma = T @ np.swapaxes(T, -1, -2)
+    sigma = 0.5 * (sigma + np.swapaxes(sigma, -1, -2))
+    Lm = np.linalg.cholesky(sigma / kappa_n[..., None, None])
+    mu = mu_n + np.einsum("...ab,...b->...a", Lm, z_mu)
+    return mu, sigma
+
+
+def niw_resample_batched(hyp, n, sum_x, sum_xxT, rng=np.random):
+    """Draw order (one vectorised rng call each): chi-squares [cells, B] -> off-diagonal normals -> mean normals."""
+    mu_n, sigma_n, kappa_n, nu_n = niw_posterior_batched(hyp["mu_0"], hyp["sigma_0"], hyp["kappa_0"], hyp["nu_0"],
+                                                         n, sum_x, sum_xxT)
+    B = mu_n.shape[-1]
+    chi2 = rng.chisquare(nu_n[..., None] - np.arange(B))
+    z_off = rng.standard_normal(n.shape + (B * (B - 1) // 2,))
+    z_mu = rng.standard_normal(n.shape + (B,))
+    return niw_draw_batched(mu_n, sigma_n, kappa_n, nu_n, chi2, z_off, z_mu)

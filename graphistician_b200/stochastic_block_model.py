@@ -16,6 +16,7 @@ from scipy.special import gammaln
 
 from . import _lib
 from .internals.weights import GaussianWeights
+from .internals.gaussian import niw_resample_batched
 from .old_abstractions import (NetworkDistribution, GaussianWeightedNetworkDistribution, FixedGaussianNetwork,
                                as_network)
 
@@ -154,17 +155,27 @@ class _GibbsSBM(_StochasticBlockModelBase):
         assert len(networks) == 1                 # :213 (TODO in the reference)
         network = as_network(networks[0])
         n_edge, n_noedge, sw, sww = self._cell_stats(network)
-        for c1 in range(self.C):                  # :221-226
-            for c2 in range(self.C):
-                self.weight_models[c1][c2].resample_from_stats(n_edge[c1, c2], sw[c1, c2], sww[c1, c2])
+        self._resample_weight_models(n_edge, sw, sww)      # :221-226
         self._resample_p_from_counts(n_edge, n_noedge)
         self.resample_c(network)
         self.resample_m()
 
-    def _resample_p_from_counts(self, n_edge, n_noedge):
-        for c1 in range(self.C):                  # :236-250
+    def _resample_weight_models(self, n_edge, sw, sww):
+        """All C^2 NIW posterior draws in one vectorised pass (internals/weights.py:88-101 per cell).  Draw order on
+        the np.random stream: chi-squares for every cell (row-major), then the Bartlett normals, then the means."""
+        wm0 = self.weight_models[0][0]
+        if self.B == 0:
+            return
+        mus, sigmas = niw_resample_batched(wm0.hypparams, n_edge, sw, sww)
+        for c1 in range(self.C):
             for c2 in range(self.C):
-                self.p[c1, c2] = np.random.beta(self.tau1 + n_edge[c1, c2], self.tau0 + n_noedge[c1, c2])
+                wm = self.weight_models[c1][c2]
+                wm.mu, wm.sigma = mus[c1, c2], sigmas[c1, c2]
+        self._mus_cache = (mus, sigmas)
+
+    def _resample_p_from_counts(self, n_edge, n_noedge):
+        # :236-250; one vectorised legacy-RandomState call draws the cells in row-major order, as the loop does
+        self.p = np.random.beta(self.tau1 + n_edge, self.tau0 + n_noedge)
 
     def resample_p(self, As):
         n_edge = np.zeros((self.C, self.C)); n_noedge = np.zeros((self.C, self.C))

@@ -120,3 +120,19 @@ def gaussian_loglik_from_stats(n, sum_x, sum_xxT, mu, sigma):
     logdet = np.linalg.slogdet(sigma)[1]
     M = sum_xxT - np.outer(mu, sum_x) - np.outer(sum_x, mu) + n * np.outer(mu, mu)
     return -0.5 * (n * (B * LOG2PI + logdet) + np.sum(Sinv * M))
+
+
+def sample_niw_injected(mu_n, sigma_n, kappa_n, nu_n, chi2, z_off, z_mu):
+    """NIW draw with the random numbers injected (chi-square branch of ``sample_invwishart`` above, i.e. the
+    Bartlett factor x = diag(sqrt(chi2)) + strict-upper normals, then the same QR / triangular-solve steps);
+    the mean uses the fixed map  mu = mu_n + chol(Sigma / kappa_n) z_mu  instead of numpy's SVD map
+    (same distribution; parity on sample paths needs one fixed map -- DESIGN.md "Host draws")."""
+    n = sigma_n.shape[0]
+    chol = np.linalg.cholesky(sigma_n)
+    x = np.diag(np.sqrt(np.atleast_1d(chi2)))
+    x[np.triu_indices_from(x, 1)] = z_off
+    R = np.linalg.qr(x, 'r')
+    T = scipy.linalg.solve_triangular(R.T, chol.T, lower=True).T
+    sigma = T.dot(T.T)
+    mu = mu_n + np.linalg.cholesky(sigma / kappa_n).dot(z_mu)
+    return mu, sigma

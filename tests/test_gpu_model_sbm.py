@@ -8,6 +8,22 @@ from oracle import sbm
 pytestmark = pytest.mark.gpu
 
 
+def _oracle_niw_cells(n_edge, sw, sww, niw):
+    """Per-cell NIW posterior + injected-draw sample (oracle/niw.py), consuming np.random in the engine's order."""
+    from oracle import niw as oniw
+    C, B = n_edge.shape[0], sw.shape[2]
+    post = [[oniw.niw_posterior(*niw, n_edge[a, b], sw[a, b], sww[a, b]) for b in range(C)] for a in range(C)]
+    nu = np.array([[post[a][b][3] for b in range(C)] for a in range(C)])
+    chi2 = np.random.chisquare(nu[..., None] - np.arange(B))
+    z_off = np.random.standard_normal((C, C, B * (B - 1) // 2))
+    z_mu = np.random.standard_normal((C, C, B))
+    mus = np.zeros((C, C, B)); sigmas = np.zeros((C, C, B, B))
+    for a in range(C):
+        for b in range(C):
+            mus[a, b], sigmas[a, b] = oniw.sample_niw_injected(*post[a][b], chi2[a, b], z_off[a, b], z_mu[a, b])
+    return mus, sigmas
+
+
 @pytest.mark.parametrize("N,C,B,dtype", [(50, 5, 2, "f64"), (160, 4, 1, "f64"), (300, 16, 2, "f32")])
 def test_resample_matches_oracle(N, C, B, dtype):
     from graphistician_b200.stochastic_block_model import GaussianStochasticBlockModel
@@ -27,7 +43,7 @@ def test_resample_matches_oracle(N, C, B, dtype):
         np.random.seed(100 + sweep)
         st = sbm.block_pair_stats(A, W, state["c"], C)
         n_edge, n_noedge, sw, sww = sbm.cell_stats_with_diag(st, include_diag=True)
-        mus, sigmas = sbm.resample_gaussians(n_edge, sw, sww, hyp["niw"])
+        mus, sigmas = _oracle_niw_cells(n_edge, sw, sww, hyp["niw"])
         p = sbm.resample_p(n_edge, n_noedge, hyp["tau1"], hyp["tau0"])
         u = np.random.random(N)
         c, _ = sbm.sbm_assign_sweep(A, W, state["c"], state["m"], p, mus, sigmas, u, sbm.SELF_OLD)
