@@ -33,6 +33,7 @@ def parse_args():
     ap.add_argument("--n", type=int, default=16384, help="nodes (metric: N=16k)")
     ap.add_argument("--k", type=int, default=16, help="SBM blocks / eigenmodel latent dimension (8)")
     ap.add_argument("--b", type=int, default=2, help="weight dimension")
+    ap.add_argument("--d", type=int, default=8, help="eigenmodel latent dimension")
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-nodes", type=int, default=0, help="nodes of the CPU-baseline sample (0 = auto)")
@@ -77,6 +78,30 @@ def make_sbm_data(N, K, B, seed=1234, rank=0):
         z = g.standard_normal((r1 - r0, N, B), dtype=np.float32)
         W[r0:r1] = (np.einsum("ijab,ijb->ija", chol[cc].astype(np.float32), z) + mus[cc].astype(np.float32))
     return dict(A=A, W=W, c=c, m=m, p=p, mus=mus, sigmas=sigmas, _keep=(keepA, keepW))
+
+
+def make_eigen_data(N, D, seed=1234, rank=0, p=0.01):
+    """F_true ~ N(0, I), lmbda = 1, mu_0 = Phi^-1(p) (eigenmodel.py:56), A ~ Bern(logistic(Mu))."""
+    from scipy.stats import norm
+    g = np.random.Generator(np.random.PCG64(seed + 7919 * rank))
+    F = g.standard_normal((N, D)).astype(np.float32)
+    mu0 = np.float32(norm.ppf(p))
+    A, keepA = pinned_empty((N, N), np.uint8)
+    rows = 1024
+    for r0 in range(0, N, rows):
+        r1 = min(N, r0 + rows)
+        eta = F[r0:r1] @ F.T + mu0
+        eta[np.arange(r1 - r0), np.arange(r0, r1)] = mu0
+        A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < 1.0 / (1.0 + np.exp(-eta))
+    return dict(A=A, W=None, F=F, mu0=float(mu0), _keep=(keepA,))
+
+
+def build_eigen_model(d, N, D, dtype):
+    from graphistician_b200.eigenmodel import LogisticEigenmodel
+    from graphistician_b200.old_abstractions import FixedGaussianNetwork
+    np.random.seed(5678)
+    model = LogisticEigenmodel(N, D, p=0.01, sigma_F=1.0, sigma_mu0=1.0, lmbda=np.ones(D), dtype=dtype)
+    return model, FixedGaussianNetwork(d["A"], None)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -163,6 +188,34 @@ def build_sbm_model(d, N, K, B, dtype):
     return model, network
 
 
+def setup_workload(args, rank):
+    N, B = args.n, args.b
+    if args.workload == "sbm":
+        K = args.k
+        d = make_sbm_data(N, K, B, rank=rank)
+        model, network = build_sbm_model(d, N, K, B, args.dtype)
+        s_W = 4 if args.dtype == "f32" else 8
+        return dict(N=N, data=d, model=model, network=network,
+                    algo_bytes=3.0 * N * N * (1 + B * s_W),       # K1 pass + K2 row pass + column pass
+                    h2d=N * N * (1 + B * 4) + N * (1 + 8 * B) + N * 12 + 8 * K * K * (2 + B + B * B),
+                    d2h=N * 4 + 8 * K * K * (1 + B + B * B) + 8, dominant=(0, "k_strip_stats"),
+                    cpu_baseline=cpu_baseline_sbm,
+                    config={"workload": "gaussian_sbm_gibbs_sweep N=%d K=%d B=%d (configs[1] model at the metric's N)" % (N, K, B),
+                            "N": N, "K": K, "B": B})
+    if args.workload == "eigen":
+        D = args.d
+        d = make_eigen_data(N, D, rank=rank)
+        model, network = build_eigen_model(d, N, D, args.dtype)
+        s_O = 4 if args.dtype == "f32" else 8
+        return dict(N=N, data=d, model=model, network=network,
+                    algo_bytes=1.0 * N * N * (2 * s_O + 1),       # write S + read S + read A
+                    h2d=N * N + N * D * 16 + 8 * D + 8, d2h=N * D * 8 + 8 * 68 + 8, dominant=(3, "k_eig_slab"),
+                    cpu_baseline=cpu_baseline_eigen,
+                    config={"workload": "logistic_eigenmodel_pg_gibbs_sweep N=%d D=%d lmbda given (configs[2])" % (N, D),
+                            "N": N, "D": D})
+    raise SystemExit("workload %s: not built yet" % args.workload)
+
+
 def run_ours(args):
     import torch
     from graphistician_b200 import _lib
@@ -175,11 +228,8 @@ def run_ours(args):
     ctx = _lib.default_context()
     stream = torch.cuda.Stream(device=dev)
     ctx.set_stream(stream.cuda_stream)
-    N, K, B = args.n, args.k, args.b
-    d = make_sbm_data(N, K, B, rank=rank)
-    model, network = build_sbm_model(d, N, K, B, args.dtype)
-    s_A, s_W = 1, (4 if args.dtype == "f32" else 8)
-    algo_bytes = 3.0 * N * N * (s_A + B * s_W)                  # K1 pass + K2 row pass + column pass
+    wl = setup_workload(args, rank)
+    N, model, network, d, algo_bytes = wl["N"], wl["model"], wl["network"], wl["data"], wl["algo_bytes"]
 
     def timed(nsteps, e2e):
         barrier(world); torch.cuda.synchronize()
@@ -204,15 +254,14 @@ def run_ours(args):
     e2e_steps = max(3, min(args.steps, 5))
     timed(1, True)
     ms_e2e = timed(e2e_steps, True)
-    h2d = N * N * (1 + B * 4) + N * (1 + 8 * B) + N * 12 + 8 * K * K * (2 + B + B * B)
-    d2h = N * 4 + 8 * K * K * (1 + B + B * B) + 8
-    # per-kernel timing pass (CUDA events around every launch of the dominant kernel, on its own stream)
+    h2d, d2h = wl["h2d"], wl["d2h"]
+    # per-kernel timing pass (CUDA events around every launch of each kernel family, on the ctx stream)
     ctx.kernel_timing(True)
     for _ in range(3):
         model.resample(network)
-    kms, kn, kbytes = ctx.kernel_timing_read(0)
-    sms, sn, _ = ctx.kernel_timing_read(1)
+    fam = {f: ctx.kernel_timing_read(f) for f in range(6)}
     ctx.kernel_timing(False)
+    kms, kn, kbytes = fam[wl["dominant"][0]]
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -220,26 +269,27 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = kbytes / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+    names = {0: "k_strip_stats", 1: "k_sbm_seq", 2: "k_eig_pg_tile", 3: "k_eig_slab", 4: "k_latent_pair", 5: "k_eig_seq"}
     out = {
         "metric": METRIC, "value": world * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-        "config": {"workload": "gaussian_sbm_gibbs_sweep N=%d K=%d B=%d (configs[1] model at the metric's N)" % (N, K, B),
-                   "N": N, "K": K, "B": B, "parallelism": "independent chains x%d" % world,
-                   "l2": "inputs (%.2f GB/sweep) exceed the 126 MB L2" % (algo_bytes / 1e9)},
+        "config": dict(wl["config"], parallelism="independent chains x%d" % world,
+                       l2="inputs (%.2f GB/sweep) exceed the 126 MB L2" % (algo_bytes / 1e9)),
         "gpu_launches": int(launches), "clocks": clocks,
         "e2e": {"value": world * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h)},
-        "roofline": {"bound": "hbm", "kernel": "k_strip_stats", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": None,
+        "roofline": {"bound": "hbm", "kernel": wl["dominant"][1], "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": wl.get("traffic"),
                      "peak_source": "measured" if peaks else "fallback",
                      "launches_per_sweep": kn / 3.0, "kernel_ms_per_sweep": kms / 3.0,
-                     "seq_sampler_ms_per_sweep": sms / 3.0,
+                     "other_kernels_ms_per_sweep": {names[f]: fam[f][0] / 3.0 for f in fam if fam[f][1] and f != wl["dominant"][0]},
                      "sweep_algorithmic_GBps": algo_bytes / (ms / args.steps * 1e-3) / 1e9},
-        "n_changed_last_sweep": int(getattr(model, "_n_changed", -1)),
     }
+    if args.workload == "sbm":
+        out["n_changed_last_sweep"] = int(getattr(model, "_n_changed", -1))
     if rank == 0 and not args.no_cpu_baseline:
-        out["cpu_baseline"] = cpu_baseline_sbm(d, model, args)
+        out["cpu_baseline"] = wl["cpu_baseline"](d, model, args)
     if rank == 0:
         print(json.dumps(out), flush=True)
     if world > 1:
@@ -277,6 +327,34 @@ def cpu_baseline_sbm(d, model, args, nodes=None):
                       "+ their sequential conditionals/draws; %.1f s measured, scaled x%.1f to a full sweep"
                       % (nodes, N, t_stats + t_sweep, N / float(nodes)),
             "measured_s": t_stats + t_sweep}
+
+
+def cpu_baseline_eigen(d, model, args, nodes=None):
+    """Oracle (port) of one logistic-eigenmodel sweep on a bounded sample: the C Devroye sampler (OpenMP, all
+    cores) for both Omega entries of the first `nodes` rows, then the per-node conditionals/draws of those nodes
+    (vectorised NumPy restatement of eigenmodel.py:876-908); scaled by N/nodes."""
+    from oracle import eigenmodel as eg, pg
+    A = d["A"]
+    N = A.shape[0]
+    nodes = nodes or args.cpu_nodes or min(N, 512)
+    F = np.asarray(model.F, dtype=np.float64); lm = np.asarray(model.lmbda, dtype=np.float64); mu0 = float(model.mu_0)
+    t0 = time.perf_counter()
+    O1 = pg.pgdraw_eigen(F, lm, mu0, seed=1, r0=0, r1=nodes)          # omega[n, :]
+    O2 = pg.pgdraw_eigen(F, lm, mu0, seed=2, r0=0, r1=nodes)          # omega[:, n]^T (Mu is symmetric)
+    t_pg = time.perf_counter() - t0
+    t0 = time.perf_counter()
+    S = O1 + O2
+    Asym = A[:nodes].astype(np.float64) + A[:, :nodes].T
+    R = Asym - 1.0 - mu0 * S
+    z = np.random.RandomState(1).randn(N, F.shape[1])
+    eg.resample_F(S, R, F, lm, model.sigma_F, z, nodes=nodes)
+    t_F = time.perf_counter() - t0
+    secs = (t_pg + t_F) * (N / float(nodes))
+    return {"value": 1.0 / secs, "unit": UNIT, "cores": pg.num_threads(), "kind": "port",
+            "sample": "oracle on the first %d of %d nodes: C Polya-gamma sampler (OpenMP x%d) for their 2N Omega entries "
+                      "(%.2f s) + sequential conditionals/draws in NumPy (%.2f s, 1 core); scaled x%.1f to a full sweep"
+                      % (nodes, N, pg.num_threads(), t_pg, t_F, N / float(nodes)),
+            "measured_s": t_pg + t_F}
 
 
 def _stats_rows(A, W, c, K, nodes):

@@ -40,6 +40,15 @@ SIGNATURES = {
     "gk_sbm_get_block": (c_int, [c_vp, c_int, c_int, c_vp]),
     "gk_sbm_set_block": (c_int, [c_vp, c_int, c_int, c_vp]),
     "gk_sbm_sweep_end": (c_int, [c_vp, c_vp, c_vp, c_vp, PI64]),
+    "gk_eig_create": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_vp)]),
+    "gk_eig_destroy": (c_int, [c_vp, c_vp]),
+    "gk_eig_device_bytes": (c_sz, [c_vp]),
+    "gk_eig_set_params": (c_int, [c_vp, c_vp, c_vp, c_dbl, c_vp]),
+    "gk_eig_pg_draw": (c_int, [c_vp, c_vp, ctypes.c_uint64, ctypes.POINTER(c_dbl)]),
+    "gk_eig_set_S": (c_int, [c_vp, c_vp, c_vp]),
+    "gk_eig_get_S": (c_int, [c_vp, c_vp, c_vp]),
+    "gk_eig_resample_F": (c_int, [c_vp, c_vp, c_dbl, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "gk_eig_log_likelihood": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_dbl)]),
 }
 
 _lib = None

@@ -1,0 +1,308 @@
+// gk_eig.cu -- host side of the eigenmodel path (K3-K6): state, launch plans, C-ABI entry points.
+#include <math.h>
+#include <string.h>
+#include <algorithm>
+#include "gk_eig_kernels.cuh"
+
+struct gk_eig {
+    gk_net *net = nullptr;
+    int N = 0, D = 0, dtype = GK_F32;
+    void *S = nullptr;                 // nrows x ld of dtype
+    double *F = nullptr, *lmbda = nullptr, *z = nullptr;   // N x D, D, N x D
+    double *acc = nullptr;             // [2][GK_EIG_NBMAX][PA_max]
+    double *glob = nullptr;            // GK_EIG_GLOB_LEN
+    double *part = nullptr; size_t npart = 0;              // per-tile partial sums of K3
+    double *scal = nullptr;            // small device scalars (sum of omega, ...)
+    double *out_prec = nullptr, *out_h = nullptr;
+    double mu0 = 0.0;
+    bool have_S = false;
+    uint32_t sweep = 0;
+};
+
+#define GK_EIG_PA_MAX (GK_EIG_MAXD * (GK_EIG_MAXD + 1) / 2 + 2 * GK_EIG_MAXD)
+
+static int ensure_asym(gk_ctx *ctx, gk_net *net) {
+    if (net->Asym) return GK_OK;
+    size_t bytes = (size_t)net->nrows * net->ld;
+    GK_CUDA(ctx, cudaMalloc(&net->Asym, bytes));
+    net->bytes += bytes;
+    k_eig_asym<<<ctx->num_sms * 8, 256, 0, ctx->stream>>>(net->A, net->At, net->Asym, net->nrows, net->N, net->ld, net->row0);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+extern "C" int gk_eig_create(gk_ctx *ctx, gk_net *net, int D, gk_eig **out) {
+    if (!ctx || !net || !out) return GK_EINVAL;
+    *out = nullptr;
+    if (D < 1 || D > GK_EIG_MAXD) return gk_fail(ctx, GK_EUNSUPPORTED, "D=%d: this build supports 1 <= D <= %d", D, GK_EIG_MAXD);
+    if (net->row0 % GK_EIG_NBMAX) return gk_fail(ctx, GK_EINVAL, "row shards must start on a multiple of %d", GK_EIG_NBMAX);
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    gk_eig *e = new gk_eig();
+    e->net = net; e->N = net->N; e->D = D; e->dtype = net->dtype;
+    const size_t N = net->N;
+    const int tiles_y = (net->nrows + GK_PG_TILE - 1) / GK_PG_TILE, tiles_x = (net->N + GK_PG_TILE - 1) / GK_PG_TILE;
+    e->npart = (size_t)tiles_x * tiles_y;
+    cudaError_t err = cudaMalloc(&e->S, (size_t)net->nrows * net->ld * gk_esize(e->dtype));
+    if (err == cudaSuccess) err = cudaMalloc(&e->F, N * D * 8);
+    if (err == cudaSuccess) err = cudaMalloc(&e->z, N * D * 8);
+    if (err == cudaSuccess) err = cudaMalloc(&e->lmbda, GK_EIG_MAXD * 8);
+    if (err == cudaSuccess) err = cudaMalloc(&e->acc, (size_t)2 * GK_EIG_NBMAX * GK_EIG_PA_MAX * 8);
+    if (err == cudaSuccess) err = cudaMalloc(&e->glob, GK_EIG_GLOB_LEN * 8);
+    if (err == cudaSuccess) err = cudaMalloc(&e->part, e->npart * 8);
+    if (err == cudaSuccess) err = cudaMalloc(&e->scal, 64);
+    if (err != cudaSuccess) {
+        cudaFree(e->S); cudaFree(e->F); cudaFree(e->z); cudaFree(e->lmbda); cudaFree(e->acc); cudaFree(e->glob); cudaFree(e->part); cudaFree(e->scal);
+        delete e;
+        return gk_fail(ctx, GK_ENOMEM, "eigenmodel state alloc: %s", cudaGetErrorString(err));
+    }
+    GK_CUDA(ctx, cudaMemsetAsync(e->S, 0, (size_t)net->nrows * net->ld * gk_esize(e->dtype), ctx->stream));
+    GK_CUDA(ctx, cudaMemsetAsync(e->acc, 0, (size_t)2 * GK_EIG_NBMAX * GK_EIG_PA_MAX * 8, ctx->stream));
+    int rc = ensure_asym(ctx, net);
+    if (rc) return rc;
+    *out = e;
+    return GK_OK;
+}
+
+extern "C" int gk_eig_destroy(gk_ctx *ctx, gk_eig *e) {
+    if (!e) return GK_OK;
+    if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
+    cudaFree(e->S); cudaFree(e->F); cudaFree(e->z); cudaFree(e->lmbda); cudaFree(e->acc); cudaFree(e->glob);
+    cudaFree(e->part); cudaFree(e->scal); cudaFree(e->out_prec); cudaFree(e->out_h);
+    delete e;
+    return GK_OK;
+}
+
+extern "C" size_t gk_eig_device_bytes(gk_eig *e) {
+    return e ? (size_t)e->net->nrows * e->net->ld * gk_esize(e->dtype) + (size_t)e->N * e->D * 16 : 0;
+}
+
+extern "C" int gk_eig_set_params(gk_ctx *ctx, gk_eig *e, const double *F, double mu0, const double *lmbda) {
+    if (!ctx || !e || !F || !lmbda) return GK_EINVAL;
+    GK_CUDA(ctx, cudaMemcpyAsync(e->F, F, (size_t)e->N * e->D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(e->lmbda, lmbda, (size_t)e->D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    e->mu0 = mu0;
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}
+
+// parity / injection path: S rows (nrows x N, host doubles, S = Omega + Omega^T with any diagonal: it is zeroed)
+template <typename T>
+__global__ void k_eig_store_S(const double *__restrict__ src, T *__restrict__ S, int nrows, int N, int ld, int row0) {
+    size_t total = (size_t)nrows * ld;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int r = (int)(i / ld), j = (int)(i - (size_t)r * ld);
+        S[i] = (j < N && j != r + row0) ? (T)src[(size_t)r * N + j] : T(0);
+    }
+}
+
+extern "C" int gk_eig_set_S(gk_ctx *ctx, gk_eig *e, const double *S_rows) {
+    if (!ctx || !e || !S_rows) return GK_EINVAL;
+    gk_net *net = e->net;
+    size_t bytes = (size_t)net->nrows * net->N * 8;
+    double *tmp = (double *)gk_scratch(ctx, 0, bytes);
+    if (!tmp) return GK_ENOMEM;
+    GK_CUDA(ctx, cudaMemcpyAsync(tmp, S_rows, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (e->dtype == GK_F32) k_eig_store_S<float><<<ctx->num_sms * 8, 256, 0, ctx->stream>>>(tmp, (float *)e->S, net->nrows, net->N, net->ld, net->row0);
+    else k_eig_store_S<double><<<ctx->num_sms * 8, 256, 0, ctx->stream>>>(tmp, (double *)e->S, net->nrows, net->N, net->ld, net->row0);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    e->have_S = true;
+    return GK_OK;
+}
+
+template <typename T>
+__global__ void k_eig_fetch_S(const T *__restrict__ S, double *__restrict__ dst, int nrows, int N, int ld) {
+    size_t total = (size_t)nrows * N;
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < total; i += (size_t)gridDim.x * blockDim.x) {
+        int r = (int)(i / N), j = (int)(i - (size_t)r * N);
+        dst[i] = (double)S[(size_t)r * ld + j];
+    }
+}
+
+extern "C" int gk_eig_get_S(gk_ctx *ctx, gk_eig *e, double *S_rows) {
+    if (!ctx || !e || !S_rows) return GK_EINVAL;
+    gk_net *net = e->net;
+    size_t bytes = (size_t)net->nrows * net->N * 8;
+    double *tmp = (double *)gk_scratch(ctx, 0, bytes);
+    if (!tmp) return GK_ENOMEM;
+    if (e->dtype == GK_F32) k_eig_fetch_S<float><<<ctx->num_sms * 8, 256, 0, ctx->stream>>>((const float *)e->S, tmp, net->nrows, net->N, net->ld);
+    else k_eig_fetch_S<double><<<ctx->num_sms * 8, 256, 0, ctx->stream>>>((const double *)e->S, tmp, net->nrows, net->N, net->ld);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaMemcpyAsync(S_rows, tmp, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K3
+// ---------------------------------------------------------------------------------------------
+extern "C" int gk_eig_pg_draw(gk_ctx *ctx, gk_eig *e, uint64_t seed, double *sum_omega) {
+    if (!ctx || !e) return GK_EINVAL;
+    gk_net *net = e->net;
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    dim3 grid((net->N + GK_PG_TILE - 1) / GK_PG_TILE, (net->nrows + GK_PG_TILE - 1) / GK_PG_TILE);
+    const double bytes = (double)net->nrows * net->N * gk_esize(e->dtype);
+    gk_time_begin(ctx, 2, bytes);
+    if (e->dtype == GK_F32)
+        k_eig_pg_tile<float><<<grid, 256, 0, ctx->stream>>>((float *)e->S, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
+    else
+        k_eig_pg_tile<double><<<grid, 256, 0, ctx->stream>>>((double *)e->S, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
+    gk_time_end(ctx, 2);
+    GK_CHECK_LAUNCH(ctx);
+    e->sweep++;
+    k_sum_partials<<<1, 1024, 0, ctx->stream>>>(e->part, (int)e->npart, e->scal);
+    GK_CHECK_LAUNCH(ctx);
+    e->have_S = true;
+    if (sum_omega) {
+        GK_CUDA(ctx, cudaMemcpyAsync(sum_omega, e->scal, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return GK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K4 + K5 (+ K6 statistics): the sequential feature sweep
+// ---------------------------------------------------------------------------------------------
+template <typename T, int D>
+static int launch_slab(gk_ctx *ctx, gk_eig *e, int n0, int nb) {
+    typedef typename gk_eacc<T>::type ACC;
+    gk_net *net = e->net;
+    // rows per chunk: a divisor of the block stride, small enough to fill the SMs
+    const int stride = gk_eig_nb<T>::NB;
+    int mc = stride;
+    while (mc > 16 && (net->nrows + mc - 1) / mc < ctx->num_sms) mc >>= 1;
+    const int nchunks = (net->nrows + mc - 1) / mc;
+    const size_t smem = (size_t)((mc + 3) / 4 * 4) * gk_edim<D>::PA * sizeof(ACC);
+    const double bytes = (double)net->nrows * nb * (sizeof(T) + 1.0);
+    gk_time_begin(ctx, 3, bytes);
+    k_eig_slab<T, D><<<nchunks, GK_EIG_SLAB_THREADS, smem, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, net->row0, net->nrows,
+                                                                         e->F, n0, nb, mc, e->acc);
+    gk_time_end(ctx, 3);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+template <typename T, int D>
+static int launch_seq(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sblk, int ldS, const uint8_t *Ablk, int ldA,
+                      double inv_sigma_F) {
+    static bool attr_set = false;
+    const size_t smem = gk_eig_seq_smem<T, D>();
+    if (!attr_set) {
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    gk_eig_seq_params P;
+    P.n0 = n0; P.nb = nb; P.N = e->N; P.Sblk = Sblk; P.ldS = ldS; P.Ablk = Ablk; P.ldA = ldA;
+    P.F = e->F; P.z = e->z; P.lmbda = e->lmbda; P.mu0 = e->mu0; P.inv_sigma_F = inv_sigma_F;
+    P.acc = e->acc; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h;
+    gk_time_begin(ctx, 5, 0.0);
+    k_eig_seq<T, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
+    gk_time_end(ctx, 5);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+template <typename T, int D>
+static int sweep_F(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
+    gk_net *net = e->net;
+    const int NB = gk_eig_nb<T>::NB;
+    for (int n0 = 0; n0 < e->N; n0 += NB) {
+        const int nb = std::min(NB, e->N - n0);
+        int rc = launch_slab<T, D>(ctx, e, n0, nb);
+        if (rc) return rc;
+        const T *Sblk = (const T *)e->S + (size_t)(n0 - net->row0) * net->ld + n0;
+        const uint8_t *Ablk = net->Asym + (size_t)(n0 - net->row0) * net->ld + n0;
+        if ((rc = launch_seq<T, D>(ctx, e, n0, nb, Sblk, net->ld, Ablk, net->ld, inv_sigma_F))) return rc;
+    }
+    return GK_OK;
+}
+
+#define GK_EIG_SWITCH_D(T, D, FN, ...)                                              \
+    ((D) == 1 ? FN<T, 1>(__VA_ARGS__) : (D) == 2 ? FN<T, 2>(__VA_ARGS__) : (D) == 3 ? FN<T, 3>(__VA_ARGS__)      \
+     : (D) == 4 ? FN<T, 4>(__VA_ARGS__) : (D) == 5 ? FN<T, 5>(__VA_ARGS__) : (D) == 6 ? FN<T, 6>(__VA_ARGS__)    \
+     : (D) == 7 ? FN<T, 7>(__VA_ARGS__) : FN<T, 8>(__VA_ARGS__))
+
+extern "C" int gk_eig_resample_F(gk_ctx *ctx, gk_eig *e, double sigma_F, const double *normals, double *F_out,
+                                 double *out_prec, double *out_h, double *stats) {
+    if (!ctx || !e || !normals) return GK_EINVAL;
+    if (!e->have_S) return gk_fail(ctx, GK_EINVAL, "gk_eig_resample_F: call gk_eig_pg_draw or gk_eig_set_S first");
+    if (!(sigma_F > 0)) return gk_fail(ctx, GK_EINVAL, "sigma_F must be positive");
+    gk_net *net = e->net;
+    if (net->row0 != 0 || net->nrows != net->N) return gk_fail(ctx, GK_EINVAL, "gk_eig_resample_F needs an unsharded network; use the block form");
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    const size_t N = e->N; const int D = e->D;
+    GK_CUDA(ctx, cudaMemcpyAsync(e->z, normals, N * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    if (out_prec && !e->out_prec) GK_CUDA(ctx, cudaMalloc(&e->out_prec, N * D * D * 8));
+    if (out_h && !e->out_h) GK_CUDA(ctx, cudaMalloc(&e->out_h, N * D * 8));
+    double *keep_prec = e->out_prec, *keep_h = e->out_h;
+    if (!out_prec) e->out_prec = nullptr;
+    if (!out_h) e->out_h = nullptr;
+    GK_CUDA(ctx, cudaMemsetAsync(e->glob, 0, GK_EIG_GLOB_LEN * 8, ctx->stream));
+    k_eig_colsum<<<1, 1024, 0, ctx->stream>>>(e->F, e->N, D, e->glob + GK_EIG_GLOB_SUMF);
+    GK_CHECK_LAUNCH(ctx);
+    int rc = e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, D, sweep_F, ctx, e, 1.0 / sigma_F)
+                                : GK_EIG_SWITCH_D(double, D, sweep_F, ctx, e, 1.0 / sigma_F);
+    e->out_prec = keep_prec; e->out_h = keep_h;
+    if (rc) return rc;
+    if (F_out) GK_CUDA(ctx, cudaMemcpyAsync(F_out, e->F, N * D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_prec) GK_CUDA(ctx, cudaMemcpyAsync(out_prec, keep_prec, N * D * D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_h) GK_CUDA(ctx, cudaMemcpyAsync(out_h, keep_h, N * D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    double g[GK_EIG_GLOB_LEN];
+    GK_CUDA(ctx, cudaMemcpyAsync(g, e->glob, sizeof g, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (stats) {
+        // stats: Pq[D*D] (full symmetric) | hS[D] | hK[D]
+        for (int a = 0; a < D; ++a)
+            for (int b = 0; b < D; ++b) stats[a * D + b] = g[GK_EIG_GLOB_PQ + gk_qidx(D, std::min(a, b), std::max(a, b))];
+        for (int a = 0; a < D; ++a) { stats[D * D + a] = g[GK_EIG_GLOB_HS + a]; stats[D * D + D + a] = g[GK_EIG_GLOB_HK + a]; }
+    }
+    return GK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K9 (eigenmodel form): log likelihood  sum A log P + (1-A) log(1-P),  P = clip(logistic(Mu), 1e-16, 1-1e-16)
+// (eigenmodel.py:110-129 with P of :803-811; link = 1 -> probit P of :227-236).  fp64 math, fixed order.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_eig_loglik(const uint8_t *__restrict__ A, int ld, int row0, int nrows, int N, int D,
+                                                    const double *__restrict__ F, const double *__restrict__ lmbda, double mu0,
+                                                    int link, double *__restrict__ part) {
+    constexpr int TS = 64;
+    __shared__ double fi[TS][GK_EIG_MAXD], fj[TS][GK_EIG_MAXD];
+    __shared__ double red[8];
+    const int tid = threadIdx.x, I = row0 + blockIdx.y * TS, J = blockIdx.x * TS;
+    for (int t = tid; t < TS * GK_EIG_MAXD; t += 256) {
+        int r = t / GK_EIG_MAXD, d = t % GK_EIG_MAXD;
+        fi[r][d] = (d < D && I + r < N) ? F[(size_t)(I + r) * D + d] * lmbda[d] : 0.0;
+        fj[r][d] = (d < D && J + r < N) ? F[(size_t)(J + r) * D + d] : 0.0;
+    }
+    __syncthreads();
+    const int j = tid & (TS - 1);
+    double local = 0.0;
+    for (int i = tid / TS; i < TS; i += 256 / TS) {
+        const int n = I + i, m = J + j;
+        if (n >= N || m >= N || n - row0 >= nrows) continue;
+        double z = mu0;
+        if (n != m) for (int d = 0; d < GK_EIG_MAXD; ++d) z += fi[i][d] * fj[j][d];
+        double p = link == 0 ? 1.0 / (1.0 + exp(-z)) : 0.5 * erfc(-z * 0.70710678118654752440);
+        p = fmin(fmax(p, 1e-16), 1.0 - 1e-16);
+        local += A[(size_t)(n - row0) * ld + m] ? log(p) : log(1.0 - p);
+    }
+    for (int o = 16; o; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((tid & 31) == 0) red[tid >> 5] = local;
+    __syncthreads();
+    if (tid == 0) { double s = 0.0; for (int w = 0; w < 8; ++w) s += red[w]; part[blockIdx.y * gridDim.x + blockIdx.x] = s; }
+}
+
+extern "C" int gk_eig_log_likelihood(gk_ctx *ctx, gk_eig *e, int link, double *ll) {
+    if (!ctx || !e || !ll || link < 0 || link > 1) return GK_EINVAL;
+    gk_net *net = e->net;
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    dim3 grid((net->N + 63) / 64, (net->nrows + 63) / 64);
+    k_eig_loglik<<<grid, 256, 0, ctx->stream>>>(net->A, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, link, e->part);
+    GK_CHECK_LAUNCH(ctx);
+    k_sum_partials<<<1, 1024, 0, ctx->stream>>>(e->part, (int)e->npart, e->scal + 1);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaMemcpyAsync(ll, e->scal + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}

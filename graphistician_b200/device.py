@@ -119,3 +119,63 @@ def _as_w(W):
     if W.dtype == np.float32:
         return np.ascontiguousarray(W), GK_F32
     return np.ascontiguousarray(W, dtype=np.float64), GK_F64
+
+
+class DeviceEigenmodel:
+    """Device state of one eigenmodel over one DeviceNetwork: S = Omega + Omega^T, F, lmbda, mu_0 (gk_eig)."""
+
+    def __init__(self, net, D):
+        self.net, self.ctx, self.D, self.N = net, net.ctx, int(D), net.N
+        h = ctypes.c_void_p()
+        self.ctx.check(self.ctx.lib.gk_eig_create(self.ctx.h, net.h, self.D, ctypes.byref(h)))
+        self.h = h
+        self._finalizer = weakref.finalize(self, _destroy_eig, self.ctx, h)
+
+    def set_params(self, F, mu_0, lmbda):
+        F = np.ascontiguousarray(F, dtype=np.float64)
+        lm = np.ascontiguousarray(lmbda, dtype=np.float64)
+        assert F.shape == (self.N, self.D) and lm.shape == (self.D,)
+        self.ctx.check(self.ctx.lib.gk_eig_set_params(self.ctx.h, self.h, ptr(F), float(mu_0), ptr(lm)))
+
+    def pg_draw(self, seed):
+        """K3: S <- Omega + Omega^T with Omega ~ PG(1, Mu); returns sum(Omega) over all N^2 entries."""
+        s = ctypes.c_double(0.0)
+        self.ctx.check(self.ctx.lib.gk_eig_pg_draw(self.ctx.h, self.h, ctypes.c_uint64(int(seed)), ctypes.byref(s)))
+        return s.value
+
+    def set_S(self, S_rows):
+        S = np.ascontiguousarray(S_rows, dtype=np.float64)
+        assert S.shape == (self.net.nrows, self.N)
+        self.ctx.check(self.ctx.lib.gk_eig_set_S(self.ctx.h, self.h, ptr(S)))
+
+    def get_S(self):
+        S = np.empty((self.net.nrows, self.N))
+        self.ctx.check(self.ctx.lib.gk_eig_get_S(self.ctx.h, self.h, ptr(S)))
+        return S
+
+    def resample_F(self, sigma_F, normals, want_conditionals=False):
+        """K4+K5.  Returns (F_new, stats dict, prec or None, h or None)."""
+        z = np.ascontiguousarray(normals, dtype=np.float64)
+        assert z.shape == (self.N, self.D)
+        D = self.D
+        F = np.empty((self.N, D))
+        prec = np.empty((self.N, D, D)) if want_conditionals else None
+        h = np.empty((self.N, D)) if want_conditionals else None
+        st = np.zeros(D * D + 2 * D)
+        self.ctx.check(self.ctx.lib.gk_eig_resample_F(self.ctx.h, self.h, float(sigma_F), ptr(z), ptr(F), ptr(prec),
+                                                     ptr(h), ptr(st)))
+        stats = dict(Pq=st[:D * D].reshape(D, D).copy(), hS=st[D * D:D * D + D].copy(), hK=st[D * D + D:].copy())
+        return F, stats, prec, h
+
+    def log_likelihood(self, link=0):
+        v = ctypes.c_double(0.0)
+        self.ctx.check(self.ctx.lib.gk_eig_log_likelihood(self.ctx.h, self.h, int(link), ctypes.byref(v)))
+        return v.value
+
+    def close(self):
+        self._finalizer()
+
+
+def _destroy_eig(ctx, h):
+    if ctx.h:
+        ctx.lib.gk_eig_destroy(ctx.h, h)

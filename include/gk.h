@@ -44,7 +44,8 @@ int gk_ctx_set_stream(gk_ctx *ctx, void *cuda_stream);      /* e.g. torch's curr
 int gk_ctx_synchronize(gk_ctx *ctx);
 int64_t gk_ctx_launch_count(gk_ctx *ctx);                   /* kernels launched so far by this ctx */
 /* per-kernel CUDA-event timing (bench.py roofline); family: 0 = strip statistics kernel,
- * 1 = sequential sampler, 2 = Polya-gamma draw, 3 = eigen slab contraction, 4 = latent pairwise */
+ * 1 = sequential sampler, 2 = Polya-gamma draw, 3 = eigen slab contraction, 4 = latent pairwise,
+ * 5 = eigen sequential feature draw */
 int gk_ctx_kernel_timing(gk_ctx *ctx, int enable);
 int gk_ctx_kernel_timing_read(gk_ctx *ctx, int family, double *ms_total, int64_t *launches, double *bytes_total);
 
@@ -97,6 +98,35 @@ int gk_sbm_block_sample(gk_ctx *ctx, gk_net *net, int n0, int nb, const double *
 int gk_sbm_get_block(gk_ctx *ctx, int n0, int nb, int32_t *c_out);
 int gk_sbm_set_block(gk_ctx *ctx, int n0, int nb, const int32_t *c_in);
 int gk_sbm_sweep_end(gk_ctx *ctx, gk_net *net, int32_t *c_out, double *out_lp, int64_t *out_nchanged);
+
+/* ---- eigenmodel (logistic / probit), K3-K6 ---------------------------------------------------------
+ * State of one eigenmodel over one network (A only; W is ignored): S = Omega + Omega^T (row shard),
+ * F (N x D), lmbda (D), mu_0.  1 <= D <= 8. */
+typedef struct gk_eig gk_eig;
+int gk_eig_create(gk_ctx *ctx, gk_net *net, int D, gk_eig **out);
+int gk_eig_destroy(gk_ctx *ctx, gk_eig *eig);
+size_t gk_eig_device_bytes(gk_eig *eig);
+/* upload the model attributes F (N x D), mu_0, lmbda (D)  (eigenmodel.py:41-73 state) */
+int gk_eig_set_params(gk_ctx *ctx, gk_eig *eig, const double *F, double mu0, const double *lmbda);
+/* K3: replaces eigenmodel.py:859-874 (ppg.pgdrawvpar over Mu.ravel()) fused with Mu of :75-83.  Draws
+ * Omega[n,m] ~ PG(1, Mu[n,m]) for all N^2 entries with a counter-based generator keyed by (seed, sweep, pair)
+ * and stores S = Omega + Omega^T (zero diagonal).  sum_omega (optional) = sum of ALL N^2 draws, diagonal
+ * included (the precision term O.sum() of eigenmodel.py:919). */
+int gk_eig_pg_draw(gk_ctx *ctx, gk_eig *eig, uint64_t seed, double *sum_omega);
+/* injection path of the parity tests: S rows (nrows x N doubles) computed by the caller from a given Omega */
+int gk_eig_set_S(gk_ctx *ctx, gk_eig *eig, const double *S_rows);
+int gk_eig_get_S(gk_ctx *ctx, gk_eig *eig, double *S_rows);
+/* K4+K5: replaces eigenmodel.py:876-908 (_resample_F), same serial semantics: node n is drawn from
+ * N(prec_n^-1 h_n, prec_n^-1) given the NEW features of m < n and the OLD ones of m > n, with the fixed map
+ * f = L^-T (L^-1 h + z), prec = L L^T, z = normals[n] (N x D standard normals supplied by the caller).
+ * Outputs (all optional): F_out N x D; out_prec N x D x D and out_h N x D = the conditionals at the moment
+ * each node was drawn; stats = Pq[D*D] | hS[D] | hK[D], the pair sums over n1 < n2 with the NEW F that the
+ * mu_0 and lmbda conditionals need (eigenmodel.py:910-965):
+ *   Pq[a,b] = sum S f1a f1b f2a f2b,  hS[a] = sum S f1a f2a,  hK[a] = sum (A12 + A21 - 1) f1a f2a. */
+int gk_eig_resample_F(gk_ctx *ctx, gk_eig *eig, double sigma_F, const double *normals, double *F_out,
+                      double *out_prec, double *out_h, double *stats);
+/* K9: replaces eigenmodel.py:110-129 with P of :803-811 (link 0, logistic) or :227-236 (link 1, probit) */
+int gk_eig_log_likelihood(gk_ctx *ctx, gk_eig *eig, int link, double *ll);
 
 #ifdef __cplusplus
 }

@@ -84,7 +84,7 @@ def logistic_resample_F_loops(A, O, F, mu_0, lmbda, sigma_F, z):
     return F, precs, hs
 
 
-def resample_F(S, Ksym_minus_mu0S, F, lmbda, sigma_F, z, base_scale=None):
+def resample_F(S, Ksym_minus_mu0S, F, lmbda, sigma_F, z, base_scale=None, nodes=None):
     """Contraction form of the sequential F sweep.
 
     S = Omega + Omega^T (logistic) or 2 (probit), zero diagonal irrelevant (skipped);
@@ -96,7 +96,7 @@ def resample_F(S, Ksym_minus_mu0S, F, lmbda, sigma_F, z, base_scale=None):
     F = F.copy()
     precs = np.zeros((N, D, D)); hs = np.zeros((N, D))
     llT = np.outer(lmbda, lmbda)
-    for n in range(N):
+    for n in range(N if nodes is None else nodes):       # nodes: bounded sample for the timed CPU baseline
         s = S[n].copy(); s[n] = 0.0
         r = Ksym_minus_mu0S[n].copy(); r[n] = 0.0
         prec = np.eye(D) / sigma_F + (F.T * s).dot(F) * llT
