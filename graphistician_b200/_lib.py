@@ -43,6 +43,7 @@ SIGNATURES = {
     "gk_eig_create": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_vp)]),
     "gk_eig_destroy": (c_int, [c_vp, c_vp]),
     "gk_eig_device_bytes": (c_sz, [c_vp]),
+    "gk_eig_set_option": (c_int, [c_vp, c_vp, c_int, c_int]),
     "gk_eig_set_params": (c_int, [c_vp, c_vp, c_vp, c_dbl, c_vp]),
     "gk_eig_pg_draw": (c_int, [c_vp, c_vp, ctypes.c_uint64, ctypes.POINTER(c_dbl)]),
     "gk_eig_set_S": (c_int, [c_vp, c_vp, c_vp]),

@@ -16,6 +16,7 @@ struct gk_eig {
     double *out_prec = nullptr, *out_h = nullptr;
     double mu0 = 0.0;
     bool have_S = false;
+    bool chol_f64 = false;             // f32 storage: factorise the D x D conditionals in fp32 unless set
     uint32_t sweep = 0;
 };
 
@@ -74,6 +75,12 @@ extern "C" int gk_eig_destroy(gk_ctx *ctx, gk_eig *e) {
 
 extern "C" size_t gk_eig_device_bytes(gk_eig *e) {
     return e ? (size_t)e->net->nrows * e->net->ld * gk_esize(e->dtype) + (size_t)e->N * e->D * 16 : 0;
+}
+
+extern "C" int gk_eig_set_option(gk_ctx *ctx, gk_eig *e, int option, int value) {
+    if (!ctx || !e) return GK_EINVAL;
+    if (option == GK_EIG_OPT_CHOL_F64) { e->chol_f64 = value != 0; return GK_OK; }
+    return gk_fail(ctx, GK_EINVAL, "unknown eigenmodel option %d", option);
 }
 
 extern "C" int gk_eig_set_params(gk_ctx *ctx, gk_eig *e, const double *F, double mu0, const double *lmbda) {
@@ -182,13 +189,13 @@ static int launch_slab(gk_ctx *ctx, gk_eig *e, int n0, int nb) {
     return GK_OK;
 }
 
-template <typename T, int D>
-static int launch_seq(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sblk, int ldS, const uint8_t *Ablk, int ldA,
-                      double inv_sigma_F) {
+template <typename T, typename CH, int D>
+static int launch_seq_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sblk, int ldS, const uint8_t *Ablk, int ldA,
+                         double inv_sigma_F) {
     static bool attr_set = false;
     const size_t smem = gk_eig_seq_smem<T, D>();
     if (!attr_set) {
-        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq<T, CH, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
     gk_eig_seq_params P;
@@ -196,10 +203,17 @@ static int launch_seq(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sblk, 
     P.F = e->F; P.z = e->z; P.lmbda = e->lmbda; P.mu0 = e->mu0; P.inv_sigma_F = inv_sigma_F;
     P.acc = e->acc; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h;
     gk_time_begin(ctx, 5, 0.0);
-    k_eig_seq<T, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
+    k_eig_seq<T, CH, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
     gk_time_end(ctx, 5);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
+}
+
+template <typename T, int D>
+static int launch_seq(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sblk, int ldS, const uint8_t *Ablk, int ldA,
+                      double inv_sigma_F) {
+    if (sizeof(T) == 4 && !e->chol_f64) return launch_seq_ch<T, float, D>(ctx, e, n0, nb, Sblk, ldS, Ablk, ldA, inv_sigma_F);
+    return launch_seq_ch<T, double, D>(ctx, e, n0, nb, Sblk, ldS, Ablk, ldA, inv_sigma_F);
 }
 
 template <typename T, int D>

@@ -265,7 +265,58 @@ size_t gk_eig_seq_smem() {
     return (size_t)2 * NB * PA * 8 + (size_t)NB * (NB + 1) * sizeof(T) + (size_t)NB * (NB + 4) + (size_t)2 * NB * D * 8 + 64;
 }
 
-template <typename T, int D>
+// factor prec = L L^T and draw f = L^-T (L^-1 h + z); forward substitution is fused into the right-looking
+// factorisation and the back substitution is column-oriented, so the dependent chain is ~3 ops per column.
+template <typename CH, int D>
+__device__ __forceinline__ void gk_chol_draw(const double *__restrict__ Lam, const double *__restrict__ hv,
+                                             const double *__restrict__ z, double *__restrict__ fout) {
+    constexpr int Q = gk_edim<D>::Q;
+    CH a[Q], rinv[D], w[D];
+#pragma unroll
+    for (int p = 0; p < Q; ++p) a[p] = (CH)Lam[p];             // packed (r <= c); L[ii][jj] lives at (jj, ii)
+#pragma unroll
+    for (int d = 0; d < D; ++d) w[d] = (CH)hv[d];
+#pragma unroll
+    for (int jj = 0; jj < D; ++jj) {
+        CH r;
+        if constexpr (sizeof(CH) == 4) r = rsqrtf(a[gk_qidx(D, jj, jj)]); else r = rsqrt(a[gk_qidx(D, jj, jj)]);
+        rinv[jj] = r;
+        w[jj] *= r;                                            // y[jj]
+#pragma unroll
+        for (int ii = jj + 1; ii < D; ++ii) {
+            a[gk_qidx(D, jj, ii)] *= r;                        // L[ii][jj]
+            w[ii] -= a[gk_qidx(D, jj, ii)] * w[jj];
+        }
+#pragma unroll
+        for (int kk = jj + 1; kk < D; ++kk)
+#pragma unroll
+            for (int ii = kk; ii < D; ++ii) a[gk_qidx(D, kk, ii)] -= a[gk_qidx(D, jj, ii)] * a[gk_qidx(D, jj, kk)];
+    }
+#pragma unroll
+    for (int d = 0; d < D; ++d) w[d] += (CH)z[d];
+#pragma unroll
+    for (int jj = D - 1; jj >= 0; --jj) {
+        w[jj] *= rinv[jj];
+#pragma unroll
+        for (int kk = 0; kk < jj; ++kk) w[kk] -= a[gk_qidx(D, kk, jj)] * w[jj];
+    }
+#pragma unroll
+    for (int d = 0; d < D; ++d) fout[d] = (double)w[d];
+}
+
+// monomial (a, b) of packed column p (p < Q: quadratic; Q <= p < P and P <= p < PA: linear in a)
+template <int D>
+__device__ __forceinline__ void gk_col_ab(int p, int &pa, int &pb) {
+    constexpr int Q = gk_edim<D>::Q, Pn = gk_edim<D>::P;
+    if (p < Q) { int a = 0, r = p; while (r >= D - a) { r -= D - a; ++a; } pa = a; pb = a + r; }
+    else if (p < Pn) pa = pb = p - Q;
+    else pa = pb = p - Pn;
+}
+
+// Warp 0 = solver: conditional, factorisation and draw of node t, then completes row t+1 itself (node t and
+// node t-1 contributions).  Warps 1..15 = updaters: while the solver works on node t they move node t-1 from
+// "upper" to "lower" in rows >= t+2 and fold node t-1's pair statistics.  One barrier per node.
+template <typename T, typename CH, int D>
 __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq(gk_eig_seq_params P) {
     constexpr int NB = gk_eig_nb<T>::NB, Q = gk_edim<D>::Q, Pn = gk_edim<D>::P, PA = gk_edim<D>::PA;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -275,8 +326,9 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq(gk_eig_seq_pa
     double *fold = zb + (size_t)NB * D;                   // [NB][D]
     T *Sb = (T *)(fold + (size_t)NB * D);                 // [NB][NB+1]
     uint8_t *Ab = (uint8_t *)(Sb + (size_t)NB * (NB + 1));   // [NB][NB+4]
-    __shared__ double Lam[gk_edim<D>::Q], hv[D], phin[gk_edim<D>::PA], phio[gk_edim<D>::PA], lam[D];
-    const int tid = threadIdx.x, nb = P.nb, n0 = P.n0;
+    __shared__ double Lam[gk_edim<D>::Q], hv[D], fnew[D], lam[D];
+    __shared__ double phin[2][gk_edim<D>::PA], phio[2][gk_edim<D>::PA];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nb = P.nb, n0 = P.n0;
 
     for (int t = tid; t < nb * PA; t += GK_EIG_SEQ_THREADS) {
         int i = t / PA, p = t - i * PA;
@@ -295,96 +347,94 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq(gk_eig_seq_pa
         Ab[i * (NB + 4) + j] = P.Ablk[(size_t)i * P.ldA + j];
     }
     if (tid < D) lam[tid] = P.lmbda[tid];
-    // per-thread role for p = tid < PA
-    int pa = 0, pb = 0;                                   // monomial (a, b) for p < Q; a for the linear parts
-    if (tid < Q) { int a = 0, r = tid; while (r >= D - a) { r -= D - a; ++a; } pa = a; pb = a + r; }
-    else if (tid < Pn) pa = pb = tid - Q;
-    else if (tid < PA) pa = pb = tid - Pn;
-    double run = 0.0, stat = 0.0;                         // sumF[a] (Q <= p < P) or prefixF[a] (p >= P); statistic
-    if (tid >= Q && tid < Pn) run = P.glob[GK_EIG_GLOB_SUMF + pa];
-    else if (tid >= Pn && tid < PA) run = P.glob[GK_EIG_GLOB_PREF + pa];
+    // solver lanes own columns p0 = lane and p1 = lane + 32; updater threads 32..32+PA-1 own statistic column tid-32
+    const int p0 = lane, p1 = lane + 32;
+    int a0 = 0, b0 = 0, a1 = 0, b1 = 0, sa = 0, sb = 0;
+    if (p0 < PA) gk_col_ab<D>(p0, a0, b0);
+    if (p1 < PA) gk_col_ab<D>(p1, a1, b1);
+    const int sp = tid - 32;                               // statistic column of an updater thread
+    if (sp >= 0 && sp < PA) gk_col_ab<D>(sp, sa, sb);
+    double sumF = 0.0, pref = 0.0, stat = 0.0;
+    if (warp == 0 && lane < D) sumF = P.glob[GK_EIG_GLOB_SUMF + lane];
+    if (sp >= Pn && sp < PA) pref = P.glob[GK_EIG_GLOB_PREF + sa];
     __syncthreads();
 
-    for (int i = 0; i < nb; ++i) {
-        const int n = n0 + i;
-        // ---- A: conditional of node n
-        if (tid < PA) {
-            const double g = GL[(size_t)i * PA + tid] + GU[(size_t)i * PA + tid];
-            if (tid < Q) {
-                const double v = (pa == pb ? P.inv_sigma_F : 0.0) + lam[pa] * lam[pb] * g;
-                Lam[tid] = v;
-                phio[tid] = fold[i * D + pa] * fold[i * D + pb];
-                if (P.out_prec) { P.out_prec[((size_t)n * D + pa) * D + pb] = v; P.out_prec[((size_t)n * D + pb) * D + pa] = v; }
-            } else if (tid < Pn) {
-                const double gh = GL[(size_t)i * PA + Pn + pa] + GU[(size_t)i * PA + Pn + pa];
-                const double v = lam[pa] * (gh - (run - fold[i * D + pa]) - P.mu0 * g);
-                hv[pa] = v;
-                phio[tid] = fold[i * D + pa];
-                if (P.out_h) P.out_h[(size_t)n * D + pa] = v;
-            } else {
-                phio[tid] = fold[i * D + pa];
+    for (int t = 0; t <= nb; ++t) {
+        if (warp == 0) {
+            if (t < nb) {
+                const int n = n0 + t, cur = t & 1;
+                // ---- A: conditional of node n from the completed row t
+                const double sF = __shfl_sync(0xffffffffu, sumF, (p0 >= Q && p0 < Pn) ? a0 : ((p1 >= Q && p1 < Pn) ? a1 : 0));
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int p = h ? p1 : p0, pa = h ? a1 : a0, pb = h ? b1 : b0;
+                    if (p < PA) {
+                        const double g = GL[(size_t)t * PA + p] + GU[(size_t)t * PA + p];
+                        if (p < Q) {
+                            const double v = (pa == pb ? P.inv_sigma_F : 0.0) + lam[pa] * lam[pb] * g;
+                            Lam[p] = v;
+                            phio[cur][p] = fold[t * D + pa] * fold[t * D + pb];
+                            if (P.out_prec) { P.out_prec[((size_t)n * D + pa) * D + pb] = v; P.out_prec[((size_t)n * D + pb) * D + pa] = v; }
+                        } else if (p < Pn) {
+                            const double gh = GL[(size_t)t * PA + Pn + pa] + GU[(size_t)t * PA + Pn + pa];
+                            const double v = lam[pa] * (gh - (sF - fold[t * D + pa]) - P.mu0 * g);
+                            hv[pa] = v;
+                            phio[cur][p] = fold[t * D + pa];
+                            if (P.out_h) P.out_h[(size_t)n * D + pa] = v;
+                        } else {
+                            phio[cur][p] = fold[t * D + pa];
+                        }
+                    }
+                }
+                __syncwarp();
+                // ---- B: factor and draw (one lane: the chain is latency-bound)
+                if (lane == 0) gk_chol_draw<CH, D>(Lam, hv, zb + t * D, fnew);
+                __syncwarp();
+                if (lane < D) { const double f = fnew[lane]; P.F[(size_t)n * D + lane] = f; sumF += f - fold[t * D + lane]; }
+#pragma unroll
+                for (int h = 0; h < 2; ++h) {
+                    const int p = h ? p1 : p0, pa = h ? a1 : a0, pb = h ? b1 : b0;
+                    if (p < PA) phin[cur][p] = p < Q ? fnew[pa] * fnew[pb] : fnew[pa];
+                }
+                __syncwarp();
+                // ---- complete row t+1: node t (just drawn) and node t-1 (the updaters start at row t+2)
+                if (t + 1 < nb) {
+#pragma unroll
+                    for (int h = 0; h < 2; ++h) {
+                        const int p = h ? p1 : p0;
+                        if (p < PA) {
+                            double x = p < Pn ? (double)Sb[t * (NB + 1) + t + 1] : (double)Ab[t * (NB + 4) + t + 1];
+                            double gl = x * phin[cur][p], gu = x * phio[cur][p];
+                            if (t > 0) {
+                                x = p < Pn ? (double)Sb[(t - 1) * (NB + 1) + t + 1] : (double)Ab[(t - 1) * (NB + 4) + t + 1];
+                                gl += x * phin[cur ^ 1][p]; gu += x * phio[cur ^ 1][p];
+                            }
+                            GL[(size_t)(t + 1) * PA + p] += gl;
+                            GU[(size_t)(t + 1) * PA + p] -= gu;
+                        }
+                    }
+                }
             }
-        }
-        __syncthreads();
-        // ---- B: factor and draw (single thread; the chain is latency-bound, not throughput-bound)
-        if (tid == 0) {
-            double a[Q], rinv[D], y[D];
-#pragma unroll
-            for (int p = 0; p < Q; ++p) a[p] = Lam[p];    // packed upper (r <= c) == lower by symmetry: a[(c,r)]
-#pragma unroll
-            for (int jj = 0; jj < D; ++jj) {
-                const double r = rsqrt(a[gk_qidx(D, jj, jj)]);
-                rinv[jj] = r;
-#pragma unroll
-                for (int ii = jj + 1; ii < D; ++ii) a[gk_qidx(D, jj, ii)] *= r;          // L[ii][jj]
-#pragma unroll
-                for (int kk = jj + 1; kk < D; ++kk)
-#pragma unroll
-                    for (int ii = kk; ii < D; ++ii) a[gk_qidx(D, kk, ii)] -= a[gk_qidx(D, jj, ii)] * a[gk_qidx(D, jj, kk)];
+        } else if (t > 0) {
+            // ---- updaters: node s = t-1
+            const int s = t - 1, buf = s & 1;
+            if (sp < PA) {                                 // pair statistics of (m < n_s, n_s) with the new features
+                const double gl = GL[(size_t)s * PA + sp];
+                if (sp < Pn) stat += phin[buf][sp] * gl;
+                else { stat += phin[buf][sp] * (gl - pref); pref += phin[buf][sp]; }
             }
-#pragma unroll
-            for (int jj = 0; jj < D; ++jj) {               // y = L^-1 h + z
-                double v = hv[jj];
-#pragma unroll
-                for (int kk = 0; kk < jj; ++kk) v -= a[gk_qidx(D, kk, jj)] * y[kk];
-                y[jj] = v * rinv[jj];
+            const int rem = (nb - t - 2) * PA;             // rows t+2 .. nb-1 (row t+1 belongs to the solver)
+            for (int e = tid - 32; e < rem; e += GK_EIG_SEQ_THREADS - 32) {
+                const int jr = e / PA, p = e - jr * PA, j = t + 2 + jr;
+                const double x = p < Pn ? (double)Sb[s * (NB + 1) + j] : (double)Ab[s * (NB + 4) + j];
+                GL[(size_t)j * PA + p] += x * phin[buf][p];
+                GU[(size_t)j * PA + p] -= x * phio[buf][p];
             }
-#pragma unroll
-            for (int jj = 0; jj < D; ++jj) y[jj] += zb[i * D + jj];
-#pragma unroll
-            for (int jj = D - 1; jj >= 0; --jj) {          // f = L^-T y
-                double v = y[jj];
-#pragma unroll
-                for (int kk = jj + 1; kk < D; ++kk) v -= a[gk_qidx(D, jj, kk)] * y[kk];
-                y[jj] = v * rinv[jj];
-            }
-#pragma unroll
-            for (int aa = 0; aa < D; ++aa) {
-                P.F[(size_t)n * D + aa] = y[aa];
-                phin[Q + aa] = y[aa]; phin[Pn + aa] = y[aa];
-#pragma unroll
-                for (int bb = aa; bb < D; ++bb) phin[gk_qidx(D, aa, bb)] = y[aa] * y[bb];
-            }
-        }
-        __syncthreads();
-        // ---- C: statistics of the pairs (m < n, n), then move node i from "upper" to "lower" in later rows
-        if (tid < PA) {
-            const double gl = GL[(size_t)i * PA + tid];
-            if (tid < Pn) stat += phin[tid] * gl;
-            else stat += phin[tid] * (gl - run);
-            if (tid >= Q && tid < Pn) run += phin[tid] - phio[tid];
-            else if (tid >= Pn) run += phin[tid];
-        }
-        const int rem = (nb - i - 1) * PA;
-        for (int t = tid; t < rem; t += GK_EIG_SEQ_THREADS) {
-            const int jr = t / PA, p = t - jr * PA, j = i + 1 + jr;
-            const double x = p < Pn ? (double)Sb[i * (NB + 1) + j] : (double)Ab[i * (NB + 4) + j];
-            GL[(size_t)j * PA + p] += x * phin[p];
-            GU[(size_t)j * PA + p] -= x * phio[p];
         }
         __syncthreads();
     }
-    if (tid < Q) P.glob[GK_EIG_GLOB_PQ + tid] += stat;
-    else if (tid < Pn) { P.glob[GK_EIG_GLOB_HS + pa] += stat; P.glob[GK_EIG_GLOB_SUMF + pa] = run; }
-    else if (tid < PA) { P.glob[GK_EIG_GLOB_HK + pa] += stat; P.glob[GK_EIG_GLOB_PREF + pa] = run; }
+    if (warp == 0 && lane < D) P.glob[GK_EIG_GLOB_SUMF + lane] = sumF;
+    if (sp >= 0 && sp < Q) P.glob[GK_EIG_GLOB_PQ + sp] += stat;
+    else if (sp >= Q && sp < Pn) P.glob[GK_EIG_GLOB_HS + sa] += stat;
+    else if (sp >= Pn && sp < PA) { P.glob[GK_EIG_GLOB_HK + sa] += stat; P.glob[GK_EIG_GLOB_PREF + sa] = pref; }
 }

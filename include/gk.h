@@ -106,6 +106,10 @@ typedef struct gk_eig gk_eig;
 int gk_eig_create(gk_ctx *ctx, gk_net *net, int D, gk_eig **out);
 int gk_eig_destroy(gk_ctx *ctx, gk_eig *eig);
 size_t gk_eig_device_bytes(gk_eig *eig);
+/* options: GK_EIG_OPT_CHOL_F64 = factorise the D x D conditionals in fp64 even with fp32 storage
+ * (default with fp32 storage: fp32 factorisation; the conditionals themselves are always fp64) */
+enum { GK_EIG_OPT_CHOL_F64 = 0 };
+int gk_eig_set_option(gk_ctx *ctx, gk_eig *eig, int option, int value);
 /* upload the model attributes F (N x D), mu_0, lmbda (D)  (eigenmodel.py:41-73 state) */
 int gk_eig_set_params(gk_ctx *ctx, gk_eig *eig, const double *F, double mu0, const double *lmbda);
 /* K3: replaces eigenmodel.py:859-874 (ppg.pgdrawvpar over Mu.ravel()) fused with Mu of :75-83.  Draws
