@@ -53,72 +53,98 @@ __global__ void k_eig_asym(const uint8_t *__restrict__ A, const uint8_t *__restr
 }
 
 // ---------------------------------------------------------------------------------------------------
-// K3: S[n,m] = omega[n,m] + omega[m,n], both ~ PG(1, Mu[n,m]) (Mu is symmetric), Philox keyed by the unordered
-// pair so any rank can regenerate any entry.  One CTA = one 64 x 64 tile; tiles strictly below the diagonal
-// whose mirror image is also local are skipped (written by the mirror tile through shared memory).
-// part[tile] = sum of the pair draws of the tile (each unordered pair once) + the diagonal draws PG(1, mu_0).
+// K3: S[n,m] = omega[n,m] + omega[m,n], both ~ PG(1, Mu[n,m]) (Mu is symmetric).  One CTA = one 64 x 64 tile,
+// always GENERATED in its canonical orientation (smaller block index first) by per-lane generators keyed by
+// (seed, sweep, canonical tile, thread), so any rank regenerates exactly the same tile; it is then written to
+// the local rows directly, transposed, or both.  Tiles below the diagonal whose mirror image is local are
+// skipped.  Pass 1 (uniform across the warp): logits and proposal masses into shared memory.  Pass 2: each lane
+// drains its own queue of 16 entries x 2 draws (gk_pg1_step), so accepted lanes do not idle.
+// part[tile] = sum of the tile's pair draws (each unordered pair counted by exactly one CTA over all ranks)
+//              + its diagonal draws PG(1, mu_0).
 // ---------------------------------------------------------------------------------------------------
 template <typename T>
 __global__ void __launch_bounds__(256) k_eig_pg_tile(T *__restrict__ S, int ld, int row0, int nrows, int N, int D,
                                                      const double *__restrict__ F, const double *__restrict__ lmbda,
                                                      double mu0, uint64_t seed, uint32_t sweep,
                                                      double *__restrict__ part) {
-    constexpr int TS = GK_PG_TILE;
+    constexpr int TS = GK_PG_TILE, NQ = TS * TS / 256;
     __shared__ float fi[TS][GK_EIG_MAXD], fj[TS][GK_EIG_MAXD];
-    __shared__ float tile[TS][TS + 1];
+    __shared__ float tile[TS][TS + 1], massb[TS][TS + 1];
     __shared__ double red[8];
     const int tid = threadIdx.x;
-    const int I = row0 + blockIdx.y * TS, J = blockIdx.x * TS;          // global node offsets
+    const int I = row0 + blockIdx.y * TS, J = blockIdx.x * TS;          // local row block, column block
     const bool mirror_local = J >= row0 && J < row0 + nrows;
     const int pidx = blockIdx.y * gridDim.x + blockIdx.x;
     if (mirror_local && J < I) { if (tid == 0) part[pidx] = 0.0; return; }
     const bool write_mirror = mirror_local && J > I;
-    const bool diag_tile = (I == J);
+    const bool swapped = I > J, diag_tile = (I == J);
+    const int cI = swapped ? J : I, cJ = swapped ? I : J;               // canonical tile origin
     for (int t = tid; t < TS * GK_EIG_MAXD; t += 256) {
         int r = t / GK_EIG_MAXD, d = t % GK_EIG_MAXD;
         float a = 0.f, b = 0.f;
         if (d < D) {
-            if (I + r < N) a = (float)(F[(size_t)(I + r) * D + d] * lmbda[d]);
-            if (J + r < N) b = (float)F[(size_t)(J + r) * D + d];
+            if (cI + r < N) a = (float)(F[(size_t)(cI + r) * D + d] * lmbda[d]);
+            if (cJ + r < N) b = (float)F[(size_t)(cJ + r) * D + d];
         }
         fi[r][d] = a; fj[r][d] = b;
     }
     __syncthreads();
-    const int j = tid & (TS - 1);
-    double local = 0.0;
-    for (int i = tid / TS; i < TS; i += 256 / TS) {
-        const int n = I + i, m = J + j;
-        float v = 0.f;
-        if (n < N && m < N && n - row0 < nrows) {
-            if (n == m) {
-                gk_philox g; g.init(seed, (uint32_t)n, (uint32_t)m, sweep);
-                local += (double)gk_pg1_draw((float)mu0, g);
-            } else if (!diag_tile || m > n) {
-                float z = (float)mu0;
+    const int j = tid & (TS - 1), i0 = tid / TS;
+    // pass 1: logit and proposal mass of every live entry of this lane's queue (mass < 0 marks a dead entry)
+#pragma unroll 4
+    for (int k = 0; k < NQ; ++k) {
+        const int i = i0 + k * (256 / TS), n = cI + i, m = cJ + j;
+        float z = 0.f, ms = -1.f;
+        if (n < N && m < N && (!diag_tile || m >= n)) {
+            z = (float)mu0;
+            if (n != m) {
 #pragma unroll
                 for (int d = 0; d < GK_EIG_MAXD; ++d) z += fi[i][d] * fj[j][d];
-                gk_philox g; g.init(seed, (uint32_t)min(n, m), (uint32_t)max(n, m), sweep);
-                v = gk_pg1_draw(z, g) + gk_pg1_draw(z, g);
-                if (write_mirror || diag_tile || n < m) local += (double)v;
+            }
+            ms = gk_pg_mass(0.5f * fabsf(z));
+        }
+        tile[i][j] = z; massb[i][j] = ms;
+    }
+    // pass 2: drain the queue
+    gk_xoshiro g; g.seed(seed, (uint32_t)tid | ((uint32_t)sweep << 8), (uint32_t)cI, (uint32_t)cJ);
+    double local = 0.0;
+    int k = 0, need = 0;
+    bool in_left = false;
+    float Z = 0.f, mass = 0.f, accv = 0.f;
+    while (k < NQ) {
+        const int i = i0 + k * (256 / TS);
+        if (need == 0) {                                   // start the next entry
+            mass = massb[i][j];
+            if (mass < 0.f) { tile[i][j] = 0.f; ++k; continue; }
+            Z = 0.5f * fabsf(tile[i][j]);
+            need = (diag_tile && i == j) ? 1 : 2;
+            accv = 0.f; in_left = false;
+        }
+        float X;
+        if (gk_pg1_step(Z, mass, in_left, g, X)) {
+            accv += 0.25f * X;
+            if (--need == 0) {
+                if (diag_tile && i == j) { local += (double)accv; tile[i][j] = 0.f; }
+                else { tile[i][j] = accv; if (!swapped) local += (double)accv; }
+                ++k;
             }
         }
-        tile[i][j] = v;
     }
     __syncthreads();
-    // write the tile (diagonal tile: mirror inside the tile) and, if local, its transpose
-    for (int i = tid / TS; i < TS; i += 256 / TS) {
+    // write: own rows I.. (direct, or transposed when the canonical tile is the mirror image), mirror rows J..
+    for (int i = i0; i < TS; i += 256 / TS) {
         const int n = I + i, m = J + j;
         if (n - row0 < nrows && n < N && m < ld) {
-            float v = tile[i][j];
-            if (diag_tile && j < i) v = tile[j][i];
+            float v;
+            if (swapped) v = tile[j][i];
+            else v = (diag_tile && j < i) ? tile[j][i] : tile[i][j];
             S[(size_t)(n - row0) * ld + m] = (m < N) ? (T)v : T(0);
         }
         if (write_mirror) {
-            const int n2 = J + i, m2 = I + j;                           // transposed tile: row n2, column m2
+            const int n2 = J + i, m2 = I + j;
             if (n2 < N && n2 - row0 < nrows && m2 < ld) S[(size_t)(n2 - row0) * ld + m2] = (m2 < N) ? (T)tile[j][i] : T(0);
         }
     }
-    // tile sum (fixed order inside the CTA)
     for (int o = 16; o; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
     if ((tid & 31) == 0) red[tid >> 5] = local;
     __syncthreads();

@@ -122,3 +122,86 @@ __device__ __forceinline__ float gk_pg1_draw(float z, gk_philox &g) {
     }
     return 0.25f * tanhf(Z) / fmaxf(Z, 1e-6f) * 0.5f;    // unreachable in practice: fall back to the mean
 }
+
+// ---- lane-queue form of the same sampler (K3 tile kernel) ---------------------------------------------
+// A rejection sampler on a 32-wide warp idles every lane that has already accepted.  Here each lane owns a
+// queue of entries and keeps proposing for ITS current entry until the queue is empty, so lanes only idle at
+// the very end of the queue.  The alternating-series test is done in ratio form r_n = a_n / a_0 =
+// (2n+1) exp(n (n+1) e), e = -pi^2 x / 2 (x > t) or -2 / x (x <= t): one exponential, no a_0.
+struct gk_xoshiro {                      // xoshiro128++ (Blackman & Vigna), seeded from one Philox block
+    uint32_t s0, s1, s2, s3;
+    __device__ __forceinline__ void seed(uint64_t key, uint32_t a, uint32_t b, uint32_t c) {
+        gk_philox ph; ph.init(key, a, b, c); ph.refill();
+        s0 = ph.out[0]; s1 = ph.out[1]; s2 = ph.out[2]; s3 = ph.out[3];
+        if ((s0 | s1 | s2 | s3) == 0u) s0 = 1u;
+    }
+    __device__ __forceinline__ uint32_t next() {
+        const uint32_t r = __funnelshift_l(s0 + s3, s0 + s3, 7) + s0;
+        const uint32_t t = s1 << 9;
+        s2 ^= s0; s3 ^= s1; s1 ^= s2; s0 ^= s3; s2 ^= t; s3 = __funnelshift_l(s3, s3, 11);
+        return r;
+    }
+    __device__ __forceinline__ float unif() { return ((float)(next() >> 8) + 0.5f) * (1.0f / 16777216.0f); }
+    __device__ __forceinline__ float expon() { return -__logf(unif()); }
+    __device__ __forceinline__ float normal() {
+        float u1 = unif(), u2 = unif();
+        return sqrtf(-2.0f * __logf(u1)) * __cosf(2.0f * GK_PI_F * u2);
+    }
+};
+
+// probability of the exponential (right) piece of the proposal for J*(1, Z), Z = |z| / 2
+__device__ __forceinline__ float gk_pg_mass(float Z) {
+    const float t = GK_PG_T, rt = 1.25f;
+    const float fz = 0.125f * GK_PI_F * GK_PI_F + 0.5f * Z * Z;
+    const float b = rt * (t * Z - 1.0f), a = -rt * (t * Z + 1.0f);
+    const float x0 = __logf(fz) + fz * t;
+    const float xb = x0 - Z + gk_log_ndtr(b), xa = x0 + Z + gk_log_ndtr(a);
+    const float qdivp = 1.27323954f * (__expf(fminf(xb, 80.f)) + __expf(fminf(xa, 80.f)));
+    return 1.0f / (1.0f + qdivp);
+}
+
+// one proposal step for the lane's current draw.  in_left: the left (truncated inverse-Gaussian) piece was
+// chosen and its inner rejection has not succeeded yet (it must be retried, NOT re-chosen).  Returns true and
+// sets X (= J*, omega = X / 4) when a variate is accepted.
+__device__ __forceinline__ bool gk_pg1_step(float Z, float mass, bool &in_left, gk_xoshiro &g, float &X) {
+    const float t = GK_PG_T;
+    bool have = false;
+    float x = 0.f;
+    if (!in_left) {
+        if (g.unif() < mass) {
+            const float fz = 0.125f * GK_PI_F * GK_PI_F + 0.5f * Z * Z;
+            x = t + __fdividef(g.expon(), fz);
+            have = true;
+        } else in_left = true;
+    }
+    if (in_left) {
+        if (Z < 1.0f / t) {
+            const float E1 = g.expon(), E2 = g.expon();
+            x = 1.0f + E1 * t;
+            x = __fdividef(t, x * x);
+            const bool ok = (E1 * E1 <= 2.0f * E2 / t) && (g.unif() <= __expf(-0.5f * Z * Z * x));
+            if (ok) { have = true; in_left = false; }
+        } else {
+            const float mu = __fdividef(1.0f, Z);
+            float Y = g.normal(); Y *= Y;
+            const float half_mu = 0.5f * mu, mu_Y = mu * Y;
+            x = mu + half_mu * mu_Y - half_mu * sqrtf(4.0f * mu_Y + mu_Y * mu_Y);
+            if (g.unif() > __fdividef(mu, mu + x)) x = __fdividef(mu * mu, x);
+            if (x <= t) { have = true; in_left = false; }
+        }
+    }
+    if (!have) return false;
+    const float e = x > t ? -0.5f * GK_PI_F * GK_PI_F * x : __fdividef(-2.0f, x);
+    const float u = g.unif();
+    float S = 1.0f - 3.0f * __expf(2.0f * e);
+    bool accept = u <= S;
+    if (!accept) {                                   // rare (< 0.6 %): continue the alternating series
+        for (int n = 2; n < 24; ++n) {
+            const float r = (float)(2 * n + 1) * __expf((float)(n * (n + 1)) * e);
+            if (n & 1) { S -= r; if (u <= S) { accept = true; break; } }
+            else { S += r; if (u > S) break; }
+        }
+    }
+    if (accept) X = x;
+    return accept;
+}

@@ -91,8 +91,17 @@ static int launch_strip(gk_ctx *ctx, gk_net *net, const uint8_t *c8, int K, int 
     typedef typename gk_acc<T, B>::type ACC;
     constexpr int S = gk_sdim<B>::S;
     int strips = nb_pad / GK_STRIP_COLS;
-    int want = (2 * ctx->num_sms + strips * ndirs - 1) / (strips * ndirs);
-    int chunk_rows = (net->nrows + want - 1) / want;
+    // row chunks per strip: fill whole waves of (2 CTAs/SM) x num_sms slots -- a 1.08-wave grid costs two waves
+    const int slots = 2 * ctx->num_sms, per = strips * ndirs;
+    const int cmin = std::max(1, (net->nrows + GK_MAX_CHUNK_ROWS - 1) / GK_MAX_CHUNK_ROWS);
+    const int cmax = std::max(cmin, std::min((net->nrows + 63) / 64, std::max(cmin + 8, slots / per)));
+    int best = cmin; double best_cost = 1e30;
+    for (int cnk = cmin; cnk <= cmax; ++cnk) {
+        const double waves = (double)per * cnk / slots, full = ceil(waves - 1e-9);
+        const double cost = full / waves * (1.0 + 0.01 * cnk);           // idle fraction, mild penalty per extra chunk
+        if (cost < best_cost - 1e-12) { best_cost = cost; best = cnk; }
+    }
+    int chunk_rows = (net->nrows + best - 1) / best;
     chunk_rows = std::min(std::max(chunk_rows, 64), GK_MAX_CHUNK_ROWS);
     chunk_rows = (chunk_rows + 3) / 4 * 4;
     int nchunks = (net->nrows + chunk_rows - 1) / chunk_rows;

@@ -131,6 +131,9 @@ class DeviceEigenmodel:
         self.h = h
         self._finalizer = weakref.finalize(self, _destroy_eig, self.ctx, h)
 
+    def set_option(self, option, value):
+        self.ctx.check(self.ctx.lib.gk_eig_set_option(self.ctx.h, self.h, int(option), int(value)))
+
     def set_params(self, F, mu_0, lmbda):
         F = np.ascontiguousarray(F, dtype=np.float64)
         lm = np.ascontiguousarray(lmbda, dtype=np.float64)

@@ -76,13 +76,20 @@ def test_feature_sweep_matches_golden_fixture(golden_dir):
     assert np.isclose(eig.log_likelihood(1), float(g["ll_probit"]), rtol=1e-12)
 
 
-@pytest.mark.parametrize("N,D", [(300, 8), (257, 2)])
-def test_feature_sweep_f32_storage(N, D):
+@pytest.mark.parametrize("N,D,chol64", [(300, 8, 0), (257, 2, 0), (300, 8, 1)])
+def test_feature_sweep_f32_storage(N, D, chol64):
     from oracle import eigenmodel as eg
+    from graphistician_b200 import DeviceNetwork
+    from graphistician_b200.device import DeviceEigenmodel
     A, O, F, lm, mu0, z = _problem(N, D, 5 + N)
     S, R = eg.logistic_sym(A.astype(float), O, mu0)
     F_ref, prec_ref, h_ref = eg.resample_F(S, R, F, lm, 1.0, z)
-    net, eig, (F_gpu, st, prec, h) = _run(A, O, F, lm, mu0, z, 1.0, "f32")
+    net = DeviceNetwork(A, None, dtype="f32")
+    eig = DeviceEigenmodel(net, D)
+    eig.set_option(0, chol64)                     # GK_EIG_OPT_CHOL_F64
+    eig.set_params(F, mu0, lm)
+    eig.set_S(O + O.T)
+    F_gpu, st, prec, h = eig.resample_F(1.0, z, want_conditionals=True)
     assert np.allclose(prec, prec_ref, rtol=1e-3, atol=1e-4 * np.abs(prec_ref).max())
     assert np.allclose(h, h_ref, rtol=1e-3, atol=1e-4 * np.abs(h_ref).max())
     assert np.allclose(F_gpu, F_ref, rtol=1e-2, atol=2e-3)
