@@ -96,6 +96,34 @@ def make_eigen_data(N, D, seed=1234, rank=0, p=0.01):
     return dict(A=A, W=None, F=F, mu0=float(mu0), _keep=(keepA,))
 
 
+def make_latent_data(N, dim, B=1, seed=1234, rank=0, sigma=2.0):
+    """L_true ~ sqrt(sigma) N(0, I) (adjacency.py:202), mu_0 = mu_self = 0,
+    A ~ Bern(logistic(-||l_i - l_j||^2 + mu_0)), W ~ N(0, 1)."""
+    g = np.random.Generator(np.random.PCG64(seed + 7919 * rank))
+    L = (np.sqrt(sigma) * g.standard_normal((N, dim))).astype(np.float32)
+    A, keepA = pinned_empty((N, N), np.uint8)
+    W, keepW = pinned_empty((N, N, B), np.float32)
+    sq = (L * L).sum(1)
+    rows = 1024
+    for r0 in range(0, N, rows):
+        r1 = min(N, r0 + rows)
+        eta = -(sq[r0:r1, None] + sq[None, :] - 2.0 * (L[r0:r1] @ L.T))
+        A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < 1.0 / (1.0 + np.exp(-eta))
+        W[r0:r1] = g.standard_normal((r1 - r0, N, B), dtype=np.float32)
+    return dict(A=A, W=W, L=L, _keep=(keepA, keepW))
+
+
+def build_latent_model(d, N, dim, B, dtype):
+    from graphistician_b200.networks import FactorizedNetworkDistribution
+    from graphistician_b200.adjacency import LatentDistanceAdjacencyDistribution
+    from graphistician_b200.weights import NIWGaussianWeightDistribution
+    from graphistician_b200.old_abstractions import network_for
+    np.random.seed(5678)
+    model = FactorizedNetworkDistribution(N, LatentDistanceAdjacencyDistribution, {"dim": dim, "sigma": 2.0, "dtype": dtype},
+                                          NIWGaussianWeightDistribution, {"B": B, "dtype": dtype})
+    return model, network_for(d["A"], d["W"])
+
+
 def build_eigen_model(d, N, D, dtype):
     from graphistician_b200.eigenmodel import LogisticEigenmodel
     from graphistician_b200.old_abstractions import FixedGaussianNetwork
@@ -213,6 +241,17 @@ def setup_workload(args, rank):
                     cpu_baseline=cpu_baseline_eigen,
                     config={"workload": "logistic_eigenmodel_pg_gibbs_sweep N=%d D=%d lmbda given (configs[2])" % (N, D),
                             "N": N, "D": D})
+    if args.workload == "latent":
+        dim, Bw = 2, 1
+        d = make_latent_data(N, dim, Bw, rank=rank)
+        model, network = build_latent_model(d, N, dim, Bw, args.dtype)
+        tup = (d["A"], d["W"])
+        return dict(N=N, data=d, model=model, network=network, step=lambda: model.resample(tup),
+                    algo_bytes=22.0 * N * N + 1.0 * N * N * (1 + Bw * 4),   # 11 + 11 pair passes + NIW statistics
+                    h2d=N * N * (1 + Bw * 4) + N * dim * 8 + N * (1 + 8 * Bw), d2h=N * dim * 8 + 64,
+                    dominant=(4, "k_latent_pair"), cpu_baseline=cpu_baseline_latent,
+                    config={"workload": "latent_distance_hmc_gibbs_sweep + NIW weights N=%d dim=%d B=%d (configs[3])" % (N, dim, Bw),
+                            "N": N, "dim": dim, "B": Bw})
     raise SystemExit("workload %s: not built yet" % args.workload)
 
 
@@ -230,6 +269,7 @@ def run_ours(args):
     ctx.set_stream(stream.cuda_stream)
     wl = setup_workload(args, rank)
     N, model, network, d, algo_bytes = wl["N"], wl["model"], wl["network"], wl["data"], wl["algo_bytes"]
+    step = wl.get("step") or (lambda: model.resample(network))
 
     def timed(nsteps, e2e):
         barrier(world); torch.cuda.synchronize()
@@ -239,7 +279,7 @@ def run_ours(args):
             for _ in range(nsteps):
                 if e2e:
                     network.invalidate()                        # host buffers -> device inside the timed region
-                model.resample(network)
+                step()
             e1.record(stream)
         torch.cuda.synchronize(); barrier(world)
         return max_over_ranks(e0.elapsed_time(e1), world, dev)
@@ -258,7 +298,7 @@ def run_ours(args):
     # per-kernel timing pass (CUDA events around every launch of each kernel family, on the ctx stream)
     ctx.kernel_timing(True)
     for _ in range(3):
-        model.resample(network)
+        step()
     fam = {f: ctx.kernel_timing_read(f) for f in range(6)}
     ctx.kernel_timing(False)
     kms, kn, kbytes = fam[wl["dominant"][0]]
@@ -355,6 +395,31 @@ def cpu_baseline_eigen(d, model, args, nodes=None):
                       "(%.2f s) + sequential conditionals/draws in NumPy (%.2f s, 1 core); scaled x%.1f to a full sweep"
                       % (nodes, N, pg.num_threads(), t_pg, t_F, N / float(nodes)),
             "measured_s": t_pg + t_F}
+
+
+def cpu_baseline_latent(d, model, args, nodes=None):
+    """Oracle (port) of one latent-distance sweep on a bounded sample: the fused value + gradient of
+    adjacency.py:244-275 (vectorised NumPy, fp64) over the first `nodes` rows, for the 22 evaluations a sweep needs
+    (11 for L, 11 for mu_0), plus the K = 1 NIW statistics of those rows; scaled by N / nodes."""
+    from oracle import latent
+    A, W = d["A"], d["W"]
+    N = A.shape[0]
+    nodes = nodes or args.cpu_nodes or min(N, 256)
+    adj = model.adjacency
+    L = np.asarray(adj.L, dtype=np.float64)
+    Ar = A[:nodes].astype(np.float64); Atr = np.ascontiguousarray(A[:, :nodes].T).astype(np.float64)
+    t0 = time.perf_counter()
+    for _ in range(22):
+        latent.rows_value_and_grad(L, adj.mu_0, adj.mu_self, Ar, Atr, 0, adj.sigma)
+    e = A[:nodes] != 0
+    We = W[:nodes][e].astype(np.float64)
+    We.sum(0); We.T.dot(We)
+    secs = time.perf_counter() - t0
+    full = secs * (N / float(nodes))
+    return {"value": 1.0 / full, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "oracle (vectorised NumPy restatement, fp64) on the first %d of %d rows: 22 value+gradient "
+                      "evaluations + NIW statistics; %.1f s measured, scaled x%.1f to a full sweep" % (nodes, N, secs, N / float(nodes)),
+            "measured_s": secs}
 
 
 def _stats_rows(A, W, c, K, nodes):

@@ -50,6 +50,21 @@ SIGNATURES = {
     "gk_eig_get_S": (c_int, [c_vp, c_vp, c_vp]),
     "gk_eig_resample_F": (c_int, [c_vp, c_vp, c_dbl, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "gk_eig_log_likelihood": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_dbl)]),
+    "gk_latent_create": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_vp)]),
+    "gk_latent_destroy": (c_int, [c_vp, c_vp]),
+    "gk_latent_set_params": (c_int, [c_vp, c_vp, c_vp, c_dbl, c_dbl, c_dbl]),
+    "gk_latent_get_params": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(c_dbl)]),
+    "gk_latent_acc_len": (c_sz, [c_vp]),
+    "gk_latent_lp_grad": (c_int, [c_vp, c_vp, ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl), c_vp, ctypes.POINTER(c_dbl),
+                                  ctypes.POINTER(c_dbl)]),
+    "gk_latent_eval_pass": (c_int, [c_vp, c_vp, c_vp]),
+    "gk_latent_eval_finish": (c_int, [c_vp, c_vp, c_vp, ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl), c_vp,
+                                      ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl)]),
+    "gk_latent_hmc": (c_int, [c_vp, c_vp, c_int, c_dbl, c_int, c_vp, c_dbl, ctypes.POINTER(c_int), ctypes.POINTER(c_dbl)]),
+    "gk_latent_hmc_begin": (c_int, [c_vp, c_vp, c_int, c_dbl, c_int, c_vp]),
+    "gk_latent_hmc_pass": (c_int, [c_vp, c_vp, c_vp]),
+    "gk_latent_hmc_advance": (c_int, [c_vp, c_vp, c_vp]),
+    "gk_latent_hmc_end": (c_int, [c_vp, c_vp, c_dbl, ctypes.POINTER(c_int), ctypes.POINTER(c_dbl)]),
 }
 
 _lib = None

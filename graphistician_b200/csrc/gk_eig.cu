@@ -22,7 +22,7 @@ struct gk_eig {
 
 #define GK_EIG_PA_MAX (GK_EIG_MAXD * (GK_EIG_MAXD + 1) / 2 + 2 * GK_EIG_MAXD)
 
-static int ensure_asym(gk_ctx *ctx, gk_net *net) {
+int gk_net_ensure_asym(gk_ctx *ctx, gk_net *net) {
     if (net->Asym) return GK_OK;
     size_t bytes = (size_t)net->nrows * net->ld;
     GK_CUDA(ctx, cudaMalloc(&net->Asym, bytes));
@@ -58,7 +58,7 @@ extern "C" int gk_eig_create(gk_ctx *ctx, gk_net *net, int D, gk_eig **out) {
     }
     GK_CUDA(ctx, cudaMemsetAsync(e->S, 0, (size_t)net->nrows * net->ld * gk_esize(e->dtype), ctx->stream));
     GK_CUDA(ctx, cudaMemsetAsync(e->acc, 0, (size_t)2 * GK_EIG_NBMAX * GK_EIG_PA_MAX * 8, ctx->stream));
-    int rc = ensure_asym(ctx, net);
+    int rc = gk_net_ensure_asym(ctx, net);
     if (rc) return rc;
     *out = e;
     return GK_OK;

@@ -182,3 +182,75 @@ class DeviceEigenmodel:
 def _destroy_eig(ctx, h):
     if ctx.h:
         ctx.lib.gk_eig_destroy(ctx.h, h)
+
+
+class DeviceLatent:
+    """Device state of one latent-distance adjacency model over one DeviceNetwork (gk_latent): L, mu_0 on the
+    device; every O(N^2) evaluation is one K8 pair pass."""
+
+    def __init__(self, net, dim):
+        self.net, self.ctx, self.dim, self.N = net, net.ctx, int(dim), net.N
+        h = ctypes.c_void_p()
+        self.ctx.check(self.ctx.lib.gk_latent_create(self.ctx.h, net.h, self.dim, ctypes.byref(h)))
+        self.h = h
+        self._finalizer = weakref.finalize(self, _destroy_latent, self.ctx, h)
+
+    def acc_len(self):
+        return int(self.ctx.lib.gk_latent_acc_len(self.h))
+
+    def set_params(self, L, mu_0, mu_self, sigma):
+        Lc = None if L is None else np.ascontiguousarray(L, dtype=np.float64)
+        assert Lc is None or Lc.shape == (self.N, self.dim)
+        self.ctx.check(self.ctx.lib.gk_latent_set_params(self.ctx.h, self.h, ptr(Lc), float(mu_0), float(mu_self),
+                                                         float(sigma)))
+
+    def get_params(self):
+        L = np.empty((self.N, self.dim))
+        mu0 = ctypes.c_double(0.0)
+        self.ctx.check(self.ctx.lib.gk_latent_get_params(self.ctx.h, self.h, ptr(L), ctypes.byref(mu0)))
+        return L, mu0.value
+
+    def lp_grad(self):
+        """(ll, lp, dlp/dL, dlp/dmu_0, dlp/dmu_self) at the current parameters."""
+        ll, lp, g0, gs = (ctypes.c_double(0.0) for _ in range(4))
+        gL = np.empty((self.N, self.dim))
+        self.ctx.check(self.ctx.lib.gk_latent_lp_grad(self.ctx.h, self.h, ctypes.byref(ll), ctypes.byref(lp), ptr(gL),
+                                                      ctypes.byref(g0), ctypes.byref(gs)))
+        return ll.value, lp.value, gL, g0.value, gs.value
+
+    def eval_pass(self, acc_ptr=None):
+        self.ctx.check(self.ctx.lib.gk_latent_eval_pass(self.ctx.h, self.h, acc_ptr))
+
+    def eval_finish(self, acc_ptr=None):
+        ll, lp, g0, gs = (ctypes.c_double(0.0) for _ in range(4))
+        gL = np.empty((self.N, self.dim))
+        self.ctx.check(self.ctx.lib.gk_latent_eval_finish(self.ctx.h, self.h, acc_ptr, ctypes.byref(ll), ctypes.byref(lp),
+                                                          ptr(gL), ctypes.byref(g0), ctypes.byref(gs)))
+        return ll.value, lp.value, gL, g0.value, gs.value
+
+    def hmc(self, target, step, nsteps, p0, log_u, allreduce=None, acc_ptr=None):
+        """One hips-style HMC transition on the device.  target 0 = L (p0: N x dim), 1 = mu_0 (p0: scalar).
+        ``allreduce`` (row-sharded form) is called between every pair pass and the update that consumes it and
+        must sum the accumulator at ``acc_ptr`` over the ranks.  Returns (accepted, log_ratio)."""
+        p = np.ascontiguousarray(np.atleast_1d(p0), dtype=np.float64)
+        acc, ratio = ctypes.c_int(0), ctypes.c_double(0.0)
+        lib, c, h = self.ctx.lib, self.ctx.h, self.h
+        if allreduce is None:
+            self.ctx.check(lib.gk_latent_hmc(c, h, int(target), float(step), int(nsteps), ptr(p), float(log_u),
+                                             ctypes.byref(acc), ctypes.byref(ratio)))
+        else:
+            self.ctx.check(lib.gk_latent_hmc_begin(c, h, int(target), float(step), int(nsteps), ptr(p)))
+            for _ in range(int(nsteps) + 1):
+                self.ctx.check(lib.gk_latent_hmc_pass(c, h, acc_ptr))
+                allreduce()
+                self.ctx.check(lib.gk_latent_hmc_advance(c, h, acc_ptr))
+            self.ctx.check(lib.gk_latent_hmc_end(c, h, float(log_u), ctypes.byref(acc), ctypes.byref(ratio)))
+        return bool(acc.value), ratio.value
+
+    def close(self):
+        self._finalizer()
+
+
+def _destroy_latent(ctx, h):
+    if ctx.h:
+        ctx.lib.gk_latent_destroy(ctx.h, h)

@@ -93,3 +93,39 @@ class NetworkDistribution(object):
 class GaussianWeightedNetworkDistribution(object):
     """Mixin: models exposing P (N x N), Mu (N x N x B), Sigma (N x N x B x B)."""
     pass
+
+
+# ------------------------------------------------------------------------------------------------------
+# new-API callers pass bare arrays -- ``adjacency.resample(A)``, ``weights.resample((A, W))``
+# (networks.py:69-71).  The device copy is found again through a small identity cache: one network object
+# per live host array A (upgraded in place when a W shows up for the same A).
+# ------------------------------------------------------------------------------------------------------
+_NETWORKS = {}
+
+
+def network_for(A, W=None):
+    """The (cached) network object that owns the device copy of the host arrays A (N x N) and W (N x N x B).
+    Data is treated as immutable, as the reference treats it (SURVEY.md 8b 'Ownership'); after an in-place edit
+    of A or W call ``network_for(A, W).invalidate()``."""
+    import weakref
+    if isinstance(A, WeightedDirectedNetwork):
+        return A
+    A = np.asarray(A)
+    key = id(A)
+    ent = _NETWORKS.get(key)
+    if ent is not None:
+        ref, net = ent
+        if ref() is A:
+            if W is not None and (net.W is None or net._W_id != id(W)):
+                net.invalidate()
+                net.__init__(A, W)
+                net._W_id = id(W)
+            return net
+        del _NETWORKS[key]
+    net = FixedGaussianNetwork(A, W)
+    net._W_id = id(W) if W is not None else None
+    try:
+        _NETWORKS[key] = (weakref.ref(A, lambda _r, k=key: _NETWORKS.pop(k, None)), net)
+    except TypeError:                      # not weak-referenceable: no caching
+        pass
+    return net

@@ -132,6 +132,40 @@ int gk_eig_resample_F(gk_ctx *ctx, gk_eig *eig, double sigma_F, const double *no
 /* K9: replaces eigenmodel.py:110-129 with P of :803-811 (link 0, logistic) or :227-236 (link 1, probit) */
 int gk_eig_log_likelihood(gk_ctx *ctx, gk_eig *eig, int link, double *ll);
 
+/* ---- latent-distance adjacency model, K8 -----------------------------------------------------------
+ * State of one LatentDistanceAdjacencyDistribution (adjacency.py:189-207) over one network (A only):
+ * L (N x dim, 1 <= dim <= 3), mu_0, mu_self, sigma.  Arithmetic in fp32 (network dtype GK_F32) with fp64
+ * accumulation, or fp64 (GK_F64, parity mode). */
+typedef struct gk_latent gk_latent;
+int gk_latent_create(gk_ctx *ctx, gk_net *net, int dim, gk_latent **out);
+int gk_latent_destroy(gk_ctx *ctx, gk_latent *lat);
+/* L may be NULL (keep the device copy) */
+int gk_latent_set_params(gk_ctx *ctx, gk_latent *lat, const double *L, double mu0, double mu_self, double sigma);
+int gk_latent_get_params(gk_ctx *ctx, gk_latent *lat, double *L, double *mu0);
+/* doubles in one accumulator of a pair pass (N*dim pair gradient sums + 4 scalars): the buffer the
+ * ranks all-reduce (SUM) in the row-sharded form */
+size_t gk_latent_acc_len(gk_latent *lat);
+/* Replaces adjacency.py:244-275 (_hmc_log_probability) and its autograd gradient (:375-379, 398, 415) at the
+ * current parameters: ll = the Bernoulli log likelihood (abstractions.py:111-115 with P of :216-219),
+ * lp = ll + log priors as :266-275 write them, gradL (N x dim) = d lp / d L, gmu0, gmuself.  All outputs
+ * optional.  Unsharded networks; the sharded form is eval_pass -> all-reduce(acc_dev) -> eval_finish
+ * (acc_dev = device buffer of gk_latent_acc_len doubles, NULL = the state's own buffer). */
+int gk_latent_lp_grad(gk_ctx *ctx, gk_latent *lat, double *ll, double *lp, double *gradL, double *gmu0, double *gmuself);
+int gk_latent_eval_pass(gk_ctx *ctx, gk_latent *lat, double *acc_dev);
+int gk_latent_eval_finish(gk_ctx *ctx, gk_latent *lat, const double *acc_dev, double *ll, double *lp, double *gradL,
+                          double *gmu0, double *gmuself);
+/* Replaces hips.inference.hmc.hmc as called by _resample_L (adjacency.py:370-385, target 0, p0 = N x dim
+ * standard normals) and _resample_mu_0 (:389-404, target 1, p0 = one standard normal): leapfrog with nsteps
+ * steps = nsteps + 1 pair passes; accepted iff log_u < U_curr - U_prop + K_curr - K_prop; on accept the
+ * device state moves to the proposal.  log_ratio (optional) returns that right-hand side. */
+int gk_latent_hmc(gk_ctx *ctx, gk_latent *lat, int target, double step, int nsteps, const double *p0, double log_u,
+                  int *accepted, double *log_ratio);
+/* the same trajectory in pieces, for row shards: begin; (nsteps + 1) x { pass -> all-reduce(acc_dev) -> advance }; end */
+int gk_latent_hmc_begin(gk_ctx *ctx, gk_latent *lat, int target, double step, int nsteps, const double *p0);
+int gk_latent_hmc_pass(gk_ctx *ctx, gk_latent *lat, double *acc_dev);
+int gk_latent_hmc_advance(gk_ctx *ctx, gk_latent *lat, const double *acc_dev);
+int gk_latent_hmc_end(gk_ctx *ctx, gk_latent *lat, double log_u, int *accepted, double *log_ratio);
+
 #ifdef __cplusplus
 }
 #endif
