@@ -27,9 +27,10 @@ struct gk_latent {
 
 static inline size_t lat_acc_len(const gk_latent *l) { return (size_t)l->N * l->dim + GK_LAT_ACC_EXTRA; }
 
+// compute-type shadow of a coordinate array, pre-scaled for the pair kernel (gk_lat_math<T>::scale())
 template <typename T>
-__global__ void k_lat_shadow(const double *__restrict__ src, T *__restrict__ dst, size_t n) {
-    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = (T)src[i];
+__global__ void k_lat_shadow(const double *__restrict__ src, T *__restrict__ dst, size_t n, double scale) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x) dst[i] = (T)(src[i] * scale);
 }
 
 __device__ __forceinline__ double lat_block_sum(double v, double *red) {
@@ -83,7 +84,7 @@ __global__ void __launch_bounds__(1024) k_lat_eval_finish(gk_lat_fin f, const do
 // 2: last (half kick; record U_prop, K_prop).  One-step trajectories (nsteps == 1) use kinds 0 then 2.
 template <typename T>
 __global__ void __launch_bounds__(1024) k_lat_advance_L(gk_lat_fin f, double *__restrict__ q, double *__restrict__ p,
-                                                        T *__restrict__ qT, double eps, int kind) {
+                                                        T *__restrict__ qT, double eps, int kind, double scale) {
     __shared__ double red[32];
     const size_t n = (size_t)f.N * f.dim;
     const double kick = kind == 1 ? eps : 0.5 * eps;
@@ -95,7 +96,7 @@ __global__ void __launch_bounds__(1024) k_lat_advance_L(gk_lat_fin f, double *__
         const double dlp = -2.0 * f.acc[i] - qi / f.sigma;      // d log p / d q ; U = -log p
         pi += kick * dlp;
         if (kind == 2) ssp += pi * pi;
-        if (kind != 2) { qi += eps * pi; q[i] = qi; qT[i] = (T)qi; }
+        if (kind != 2) { qi += eps * pi; q[i] = qi; qT[i] = (T)(qi * scale); }
         p[i] = pi;
     }
     if (kind == 1) return;
@@ -151,12 +152,13 @@ extern "C" int gk_latent_create(gk_ctx *ctx, gk_net *net, int dim, gk_latent **o
     gk_latent *l = new gk_latent();
     l->net = net; l->N = net->N; l->dim = dim; l->f64 = net->dtype == GK_F64;
     const size_t n = (size_t)net->N * dim, ts = l->f64 ? 8 : 4;
+    const size_t npad = (size_t)((net->N + GK_LAT_TILE - 1) / GK_LAT_TILE) * GK_LAT_TILE * dim;   // shadows are zero padded to whole tiles
     cudaError_t e = cudaMalloc(&l->L, n * 8);
     if (e == cudaSuccess) e = cudaMalloc(&l->q, n * 8);
     if (e == cudaSuccess) e = cudaMalloc(&l->p, n * 8);
     if (e == cudaSuccess) e = cudaMalloc(&l->grad, n * 8);
-    if (e == cudaSuccess) e = cudaMalloc(&l->LT, n * ts);
-    if (e == cudaSuccess) e = cudaMalloc(&l->qT, n * ts);
+    if (e == cudaSuccess) e = cudaMalloc(&l->LT, npad * ts);
+    if (e == cudaSuccess) e = cudaMalloc(&l->qT, npad * ts);
     if (e == cudaSuccess) e = cudaMalloc(&l->sc, SC_LEN * 8);
     if (e == cudaSuccess) e = cudaMalloc(&l->acc, lat_acc_len(l) * 8);
     if (e != cudaSuccess) {
@@ -165,7 +167,8 @@ extern "C" int gk_latent_create(gk_ctx *ctx, gk_net *net, int dim, gk_latent **o
         return gk_fail(ctx, GK_ENOMEM, "latent state alloc: %s", cudaGetErrorString(e));
     }
     GK_CUDA(ctx, cudaMemsetAsync(l->L, 0, n * 8, ctx->stream));
-    GK_CUDA(ctx, cudaMemsetAsync(l->LT, 0, n * ts, ctx->stream));
+    GK_CUDA(ctx, cudaMemsetAsync(l->LT, 0, npad * ts, ctx->stream));
+    GK_CUDA(ctx, cudaMemsetAsync(l->qT, 0, npad * ts, ctx->stream));
     GK_CUDA(ctx, cudaMemsetAsync(l->sc, 0, SC_LEN * 8, ctx->stream));
     std::vector<uint8_t> d(net->N);
     GK_CUDA(ctx, cudaMemcpyAsync(d.data(), net->diagA, net->N, cudaMemcpyDeviceToHost, ctx->stream));
@@ -188,8 +191,8 @@ extern "C" size_t gk_latent_acc_len(gk_latent *l) { return l ? lat_acc_len(l) : 
 static int lat_shadow(gk_ctx *ctx, gk_latent *l, const double *src, void *dst) {
     const size_t n = (size_t)l->N * l->dim;
     const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)ctx->num_sms * 4);
-    if (l->f64) k_lat_shadow<double><<<grid, 256, 0, ctx->stream>>>(src, (double *)dst, n);
-    else k_lat_shadow<float><<<grid, 256, 0, ctx->stream>>>(src, (float *)dst, n);
+    if (l->f64) k_lat_shadow<double><<<grid, 256, 0, ctx->stream>>>(src, (double *)dst, n, 1.0);
+    else k_lat_shadow<float><<<grid, 256, 0, ctx->stream>>>(src, (float *)dst, n, GK_LAT_SCALE_F32);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
 }
@@ -232,7 +235,7 @@ static int lat_pass(gk_ctx *ctx, gk_latent *l, const void *Lq, const double *mu0
     GK_CUDA(ctx, cudaMemsetAsync(acc_dev, 0, lat_acc_len(l) * 8, ctx->stream));
     gk_lat_pass_params P;
     P.Asym = net->Asym; P.ld = net->ld; P.row0 = net->row0; P.nrows = net->nrows; P.N = net->N;
-    P.Lq = Lq; P.mu0 = mu0_dev; P.acc = acc_dev;
+    P.Lq = Lq; P.mu0 = mu0_dev; P.acc = acc_dev; P.magic = 0x4B000000u;
     P.NT = (net->N + GK_LAT_TILE - 1) / GK_LAT_TILE;
     P.nkc = (P.NT / 2 + 1 + GK_LAT_KCH - 1) / GK_LAT_KCH;
     P.nunits = ((net->nrows + GK_LAT_TILE - 1) / GK_LAT_TILE) * P.nkc;
@@ -319,8 +322,8 @@ extern "C" int gk_latent_hmc_advance(gk_ctx *ctx, gk_latent *l, const double *ac
     const int kind = l->stage == 0 ? 0 : (l->stage == l->nsteps ? 2 : 1);
     gk_lat_fin f = lat_fin(l, acc_dev ? acc_dev : l->acc);
     if (l->target == 0) {
-        if (l->f64) k_lat_advance_L<double><<<1, 1024, 0, ctx->stream>>>(f, l->q, l->p, (double *)l->qT, l->step, kind);
-        else k_lat_advance_L<float><<<1, 1024, 0, ctx->stream>>>(f, l->q, l->p, (float *)l->qT, l->step, kind);
+        if (l->f64) k_lat_advance_L<double><<<1, 1024, 0, ctx->stream>>>(f, l->q, l->p, (double *)l->qT, l->step, kind, 1.0);
+        else k_lat_advance_L<float><<<1, 1024, 0, ctx->stream>>>(f, l->q, l->p, (float *)l->qT, l->step, kind, GK_LAT_SCALE_F32);
     } else {
         k_lat_advance_mu0<<<1, 32, 0, ctx->stream>>>(f, l->step, kind);
     }

@@ -16,16 +16,19 @@
 // Tiling: the N x N pair space is cut into 128 x 128 tiles; block-row I owns the tiles (I, (I + k) mod NT) for
 // k = 0 .. NT/2 (k = 0: strict upper triangle of the diagonal tile; k = NT/2 with NT even: only I < NT/2), a
 // "circular half" that gives every block-row the same amount of work, so a row shard of Asym is also a balanced
-// shard of the pairs.  A CTA takes work units (block-row, GK_LAT_KCH consecutive k) round-robin; a thread owns an
-// 8 x 8 register block of the tile: G_i lives in registers for the whole unit, G_j is reduced through shared
-// memory once per tile and leaves as 128*DIM fp64 atomics.
+// shard of the pairs.  A CTA takes work units (block-row, GK_LAT_KCH consecutive k) round-robin and walks a unit in
+// half tiles of 128 x 64; a thread owns an 8 x 4 register block: G_i lives in registers for the whole unit, G_j is
+// reduced through (double-buffered) shared memory once per half tile and leaves as 64*DIM fp64 atomics.  fp32 mode
+// works in coordinates scaled by sqrt(log2 e), so the logistic is ex2 + rcp (2 SFU ops per pair) with no multiply.
 #pragma once
 #include "gk_internal.cuh"
 
 #define GK_LAT_TILE 128
 #define GK_LAT_THREADS 256
 #define GK_LAT_KCH 4
+#define GK_LAT_HALF 64            // columns per inner step
 #define GK_LAT_MAXDIM 3
+#define GK_LAT_SCALE_F32 1.2011224087864498   // sqrt(log2 e): fp32 shadows of L hold L * this
 
 // accumulator layout of one pass: acc[0 .. N*DIM) = G, then the scalars
 #define GK_LAT_ACC_SW 0
@@ -34,65 +37,93 @@
 
 template <typename T> struct gk_lat_math;
 template <> struct gk_lat_math<float> {
-    // gradient passes: MUFU ex2 + rcp (2 SFU ops per pair); value passes: full-precision expf / log1pf
-    static __device__ __forceinline__ float sigmoid_from_negx(float negx) { return __fdividef(1.0f, 1.0f + __expf(negx)); }
-    static __device__ __forceinline__ void sig_softplus(float x, float &s, float &sp) {
-        const float e = expf(-fabsf(x)), r = 1.0f / (1.0f + e);
-        s = x >= 0.0f ? r : e * r;
-        sp = fmaxf(x, 0.0f) + log1pf(e);
+    // coordinates are pre-multiplied by sqrt(log2 e): d2s = log2(e) ||l_i - l_j||^2, mu0s = log2(e) mu_0
+    static __device__ __forceinline__ float scale() { return 1.2011224087864498f; }        // sqrt(log2 e)
+    static __device__ __forceinline__ float scale2() { return 1.4426950408889634f; }       // log2 e
+    // gradient passes: s = 1 / (1 + 2^(d2s - mu0s)), MUFU ex2 + rcp
+    static __device__ __forceinline__ float sigmoid_scaled(float t) {
+        float e, r;
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(t));
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(1.0f + e));
+        return r;
     }
-    static __device__ __forceinline__ float byte_to(uint32_t word, int c) {
-        return __uint_as_float(__byte_perm(word, 0x4B000000u, 0x7650u + c)) - 8388608.0f;
+    // value passes: t = -x log2(e).  e = 2^-|t| and r = 1/(1+e) on the SFU; log1p(e) by lg2 where 1 + e keeps its
+    // bits and by its series where it does not (e < 2^-6), so small terms keep their RELATIVE accuracy and the
+    // 1.3e8-term sum has no systematic bias.  3 SFU ops per pair.
+    static __device__ __forceinline__ void sig_softplus_scaled(float t, float &x, float &s, float &sp) {
+        float e, r, lg;
+        const float den_arg = -fabsf(t);
+        asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(den_arg));
+        const float den = 1.0f + e;
+        asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(den));
+        asm("lg2.approx.ftz.f32 %0, %1;" : "=f"(lg) : "f"(den));
+        const float series = e * fmaf(e, fmaf(e, 0.33333333f, -0.5f), 1.0f);
+        const float l1p = e < 0.015625f ? series : lg * 0.6931471805599453f;
+        x = t * -0.6931471805599453f;
+        s = t <= 0.0f ? r : e * r;
+        sp = fmaxf(x, 0.0f) + l1p;
+    }
+    // byte c of word -> float through the 2^23 magic number (one PRMT + one FADD, no I2F)
+    static __device__ __forceinline__ float byte_to(uint32_t word, int c, uint32_t magic) {
+        return __uint_as_float(__byte_perm(word, magic, 0x7650u + c)) - 8388608.0f;
     }
 };
 template <> struct gk_lat_math<double> {
-    static __device__ __forceinline__ double sigmoid_from_negx(double negx) { return 1.0 / (1.0 + exp(negx)); }
-    static __device__ __forceinline__ void sig_softplus(double x, double &s, double &sp) {
+    static __device__ __forceinline__ double scale() { return 1.0; }
+    static __device__ __forceinline__ double scale2() { return 1.0; }
+    static __device__ __forceinline__ double sigmoid_scaled(double t) { return 1.0 / (1.0 + exp(t)); }
+    static __device__ __forceinline__ void sig_softplus_scaled(double t, double &x, double &s, double &sp) {
+        x = -t;
         const double e = exp(-fabs(x)), r = 1.0 / (1.0 + e);
         s = x >= 0.0 ? r : e * r;
         sp = fmax(x, 0.0) + log1p(e);
     }
-    static __device__ __forceinline__ double byte_to(uint32_t word, int c) { return (double)((word >> (8 * c)) & 0xffu); }
+    static __device__ __forceinline__ double byte_to(uint32_t word, int c, uint32_t) { return (double)((word >> (8 * c)) & 0xffu); }
 };
 
 struct gk_lat_pass_params {
     const uint8_t *Asym;   // nrows x ld (this rank's rows), zero diagonal
     int ld, row0, nrows, N;
-    const void *Lq;        // N x DIM of the compute type: the evaluation point
+    const void *Lq;        // NT*128 x DIM of the compute type, zero padded, PRE-SCALED by gk_lat_math<T>::scale(): the evaluation point
     const double *mu0;     // device scalar: the evaluation point's mu_0
     double *acc;           // N*DIM + GK_LAT_ACC_EXTRA doubles, zeroed by the caller
     int NT, nkc, nunits;   // tiles per side, k-chunks per block-row, work units of this rank
+    uint32_t magic;        // 0x4B000000, passed as data so that it stays in a register (PRMT selector immediate)
 };
 
-// one 8 x 8 register block of a tile.  SPECIAL tiles (diagonal tile, ragged last block-row/column) mask per pair.
-template <typename T, int DIM, bool VALUE, bool GRAD, bool SPECIAL>
-__device__ __forceinline__ void gk_lat_block(const uint2 (&a)[8], const T (&li)[8][DIM], const T (&lj)[8][DIM], T mu0,
-                                             T (&gi)[8][DIM], T (&gj)[8][DIM], T &tw, T &tv, int i0, int j0, int N,
-                                             bool diag) {
+// one 8 x 4 register block.  SPECIAL blocks (diagonal tile, ragged last block-row/column) mask per pair.
+//   WANT_W: the pass needs SW = sum w (mu_0 gradient);  VALUE: it needs SV;  GRAD: it needs G.
+template <typename T, int DIM, bool VALUE, bool GRAD, bool WANT_W, bool SPECIAL>
+__device__ __forceinline__ void gk_lat_block(const uint32_t (&a)[8], const T (&li)[8][DIM], const T (&lj)[4][DIM], T mu0s,
+                                             T (&gi)[8][DIM], T (&gj)[4][DIM], T &tw, T &tv, int i0, int j0, int N,
+                                             bool diag, uint32_t magic) {
     typedef gk_lat_math<T> M;
+    constexpr bool AF = VALUE || GRAD || SPECIAL;
 #pragma unroll
     for (int r = 0; r < 8; ++r) {
 #pragma unroll
-        for (int c = 0; c < 8; ++c) {
-            const T af = M::byte_to(c < 4 ? a[r].x : a[r].y, c & 3);
+        for (int c = 0; c < 4; ++c) {
             T dd[DIM], d2 = T(0);
 #pragma unroll
             for (int d = 0; d < DIM; ++d) { dd[d] = li[r][d] - lj[c][d]; d2 = fma(dd[d], dd[d], d2); }
-            T s, v = T(0);
+            T s, v = T(0), w;
             if (VALUE) {
-                T sp; const T x = mu0 - d2;
-                M::sig_softplus(x, s, sp);
+                T sp, x;
+                M::sig_softplus_scaled(d2 - mu0s, x, s, sp);
+                const T af = M::byte_to(a[r], c, magic);
                 v = fma(af, x, T(-2) * sp);
+                w = fma(T(-2), s, af);
             } else {
-                s = M::sigmoid_from_negx(d2 - mu0);
+                s = M::sigmoid_scaled(d2 - mu0s);
+                // without G only sum w is wanted: its edge part is added per word below (dp4a), not per pair
+                w = AF ? fma(T(-2), s, M::byte_to(a[r], c, magic)) : T(-2) * s;
             }
-            T w = fma(T(-2), s, af);
             if (SPECIAL) {
                 const int i = i0 + r, j = j0 + c;
                 const bool ok = i < N && j < N && (!diag || j > i);
                 w = ok ? w : T(0); v = ok ? v : T(0);
             }
-            tw += w;
+            if (WANT_W) tw += w;
             if (VALUE) tv += v;
             if (GRAD) {
 #pragma unroll
@@ -100,19 +131,36 @@ __device__ __forceinline__ void gk_lat_block(const uint2 (&a)[8], const T (&li)[
             }
         }
     }
+    if (!AF && WANT_W) {
+        int cnt = 0;
+#pragma unroll
+        for (int r = 0; r < 8; ++r) cnt = (int)__dp4a((unsigned)a[r], 0x01010101u, (unsigned)cnt);
+        tw += (T)cnt;
+    }
 }
 
+template <typename T> struct __align__(16) gk_vec16 { T v[16 / sizeof(T)]; };
+
 template <typename T, int DIM, bool VALUE, bool GRAD>
-__global__ void __launch_bounds__(GK_LAT_THREADS, 2) k_latent_pair(gk_lat_pass_params P) {
-    constexpr int TS = GK_LAT_TILE;
-    __shared__ T sLj[TS * DIM];
-    __shared__ T sRed[GRAD ? 8 * TS * DIM : 1];           // [warp][col * DIM + d]
+__global__ void __launch_bounds__(GK_LAT_THREADS, VALUE ? 2 : 3) k_latent_pair(gk_lat_pass_params P) {
+    typedef gk_lat_math<T> M;
+    typedef gk_vec16<T> V;
+    constexpr int TS = GK_LAT_TILE, HS = GK_LAT_HALF, VE = 16 / (int)sizeof(T);
+    constexpr int CW = 4 * DIM;                              // values a thread owns per half tile (4 columns)
+    constexpr int RW = HS * DIM;                             // values per row group of the reduction buffer
+    constexpr int NBUF = sizeof(T) == 4 ? 2 : 1;             // fp64 (parity mode): one buffer, one more barrier
+    constexpr bool WANT_W = VALUE || !GRAD;
+    __shared__ V sRedV[GRAD ? NBUF * 16 * RW / VE : 1];      // [buffer][row group ty][col * DIM + d]
     __shared__ double sScal[GK_LAT_THREADS / 32][2];
+    T *sRed = (T *)sRedV;
     const int tid = threadIdx.x, tx = tid & 15, ty = tid >> 4, lane = tid & 31, warp = tid >> 5;
     const T *__restrict__ Lq = (const T *)P.Lq;
-    const T mu0 = (T)__ldg(P.mu0);
+    const T mu0s = (T)__ldg(P.mu0) * M::scale2();
+    const T inv_scale = T(1) / M::scale();
     const int N = P.N, NT = P.NT;
+    const uint32_t magic = P.magic;
     double dw = 0.0, dv = 0.0;
+    int it = 0;                                              // reduced half tiles so far (buffer / reducer-warp rotation)
 
     for (int u = blockIdx.x; u < P.nunits; u += gridDim.x) {
         const int Iloc = u / P.nkc, kc = u - Iloc * P.nkc;
@@ -124,59 +172,77 @@ __global__ void __launch_bounds__(GK_LAT_THREADS, 2) k_latent_pair(gk_lat_pass_p
 
         const int i0 = I * TS + ty * 8;
         T li[8][DIM], gi[8][DIM];
-        const uint8_t *rowp[8];
+        uint32_t roff[8];                                      // byte offset of row r (clamped: ragged rows are masked)
 #pragma unroll
         for (int r = 0; r < 8; ++r) {
-            const int i = i0 + r;
-            const bool ok = i < P.row0 + P.nrows;
-            rowp[r] = ok ? P.Asym + (size_t)(i - P.row0) * P.ld + tx * 8 : nullptr;
+            const int il = min(i0 + r - P.row0, P.nrows - 1);
+            roff[r] = (uint32_t)il * (uint32_t)P.ld + tx * 4;  // nrows * ld < 2^32 (N <= 65536)
 #pragma unroll
-            for (int d = 0; d < DIM; ++d) { li[r][d] = ok ? Lq[(size_t)i * DIM + d] : T(0); gi[r][d] = T(0); }
+            for (int d = 0; d < DIM; ++d) { li[r][d] = Lq[(size_t)(i0 + r) * DIM + d]; gi[r][d] = T(0); }
         }
-        uint2 a_cur[8], a_nxt[8];
+        const int nst = 2 * (k1 - k0 + 1);                     // half tiles of this unit
+        auto colbase = [&](int st) { int J = I + k0 + (st >> 1); if (J >= NT) J -= NT; return J * TS + (st & 1) * HS; };
+        uint32_t a_cur[8], a_nxt[8];
         {
-            int J = I + k0; if (J >= NT) J -= NT;
+            const uint8_t *base = P.Asym + colbase(0);
 #pragma unroll
-            for (int r = 0; r < 8; ++r) a_cur[r] = rowp[r] ? __ldg((const uint2 *)(rowp[r] + (size_t)J * TS)) : make_uint2(0u, 0u);
+            for (int r = 0; r < 8; ++r) a_cur[r] = __ldg((const uint32_t *)(base + roff[r]));
         }
-        for (int k = k0; k <= k1; ++k) {
-            int J = I + k; if (J >= NT) J -= NT;
-            if (k < k1) {
-                int Jn = I + k + 1; if (Jn >= NT) Jn -= NT;
+        for (int st = 0; st < nst; ++st) {
+            const int jb = colbase(st), k = k0 + (st >> 1);
+            if (st + 1 < nst) {
+                const uint8_t *base = P.Asym + colbase(st + 1);
 #pragma unroll
-                for (int r = 0; r < 8; ++r) a_nxt[r] = rowp[r] ? __ldg((const uint2 *)(rowp[r] + (size_t)Jn * TS)) : make_uint2(0u, 0u);
+                for (int r = 0; r < 8; ++r) a_nxt[r] = __ldg((const uint32_t *)(base + roff[r]));
             }
-            __syncthreads();                                   // previous tile's sLj / sRed readers are done
-            for (int idx = tid; idx < TS * DIM; idx += GK_LAT_THREADS) {
-                const size_t g = (size_t)J * TS * DIM + idx;
-                sLj[idx] = g < (size_t)N * DIM ? Lq[g] : T(0);
-            }
-            __syncthreads();
-            T lj[8][DIM], gj[8][DIM];
+            if (jb < N) {                                      // (a ragged last tile may have an empty second half)
+                T lj[4][DIM], gj[4][DIM];
+                {
+                    const V *src = (const V *)(Lq + (size_t)(jb + tx * 4) * DIM);
+                    T tmp[CW];
 #pragma unroll
-            for (int c = 0; c < 8; ++c)
+                    for (int e = 0; e < CW / VE; ++e) { V v; *(uint4 *)&v = __ldg((const uint4 *)src + e);
 #pragma unroll
-                for (int d = 0; d < DIM; ++d) { lj[c][d] = sLj[(tx * 8 + c) * DIM + d]; gj[c][d] = T(0); }
-            T tw = T(0), tv = T(0);
-            const bool special = (k == 0) || ((N % TS) != 0 && (I == NT - 1 || J == NT - 1));
-            if (special) gk_lat_block<T, DIM, VALUE, GRAD, true>(a_cur, li, lj, mu0, gi, gj, tw, tv, i0, J * TS + tx * 8, N, k == 0);
-            else gk_lat_block<T, DIM, VALUE, GRAD, false>(a_cur, li, lj, mu0, gi, gj, tw, tv, i0, J * TS + tx * 8, N, false);
-            dw += (double)tw; dv += (double)tv;
-            if (GRAD) {
+                        for (int q = 0; q < VE; ++q) tmp[e * VE + q] = v.v[q]; }
 #pragma unroll
-                for (int c = 0; c < 8; ++c)
+                    for (int c = 0; c < 4; ++c)
 #pragma unroll
-                    for (int d = 0; d < DIM; ++d) {          // the warp's two row groups first, then one slot per warp
-                        const T v = gj[c][d] + __shfl_xor_sync(0xffffffffu, gj[c][d], 16);
-                        if (lane < 16) sRed[(warp * TS + tx * 8 + c) * DIM + d] = v;
+                        for (int d = 0; d < DIM; ++d) { lj[c][d] = tmp[c * DIM + d]; gj[c][d] = T(0); }
+                }
+                T tw = T(0), tv = T(0);
+                const int J = jb / TS;
+                const bool special = (k == 0) || ((N % TS) != 0 && (I == NT - 1 || J == NT - 1));
+                if (special) gk_lat_block<T, DIM, VALUE, GRAD, WANT_W, true>(a_cur, li, lj, mu0s, gi, gj, tw, tv, i0, jb + tx * 4, N, k == 0, magic);
+                else gk_lat_block<T, DIM, VALUE, GRAD, WANT_W, false>(a_cur, li, lj, mu0s, gi, gj, tw, tv, i0, jb + tx * 4, N, false, magic);
+                if (WANT_W) dw += (double)tw;
+                if (VALUE) dv += (double)tv;
+                if (GRAD) {
+                    T *red = sRed + (NBUF == 2 ? (it & 1) * (16 * RW) : 0);
+                    if (NBUF == 1) __syncthreads();            // previous half tile's reducer is done
+                    {
+                        V *dst = (V *)(red + ty * RW + tx * CW);
+#pragma unroll
+                        for (int e = 0; e < CW / VE; ++e) { V v;
+#pragma unroll
+                            for (int q = 0; q < VE; ++q) { const int f = e * VE + q; v.v[q] = gj[f / DIM][f % DIM]; }
+                            dst[e] = v; }
                     }
-                __syncthreads();
-                for (int idx = tid; idx < TS * DIM; idx += GK_LAT_THREADS) {
-                    T s = T(0);
+                    __syncthreads();                           // with two buffers: the only barrier per half tile
+                    if (warp == (it & 7)) {                    // one warp (rotating) folds the 16 row groups and flushes
+                        for (int g = lane; g < RW / VE; g += 32) {
+                            V s = *(const V *)(red + g * VE);
 #pragma unroll
-                    for (int t = 0; t < 8; ++t) s += sRed[t * TS * DIM + idx];
-                    const size_t g = (size_t)J * TS * DIM + idx;
-                    if (g < (size_t)N * DIM) atomicAdd(&P.acc[g], -(double)s);
+                            for (int t = 1; t < 16; ++t) { const V v = *(const V *)(red + t * RW + g * VE);
+#pragma unroll
+                                for (int q = 0; q < VE; ++q) s.v[q] += v.v[q]; }
+#pragma unroll
+                            for (int q = 0; q < VE; ++q) {
+                                const size_t gidx = (size_t)jb * DIM + g * VE + q;
+                                if (gidx < (size_t)N * DIM) atomicAdd(&P.acc[gidx], -(double)(s.v[q] * inv_scale));
+                            }
+                        }
+                    }
+                    ++it;
                 }
             }
 #pragma unroll
@@ -190,7 +256,7 @@ __global__ void __launch_bounds__(GK_LAT_THREADS, 2) k_latent_pair(gk_lat_pass_p
                     T v = gi[r][d];
                     v += __shfl_xor_sync(0xffffffffu, v, 1); v += __shfl_xor_sync(0xffffffffu, v, 2);
                     v += __shfl_xor_sync(0xffffffffu, v, 4); v += __shfl_xor_sync(0xffffffffu, v, 8);
-                    if (tx == 0 && i0 + r < N) atomicAdd(&P.acc[(size_t)(i0 + r) * DIM + d], (double)v);
+                    if (tx == 0 && i0 + r < N) atomicAdd(&P.acc[(size_t)(i0 + r) * DIM + d], (double)(v * inv_scale));
                 }
         }
     }
@@ -200,7 +266,7 @@ __global__ void __launch_bounds__(GK_LAT_THREADS, 2) k_latent_pair(gk_lat_pass_p
     if (tid == 0) {
         double a = 0.0, b = 0.0;
         for (int w = 0; w < GK_LAT_THREADS / 32; ++w) { a += sScal[w][0]; b += sScal[w][1]; }
-        atomicAdd(&P.acc[(size_t)N * DIM + GK_LAT_ACC_SW], a);
+        if (WANT_W) atomicAdd(&P.acc[(size_t)N * DIM + GK_LAT_ACC_SW], a);
         if (VALUE) atomicAdd(&P.acc[(size_t)N * DIM + GK_LAT_ACC_SV], b);
     }
 }
