@@ -35,6 +35,9 @@ def parse_args():
     ap.add_argument("--b", type=int, default=2, help="weight dimension")
     ap.add_argument("--d", type=int, default=8, help="eigenmodel latent dimension")
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
+    ap.add_argument("--shard", default="chains", choices=["chains", "rows"],
+                    help="N > 1: independent chains per GPU (weak scaling, default) or ONE chain with rows of A/W sharded "
+                         "over the GPUs and NCCL all-reduces of the statistics (strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--cpu-nodes", type=int, default=0, help="nodes of the CPU-baseline sample (0 = auto)")
     return ap.parse_args()
@@ -267,7 +270,12 @@ def run_ours(args):
     ctx = _lib.default_context()
     stream = torch.cuda.Stream(device=dev)
     ctx.set_stream(stream.cuda_stream)
-    wl = setup_workload(args, rank)
+    rows = args.shard == "rows" and world > 1
+    wl = setup_workload(args, 0 if rows else rank)
+    if rows:                                                   # one chain, rows of A / W sharded over the ranks
+        from graphistician_b200.sharding import Comm
+        torch.cuda.set_stream(stream)                          # libgk and NCCL share this stream
+        wl["network"].shard(Comm())
     N, model, network, d, algo_bytes = wl["N"], wl["model"], wl["network"], wl["data"], wl["algo_bytes"]
     step = wl.get("step") or (lambda: model.resample(network))
 
@@ -311,13 +319,13 @@ def run_ours(args):
     achieved = kbytes / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
     names = {0: "k_strip_stats", 1: "k_sbm_seq", 2: "k_eig_pg_tile", 3: "k_eig_slab", 4: "k_latent_pair", 5: "k_eig_seq"}
     out = {
-        "metric": METRIC, "value": world * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
+        "metric": METRIC, "value": (1 if rows else world) * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-        "config": dict(wl["config"], parallelism="independent chains x%d" % world,
+        "scaling": "strong" if rows else "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+        "config": dict(wl["config"], parallelism=("one chain, rows sharded x%d" if rows else "independent chains x%d") % world,
                        l2="inputs (%.2f GB/sweep) exceed the 126 MB L2" % (algo_bytes / 1e9)),
         "gpu_launches": int(launches), "clocks": clocks,
-        "e2e": {"value": world * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
+        "e2e": {"value": (1 if rows else world) * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
                 "d2h_bytes_per_step": int(d2h)},
         "roofline": {"bound": "hbm", "kernel": wl["dominant"][1], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": wl.get("traffic"),

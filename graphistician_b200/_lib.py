@@ -50,6 +50,13 @@ SIGNATURES = {
     "gk_eig_get_S": (c_int, [c_vp, c_vp, c_vp]),
     "gk_eig_resample_F": (c_int, [c_vp, c_vp, c_dbl, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "gk_eig_log_likelihood": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_dbl)]),
+    "gk_eig_sweep_begin": (c_int, [c_vp, c_vp, c_dbl, c_vp]),
+    "gk_eig_acc_len": (c_sz, [c_vp]),
+    "gk_eig_block_nodes": (c_int, [c_vp]),
+    "gk_eig_block_partials": (c_int, [c_vp, c_vp, c_int, c_int, c_vp]),
+    "gk_eig_block_sample": (c_int, [c_vp, c_vp, c_int, c_int, c_vp, c_vp]),
+    "gk_eig_set_block": (c_int, [c_vp, c_vp, c_int, c_int, c_vp]),
+    "gk_eig_sweep_end": (c_int, [c_vp, c_vp, c_vp, c_vp]),
     "gk_latent_create": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_vp)]),
     "gk_latent_destroy": (c_int, [c_vp, c_vp]),
     "gk_latent_set_params": (c_int, [c_vp, c_vp, c_vp, c_dbl, c_dbl, c_dbl]),

@@ -17,6 +17,7 @@ struct gk_eig {
     double mu0 = 0.0;
     bool have_S = false;
     bool chol_f64 = false;             // f32 storage: factorise the D x D conditionals in fp32 unless set
+    double inv_sigma_F = 1.0;          // of the open block-form sweep
     uint32_t sweep = 0;
 };
 
@@ -171,7 +172,7 @@ extern "C" int gk_eig_pg_draw(gk_ctx *ctx, gk_eig *e, uint64_t seed, double *sum
 // K4 + K5 (+ K6 statistics): the sequential feature sweep
 // ---------------------------------------------------------------------------------------------
 template <typename T, int D>
-static int launch_slab(gk_ctx *ctx, gk_eig *e, int n0, int nb) {
+static int launch_slab(gk_ctx *ctx, gk_eig *e, int n0, int nb, double *acc) {
     typedef typename gk_eacc<T>::type ACC;
     gk_net *net = e->net;
     // rows per chunk: a divisor of the block stride, small enough to fill the SMs
@@ -183,7 +184,7 @@ static int launch_slab(gk_ctx *ctx, gk_eig *e, int n0, int nb) {
     const double bytes = (double)net->nrows * nb * (sizeof(T) + 1.0);
     gk_time_begin(ctx, 3, bytes);
     k_eig_slab<T, D><<<nchunks, GK_EIG_SLAB_THREADS, smem, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, net->row0, net->nrows,
-                                                                         e->F, n0, nb, mc, e->acc);
+                                                                         e->F, n0, nb, mc, acc);
     gk_time_end(ctx, 3);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
@@ -191,7 +192,7 @@ static int launch_slab(gk_ctx *ctx, gk_eig *e, int n0, int nb) {
 
 template <typename T, typename CH, int D>
 static int launch_seq_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sblk, int ldS, const uint8_t *Ablk, int ldA,
-                         double inv_sigma_F) {
+                         double inv_sigma_F, double *acc) {
     static bool attr_set = false;
     const size_t smem = gk_eig_seq_smem<T, D>();
     if (!attr_set) {
@@ -201,7 +202,7 @@ static int launch_seq_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sbl
     gk_eig_seq_params P;
     P.n0 = n0; P.nb = nb; P.N = e->N; P.Sblk = Sblk; P.ldS = ldS; P.Ablk = Ablk; P.ldA = ldA;
     P.F = e->F; P.z = e->z; P.lmbda = e->lmbda; P.mu0 = e->mu0; P.inv_sigma_F = inv_sigma_F;
-    P.acc = e->acc; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h;
+    P.acc = acc; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h;
     gk_time_begin(ctx, 5, 0.0);
     k_eig_seq<T, CH, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
     gk_time_end(ctx, 5);
@@ -211,9 +212,24 @@ static int launch_seq_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sbl
 
 template <typename T, int D>
 static int launch_seq(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sblk, int ldS, const uint8_t *Ablk, int ldA,
-                      double inv_sigma_F) {
-    if (sizeof(T) == 4 && !e->chol_f64) return launch_seq_ch<T, float, D>(ctx, e, n0, nb, Sblk, ldS, Ablk, ldA, inv_sigma_F);
-    return launch_seq_ch<T, double, D>(ctx, e, n0, nb, Sblk, ldS, Ablk, ldA, inv_sigma_F);
+                      double inv_sigma_F, double *acc) {
+    if (sizeof(T) == 4 && !e->chol_f64) return launch_seq_ch<T, float, D>(ctx, e, n0, nb, Sblk, ldS, Ablk, ldA, inv_sigma_F, acc);
+    return launch_seq_ch<T, double, D>(ctx, e, n0, nb, Sblk, ldS, Ablk, ldA, inv_sigma_F, acc);
+}
+
+// block form (row shards): slab partials of one node block / the owner's sequential draw of it
+template <typename T, int D>
+static int block_partials_T(gk_ctx *ctx, gk_eig *e, int n0, int nb, double *acc) {
+    if (n0 % gk_eig_nb<T>::NB || nb > gk_eig_nb<T>::NB) return gk_fail(ctx, GK_EINVAL, "node blocks are %d-aligned", gk_eig_nb<T>::NB);
+    return launch_slab<T, D>(ctx, e, n0, nb, acc);
+}
+template <typename T, int D>
+static int block_sample_T(gk_ctx *ctx, gk_eig *e, int n0, int nb, double *acc) {
+    gk_net *net = e->net;
+    if (n0 < net->row0 || n0 + nb > net->row0 + net->nrows) return gk_fail(ctx, GK_EINVAL, "the sampling rank must own rows [%d,%d)", n0, n0 + nb);
+    const T *Sblk = (const T *)e->S + (size_t)(n0 - net->row0) * net->ld + n0;
+    const uint8_t *Ablk = net->Asym + (size_t)(n0 - net->row0) * net->ld + n0;
+    return launch_seq<T, D>(ctx, e, n0, nb, Sblk, net->ld, Ablk, net->ld, e->inv_sigma_F, acc);
 }
 
 template <typename T, int D>
@@ -222,11 +238,11 @@ static int sweep_F(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
     const int NB = gk_eig_nb<T>::NB;
     for (int n0 = 0; n0 < e->N; n0 += NB) {
         const int nb = std::min(NB, e->N - n0);
-        int rc = launch_slab<T, D>(ctx, e, n0, nb);
+        int rc = launch_slab<T, D>(ctx, e, n0, nb, e->acc);
         if (rc) return rc;
         const T *Sblk = (const T *)e->S + (size_t)(n0 - net->row0) * net->ld + n0;
         const uint8_t *Ablk = net->Asym + (size_t)(n0 - net->row0) * net->ld + n0;
-        if ((rc = launch_seq<T, D>(ctx, e, n0, nb, Sblk, net->ld, Ablk, net->ld, inv_sigma_F))) return rc;
+        if ((rc = launch_seq<T, D>(ctx, e, n0, nb, Sblk, net->ld, Ablk, net->ld, inv_sigma_F, e->acc))) return rc;
     }
     return GK_OK;
 }
@@ -266,6 +282,79 @@ extern "C" int gk_eig_resample_F(gk_ctx *ctx, gk_eig *e, double sigma_F, const d
     GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     if (stats) {
         // stats: Pq[D*D] (full symmetric) | hS[D] | hK[D]
+        for (int a = 0; a < D; ++a)
+            for (int b = 0; b < D; ++b) stats[a * D + b] = g[GK_EIG_GLOB_PQ + gk_qidx(D, std::min(a, b), std::max(a, b))];
+        for (int a = 0; a < D; ++a) { stats[D * D + a] = g[GK_EIG_GLOB_HS + a]; stats[D * D + D + a] = g[GK_EIG_GLOB_HK + a]; }
+    }
+    return GK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// block form of the same sweep, for row shards: begin; per node block { partials on every rank ->
+// all-reduce(acc_dev) -> sample on the owner -> broadcast(fblk_dev) -> set_block on the others }; end.
+// The pair statistics accumulate on whichever rank draws a block, so the caller sums `stats` over the ranks.
+// ---------------------------------------------------------------------------------------------
+__global__ void k_eig_set_block(double *__restrict__ F, const double *__restrict__ fblk, int n0, int nb, int D, double *__restrict__ glob) {
+    __shared__ double dsum[GK_EIG_MAXD], dnew[GK_EIG_MAXD];
+    if (threadIdx.x < GK_EIG_MAXD) { dsum[threadIdx.x] = 0.0; dnew[threadIdx.x] = 0.0; }
+    __syncthreads();
+    for (int t = threadIdx.x; t < nb * D; t += blockDim.x) {
+        const int d = t % D;
+        const double o = F[(size_t)n0 * D + t], v = fblk[t];
+        F[(size_t)n0 * D + t] = v;
+        atomicAdd(&dsum[d], v - o); atomicAdd(&dnew[d], v);
+    }
+    __syncthreads();
+    if (threadIdx.x < D) { glob[GK_EIG_GLOB_SUMF + threadIdx.x] += dsum[threadIdx.x]; glob[GK_EIG_GLOB_PREF + threadIdx.x] += dnew[threadIdx.x]; }
+}
+
+extern "C" int gk_eig_sweep_begin(gk_ctx *ctx, gk_eig *e, double sigma_F, const double *normals) {
+    if (!ctx || !e || !normals) return GK_EINVAL;
+    if (!e->have_S) return gk_fail(ctx, GK_EINVAL, "gk_eig_sweep_begin: call gk_eig_pg_draw or gk_eig_set_S first");
+    if (!(sigma_F > 0)) return gk_fail(ctx, GK_EINVAL, "sigma_F must be positive");
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    GK_CUDA(ctx, cudaMemcpyAsync(e->z, normals, (size_t)e->N * e->D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemsetAsync(e->glob, 0, GK_EIG_GLOB_LEN * 8, ctx->stream));
+    k_eig_colsum<<<1, 1024, 0, ctx->stream>>>(e->F, e->N, e->D, e->glob + GK_EIG_GLOB_SUMF);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));       // normals is a host temporary
+    e->inv_sigma_F = 1.0 / sigma_F;
+    return GK_OK;
+}
+extern "C" size_t gk_eig_acc_len(gk_eig *e) { return e ? (size_t)2 * GK_EIG_NBMAX * GK_EIG_PA_MAX : 0; }
+extern "C" int gk_eig_block_nodes(gk_eig *e) { return !e ? 0 : (e->dtype == GK_F32 ? gk_eig_nb<float>::NB : gk_eig_nb<double>::NB); }
+
+extern "C" int gk_eig_block_partials(gk_ctx *ctx, gk_eig *e, int n0, int nb, double *acc_dev) {
+    if (!ctx || !e || !acc_dev || n0 < 0 || nb <= 0 || n0 + nb > e->N) return GK_EINVAL;
+    GK_CUDA(ctx, cudaMemsetAsync(acc_dev, 0, gk_eig_acc_len(e) * 8, ctx->stream));
+    return e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, e->D, block_partials_T, ctx, e, n0, nb, acc_dev)
+                              : GK_EIG_SWITCH_D(double, e->D, block_partials_T, ctx, e, n0, nb, acc_dev);
+}
+extern "C" int gk_eig_block_sample(gk_ctx *ctx, gk_eig *e, int n0, int nb, double *acc_dev, double *fblk_dev) {
+    if (!ctx || !e || !acc_dev || n0 < 0 || nb <= 0 || n0 + nb > e->N) return GK_EINVAL;
+    double *kp = e->out_prec, *kh = e->out_h;
+    e->out_prec = nullptr; e->out_h = nullptr;
+    int rc = e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, e->D, block_sample_T, ctx, e, n0, nb, acc_dev)
+                                : GK_EIG_SWITCH_D(double, e->D, block_sample_T, ctx, e, n0, nb, acc_dev);
+    e->out_prec = kp; e->out_h = kh;
+    if (rc) return rc;
+    if (fblk_dev) GK_CUDA(ctx, cudaMemcpyAsync(fblk_dev, e->F + (size_t)n0 * e->D, (size_t)nb * e->D * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    return GK_OK;
+}
+extern "C" int gk_eig_set_block(gk_ctx *ctx, gk_eig *e, int n0, int nb, const double *fblk_dev) {
+    if (!ctx || !e || !fblk_dev || n0 < 0 || nb <= 0 || n0 + nb > e->N) return GK_EINVAL;
+    k_eig_set_block<<<1, 256, 0, ctx->stream>>>(e->F, fblk_dev, n0, nb, e->D, e->glob);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+extern "C" int gk_eig_sweep_end(gk_ctx *ctx, gk_eig *e, double *F_out, double *stats) {
+    if (!ctx || !e) return GK_EINVAL;
+    const int D = e->D;
+    if (F_out) GK_CUDA(ctx, cudaMemcpyAsync(F_out, e->F, (size_t)e->N * D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    double g[GK_EIG_GLOB_LEN];
+    GK_CUDA(ctx, cudaMemcpyAsync(g, e->glob, sizeof g, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (stats) {
         for (int a = 0; a < D; ++a)
             for (int b = 0; b < D; ++b) stats[a * D + b] = g[GK_EIG_GLOB_PQ + gk_qidx(D, std::min(a, b), std::max(a, b))];
         for (int a = 0; a < D; ++a) { stats[D * D + a] = g[GK_EIG_GLOB_HS + a]; stats[D * D + D + a] = g[GK_EIG_GLOB_HK + a]; }

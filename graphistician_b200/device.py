@@ -125,11 +125,17 @@ class DeviceEigenmodel:
     """Device state of one eigenmodel over one DeviceNetwork: S = Omega + Omega^T, F, lmbda, mu_0 (gk_eig)."""
 
     def __init__(self, net, D):
-        self.net, self.ctx, self.D, self.N = net, net.ctx, int(D), net.N
+        # a row-sharded network (sharding.ShardedDeviceNetwork) carries its communicator and its local shard
+        self.comm = getattr(net, "comm", None)
+        local = getattr(net, "local", net)
+        self.net, self.local, self.ctx, self.D, self.N = net, local, local.ctx, int(D), net.N
         h = ctypes.c_void_p()
-        self.ctx.check(self.ctx.lib.gk_eig_create(self.ctx.h, net.h, self.D, ctypes.byref(h)))
+        self.ctx.check(self.ctx.lib.gk_eig_create(self.ctx.h, local.h, self.D, ctypes.byref(h)))
         self.h = h
         self._finalizer = weakref.finalize(self, _destroy_eig, self.ctx, h)
+        if self.comm is not None:
+            self._acc = self.comm.buffer(int(self.ctx.lib.gk_eig_acc_len(self.h)))
+            self._fblk = self.comm.buffer(int(self.ctx.lib.gk_eig_block_nodes(self.h)) * self.D)
 
     def set_option(self, option, value):
         self.ctx.check(self.ctx.lib.gk_eig_set_option(self.ctx.h, self.h, int(option), int(value)))
@@ -144,15 +150,17 @@ class DeviceEigenmodel:
         """K3: S <- Omega + Omega^T with Omega ~ PG(1, Mu); returns sum(Omega) over all N^2 entries."""
         s = ctypes.c_double(0.0)
         self.ctx.check(self.ctx.lib.gk_eig_pg_draw(self.ctx.h, self.h, ctypes.c_uint64(int(seed)), ctypes.byref(s)))
+        if self.comm is not None:                   # every unordered pair is drawn by exactly one rank
+            return float(self.comm.allreduce_np(np.array([s.value]))[0])
         return s.value
 
     def set_S(self, S_rows):
         S = np.ascontiguousarray(S_rows, dtype=np.float64)
-        assert S.shape == (self.net.nrows, self.N)
+        assert S.shape == (self.local.nrows, self.N)
         self.ctx.check(self.ctx.lib.gk_eig_set_S(self.ctx.h, self.h, ptr(S)))
 
     def get_S(self):
-        S = np.empty((self.net.nrows, self.N))
+        S = np.empty((self.local.nrows, self.N))
         self.ctx.check(self.ctx.lib.gk_eig_get_S(self.ctx.h, self.h, ptr(S)))
         return S
 
@@ -161,6 +169,9 @@ class DeviceEigenmodel:
         z = np.ascontiguousarray(normals, dtype=np.float64)
         assert z.shape == (self.N, self.D)
         D = self.D
+        if self.comm is not None:
+            assert not want_conditionals, "per-node conditionals are available on single-rank networks only"
+            return self._resample_F_sharded(sigma_F, z)
         F = np.empty((self.N, D))
         prec = np.empty((self.N, D, D)) if want_conditionals else None
         h = np.empty((self.N, D)) if want_conditionals else None
@@ -170,9 +181,38 @@ class DeviceEigenmodel:
         stats = dict(Pq=st[:D * D].reshape(D, D).copy(), hS=st[D * D:D * D + D].copy(), hK=st[D * D + D:].copy())
         return F, stats, prec, h
 
+    def _resample_F_sharded(self, sigma_F, z):
+        """Block form (include/gk.h): slab partials on every rank -> all-reduce -> the owner of the block's rows draws
+        it -> feature broadcast; the pair statistics are summed over the ranks at the end."""
+        from .sharding import row_range
+        lib, c, h, comm, D = self.ctx.lib, self.ctx.h, self.h, self.comm, self.D
+        acc, fblk = ctypes.c_void_p(self._acc.data_ptr()), ctypes.c_void_p(self._fblk.data_ptr())
+        self.ctx.check(lib.gk_eig_sweep_begin(c, h, float(sigma_F), ptr(z)))
+        bn = int(lib.gk_eig_block_nodes(h))
+        for rk in range(comm.world):
+            s0, s1 = row_range(self.N, rk, comm.world)
+            for n0 in range(s0, s1, bn):
+                nb = min(bn, s1 - n0)
+                self.ctx.check(lib.gk_eig_block_partials(c, h, n0, nb, acc))
+                comm.allreduce_(self._acc)
+                if comm.rank == rk:
+                    self.ctx.check(lib.gk_eig_block_sample(c, h, n0, nb, acc, fblk))
+                if comm.dist is not None and comm.world > 1:
+                    comm.dist.broadcast(self._fblk, src=comm._global(rk), group=comm.group)
+                if comm.rank != rk:
+                    self.ctx.check(lib.gk_eig_set_block(c, h, n0, nb, fblk))
+        F = np.empty((self.N, D))
+        st = np.zeros(D * D + 2 * D)
+        self.ctx.check(lib.gk_eig_sweep_end(c, h, ptr(F), ptr(st)))
+        st = comm.allreduce_np(st)
+        stats = dict(Pq=st[:D * D].reshape(D, D).copy(), hS=st[D * D:D * D + D].copy(), hK=st[D * D + D:].copy())
+        return F, stats, None, None
+
     def log_likelihood(self, link=0):
         v = ctypes.c_double(0.0)
         self.ctx.check(self.ctx.lib.gk_eig_log_likelihood(self.ctx.h, self.h, int(link), ctypes.byref(v)))
+        if self.comm is not None:
+            return float(self.comm.allreduce_np(np.array([v.value]))[0])
         return v.value
 
     def close(self):
@@ -189,11 +229,15 @@ class DeviceLatent:
     device; every O(N^2) evaluation is one K8 pair pass."""
 
     def __init__(self, net, dim):
-        self.net, self.ctx, self.dim, self.N = net, net.ctx, int(dim), net.N
+        # a row-sharded network (sharding.ShardedDeviceNetwork) carries its communicator and its local shard
+        self.comm = getattr(net, "comm", None)
+        local = getattr(net, "local", net)
+        self.net, self.ctx, self.dim, self.N = net, local.ctx, int(dim), net.N
         h = ctypes.c_void_p()
-        self.ctx.check(self.ctx.lib.gk_latent_create(self.ctx.h, net.h, self.dim, ctypes.byref(h)))
+        self.ctx.check(self.ctx.lib.gk_latent_create(self.ctx.h, local.h, self.dim, ctypes.byref(h)))
         self.h = h
         self._finalizer = weakref.finalize(self, _destroy_latent, self.ctx, h)
+        self._acc = self.comm.buffer(self.acc_len()) if self.comm is not None else None
 
     def acc_len(self):
         return int(self.ctx.lib.gk_latent_acc_len(self.h))
@@ -212,6 +256,11 @@ class DeviceLatent:
 
     def lp_grad(self):
         """(ll, lp, dlp/dL, dlp/dmu_0, dlp/dmu_self) at the current parameters."""
+        if self.comm is not None:
+            acc = ctypes.c_void_p(self._acc.data_ptr())
+            self.eval_pass(acc)
+            self.comm.allreduce_(self._acc)
+            return self.eval_finish(acc)
         ll, lp, g0, gs = (ctypes.c_double(0.0) for _ in range(4))
         gL = np.empty((self.N, self.dim))
         self.ctx.check(self.ctx.lib.gk_latent_lp_grad(self.ctx.h, self.h, ctypes.byref(ll), ctypes.byref(lp), ptr(gL),
@@ -233,6 +282,8 @@ class DeviceLatent:
         ``allreduce`` (row-sharded form) is called between every pair pass and the update that consumes it and
         must sum the accumulator at ``acc_ptr`` over the ranks.  Returns (accepted, log_ratio)."""
         p = np.ascontiguousarray(np.atleast_1d(p0), dtype=np.float64)
+        if allreduce is None and self.comm is not None:
+            allreduce, acc_ptr = (lambda: self.comm.allreduce_(self._acc)), ctypes.c_void_p(self._acc.data_ptr())
         acc, ratio = ctypes.c_int(0), ctypes.c_double(0.0)
         lib, c, h = self.ctx.lib, self.ctx.h, self.h
         if allreduce is None:

@@ -151,7 +151,10 @@ class _GibbsLogisticEigenmodel(_LogisticEigenmodelBase):
             self._pg_calls += 1
         else:
             omega = np.asarray(omega, dtype=np.float64)
-            dev.set_S(omega + omega.T)
+            S = omega + omega.T
+            if dev.comm is not None:                     # row-sharded: this rank's rows only
+                S = S[dev.local.row0:dev.local.row0 + dev.local.nrows]
+            dev.set_S(S)
             sum_omega = omega.sum()
         # F (K4 + K5); the pair statistics for mu_0 and lmbda come back with it (K6)
         z = np.random.randn(self.N, self.D) if normals is None else normals

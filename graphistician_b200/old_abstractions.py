@@ -49,8 +49,20 @@ class FixedGaussianNetwork(WeightedDirectedNetwork):
         """Device-resident copy (uploaded on first use; see SURVEY.md 8b 'Ownership': data is never mutated)."""
         key = (dtype, id(ctx))
         if key not in self._dev:
-            self._dev[key] = DeviceNetwork(self.A, self.W, dtype=dtype, ctx=ctx)
+            comm = getattr(self, "_comm", None)
+            if comm is not None and comm.world > 1:
+                from .sharding import sharded_device_network
+                self._dev[key] = sharded_device_network(self.A, self.W, comm, dtype=dtype, ctx=ctx)
+            else:
+                self._dev[key] = DeviceNetwork(self.A, self.W, dtype=dtype, ctx=ctx)
         return self._dev[key]
+
+    def shard(self, comm):
+        """Row-shard the device copy over the ranks of ``comm`` (graphistician_b200.sharding.Comm): each rank then
+        uploads only its rows, and every device pass of ``model.resample(network)`` becomes collective."""
+        self.invalidate()
+        self._comm = comm
+        return self
 
     def invalidate(self):
         """Drop device copies (call after mutating A or W in place)."""

@@ -129,6 +129,17 @@ int gk_eig_get_S(gk_ctx *ctx, gk_eig *eig, double *S_rows);
  *   Pq[a,b] = sum S f1a f1b f2a f2b,  hS[a] = sum S f1a f2a,  hK[a] = sum (A12 + A21 - 1) f1a f2a. */
 int gk_eig_resample_F(gk_ctx *ctx, gk_eig *eig, double sigma_F, const double *normals, double *F_out,
                       double *out_prec, double *out_h, double *stats);
+/* Sharded form of the same sweep: begin; per node block of gk_eig_block_nodes() nodes
+ * { block_partials on every rank -> all-reduce(acc_dev, gk_eig_acc_len doubles) -> block_sample on the rank that owns
+ * the block's rows (writes the new features, nb x D doubles, to fblk_dev) -> broadcast(fblk_dev) -> set_block on the
+ * other ranks }; end.  The pair statistics accumulate on the rank that draws a block: sum `stats` over the ranks. */
+int gk_eig_sweep_begin(gk_ctx *ctx, gk_eig *eig, double sigma_F, const double *normals);
+size_t gk_eig_acc_len(gk_eig *eig);
+int gk_eig_block_nodes(gk_eig *eig);
+int gk_eig_block_partials(gk_ctx *ctx, gk_eig *eig, int n0, int nb, double *acc_dev);
+int gk_eig_block_sample(gk_ctx *ctx, gk_eig *eig, int n0, int nb, double *acc_dev, double *fblk_dev);
+int gk_eig_set_block(gk_ctx *ctx, gk_eig *eig, int n0, int nb, const double *fblk_dev);
+int gk_eig_sweep_end(gk_ctx *ctx, gk_eig *eig, double *F_out, double *stats);
 /* K9: replaces eigenmodel.py:110-129 with P of :803-811 (link 0, logistic) or :227-236 (link 1, probit) */
 int gk_eig_log_likelihood(gk_ctx *ctx, gk_eig *eig, int link, double *ll);
 
