@@ -18,6 +18,7 @@ struct gk_eig {
     bool have_S = false;
     bool chol_f64 = false;             // f32 storage: factorise the D x D conditionals in fp32 unless set
     double inv_sigma_F = 1.0;          // of the open block-form sweep
+    int probit = 0;                    // 1 after gk_eig_tn_draw / gk_eig_set_Zsym: the S buffer holds Z + Z^T (probit link)
     uint32_t sweep = 0;
 };
 
@@ -114,8 +115,15 @@ extern "C" int gk_eig_set_S(gk_ctx *ctx, gk_eig *e, const double *S_rows) {
     else k_eig_store_S<double><<<ctx->num_sms * 8, 256, 0, ctx->stream>>>(tmp, (double *)e->S, net->nrows, net->N, net->ld, net->row0);
     GK_CHECK_LAUNCH(ctx);
     GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-    e->have_S = true;
+    e->have_S = true; e->probit = 0;
     return GK_OK;
+}
+
+// probit injection path: rows of Z + Z^T (any diagonal: it is zeroed); switches the state to the probit link
+extern "C" int gk_eig_set_Zsym(gk_ctx *ctx, gk_eig *e, const double *Zsym_rows) {
+    int rc = gk_eig_set_S(ctx, e, Zsym_rows);
+    if (rc == GK_OK) e->probit = 1;
+    return rc;
 }
 
 template <typename T>
@@ -160,11 +168,116 @@ extern "C" int gk_eig_pg_draw(gk_ctx *ctx, gk_eig *e, uint64_t seed, double *sum
     e->sweep++;
     k_sum_partials<<<1, 1024, 0, ctx->stream>>>(e->part, (int)e->npart, e->scal);
     GK_CHECK_LAUNCH(ctx);
-    e->have_S = true;
+    e->have_S = true; e->probit = 0;
     if (sum_omega) {
         GK_CUDA(ctx, cudaMemcpyAsync(sum_omega, e->scal, 8, cudaMemcpyDeviceToHost, ctx->stream));
         GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
+    return GK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K7 (probit): Z[n,m] ~ N(Mu[n,m], 1) truncated to [0, inf) if A[n,m] else (-inf, 0]  (eigenmodel.py:268-287 with
+// internals/utils.py:53-76: inverse-CDF map  z = mu - sqrt(2) erfcinv(2 clip(Phi_lb + u (Phi_ub - Phi_lb), 1e-15, 1-1e-15)),
+// the 1e-15 clip included), fused with Mu of :75-83.  The uniform of the directed entry (src, dst) is a counter-based hash
+// of (seed, sweep, src, dst), so entry (n,m) and its mirror (m,n) -- possibly on another rank -- see the same two draws.
+// Stores Z + Z^T (zero diagonal) in the S buffer; part[tile] = sum of this tile's Z[n,m], n != m.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ double gk_hash_uniform(uint64_t seed, uint32_t sweep, uint32_t src, uint32_t dst) {
+    uint64_t x = seed + 0x9E3779B97F4A7C15ull * ((uint64_t)sweep + 1) + (((uint64_t)src << 32) | (uint64_t)dst);
+    x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+    x += 0x9E3779B97F4A7C15ull;
+    x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+    return ((double)(x >> 11) + 0.5) * (1.0 / 9007199254740992.0);
+}
+__device__ __forceinline__ double gk_truncnorm(double mu, bool edge, double u) {
+    const double c0 = 0.5 * erfc(mu * 0.70710678118654752440);          // Phi(0 - mu)
+    const double cl = edge ? c0 : 0.0, cu = edge ? 1.0 : c0;
+    double cdf = cl + u * (cu - cl);
+    cdf = fmin(fmax(cdf, 1e-15), 1.0 - 1e-15);
+    return mu - 1.41421356237309504880 * erfcinv(2.0 * cdf);
+}
+
+template <typename T>
+__global__ void __launch_bounds__(256) k_eig_tn_tile(T *__restrict__ S, const uint8_t *__restrict__ A, const uint8_t *__restrict__ At,
+                                                     int ld, int row0, int nrows, int N, int D, const double *__restrict__ F,
+                                                     const double *__restrict__ lmbda, double mu0, uint64_t seed, uint32_t sweep,
+                                                     double *__restrict__ part) {
+    constexpr int TS = GK_PG_TILE;
+    __shared__ double fi[TS][GK_EIG_MAXD], fj[TS][GK_EIG_MAXD];
+    __shared__ double red[8];
+    const int tid = threadIdx.x, I = row0 + blockIdx.y * TS, J = blockIdx.x * TS;
+    for (int t = tid; t < TS * GK_EIG_MAXD; t += 256) {
+        int r = t / GK_EIG_MAXD, d = t % GK_EIG_MAXD;
+        fi[r][d] = (d < D && I + r < N) ? F[(size_t)(I + r) * D + d] * lmbda[d] : 0.0;
+        fj[r][d] = (d < D && J + r < N) ? F[(size_t)(J + r) * D + d] : 0.0;
+    }
+    __syncthreads();
+    const int j = tid & (TS - 1);
+    double local = 0.0;
+    for (int i = tid / TS; i < TS; i += 256 / TS) {
+        const int n = I + i, m = J + j;
+        if (n >= N || m >= N || n - row0 >= nrows) continue;
+        const size_t off = (size_t)(n - row0) * ld + m;
+        if (n == m) { S[off] = T(0); continue; }
+        double mu = mu0;
+#pragma unroll
+        for (int d = 0; d < GK_EIG_MAXD; ++d) mu += fi[i][d] * fj[j][d];
+        const double z1 = gk_truncnorm(mu, A[off] != 0, gk_hash_uniform(seed, sweep, (uint32_t)n, (uint32_t)m));
+        const double z2 = gk_truncnorm(mu, At[off] != 0, gk_hash_uniform(seed, sweep, (uint32_t)m, (uint32_t)n));
+        S[off] = (T)(z1 + z2);
+        local += z1;
+    }
+    for (int o = 16; o; o >>= 1) local += __shfl_xor_sync(0xffffffffu, local, o);
+    if ((tid & 31) == 0) red[tid >> 5] = local;
+    __syncthreads();
+    if (tid == 0) { double s = 0.0; for (int w = 0; w < 8; ++w) s += red[w]; part[blockIdx.y * gridDim.x + blockIdx.x] = s; }
+}
+
+extern "C" int gk_eig_tn_draw(gk_ctx *ctx, gk_eig *e, uint64_t seed, double *sum_z) {
+    if (!ctx || !e) return GK_EINVAL;
+    gk_net *net = e->net;
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    dim3 grid((net->N + GK_PG_TILE - 1) / GK_PG_TILE, (net->nrows + GK_PG_TILE - 1) / GK_PG_TILE);
+    gk_time_begin(ctx, 2, (double)net->nrows * net->N * (gk_esize(e->dtype) + 2.0));
+    if (e->dtype == GK_F32)
+        k_eig_tn_tile<float><<<grid, 256, 0, ctx->stream>>>((float *)e->S, net->A, net->At, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
+    else
+        k_eig_tn_tile<double><<<grid, 256, 0, ctx->stream>>>((double *)e->S, net->A, net->At, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
+    gk_time_end(ctx, 2);
+    GK_CHECK_LAUNCH(ctx);
+    e->sweep++;
+    k_sum_partials<<<1, 1024, 0, ctx->stream>>>(e->part, (int)e->npart, e->scal);
+    GK_CHECK_LAUNCH(ctx);
+    e->have_S = true; e->probit = 1;
+    if (sum_z) {
+        GK_CUDA(ctx, cudaMemcpyAsync(sum_z, e->scal, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return GK_OK;
+}
+
+// the same inverse-CDF map elementwise, with the uniforms supplied (known-answer tests against the reference's own
+// sample_truncnorm, internals/utils.py:53-76; also the injection path of the parity tests)
+__global__ void k_truncnorm(const double *__restrict__ mu, const uint8_t *__restrict__ a, const double *__restrict__ u,
+                            double *__restrict__ out, size_t n) {
+    for (size_t i = blockIdx.x * (size_t)blockDim.x + threadIdx.x; i < n; i += (size_t)gridDim.x * blockDim.x)
+        out[i] = gk_truncnorm(mu[i], a[i] != 0, u[i]);
+}
+extern "C" int gk_truncnorm_draw(gk_ctx *ctx, const double *mu, const uint8_t *edge, const double *u, double *out, size_t n) {
+    if (!ctx || !mu || !edge || !u || !out) return GK_EINVAL;
+    if (n == 0) return GK_OK;
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    char *buf = (char *)gk_scratch(ctx, 0, n * 25 + 1024);
+    if (!buf) return GK_ENOMEM;
+    double *dmu = (double *)buf, *du = dmu + n, *dout = du + n; uint8_t *da = (uint8_t *)(dout + n);
+    GK_CUDA(ctx, cudaMemcpyAsync(dmu, mu, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(du, u, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(da, edge, n, cudaMemcpyHostToDevice, ctx->stream));
+    k_truncnorm<<<(int)std::min<size_t>((n + 255) / 256, (size_t)ctx->num_sms * 8), 256, 0, ctx->stream>>>(dmu, da, du, dout, n);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaMemcpyAsync(out, dout, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return GK_OK;
 }
 
@@ -184,7 +297,7 @@ static int launch_slab(gk_ctx *ctx, gk_eig *e, int n0, int nb, double *acc) {
     const double bytes = (double)net->nrows * nb * (sizeof(T) + 1.0);
     gk_time_begin(ctx, 3, bytes);
     k_eig_slab<T, D><<<nchunks, GK_EIG_SLAB_THREADS, smem, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, net->row0, net->nrows,
-                                                                         e->F, n0, nb, mc, acc);
+                                                                         e->F, n0, nb, mc, acc, e->probit);
     gk_time_end(ctx, 3);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
@@ -202,7 +315,7 @@ static int launch_seq_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sbl
     gk_eig_seq_params P;
     P.n0 = n0; P.nb = nb; P.N = e->N; P.Sblk = Sblk; P.ldS = ldS; P.Ablk = Ablk; P.ldA = ldA;
     P.F = e->F; P.z = e->z; P.lmbda = e->lmbda; P.mu0 = e->mu0; P.inv_sigma_F = inv_sigma_F;
-    P.acc = acc; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h;
+    P.acc = acc; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h; P.probit = e->probit;
     gk_time_begin(ctx, 5, 0.0);
     k_eig_seq<T, CH, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
     gk_time_end(ctx, 5);

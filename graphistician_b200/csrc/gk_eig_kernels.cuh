@@ -190,7 +190,7 @@ __global__ void k_eig_colsum(const double *__restrict__ F, int N, int D, double 
 template <typename T, int D, int HALF>
 __device__ __forceinline__ void gk_slab_body(const T *__restrict__ Sp, const uint8_t *__restrict__ Ap, size_t ld,
                                              int mrows, const typename gk_eacc<T>::type *__restrict__ phi,
-                                             double *__restrict__ accp, bool active) {
+                                             double *__restrict__ accp, bool active, bool probit, int diag_m) {
     typedef typename gk_eacc<T>::type ACC;
     constexpr int Pn = gk_edim<D>::P, PA = gk_edim<D>::PA, PH = gk_edim<D>::PH;
     constexpr int p0 = HALF * PH, np = HALF == 0 ? PH : PA - PH;
@@ -202,8 +202,14 @@ __device__ __forceinline__ void gk_slab_body(const T *__restrict__ Sp, const uin
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
             const bool ok = active && (m + u < mrows);
-            s[u] = ok ? (ACC)__ldg(Sp + (size_t)(m + u) * ld) : ACC(0);
-            a[u] = ok ? (ACC)__ldg(Ap + (size_t)(m + u) * ld) : ACC(0);
+            const ACC sv = ok ? (ACC)__ldg(Sp + (size_t)(m + u) * ld) : ACC(0);
+            if (probit) {                                   // S == 2 off the diagonal; the buffer holds Z + Z^T
+                s[u] = (ok && m + u != diag_m) ? ACC(2) : ACC(0);
+                a[u] = sv;
+            } else {
+                s[u] = sv;
+                a[u] = ok ? (ACC)__ldg(Ap + (size_t)(m + u) * ld) : ACC(0);
+            }
         }
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
@@ -221,7 +227,7 @@ __device__ __forceinline__ void gk_slab_body(const T *__restrict__ Sp, const uin
 template <typename T, int D>
 __global__ void __launch_bounds__(GK_EIG_SLAB_THREADS) k_eig_slab(const T *__restrict__ S, const uint8_t *__restrict__ Asym,
                                                                    int ld, int row0, int nrows, const double *__restrict__ F,
-                                                                   int n0, int nb, int mc, double *__restrict__ acc) {
+                                                                   int n0, int nb, int mc, double *__restrict__ acc, int probit) {
     typedef typename gk_eacc<T>::type ACC;
     constexpr int Q = gk_edim<D>::Q, Pn = gk_edim<D>::P, PA = gk_edim<D>::PA;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -251,8 +257,9 @@ __global__ void __launch_bounds__(GK_EIG_SLAB_THREADS) k_eig_slab(const T *__res
     const T *Sp = S + (size_t)r0 * ld + n0 + i;
     const uint8_t *Ap = Asym + (size_t)r0 * ld + n0 + i;
     double *accp = acc + ((size_t)part * GK_EIG_NBMAX + i) * PA;
-    if (half == 0) gk_slab_body<T, D, 0>(Sp, Ap, (size_t)ld, mrows, phi, accp, active);
-    else gk_slab_body<T, D, 1>(Sp, Ap, (size_t)ld, mrows, phi, accp, active);
+    const int diag_m = n0 + i - (row0 + r0);               // local row at which this column is the diagonal
+    if (half == 0) gk_slab_body<T, D, 0>(Sp, Ap, (size_t)ld, mrows, phi, accp, active, probit != 0, diag_m);
+    else gk_slab_body<T, D, 1>(Sp, Ap, (size_t)ld, mrows, phi, accp, active, probit != 0, diag_m);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -275,6 +282,7 @@ struct gk_eig_seq_params {
     double *acc;                         // [2][GK_EIG_NBMAX][PA]; consumed and zeroed
     double *glob;
     double *out_prec, *out_h;            // optional [N][D][D], [N][D]
+    int probit;                          // 1: S == 2 off the diagonal, Sblk holds Z + Z^T (the "A" operand), no kappa offset
 };
 #define GK_EIG_GLOB_SUMF 0
 #define GK_EIG_GLOB_PREF 8
@@ -367,11 +375,15 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq(gk_eig_seq_pa
         zb[t] = P.z[(size_t)n0 * D + t];
         fold[t] = P.F[(size_t)n0 * D + t];
     }
+    const bool probit = P.probit != 0;
     for (int t = tid; t < nb * nb; t += GK_EIG_SEQ_THREADS) {
         int i = t / nb, j = t - i * nb;
         Sb[i * (NB + 1) + j] = ((const T *)P.Sblk)[(size_t)i * P.ldS + j];
-        Ab[i * (NB + 4) + j] = P.Ablk[(size_t)i * P.ldA + j];
+        if (!probit) Ab[i * (NB + 4) + j] = P.Ablk[(size_t)i * P.ldA + j];
     }
+    // operands of the in-block moves: xS multiplies the quadratic/linear S columns, xA the "A" columns
+    auto xS = [&](int i, int j) -> double { return probit ? (i != j ? 2.0 : 0.0) : (double)Sb[i * (NB + 1) + j]; };
+    auto xA = [&](int i, int j) -> double { return probit ? (double)Sb[i * (NB + 1) + j] : (double)Ab[i * (NB + 4) + j]; };
     if (tid < D) lam[tid] = P.lmbda[tid];
     // solver lanes own columns p0 = lane and p1 = lane + 32; updater threads 32..32+PA-1 own statistic column tid-32
     const int p0 = lane, p1 = lane + 32;
@@ -403,7 +415,7 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq(gk_eig_seq_pa
                             if (P.out_prec) { P.out_prec[((size_t)n * D + pa) * D + pb] = v; P.out_prec[((size_t)n * D + pb) * D + pa] = v; }
                         } else if (p < Pn) {
                             const double gh = GL[(size_t)t * PA + Pn + pa] + GU[(size_t)t * PA + Pn + pa];
-                            const double v = lam[pa] * (gh - (sF - fold[t * D + pa]) - P.mu0 * g);
+                            const double v = lam[pa] * (gh - (probit ? 0.0 : (sF - fold[t * D + pa])) - P.mu0 * g);
                             hv[pa] = v;
                             phio[cur][p] = fold[t * D + pa];
                             if (P.out_h) P.out_h[(size_t)n * D + pa] = v;
@@ -429,10 +441,10 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq(gk_eig_seq_pa
                     for (int h = 0; h < 2; ++h) {
                         const int p = h ? p1 : p0;
                         if (p < PA) {
-                            double x = p < Pn ? (double)Sb[t * (NB + 1) + t + 1] : (double)Ab[t * (NB + 4) + t + 1];
+                            double x = p < Pn ? xS(t, t + 1) : xA(t, t + 1);
                             double gl = x * phin[cur][p], gu = x * phio[cur][p];
                             if (t > 0) {
-                                x = p < Pn ? (double)Sb[(t - 1) * (NB + 1) + t + 1] : (double)Ab[(t - 1) * (NB + 4) + t + 1];
+                                x = p < Pn ? xS(t - 1, t + 1) : xA(t - 1, t + 1);
                                 gl += x * phin[cur ^ 1][p]; gu += x * phio[cur ^ 1][p];
                             }
                             GL[(size_t)(t + 1) * PA + p] += gl;
@@ -447,12 +459,12 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq(gk_eig_seq_pa
             if (sp < PA) {                                 // pair statistics of (m < n_s, n_s) with the new features
                 const double gl = GL[(size_t)s * PA + sp];
                 if (sp < Pn) stat += phin[buf][sp] * gl;
-                else { stat += phin[buf][sp] * (gl - pref); pref += phin[buf][sp]; }
+                else { stat += phin[buf][sp] * (gl - (probit ? 0.0 : pref)); pref += phin[buf][sp]; }
             }
             const int rem = (nb - t - 2) * PA;             // rows t+2 .. nb-1 (row t+1 belongs to the solver)
             for (int e = tid - 32; e < rem; e += GK_EIG_SEQ_THREADS - 32) {
                 const int jr = e / PA, p = e - jr * PA, j = t + 2 + jr;
-                const double x = p < Pn ? (double)Sb[s * (NB + 1) + j] : (double)Ab[s * (NB + 4) + j];
+                const double x = p < Pn ? xS(s, j) : xA(s, j);
                 GL[(size_t)j * PA + p] += x * phin[buf][p];
                 GU[(size_t)j * PA + p] -= x * phio[buf][p];
             }

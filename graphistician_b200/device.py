@@ -159,6 +159,19 @@ class DeviceEigenmodel:
         assert S.shape == (self.local.nrows, self.N)
         self.ctx.check(self.ctx.lib.gk_eig_set_S(self.ctx.h, self.h, ptr(S)))
 
+    def tn_draw(self, seed):
+        """K7 (probit): S buffer <- Z + Z^T with Z ~ truncated N(Mu, 1); returns sum of Z over n != m."""
+        s = ctypes.c_double(0.0)
+        self.ctx.check(self.ctx.lib.gk_eig_tn_draw(self.ctx.h, self.h, ctypes.c_uint64(int(seed)), ctypes.byref(s)))
+        if self.comm is not None:
+            return float(self.comm.allreduce_np(np.array([s.value]))[0])
+        return s.value
+
+    def set_Zsym(self, Zsym_rows):
+        Z = np.ascontiguousarray(Zsym_rows, dtype=np.float64)
+        assert Z.shape == (self.local.nrows, self.N)
+        self.ctx.check(self.ctx.lib.gk_eig_set_Zsym(self.ctx.h, self.h, ptr(Z)))
+
     def get_S(self):
         S = np.empty((self.local.nrows, self.N))
         self.ctx.check(self.ctx.lib.gk_eig_get_S(self.ctx.h, self.h, ptr(S)))
@@ -305,3 +318,16 @@ class DeviceLatent:
 def _destroy_latent(ctx, h):
     if ctx.h:
         ctx.lib.gk_latent_destroy(ctx.h, h)
+
+
+def truncnorm_draw(mu, edge, u, ctx=None):
+    """Device form of the reference's ``sample_truncnorm`` (internals/utils.py:53-76) with the uniforms supplied:
+    N(mu, 1) truncated to [0, inf) where ``edge`` else (-inf, 0]."""
+    ctx = ctx or _lib.default_context()
+    mu = np.ascontiguousarray(mu, dtype=np.float64)
+    e8 = np.ascontiguousarray(np.asarray(edge) != 0, dtype=np.uint8)
+    uu = np.ascontiguousarray(u, dtype=np.float64)
+    assert mu.shape == e8.shape == uu.shape
+    out = np.empty_like(mu)
+    ctx.check(ctx.lib.gk_truncnorm_draw(ctx.h, ptr(mu), ptr(e8), ptr(uu), ptr(out), mu.size))
+    return out

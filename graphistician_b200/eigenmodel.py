@@ -201,3 +201,86 @@ class _GibbsLogisticEigenmodel(_LogisticEigenmodelBase):
 class LogisticEigenmodel(_GibbsLogisticEigenmodel):
     """eigenmodel.py:1313 (Gibbs part; the mean-field mixin is a later row of SURVEY.md 8a)."""
     pass
+
+
+# ------------------------------------------------------------------------------------------------------
+# probit link (eigenmodel.py:222-379, 772)
+# ------------------------------------------------------------------------------------------------------
+class _ProbitEigenmodelBase(_EigenmodelBase):
+    """eigenmodel.py:222-236."""
+    _link = 1
+
+    @property
+    def P(self):
+        from scipy.special import erf
+        return np.clip(0.5 * (1 + erf(self.Mu / np.sqrt(2.0))), 1e-16, 1 - 1e-16)
+
+
+class _GibbsProbitEigenmodel(_ProbitEigenmodelBase):
+    """eigenmodel.py:238-379.  Every O(N^2) step of ``resample(A)`` runs in libgk:
+
+      Z      <- gk_eig_tn_draw      K7    (replaces sample_truncnorm over N x N, :268-287)
+      F      <- gk_eig_resample_F   K4+K5 in probit mode (S == 2, h from Z - mu_0; replaces the N^2 loop of :289-321)
+      mu_0, lmbda: host draws from the pair statistics of the feature sweep (:323-379)."""
+
+    def __init__(self, N, D, **kwargs):
+        super(_GibbsProbitEigenmodel, self).__init__(N, D, **kwargs)
+        self._tn_seed = int(np.random.randint(0, 2 ** 31 - 1))
+        self._tn_calls = 0
+        self.resample()
+
+    def resample(self, data=[], uniforms=None, normals=None, want_conditionals=False):
+        """eigenmodel.py:244-266.  ``uniforms`` (N x N) / ``normals`` (N x D) inject the random draws (parity tests)."""
+        if not isinstance(data, list):
+            data = [data]
+        if len(data) == 0:
+            return self._resample_prior()
+        if len(data) > 1:
+            raise NotImplementedError("this build resamples given one network (the reference's demos and tests pass one)")
+        network = as_network(data[0])
+        dev = self._device_state(network)
+        dev.set_params(self.F, self.mu_0, self.lmbda)
+        if uniforms is None:
+            sum_z = dev.tn_draw((self._tn_seed << 20) + self._tn_calls)
+            self._tn_calls += 1
+        else:
+            from .device import truncnorm_draw
+            Z = truncnorm_draw(self.Mu, network.A, uniforms, dev.ctx)
+            np.fill_diagonal(Z, 0.0)
+            sum_z = Z.sum()
+            Zs = Z + Z.T
+            if dev.comm is not None:
+                Zs = Zs[dev.local.row0:dev.local.row0 + dev.local.nrows]
+            dev.set_Zsym(Zs)
+        z = np.random.randn(self.N, self.D) if normals is None else normals
+        self.F, st, prec, h = dev.resample_F(self.sigma_F, z, want_conditionals)
+        self._last_conditionals = dict(prec=prec, h=h, sum_z=sum_z, stats=st)
+        # mu_0 (:323-347): Zcent = Z - F diag(lmbda) F^T off the diagonal; sum_{n1 != n2} f1 Lambda f2 = lmbda . hS
+        post_prec = 1.0 / self.sigma_mu0 + self.N ** 2 - self.N
+        hm = self.mu_mu_0 / self.sigma_mu0 + sum_z - float(np.dot(self.lmbda, st["hS"]))
+        self._last_conditionals["mu0"] = (post_prec, hm)
+        self.mu_0 = np.random.normal(hm / post_prec, np.sqrt(1.0 / post_prec))
+        if not self.lmbda_given:
+            # lmbda (:349-379) with the NEW mu_0: zcent pair sums = hK - mu_0 hS
+            pp = 1.0 / self.sigma_lmbda * np.eye(self.D) + st["Pq"]
+            hl = self.mu_lmbda / self.sigma_lmbda + st["hK"] - self.mu_0 * st["hS"]
+            self._last_conditionals["lmbda"] = (pp, hl)
+            cov = np.linalg.inv(pp)
+            self.lmbda = np.random.multivariate_normal(cov.dot(hl), cov)
+
+    def _resample_prior(self):
+        """``resample()`` with no data (the constructor's call, :242): every data sum is empty."""
+        cov = self.sigma_F * np.eye(self.D)
+        for n in range(self.N):
+            self.F[n, :] = np.random.multivariate_normal(np.zeros(self.D), cov)
+        self.mu_0 = np.random.normal(self.mu_mu_0, np.sqrt(self.sigma_mu0))
+        if not self.lmbda_given:
+            self.lmbda = np.random.multivariate_normal(self.mu_lmbda, self.sigma_lmbda * np.eye(self.D))
+
+
+class ProbitEigenmodel(_GibbsProbitEigenmodel):
+    """eigenmodel.py:772 (Gibbs part)."""
+    pass
+
+
+Eigenmodel = ProbitEigenmodel        # the name test/test_probit_eigenmodel_geweke.py:8 imports

@@ -120,6 +120,16 @@ int gk_eig_pg_draw(gk_ctx *ctx, gk_eig *eig, uint64_t seed, double *sum_omega);
 /* injection path of the parity tests: S rows (nrows x N doubles) computed by the caller from a given Omega */
 int gk_eig_set_S(gk_ctx *ctx, gk_eig *eig, const double *S_rows);
 int gk_eig_get_S(gk_ctx *ctx, gk_eig *eig, double *S_rows);
+/* K7 (probit link): replaces eigenmodel.py:268-287 (_resample_Z) with internals/utils.py:53-76 (sample_truncnorm, its
+ * 1e-15 clip included) fused with Mu of :75-83.  Draws Z[n,m] for all n != m with a counter-based generator keyed by
+ * (seed, sweep, n, m), stores Z + Z^T (zero diagonal) in the S buffer and switches the state to the probit link: the
+ * feature sweep then runs eigenmodel.py:289-321 (S == 2, h from Z - mu_0) and `stats` feed :323-379.
+ * sum_z (optional) = sum of Z[n,m] over n != m (eigenmodel.py:336-342). */
+int gk_eig_tn_draw(gk_ctx *ctx, gk_eig *eig, uint64_t seed, double *sum_z);
+/* injection path of the probit parity tests: rows of Z + Z^T computed by the caller (nrows x N doubles) */
+int gk_eig_set_Zsym(gk_ctx *ctx, gk_eig *eig, const double *Zsym_rows);
+/* the truncated-normal map by itself, uniforms supplied: out[i] = sample_truncnorm(mu[i], lb/ub from edge[i]; u[i]) */
+int gk_truncnorm_draw(gk_ctx *ctx, const double *mu, const uint8_t *edge, const double *u, double *out, size_t n);
 /* K4+K5: replaces eigenmodel.py:876-908 (_resample_F), same serial semantics: node n is drawn from
  * N(prec_n^-1 h_n, prec_n^-1) given the NEW features of m < n and the OLD ones of m > n, with the fixed map
  * f = L^-T (L^-1 h + z), prec = L L^T, z = normals[n] (N x D standard normals supplied by the caller).
