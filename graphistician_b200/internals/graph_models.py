@@ -1,0 +1,282 @@
+"""Aldous-Hoover graph models for AIS marginal-likelihood estimation (mirrors ``graphistician.internals.graph_models``
+:12-371, 529-544 and the driver of examples/demo_ais.py:10-62).
+
+The O(N^2) work of every AIS step runs in libgk on the device copy of A:
+
+  ErdosRenyiNetwork.sample_theta / log_lkhd   <- one gk_block_stats pass (K = 1), cached: nnz(A) never changes
+  StochasticBlockModel.sample_theta           <- gk_block_stats (tempered Beta posterior, :337-371)
+  StochasticBlockModel.sample_f for n = 0..N-1 (the driver's loop, demo_ais.py:44-46)
+                                               <- gk_sbm_sweep with beta, diagonal counted in both directions
+                                                  (GK_SELF_TWICE, :275-293) and hips' log_sum_exp_sample (GK_SAMPLER_LSE)
+  log_lkhd                                     <- gk_block_stats (replaces the N^2 Python loop of :42-48)
+
+Independent AIS particles are partitioned over the ranks of a ``sharding.Comm``: no data-path
+collective, one gather of the log weights at the end.
+"""
+import copy
+
+import numpy as np
+from scipy.special import betaln, logsumexp
+
+from .. import _lib
+from ..old_abstractions import network_for
+
+
+def _device(A, dtype="f32"):
+    return network_for(A).device(dtype)
+
+
+def _total_edge_stats(A, z, R):
+    """(edges, ordered pairs) per block cell, diagonal INCLUDED (the loops of :42-48, :354-367 run over all i, j)."""
+    dev = _device(A)
+    z = np.asarray(z, dtype=np.int64)
+    n_edge = dev.block_stats(z, R)[0]
+    d = dev.diag_stats(z, R)
+    k = np.arange(R)
+    n_edge[k, k] += d["d_edge"]
+    sz = d["d_cnt"]
+    return n_edge, np.outer(sz, sz)
+
+
+class AldousHooverNetwork(object):
+    """internals/graph_models.py:12-102."""
+
+    def __init__(self, A=None):
+        pass
+
+    def pr_A_given_f(self, f1, f2, theta):
+        raise Exception("pr_A_given_f is not implemented!")
+
+    def logpr_f(self, f, theta):
+        raise Exception("logpr_f is not implemented!")
+
+    def logpr_theta(self, theta):
+        raise Exception("logpr_theta is not implemented!")
+
+    def log_lkhd(self, A, f, theta):
+        raise Exception("log_lkhd is not implemented!")
+
+    def logpr(self, A, f, theta, beta=1.0):
+        """internals/graph_models.py:50-64."""
+        lp = self.logpr_theta(theta)
+        lp += self.logpr_fs(f, theta)
+        lp += beta * self.log_lkhd(A, f, theta)
+        return lp
+
+    def logpr_fs(self, f, theta):
+        return sum(self.logpr_f(fi, theta) for fi in f)
+
+    def sample_f(self, theta, naf=(None, None, None), beta=1.0):
+        raise Exception("sample f is not implemented!")
+
+    def sample_fs(self, theta, A, f, beta=1.0, uniforms=None):
+        """The driver's inner loop ``for n in arange(N): f[n] = model.sample_f(theta, (n, A, f), beta)``
+        (examples/demo_ais.py:44-46) as one call."""
+        for n in range(len(f)):
+            f[n] = self.sample_f(theta, (n, A, f), beta=beta)
+        return f
+
+    def sample_theta(self, Af=(None, None), beta=1.0):
+        raise Exception("sample_theta is not implemented!")
+
+    def sample_A(self, f, theta):
+        """internals/graph_models.py:86-96 (row-major uniforms, one per entry)."""
+        N = len(f)
+        P = self.P_matrix(f, theta)
+        return (np.random.rand(N, N) < P).astype(np.float64)
+
+    def sample_Aij(self, fi, fj, theta):
+        return np.random.rand() < self.pr_A_given_f(fi, fj, theta)
+
+
+class ErdosRenyiNetwork(AldousHooverNetwork):
+    """internals/graph_models.py:105-182."""
+
+    def __init__(self, rho=None, x=None):
+        if rho is None:
+            if x is None:
+                raise Exception("Either rho or (a,b) must be specified")
+            (a, b) = x
+        else:
+            if x is not None:
+                raise Exception("Either rho or (a,b) must be specified")
+            a = b = None
+        self.rho, self.a, self.b = rho, a, b
+
+    def pr_A_given_f(self, fi, fj, theta):
+        return theta
+
+    def P_matrix(self, f, theta):
+        return theta * np.ones((len(f), len(f)))
+
+    def logpr_f(self, f, theta):
+        return 0.0
+
+    def logpr_fs(self, f, theta):
+        return 0.0
+
+    def logpr_theta(self, theta):
+        rho = theta
+        if self.rho is not None:
+            return 0.0 if self.rho == rho else -np.inf
+        return (self.a - 1.0) * np.log(rho) + (self.b - 1.0) * np.log(1.0 - rho) - betaln(self.a, self.b)
+
+    def _nnz(self, A):
+        """sum(A) over all N^2 entries from the device (cached on the network object: the data never changes)."""
+        net = network_for(A)
+        if not hasattr(net, "_nnz_total"):
+            n_edge, _ = _total_edge_stats(A, np.zeros(net.N, np.int64), 1)
+            net._nnz_total = float(n_edge[0, 0])
+        return net._nnz_total
+
+    def log_lkhd(self, A, f, theta):
+        N = A.shape[0]
+        nnz = self._nnz(A)
+        return nnz * np.log(theta) + (N ** 2 - nnz) * np.log(1 - theta)
+
+    def sample_f(self, theta, naf=(None, None, None), beta=1.0):
+        return None
+
+    def sample_fs(self, theta, A, f, beta=1.0, uniforms=None):
+        return f
+
+    def sample_theta(self, Af=(None, None), beta=1.0):
+        """internals/graph_models.py:168-182: rho ~ Beta(a + beta nnz, b + beta (N^2 - nnz))."""
+        A, f = Af
+        if self.rho is not None:
+            return self.rho
+        if A is None and f is None:
+            return np.random.beta(self.a, self.b)
+        N = A.shape[0]
+        nnz = self._nnz(A)
+        return np.random.beta(self.a + beta * nnz, self.b + beta * (N ** 2 - nnz))
+
+
+class StochasticBlockModel(AldousHooverNetwork):
+    """internals/graph_models.py:185-371.  theta = (B, pi): B[r, r'] edge probability between blocks, pi block weights;
+    features f = block labels.  (The reference stores B as float32, :353; values here are rounded through float32
+    the same way and used in fp64 arithmetic.)"""
+
+    def __init__(self, R, b0, b1, alpha0):
+        self.R, self.b0, self.b1, self.alpha0 = R, b0, b1, np.asarray(alpha0, dtype=np.float64)
+
+    def pr_A_given_f(self, fi, fj, theta):
+        (B, pi) = theta
+        return B[fi, fj]
+
+    def P_matrix(self, f, theta):
+        (B, pi) = theta
+        z = np.asarray(f, dtype=np.int64)
+        return B[np.ix_(z, z)]
+
+    def logpr_f(self, f, theta):
+        (B, pi) = theta
+        return float(np.sum(np.log(pi[np.array(f).astype(int)])))
+
+    def logpr_fs(self, f, theta):
+        return self.logpr_f(f, theta)
+
+    def logpr_theta(self, theta):
+        """internals/graph_models.py:222-240, including its quirk of adding the Dirichlet term R times (:237-238)."""
+        (B, pi) = theta
+        lp = np.sum((self.b1 - 1.0) * np.log(B) + (self.b0 - 1.0) * np.log(1.0 - B) - betaln(self.b1, self.b0))
+        lp += self.R * np.sum((self.alpha0 - 1.0) * np.log(pi))
+        return float(lp)
+
+    def log_lkhd(self, A, f, theta):
+        """internals/graph_models.py:42-48 (an N^2 Python loop) from the block counts of one K1 pass."""
+        (B, pi) = theta
+        n_edge, n_pair = _total_edge_stats(A, f, self.R)
+        B = np.asarray(B, dtype=np.float64)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            t1 = np.where(n_edge > 0, n_edge * np.log(B), 0.0)
+            t0 = np.where(n_pair - n_edge > 0, (n_pair - n_edge) * np.log(1 - B), 0.0)
+        return float(np.sum(t1 + t0))
+
+    def sample_f(self, theta, naf=(None, None, None), beta=1.0):
+        """One node (:242-259): the prior draw; conditional single-node draws go through ``sample_fs``."""
+        (B, pi) = theta
+        n, A, f = naf
+        if n is None and A is None and f is None:
+            return int(np.sum(np.random.rand() > np.cumsum(pi)))           # hips discrete_sample: inverse cdf
+        z = np.array(f, dtype=np.int64)
+        u = np.full(len(z), 0.5); u[n] = np.random.rand()
+        return int(self._sweep(theta, A, z, beta, u, only=n)[n])
+
+    def _sweep(self, theta, A, z, beta, u, only=None):
+        (B, pi) = theta
+        dev = _device(A)
+        if only is not None:
+            raise NotImplementedError("single-node conditional draws: use sample_fs (the driver's full loop)")
+        c, _, _ = dev.sbm_sweep(z, np.log(pi), np.asarray(B, dtype=np.float64), None, None, u,
+                                self_mode=_lib.SELF_TWICE, sampler=_lib.SAMPLER_LSE, beta=float(beta))
+        return c
+
+    def sample_fs(self, theta, A, f, beta=1.0, uniforms=None):
+        """``for n in arange(N): f[n] = model.sample_f(theta, (n, A, f), beta)`` (examples/demo_ais.py:44-46) as ONE
+        exact sequential device sweep: naive_sample_f (:261-297) for n = 0..N-1 in order, one uniform per node."""
+        z = np.array(f, dtype=np.int64)
+        u = np.random.rand(len(z)) if uniforms is None else uniforms
+        return self._sweep(theta, A, z, beta, u)
+
+    def sample_theta(self, Af=(None, None), beta=1.0):
+        """internals/graph_models.py:337-371: pi ~ Dir(alpha0 + counts) (NOT tempered), then
+        B[r1, r2] ~ Beta(b1 + beta edges, b0 + beta non-edges) over A[z == r1][:, z == r2], row-major."""
+        A, f = Af
+        if A is None and f is None:
+            B = np.random.beta(self.b1, self.b0, (self.R, self.R))
+            pi = np.random.dirichlet(self.alpha0)
+            return (B, pi)
+        z = np.array(f, dtype=np.int64)
+        pi = np.random.dirichlet(self.alpha0 + np.bincount(z, minlength=self.R))
+        n_edge, n_pair = _total_edge_stats(A, z, self.R)
+        B = np.random.beta(self.b1 + beta * n_edge, self.b0 + beta * (n_pair - n_edge))
+        return (B.astype(np.float32).astype(np.float64), pi)
+
+
+def invariant_sbm_order(f, R):
+    """The free function examples/demo_ais.py:87 calls (only the methods adjacency.py:575 /
+    stochastic_block_model.py:165 exist in the reference): nodes ordered by block, blocks ordered by size."""
+    z = np.asarray(f, dtype=np.int64)
+    corder = np.argsort(np.bincount(z, minlength=R))
+    newc = np.zeros(len(z))
+    for c in range(R):
+        newc[z == corder[c]] = c
+    return np.argsort(-newc)
+
+
+def sample_network(model, N):
+    """internals/graph_models.py:529-544."""
+    theta = model.sample_theta()
+    f = [model.sample_f(theta) for _ in range(N)]
+    A = model.sample_A(f, theta)
+    return (A, f, theta)
+
+
+def estimate_marginal_likelihood(A, f0, theta0, model, N_samples=1000, B=100, steps_per_B=11, comm=None,
+                                 return_weights=False):
+    """AIS estimate of log p(A | model) (examples/demo_ais.py:10-62): B temperatures, ``steps_per_B`` Gibbs steps
+    (sample_theta, then the sequential feature sweep) per temperature, log weight = sum_b (beta_b - beta_{b-1}) ll.
+
+    With ``comm`` (sharding.Comm) the particles m = rank, rank + world, ... run on this rank's GPU and the log
+    weights are gathered at the end (particles partitioned, no data-path collective); every rank must
+    then seed ``np.random`` differently."""
+    betas = np.linspace(0, 1, B)
+    rank, world = (comm.rank, comm.world) if comm is not None else (0, 1)
+    mine = list(range(rank, N_samples, world))
+    log_weights = np.zeros(N_samples)
+    for m in mine:
+        f, theta = copy.deepcopy((f0, theta0))
+        ratios = np.zeros(B - 1)
+        for b in range(1, B):
+            beta = betas[b]
+            for s in range(steps_per_B):
+                theta = model.sample_theta((A, f), beta=beta)
+                f = model.sample_fs(theta, A, f, beta=beta)
+            # logpr(beta_b) - logpr(beta_{b-1}) at the same (f, theta): the prior terms cancel exactly
+            ratios[b - 1] = (beta - betas[b - 1]) * model.log_lkhd(A, f, theta)
+        log_weights[m] = np.sum(ratios)
+    if comm is not None and world > 1:
+        log_weights = comm.allreduce_np(log_weights)
+    log_Z = -np.log(N_samples) + logsumexp(log_weights)
+    return (log_Z, log_weights) if return_weights else log_Z
