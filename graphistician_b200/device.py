@@ -96,6 +96,31 @@ class DeviceNetwork:
                                                  ctypes.byref(nch)))
         return c32.astype(np.int64), lp, int(nch.value)
 
+    # ---- K10 (mean field) ------------------------------------------------------------------------
+    def mf_soft_stats(self, mf_m):
+        """Off-diagonal soft block-pair statistics mf_m^T (A o x) mf_m (fp64)."""
+        m = np.ascontiguousarray(mf_m, dtype=np.float64)
+        K, B = m.shape[1], self.B
+        assert m.shape == (self.N, K)
+        n_soft = np.zeros((K, K)); sum_w = np.zeros((K, K, B)); sum_ww = np.zeros((K, K, B, B))
+        self.ctx.check(self.ctx.lib.gk_mf_sbm_soft_stats(self.ctx.h, self.h, ptr(m), K, ptr(n_soft),
+                                                         ptr(sum_w) if B else None, ptr(sum_ww) if B else None))
+        return n_soft, sum_w, sum_ww
+
+    def mf_update_c(self, mf_m, E_log_m, base_out, base_in, coef_out, coef_in, stepsize=1.0, block_nodes=0,
+                    want_lp=False):
+        """Sequential mean-field update of the class probabilities.  Returns (mf_m_new, lp or None)."""
+        m = np.array(mf_m, dtype=np.float64, copy=True, order="C")
+        K = m.shape[1]
+        S = 1 + self.B + self.B * (self.B + 1) // 2
+        args = [np.ascontiguousarray(a, dtype=np.float64) for a in (E_log_m, base_out, base_in, coef_out, coef_in)]
+        assert args[0].shape == (K,) and args[1].shape == (K, K) and args[2].shape == (K, K)
+        assert args[3].shape == (K, K, S) and args[4].shape == (K, K, S)
+        lp = np.zeros((self.N, K)) if want_lp else None
+        self.ctx.check(self.ctx.lib.gk_mf_sbm_update_c(self.ctx.h, self.h, ptr(m), K, *[ptr(a) for a in args],
+                                                       float(stepsize), int(block_nodes), ptr(lp)))
+        return m, lp
+
     def close(self):
         self._finalizer()
 

@@ -89,6 +89,77 @@ class Gaussian(object):
         data = np.asarray(data, dtype=np.float64).reshape(-1, self.D)
         return self.resample_from_stats(data.shape[0], data.sum(0), data.T.dot(data), rng)
 
+    # ---- mean field: natural parameters of the NIW (pybasicbayes Gaussian, natural-parameter form) --------------
+    @staticmethod
+    def _standard_to_natural(mu, sigma, kappa, nu):
+        D = sigma.shape[0]
+        out = np.zeros((D + 2, D + 2))
+        out[:D, :D] = sigma + kappa * np.outer(mu, mu)
+        out[:D, -2] = out[-2, :D] = kappa * mu
+        out[-2, -2] = kappa
+        out[-1, -1] = nu + 2 + D
+        return out
+
+    @staticmethod
+    def _natural_to_standard(nat):
+        D = nat.shape[0] - 2
+        A, b, c, d = nat[:D, :D], nat[:D, -2], nat[-2, -2], nat[-1, -1]
+        return b / c, A - np.outer(b, b) / c, c, d - 2 - D
+
+    @property
+    def natural_hypparam(self):
+        return self._standard_to_natural(self.mu_0, self.sigma_0, self.kappa_0, self.nu_0)
+
+    @property
+    def mf_natural_hypparam(self):
+        if getattr(self, "_mf_nat", None) is None:
+            self._mf_nat = self.natural_hypparam          # q starts at the prior
+        return self._mf_nat
+
+    @mf_natural_hypparam.setter
+    def mf_natural_hypparam(self, nat):
+        self._mf_nat = np.array(nat, dtype=np.float64)
+
+    @property
+    def mu_mf(self):
+        return self._natural_to_standard(self.mf_natural_hypparam)[0]
+
+    @property
+    def sigma_mf(self):
+        return self._natural_to_standard(self.mf_natural_hypparam)[1]
+
+    @property
+    def kappa_mf(self):
+        return self._natural_to_standard(self.mf_natural_hypparam)[2]
+
+    @property
+    def nu_mf(self):
+        return self._natural_to_standard(self.mf_natural_hypparam)[3]
+
+    @staticmethod
+    def _statistics_matrix(n, sum_x, sum_xxT):
+        """layout of pybasicbayes' `_get_statistics` / the reference's `_get_weighted_statistics`
+        (internals/weights.py:158-171)"""
+        D = len(sum_x)
+        out = np.zeros((D + 2, D + 2))
+        out[:D, :D] = sum_xxT
+        out[-2, :D] = out[:D, -2] = sum_x
+        out[-2, -2] = out[-1, -1] = n
+        return out
+
+    def _loglmbdatilde(self):
+        """E_q[log |Sigma^-1|]"""
+        from scipy.special import psi
+        D, sigma_mf, nu_mf = self.D, self.sigma_mf, self.nu_mf
+        chol = np.linalg.cholesky(sigma_mf)
+        return -2 * np.log(np.diag(chol)).sum() + D * np.log(2) + psi((nu_mf - np.arange(D)) / 2.0).sum()
+
+    def _resample_from_mf(self, rng=np.random):
+        mu_n, sigma_n, kappa_n, nu_n = self._natural_to_standard(self.mf_natural_hypparam)
+        self.sigma = invwishart_draw(0.5 * (sigma_n + sigma_n.T), nu_n, rng)
+        self.mu = rng.multivariate_normal(mu_n, self.sigma / kappa_n)
+        return self
+
     # ---- likelihood / sampling ---------------------------------------------------------------------
     def log_likelihood(self, x):
         x = np.asarray(x, dtype=np.float64).reshape(-1, self.D)

@@ -33,3 +33,38 @@ class GaussianWeights(Gaussian):
             sw += s1[0, 0] + d["d_sum_w"][0]
             sww += s2[0, 0] + d["d_sum_ww"][0]
         return self.resample_from_stats(n, sw, sww, rng)
+
+    # ---- mean field (internals/weights.py:105-132, 200-221) -------------------------------------------------
+    def meanfieldupdate_from_stats(self, n, sum_w, sum_ww, stepsize=1.0, minibatchfrac=1.0):
+        """`meanfieldupdate` (:105-132; stepsize == 1) / `svi_step` (:134-156) given the weighted statistics
+        sum_ij weights[i,j] * (1, E_W, E_WWT) -- the N^2 reduction itself runs on the device (gk_mf_sbm_soft_stats)."""
+        stats = self._statistics_matrix(n, sum_w, sum_ww)
+        target = self.natural_hypparam + stats / minibatchfrac
+        self.mf_natural_hypparam = (1 - stepsize) * self.mf_natural_hypparam + stepsize * target
+
+    def mf_expected_mu(self):
+        return self.mu_mf
+
+    def mf_expected_Sigma(self):
+        return self.sigma_mf / (self.nu_mf - self.D - 1)
+
+    def mf_expected_mumuT(self):
+        E_mu = self.mu_mf
+        return self.mf_expected_Sigma() + np.outer(E_mu, E_mu)
+
+    def mf_expected_Sigma_inv(self):
+        return self.nu_mf * np.linalg.inv(self.sigma_mf)
+
+    def mf_expected_logdet_Sigma(self):
+        return -self._loglmbdatilde()
+
+    def resample_from_mf(self):
+        self._resample_from_mf()
+
+    def expected_log_likelihood_coefficients(self):
+        """Coefficients (c0, c1[B], C2[B,B]) of E_q[ln N(w | mu, Sigma)] = c0 + c1.w + w^T C2 w as the reference's
+        Gaussian.negentropy writes it (internals/distributions.py:278-308; its -0.5*log(2*pi) constant kept)."""
+        E_Sinv = self.mf_expected_Sigma_inv()
+        c0 = -0.5 * np.log(2 * np.pi) - 0.5 * self.mf_expected_logdet_Sigma() \
+            - 0.5 * np.trace(E_Sinv.dot(self.mf_expected_mumuT()))
+        return c0, E_Sinv.dot(self.mf_expected_mu()), -0.5 * E_Sinv

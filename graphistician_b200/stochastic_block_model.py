@@ -12,7 +12,7 @@ reference's order: weight models (row-major cells) -> p (row-major) -> N uniform
 import copy
 
 import numpy as np
-from scipy.special import gammaln
+from scipy.special import gammaln, psi
 
 from . import _lib
 from .internals.weights import GaussianWeights
@@ -205,7 +205,183 @@ class _GibbsSBM(_StochasticBlockModelBase):
         self.m = np.random.dirichlet(self.pi + np.bincount(self.c, minlength=self.C))
 
 
-class GaussianStochasticBlockModel(_GibbsSBM, GaussianWeightedNetworkDistribution):
+class _MeanFieldSBM(_StochasticBlockModelBase):
+    """stochastic_block_model.py:310-584.  The N^2 reductions run in libgk for FIXED networks (E_A = A, E_W = W,
+    E_WWT = W W^T -- what FixedGaussianNetwork reports, the only network class the reference's drivers build):
+
+      mf_update_p, weight-model statistics  <- gk_mf_sbm_soft_stats   (the C x C loops of :340-344, 366-389)
+      mf_update_c                            <- gk_mf_sbm_update_c    (the N*C*N*C loop of :392-445, serial in n1)
+
+    `literal_reverse_edge` (default True) keeps a reference quirk: the reverse-edge branch `if n2 != n1:` (:425) sits
+    one indentation level outside the `for cn2` loop, so only cn2 == C-1 contributes to the reverse term; False gives
+    the evidently intended sum over cn2."""
+    literal_reverse_edge = True
+
+    def __init__(self, N, B, **kwargs):
+        super(_MeanFieldSBM, self).__init__(N, B, **kwargs)
+        self.mf_pi = np.ones(self.C)
+        self.mf_m = np.random.dirichlet(10 * np.ones(self.C), size=(self.N,))      # :323 symmetry breaking
+        self.mf_tau0 = self.tau0 * np.ones((self.C, self.C))
+        self.mf_tau1 = self.tau1 * np.ones((self.C, self.C))
+
+    # ---- device statistics ---------------------------------------------------------------------------
+    def _soft_stats(self, network):
+        """sum_ij mf_m[i,c1] mf_m[j,c2] A_ij (1, W_ij, W_ij W_ij^T), diagonal pairs included (as :340-344, :378-384)."""
+        dev = network.device(self.dtype)
+        n, sw, sww = dev.mf_soft_stats(self.mf_m)
+        e = dev.diagA != 0
+        if e.any():
+            me = self.mf_m[e]
+            n += me.T.dot(me)
+            if self.B > 0:
+                w = dev.diagW[e]
+                sw += np.einsum("ik,il,ib->klb", me, me, w)
+                sww += np.einsum("ik,il,ib,ic->klbc", me, me, w, w)
+        return n, sw, sww
+
+    def meanfieldupdate(self, network):
+        """:327-344"""
+        network = as_network(network)
+        self.mf_update_p(network)
+        self.mf_update_c(network)
+        self.mf_update_m()
+        self._mf_update_weight_models(network)
+
+    def meanfield_sgdstep(self, network, minibatchfrac, stepsize):
+        """:346-356 (the reference's order: p, m, c, weights)"""
+        network = as_network(network)
+        self.mf_update_p(network, stepsize=stepsize)
+        self.mf_update_m(stepsize=stepsize)
+        self.mf_update_c(network, stepsize=stepsize)
+        self._mf_update_weight_models(network, stepsize=stepsize)
+
+    def _mf_update_weight_models(self, network, stepsize=1.0):
+        if self.B == 0:
+            return
+        n, sw, sww = self._soft_stats(network)
+        for c1 in range(self.C):
+            for c2 in range(self.C):
+                self.weight_models[c1][c2].meanfieldupdate_from_stats(n[c1, c2], sw[c1, c2], sww[c1, c2], stepsize)
+
+    def mf_update_m(self, stepsize=1.0):
+        """:358-364"""
+        pi_hat = self.pi + self.mf_m.sum(axis=0)
+        self.mf_pi = (1.0 - stepsize) * self.mf_pi + stepsize * pi_hat
+
+    def mf_update_p(self, network, stepsize=1.0):
+        """:366-389 -- tau1_hat = tau1 + mf_m^T E_A mf_m, tau0_hat = tau0 + mf_m^T (1 - E_A) mf_m."""
+        network = as_network(network)
+        n1, _, _ = self._soft_stats(network)
+        ms = self.mf_m.sum(0)
+        n0 = np.outer(ms, ms) - n1
+        self.mf_tau1 = (1.0 - stepsize) * self.mf_tau1 + stepsize * (self.tau1 + n1)
+        self.mf_tau0 = (1.0 - stepsize) * self.mf_tau0 + stepsize * (self.tau0 + n0)
+
+    def _mf_cell_tables(self):
+        """Per-cell coefficients of the pair terms of mf_update_c (:410-435) in the layout gk_mf_sbm_update_c takes."""
+        C, B = self.C, self.B
+        S = 1 + B + B * (B + 1) // 2
+        E_ln_p = psi(self.mf_tau1) - psi(self.mf_tau0 + self.mf_tau1)          # Beta.expected_log_p
+        E_ln_notp = psi(self.mf_tau0) - psi(self.mf_tau0 + self.mf_tau1)
+        coef = np.zeros((C, C, S))
+        coef[:, :, 0] = E_ln_p - E_ln_notp
+        if B > 0:
+            for c1 in range(C):
+                for c2 in range(C):
+                    c0, c1v, C2 = self.weight_models[c1][c2].expected_log_likelihood_coefficients()
+                    coef[c1, c2, 0] += c0
+                    coef[c1, c2, 1:1 + B] = c1v
+                    j = 1 + B
+                    for b in range(B):
+                        for b2 in range(b, B):
+                            coef[c1, c2, j] = C2[b, b] if b2 == b else C2[b, b2] + C2[b2, b]
+                            j += 1
+        mask = np.ones(C)
+        if self.literal_reverse_edge:
+            mask[:] = 0.0
+            mask[C - 1] = 1.0
+        base_out, coef_out = E_ln_notp, coef
+        base_in = E_ln_notp.T * mask[None, :]
+        coef_in = np.transpose(coef, (1, 0, 2)) * mask[None, :, None]
+        return base_out, base_in, coef_out, coef_in
+
+    def mf_update_c(self, network, stepsize=1.0, want_lp=False):
+        """:392-445, sequential in n1."""
+        network = as_network(network)
+        dev = network.device(self.dtype)
+        base_out, base_in, coef_out, coef_in = self._mf_cell_tables()
+        self.mf_m, lp = dev.mf_update_c(self.mf_m, self.mf_expected_log_m(), base_out, base_in, coef_out, coef_in,
+                                        stepsize=stepsize, want_lp=want_lp)
+        return lp
+
+    # ---- expectations (:457-531) ------------------------------------------------------------------------
+    def _mf_mix(self, cell):
+        """sum_{c1,c2} mf_m[:,c1] mf_m[:,c2]^T cell[c1,c2,...]"""
+        return np.einsum("ik,jl,kl...->ij...", self.mf_m, self.mf_m, cell)
+
+    def mf_expected_p(self):
+        E_p = self._mf_mix(self.mf_tau1 / (self.mf_tau0 + self.mf_tau1))
+        if not self.allow_self_connections:
+            np.fill_diagonal(E_p, 0.0)
+        return E_p
+
+    def mf_expected_notp(self):
+        return 1.0 - self.mf_expected_p()
+
+    def mf_expected_log_p(self):
+        E = self._mf_mix(psi(self.mf_tau1) - psi(self.mf_tau0 + self.mf_tau1))
+        if not self.allow_self_connections:
+            np.fill_diagonal(E, -np.inf)
+        return E
+
+    def mf_expected_log_notp(self):
+        E = self._mf_mix(psi(self.mf_tau0) - psi(self.mf_tau0 + self.mf_tau1))
+        if not self.allow_self_connections:
+            np.fill_diagonal(E, 0.0)
+        return E
+
+    def mf_expected_m(self):
+        return self.mf_pi / self.mf_pi.sum()
+
+    def mf_expected_log_m(self):
+        return psi(self.mf_pi) - psi(self.mf_pi.sum())
+
+    def expected_log_likelihood(self, network):
+        raise NotImplementedError()               # :531-532
+
+    def resample_from_mf(self):
+        """:570-584"""
+        self.m = np.random.dirichlet(self.mf_pi)
+        self.p = np.random.beta(self.mf_tau1, self.mf_tau0)
+        for c1 in range(self.C):
+            for c2 in range(self.C):
+                self.weight_models[c1][c2].resample_from_mf()
+        self.c = np.zeros(self.N, dtype=np.int64)
+        for k in range(self.N):
+            self.c[k] = int(np.random.choice(self.C, p=self.mf_m[k, :]))
+        self.__dict__.pop("_mus_cache", None)
+
+    def svi_step(self, augmented_data, minibatchfrac, stepsize):
+        raise NotImplementedError()               # :586-587
+
+
+class GaussianStochasticBlockModel(_GibbsSBM, _MeanFieldSBM, GaussianWeightedNetworkDistribution):
     """stochastic_block_model.py:589-592."""
     _weight_class = GaussianWeights
     _default_weight_hypers = {}
+
+    # ---- mean-field expectations of the weights (:646-678) ----------------------------------------------------
+    def _wm_cells(self, fn):
+        return np.array([[fn(self.weight_models[c1][c2]) for c2 in range(self.C)] for c1 in range(self.C)])
+
+    def mf_expected_mu(self):
+        return self._mf_mix(self._wm_cells(lambda w: w.mf_expected_mu()))
+
+    def mf_expected_mumuT(self):
+        return self._mf_mix(self._wm_cells(lambda w: w.mf_expected_mumuT()))
+
+    def mf_expected_Sigma_inv(self):
+        return self._mf_mix(self._wm_cells(lambda w: w.mf_expected_Sigma_inv()))
+
+    def mf_expected_logdet_Sigma(self):
+        return self._mf_mix(self._wm_cells(lambda w: w.mf_expected_logdet_Sigma()))

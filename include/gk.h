@@ -45,7 +45,7 @@ int gk_ctx_synchronize(gk_ctx *ctx);
 int64_t gk_ctx_launch_count(gk_ctx *ctx);                   /* kernels launched so far by this ctx */
 /* per-kernel CUDA-event timing (bench.py roofline); family: 0 = strip statistics kernel,
  * 1 = sequential sampler, 2 = Polya-gamma draw, 3 = eigen slab contraction, 4 = latent pairwise,
- * 5 = eigen sequential feature draw */
+ * 5 = eigen sequential feature draw, 6 = mean-field soft strip statistics, 7 = mean-field sequential update */
 int gk_ctx_kernel_timing(gk_ctx *ctx, int enable);
 int gk_ctx_kernel_timing_read(gk_ctx *ctx, int family, double *ms_total, int64_t *launches, double *bytes_total);
 
@@ -186,6 +186,26 @@ int gk_latent_hmc_begin(gk_ctx *ctx, gk_latent *lat, int target, double step, in
 int gk_latent_hmc_pass(gk_ctx *ctx, gk_latent *lat, double *acc_dev);
 int gk_latent_hmc_advance(gk_ctx *ctx, gk_latent *lat, const double *acc_dev);
 int gk_latent_hmc_end(gk_ctx *ctx, gk_latent *lat, double log_u, int *accepted, double *log_ratio);
+
+/* ---- K10: mean-field SBM ---------------------------------------------------------
+ * Fixed networks only (E_A = A, E_W = W, E_WWT = W W^T: the reference's FixedGaussianNetwork); unsharded.
+ * gk_mf_sbm_soft_stats replaces the C x C loops of stochastic_block_model.py:366-389 (mf_update_p) and :340-344 with
+ * internals/weights.py:158-171 (weighted NIW statistics): n_soft[c1,c2] = sum_{i != j} mf_m[i,c1] mf_m[j,c2] A[i,j],
+ * sum_w / sum_ww the same sums of A*W_b / A*W_b*W_b'.  Off-diagonal pairs only; the O(N) diagonal terms are composed
+ * by the host class.  mf_m: N x K row-major. */
+int gk_mf_sbm_soft_stats(gk_ctx *ctx, gk_net *net, const double *mf_m, int K, double *n_soft, double *sum_w,
+                         double *sum_ww);
+/* gk_mf_sbm_update_c replaces stochastic_block_model.py:392-445 (mf_update_c), same serial semantics: node n1's
+ * class probabilities are recomputed from the CURRENT mf_m of all other nodes, in index order.  Per-partner terms of
+ * lp[k] for a partner of class k' (tables K x K [x S], candidate class k first, S = 1 + B + B(B+1)/2 packed
+ * statistics (a, a*w_b, a*w_b*w_b' for b <= b')):
+ *   forward  n1 -> n2 (n2 == n1 included):  base_out[k,k'] + sum_s x_s(n1,n2) coef_out[k,k',s]
+ *   reverse  n2 -> n1 (n2 != n1):           base_in [k,k'] + sum_s x_s(n2,n1) coef_in [k,k',s]
+ * mf_m[n1,:] <- (1-stepsize) mf_m[n1,:] + stepsize softmax(lp).  out_lp (N x K, optional) = lp of each node at the
+ * moment it was updated.  block_nodes: nodes per parallel statistics phase (0 = auto, <= 256). */
+int gk_mf_sbm_update_c(gk_ctx *ctx, gk_net *net, double *mf_m_inout, int K, const double *E_log_m,
+                       const double *base_out, const double *base_in, const double *coef_out, const double *coef_in,
+                       double stepsize, int block_nodes, double *out_lp);
 
 #ifdef __cplusplus
 }

@@ -161,8 +161,67 @@ def make_latent():
     print("latent_small.npz")
 
 
+def make_mf_sbm():
+    """mf_sbm_small.npz: the literal mf_update_c loop nest (stochastic_block_model.py:392-445) run with the REFERENCE'S
+    OWN Beta / Bernoulli / Gaussian classes (internals/distributions.py, imported unmodified) doing the per-pair
+    arithmetic -- this fixture pins oracle/mf_sbm.py's restatement of them."""
+    from oracle import mf_sbm as M
+    _, dist = _import_reference_internals()
+
+    class RefDists(object):
+        @staticmethod
+        def beta_logs(t1, t0):
+            b = dist.Beta(t1, t0)
+            return float(b.expected_log_p()[0]), float(b.expected_log_notp()[0])
+
+        @staticmethod
+        def bern_negentropy(E_x, E_notx, E_ln_p, E_ln_notp):
+            return dist.Bernoulli().negentropy(E_x=np.float64(E_x), E_notx=np.float64(E_notx),
+                                               E_ln_p=E_ln_p, E_ln_notp=E_ln_notp)
+
+        @staticmethod
+        def gauss_negentropy(**kw):
+            return dist.Gaussian().negentropy(**kw)
+
+    rng = np.random.RandomState(2468)
+    N, C, B = 10, 3, 2
+    A = (rng.rand(N, N) < 0.45).astype(np.uint8)
+    W = rng.randn(N, N, B)
+    E_WWT = W[:, :, :, None] * W[:, :, None, :]
+    mf_m = rng.dirichlet(2 * np.ones(C), size=N)
+    mf_pi = rng.gamma(2.0, 1.0, C) + 0.5
+    t1 = rng.gamma(2.0, 2.0, (C, C)) + 0.3
+    t0 = rng.gamma(2.0, 2.0, (C, C)) + 0.3
+    niw = np.zeros((C, C, 2 + B + B * B))          # (kappa, nu, mu[B], sigma[B*B]) of each cell's q
+    wexp = [[None] * C for _ in range(C)]
+    for a in range(C):
+        for b in range(C):
+            X = rng.randn(B, B)
+            mu, sig, kap, nu = rng.randn(B), X.dot(X.T) + np.eye(B), 1.0 + rng.rand(), B + 2.0 + 3 * rng.rand()
+            niw[a, b] = np.concatenate([[kap, nu], mu, sig.ravel()])
+            wexp[a][b] = M.weight_expectations(mu, sig, kap, nu)
+    Af = A.astype(float)
+    out = dict(A=A, W=W, mf_m=mf_m, mf_pi=mf_pi, mf_tau1=t1, mf_tau0=t0, niw=niw)
+    for lit in (1, 0):
+        for tag, st in (("full", 1.0), ("step", 0.35)):
+            m_ref, lp_ref = M.mf_update_c_loops(Af, W, E_WWT, mf_m, mf_pi, t1, t0, wexp, st, dists=RefDists,
+                                                literal_reverse=bool(lit))
+            out["m_%s_lit%d" % (tag, lit)] = m_ref
+            out["lp_%s_lit%d" % (tag, lit)] = lp_ref
+    m_noW, lp_noW = M.mf_update_c_loops(Af, W, E_WWT, mf_m, mf_pi, t1, t0, None, 1.0, dists=RefDists)
+    out.update(m_noW=m_noW, lp_noW=lp_noW)
+    nt1, nt0 = M.mf_update_p_loops(Af, mf_m, 1.0, 1.0, t1, t0, 0.6)
+    out.update(p_tau1=nt1, p_tau0=nt0)
+    nat0 = [[M.standard_to_natural(np.zeros(B), np.eye(B), 1.0, B + 2.0) for _ in range(C)] for _ in range(C)]
+    nat = M.mf_update_weight_models_loops(Af, W, E_WWT, mf_m, nat0)
+    out["w_nat"] = np.array(nat)
+    np.savez(os.path.join(HERE, "mf_sbm_small.npz"), **out)
+    print("mf_sbm_small.npz")
+
+
 if __name__ == "__main__":
     make_ref_internals()
     make_sbm()
     make_eigen()
     make_latent()
+    make_mf_sbm()
