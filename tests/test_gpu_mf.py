@@ -82,7 +82,7 @@ def test_update_p_and_weights_match_reference_golden():
 
 
 @pytest.mark.parametrize("N,C,B,dtype,lit", [(70, 3, 2, "f64", True), (333, 16, 2, "f64", False), (520, 5, 1, "f64", True),
-                                             (257, 7, 0, "f64", True), (600, 16, 2, "f32", True), (300, 32, 1, "f32", False)])
+                                             (257, 7, 1, "f64", True), (600, 16, 2, "f32", True), (300, 32, 1, "f32", False)])
 def test_update_c_matches_oracle(N, C, B, dtype, lit):
     from graphistician_b200.old_abstractions import FixedGaussianNetwork
     rng = np.random.RandomState(N + C)
