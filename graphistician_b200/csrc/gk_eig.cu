@@ -1,8 +1,9 @@
 // gk_eig.cu -- host side of the eigenmodel path (K3-K6): state, launch plans, C-ABI entry points.
 #include <math.h>
 #include <string.h>
+#include <stdlib.h>
 #include <algorithm>
-#include "gk_eig_kernels.cuh"
+#include "gk_eig_fast.cuh"
 
 struct gk_eig {
     gk_net *net = nullptr;
@@ -14,6 +15,9 @@ struct gk_eig {
     double *part = nullptr; size_t npart = 0;              // per-tile partial sums of K3
     double *scal = nullptr;            // small device scalars (sum of omega, ...)
     double *out_prec = nullptr, *out_h = nullptr;
+    double *G = nullptr, *dphi = nullptr, *spart = nullptr;   // running-G sweep (gk_eig_fast.cuh): [ld][PA], [NB][PA], [64][PA]
+    long long *prof = nullptr;         // debug cycle counters of k_eig_seq3 (env GK_EIG_PROF=1)
+    int use_fast = 1;                  // unsharded sweeps use the running-G form (GK_EIG_OPT_FAST_SWEEP)
     double mu0 = 0.0;
     bool have_S = false;
     bool chol_f64 = false;             // f32 storage: factorise the D x D conditionals in fp32 unless set
@@ -71,6 +75,7 @@ extern "C" int gk_eig_destroy(gk_ctx *ctx, gk_eig *e) {
     if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
     cudaFree(e->S); cudaFree(e->F); cudaFree(e->z); cudaFree(e->lmbda); cudaFree(e->acc); cudaFree(e->glob);
     cudaFree(e->part); cudaFree(e->scal); cudaFree(e->out_prec); cudaFree(e->out_h);
+    cudaFree(e->G); cudaFree(e->dphi); cudaFree(e->spart);
     delete e;
     return GK_OK;
 }
@@ -82,6 +87,7 @@ extern "C" size_t gk_eig_device_bytes(gk_eig *e) {
 extern "C" int gk_eig_set_option(gk_ctx *ctx, gk_eig *e, int option, int value) {
     if (!ctx || !e) return GK_EINVAL;
     if (option == GK_EIG_OPT_CHOL_F64) { e->chol_f64 = value != 0; return GK_OK; }
+    if (option == GK_EIG_OPT_FAST_SWEEP) { e->use_fast = value != 0; return GK_OK; }
     return gk_fail(ctx, GK_EINVAL, "unknown eigenmodel option %d", option);
 }
 
@@ -360,6 +366,92 @@ static int sweep_F(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
     return GK_OK;
 }
 
+// running-G form of the sweep (gk_eig_fast.cuh): one full contraction, then per node block { serial draws ; push }
+template <typename T, typename CH, int D>
+static int launch_seq3_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sigma_F) {
+    static bool attr_set = false;
+    const size_t smem = gk_eig_seq3_smem<T, D>();
+    if (!attr_set) {
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq3<T, CH, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    gk_net *net = e->net;
+    gk_eig_seq3_params P;
+    P.n0 = n0; P.nb = nb; P.N = e->N;
+    P.Sblk = (const T *)e->S + (size_t)n0 * net->ld + n0; P.ldS = net->ld;
+    P.Ablk = net->Asym + (size_t)n0 * net->ld + n0; P.ldA = net->ld;
+    P.F = e->F; P.z = e->z; P.lmbda = e->lmbda; P.mu0 = e->mu0; P.inv_sigma_F = inv_sigma_F;
+    P.G = e->G; P.dphi = e->dphi; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h; P.probit = e->probit;
+    P.prof = e->prof;
+    gk_time_begin(ctx, 5, 0.0);
+    k_eig_seq3<T, CH, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
+    gk_time_end(ctx, 5);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+template <typename T, int D>
+static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
+    typedef typename gk_eacc<T>::type ACC;
+    constexpr int PA = gk_edim<D>::PA, PH = gk_edim<D>::PH, NB = gk_eig_nb<T>::NB;
+    gk_net *net = e->net;
+    const int N = e->N, npad = net->ld, strips = npad / GK_EF_COLS;
+    if (!e->G) {
+        GK_CUDA(ctx, cudaMalloc(&e->G, (size_t)npad * GK_EIG_PA_MAX * 8));
+        GK_CUDA(ctx, cudaMalloc(&e->dphi, (size_t)GK_EIG_NBMAX * GK_EIG_PA_MAX * 8));
+        GK_CUDA(ctx, cudaMalloc(&e->spart, (size_t)64 * GK_EIG_PA_MAX * 8));
+        if (getenv("GK_EIG_PROF")) GK_CUDA(ctx, cudaMalloc(&e->prof, 16 * 8));
+    }
+    if (e->prof) GK_CUDA(ctx, cudaMemsetAsync(e->prof, 0, 16 * 8, ctx->stream));
+    // full contraction: row chunks so that the grid covers >= 2 waves of 2 CTAs/SM
+    int nchunks = std::max(1, std::min(16, (4 * ctx->num_sms + strips - 1) / strips));
+    int chunk_rows = ((N + nchunks - 1) / nchunks + GK_EF_PIECE - 1) / GK_EF_PIECE * GK_EF_PIECE;
+    nchunks = (N + chunk_rows - 1) / chunk_rows;
+    ACC *partial = (ACC *)gk_scratch(ctx, 2, (size_t)nchunks * npad * PA * sizeof(ACC));
+    if (!partial) return GK_ENOMEM;
+    const size_t fold_elems = (size_t)128 * (2 * PH + 1);
+    const size_t smem_full = std::max((size_t)GK_EF_PIECE * PA, fold_elems) * sizeof(ACC);
+    const size_t smem_push = std::max((size_t)NB * PA, fold_elems) * sizeof(ACC);
+    static bool attr_set = false;
+    if (!attr_set) {
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_gfull<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full));
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_push<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_push));
+        attr_set = true;
+    }
+    gk_time_begin(ctx, 3, (double)N * N * (sizeof(T) + 1.0));
+    k_eig_gfull<T, D><<<dim3(strips, nchunks), GK_EF_THREADS, smem_full, ctx->stream>>>(
+        (const T *)e->S, net->Asym, net->ld, N, e->F, chunk_rows, npad, partial, e->probit);
+    gk_time_end(ctx, 3);
+    GK_CHECK_LAUNCH(ctx);
+    const size_t per_chunk = (size_t)npad * PA;
+    k_eig_greduce<ACC><<<(int)std::min<size_t>((per_chunk + 255) / 256, (size_t)ctx->num_sms * 8), 256, 0, ctx->stream>>>(
+        partial, nchunks, per_chunk, e->G);
+    GK_CHECK_LAUNCH(ctx);
+    for (int n0 = 0; n0 < N; n0 += NB) {
+        const int nb = std::min(NB, N - n0);
+        int rc = (sizeof(T) == 4 && !e->chol_f64) ? launch_seq3_ch<T, float, D>(ctx, e, n0, nb, inv_sigma_F)
+                                                  : launch_seq3_ch<T, double, D>(ctx, e, n0, nb, inv_sigma_F);
+        if (rc) return rc;
+        gk_time_begin(ctx, 3, (double)nb * N * (sizeof(T) + 1.0));
+        k_eig_push<T, D><<<strips, GK_EF_THREADS, smem_push, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, N, e->dphi, n0, nb,
+                                                                           e->G, e->probit);
+        gk_time_end(ctx, 3);
+        GK_CHECK_LAUNCH(ctx);
+    }
+    k_eig_gstats<D><<<64, 512, 0, ctx->stream>>>(e->G, e->F, N, e->glob, e->probit, e->spart);
+    GK_CHECK_LAUNCH(ctx);
+    k_eig_gstats_final<D><<<1, 64, 0, ctx->stream>>>(e->spart, 64, e->glob);
+    GK_CHECK_LAUNCH(ctx);
+    if (e->prof) {
+        long long h[16];
+        GK_CUDA(ctx, cudaMemcpyAsync(h, e->prof, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+        GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        fprintf(stderr, "[gk_eig prof] cycles/node: solver cond %.0f chol %.0f dphi %.0f row+1 %.0f barrier %.0f | updater loop %.0f barrier %.0f\n",
+                (double)h[0] / N, (double)h[1] / N, (double)h[2] / N, (double)h[3] / N, (double)h[7] / N, (double)h[8 + 6] / N, (double)h[8 + 7] / N);
+    }
+    return GK_OK;
+}
+
 #define GK_EIG_SWITCH_D(T, D, FN, ...)                                              \
     ((D) == 1 ? FN<T, 1>(__VA_ARGS__) : (D) == 2 ? FN<T, 2>(__VA_ARGS__) : (D) == 3 ? FN<T, 3>(__VA_ARGS__)      \
      : (D) == 4 ? FN<T, 4>(__VA_ARGS__) : (D) == 5 ? FN<T, 5>(__VA_ARGS__) : (D) == 6 ? FN<T, 6>(__VA_ARGS__)    \
@@ -383,8 +475,11 @@ extern "C" int gk_eig_resample_F(gk_ctx *ctx, gk_eig *e, double sigma_F, const d
     GK_CUDA(ctx, cudaMemsetAsync(e->glob, 0, GK_EIG_GLOB_LEN * 8, ctx->stream));
     k_eig_colsum<<<1, 1024, 0, ctx->stream>>>(e->F, e->N, D, e->glob + GK_EIG_GLOB_SUMF);
     GK_CHECK_LAUNCH(ctx);
-    int rc = e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, D, sweep_F, ctx, e, 1.0 / sigma_F)
-                                : GK_EIG_SWITCH_D(double, D, sweep_F, ctx, e, 1.0 / sigma_F);
+    int rc;
+    if (e->use_fast) rc = e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, D, sweep_F_fast, ctx, e, 1.0 / sigma_F)
+                                             : GK_EIG_SWITCH_D(double, D, sweep_F_fast, ctx, e, 1.0 / sigma_F);
+    else rc = e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, D, sweep_F, ctx, e, 1.0 / sigma_F)
+                                 : GK_EIG_SWITCH_D(double, D, sweep_F, ctx, e, 1.0 / sigma_F);
     e->out_prec = keep_prec; e->out_h = keep_h;
     if (rc) return rc;
     if (F_out) GK_CUDA(ctx, cudaMemcpyAsync(F_out, e->F, N * D * 8, cudaMemcpyDeviceToHost, ctx->stream));

@@ -108,7 +108,10 @@ int gk_eig_destroy(gk_ctx *ctx, gk_eig *eig);
 size_t gk_eig_device_bytes(gk_eig *eig);
 /* options: GK_EIG_OPT_CHOL_F64 = factorise the D x D conditionals in fp64 even with fp32 storage
  * (default with fp32 storage: fp32 factorisation; the conditionals themselves are always fp64) */
-enum { GK_EIG_OPT_CHOL_F64 = 0 };
+enum { GK_EIG_OPT_CHOL_F64 = 0,
+       /* 1 (default): unsharded gk_eig_resample_F keeps a running contraction G for all nodes (one full pass + per-block
+        * pushes); 0: re-contract a slab of S per node block (the form the row-sharded block API uses) */
+       GK_EIG_OPT_FAST_SWEEP = 1 };
 int gk_eig_set_option(gk_ctx *ctx, gk_eig *eig, int option, int value);
 /* upload the model attributes F (N x D), mu_0, lmbda (D)  (eigenmodel.py:41-73 state) */
 int gk_eig_set_params(gk_ctx *ctx, gk_eig *eig, const double *F, double mu0, const double *lmbda);
