@@ -15,7 +15,7 @@ struct gk_eig {
     double *part = nullptr; size_t npart = 0;              // per-tile partial sums of K3
     double *scal = nullptr;            // small device scalars (sum of omega, ...)
     double *out_prec = nullptr, *out_h = nullptr;
-    double *G = nullptr, *dphi = nullptr, *spart = nullptr;   // running-G sweep (gk_eig_fast.cuh): [ld][PA], [NB][PA], [64][PA]
+    double *G = nullptr, *spart = nullptr; void *dphi = nullptr;   // running-G sweep (gk_eig_fast.cuh): [ld][PA], [NB][PA], [64][PA]
     long long *prof = nullptr;         // debug cycle counters of k_eig_seq3 (env GK_EIG_PROF=1)
     int use_fast = 1;                  // unsharded sweeps use the running-G form (GK_EIG_OPT_FAST_SWEEP)
     double mu0 = 0.0;
@@ -368,15 +368,15 @@ static int sweep_F(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
 
 // running-G form of the sweep (gk_eig_fast.cuh): one full contraction, then per node block { serial draws ; push }
 template <typename T, typename CH, int D>
-static int launch_seq3_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sigma_F) {
+static int launch_seq4_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sigma_F) {
     static bool attr_set = false;
-    const size_t smem = gk_eig_seq3_smem<T, D>();
+    const size_t smem = gk_eig_seq4_smem<T, CH, D>();
     if (!attr_set) {
-        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq3<T, CH, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq4<T, CH, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         attr_set = true;
     }
     gk_net *net = e->net;
-    gk_eig_seq3_params P;
+    gk_eig_seq4_params P;
     P.n0 = n0; P.nb = nb; P.N = e->N;
     P.Sblk = (const T *)e->S + (size_t)n0 * net->ld + n0; P.ldS = net->ld;
     P.Ablk = net->Asym + (size_t)n0 * net->ld + n0; P.ldA = net->ld;
@@ -384,7 +384,7 @@ static int launch_seq3_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sig
     P.G = e->G; P.dphi = e->dphi; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h; P.probit = e->probit;
     P.prof = e->prof;
     gk_time_begin(ctx, 5, 0.0);
-    k_eig_seq3<T, CH, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
+    k_eig_seq4<T, CH, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
     gk_time_end(ctx, 5);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
@@ -398,7 +398,7 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
     const int N = e->N, npad = net->ld, strips = npad / GK_EF_COLS;
     if (!e->G) {
         GK_CUDA(ctx, cudaMalloc(&e->G, (size_t)npad * GK_EIG_PA_MAX * 8));
-        GK_CUDA(ctx, cudaMalloc(&e->dphi, (size_t)GK_EIG_NBMAX * GK_EIG_PA_MAX * 8));
+        GK_CUDA(ctx, cudaMalloc(&e->dphi, (size_t)GK_EIG_NBMAX * GK_EIG_PA_MAX * 8));       // U [NB][PA]
         GK_CUDA(ctx, cudaMalloc(&e->spart, (size_t)64 * GK_EIG_PA_MAX * 8));
         if (getenv("GK_EIG_PROF")) GK_CUDA(ctx, cudaMalloc(&e->prof, 16 * 8));
     }
@@ -429,11 +429,11 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
     GK_CHECK_LAUNCH(ctx);
     for (int n0 = 0; n0 < N; n0 += NB) {
         const int nb = std::min(NB, N - n0);
-        int rc = (sizeof(T) == 4 && !e->chol_f64) ? launch_seq3_ch<T, float, D>(ctx, e, n0, nb, inv_sigma_F)
-                                                  : launch_seq3_ch<T, double, D>(ctx, e, n0, nb, inv_sigma_F);
+        int rc = (sizeof(T) == 4 && !e->chol_f64) ? launch_seq4_ch<T, float, D>(ctx, e, n0, nb, inv_sigma_F)
+                                                  : launch_seq4_ch<T, double, D>(ctx, e, n0, nb, inv_sigma_F);
         if (rc) return rc;
         gk_time_begin(ctx, 3, (double)nb * N * (sizeof(T) + 1.0));
-        k_eig_push<T, D><<<strips, GK_EF_THREADS, smem_push, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, N, e->dphi, n0, nb,
+        k_eig_push<T, D><<<strips, GK_EF_THREADS, smem_push, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, N, (const ACC *)e->dphi, n0, nb,
                                                                            e->G, e->probit);
         gk_time_end(ctx, 3);
         GK_CHECK_LAUNCH(ctx);
@@ -446,7 +446,7 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
         long long h[16];
         GK_CUDA(ctx, cudaMemcpyAsync(h, e->prof, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        fprintf(stderr, "[gk_eig prof] cycles/node: solver cond %.0f chol %.0f dphi %.0f row+1 %.0f barrier %.0f | updater loop %.0f barrier %.0f\n",
+        fprintf(stderr, "[gk_eig prof] cycles/node: solver cond %.0f chol %.0f dphi+carry %.0f (unused %.0f) barrier %.0f | updater loop %.0f barrier %.0f\n",
                 (double)h[0] / N, (double)h[1] / N, (double)h[2] / N, (double)h[3] / N, (double)h[7] / N, (double)h[8 + 6] / N, (double)h[8 + 7] / N);
     }
     return GK_OK;
