@@ -447,7 +447,8 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
         GK_CUDA(ctx, cudaMemcpyAsync(h, e->prof, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         fprintf(stderr, "[gk_eig prof] cycles/node: solver cond %.0f chol %.0f dphi+carry %.0f (unused %.0f) barrier %.0f | updater loop %.0f barrier %.0f\n",
-                (double)h[0] / N, (double)h[1] / N, (double)h[2] / N, (double)h[3] / N, (double)h[7] / N, (double)h[8 + 6] / N, (double)h[8 + 7] / N);
+                (double)h[0] / N, (double)h[1] / N, (double)h[2] / N, 0.0, (double)h[7] / N, (double)h[8 + 6] / N, (double)h[8 + 7] / N);
+        fprintf(stderr, "[gk_eig prof] cycles/node: loop %.0f setup %.0f whole kernel %.0f\n", (double)h[3] / N, (double)h[4] / N, (double)h[5] / N);
     }
     return GK_OK;
 }
