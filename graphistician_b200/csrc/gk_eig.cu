@@ -402,7 +402,9 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
         GK_CUDA(ctx, cudaMalloc(&e->spart, (size_t)64 * GK_EIG_PA_MAX * 8));
         if (getenv("GK_EIG_PROF")) GK_CUDA(ctx, cudaMalloc(&e->prof, 16 * 8));
     }
-    if (e->prof) GK_CUDA(ctx, cudaMemsetAsync(e->prof, 0, 16 * 8, ctx->stream));
+    if (e->prof) {
+        GK_CUDA(ctx, cudaMemsetAsync(e->prof, 0, 16 * 8, ctx->stream));
+    }
     // full contraction: row chunks so that the grid covers >= 2 waves of 2 CTAs/SM
     int nchunks = std::max(1, std::min(16, (4 * ctx->num_sms + strips - 1) / strips));
     int chunk_rows = ((N + nchunks - 1) / nchunks + GK_EF_PIECE - 1) / GK_EF_PIECE * GK_EF_PIECE;
@@ -446,9 +448,9 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
         long long h[16];
         GK_CUDA(ctx, cudaMemcpyAsync(h, e->prof, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
-        fprintf(stderr, "[gk_eig prof] cycles/node: solver cond %.0f chol %.0f dphi+carry %.0f (unused %.0f) barrier %.0f | updater loop %.0f barrier %.0f\n",
-                (double)h[0] / N, (double)h[1] / N, (double)h[2] / N, 0.0, (double)h[7] / N, (double)h[8 + 6] / N, (double)h[8 + 7] / N);
-        fprintf(stderr, "[gk_eig prof] cycles/node: loop %.0f setup %.0f whole kernel %.0f\n", (double)h[3] / N, (double)h[4] / N, (double)h[5] / N);
+        fprintf(stderr, "[gk_eig prof] cycles/node: solver busy %.0f barrier wait %.0f | updater(63) busy %.0f barrier wait %.0f\n",
+                (double)h[0] / N, (double)h[7] / N, (double)h[8] / N, (double)h[8 + 7] / N);
+        fprintf(stderr, "[gk_eig prof] cycles/node: loop %.0f setup %.0f flush %.0f whole kernel %.0f\n", (double)h[3] / N, (double)h[4] / N, (double)h[5] / N, (double)h[6] / N);
     }
     return GK_OK;
 }

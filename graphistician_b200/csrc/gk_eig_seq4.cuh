@@ -13,6 +13,11 @@
 // On exit: G[n0+j] += Gd[j], F <- new features, sumF, and dphi[i] = Phi(new f_i) - Phi(old f_i) for k_eig_push.
 #pragma once
 
+// cycle counter the compiler may not move across memory operations or barriers (debug probes, env GK_EIG_PROF).
+// NB: on B200 %clock64 advanced ~0.58 ticks per SM cycle in these kernels (ncu sm__cycles_elapsed vs these counters), so the
+// probes give the SHARE of each phase, not SM cycles; each read also costs tens of cycles.
+__device__ __forceinline__ long long gk_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory"); return t; }
+
 // factor prec = L L^T (packed upper, in the factorisation type) and draw f = L^-T (L^-1 h + z): right-looking
 // factorisation with the forward substitution fused in, column-oriented back substitution.
 template <typename CH, int D>
@@ -100,7 +105,7 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
     __shared__ double sF0[D];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nb = P.nb, n0 = P.n0;
     const bool probit = P.probit != 0;
-    const long long kstart = P.prof ? clock64() : 0;
+    const long long kstart = P.prof ? gk_clock() : 0;
 
     // ---- block entry: in-block tiles of S / Asym (16-byte loads), G rows, features, normals
     if (tid < D) sF0[tid] = P.glob[GK_EIG_GLOB_SUMF + tid];
@@ -152,11 +157,11 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
 
     long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, ck0 = 0, ck1 = 0;
     const bool prof = P.prof != nullptr;
-    const long long lstart = prof ? clock64() : 0;
+    const long long lstart = prof ? gk_clock() : 0;
     for (int t = 0; t <= nb; ++t) {
         if (warp == 0) {
             if (t < nb) {
-                if (prof) ck0 = clock64();
+                if (prof) ck0 = gk_clock();
                 const int n = n0 + t, cur = t & 1, row = t * PA;
                 // ---- conditional of node t (no fp64 when C == float); all loads first, then arithmetic, then stores
                 const C gd0 = has0 ? Gd[row + c0] : C(0), gb0 = has0 ? Gb[row + c0] : C(0);
@@ -177,11 +182,9 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
                 }
                 if (P.out_h && lin) P.out_h[(size_t)n * D + la] = (double)y1;
                 __syncwarp();
-                if (prof) { ck1 = clock64(); pc[0] += ck1 - ck0; ck0 = ck1; }
                 // ---- factor and draw (one lane: the chain is latency-bound)
                 if (lane == 0) gk_chol_draw4<CH, D>(LamC, hvC, zc + t * D, fnS + t * D);
                 __syncwarp();
-                if (prof) { ck1 = clock64(); pc[1] += ck1 - ck0; ck0 = ck1; }
                 // ---- the node's change, and its carry into row t+1 (loads first)
                 const bool nx = t + 1 < nb;
                 const CH *fn = fnS + t * D;
@@ -195,10 +198,9 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
                 if (has0) { dph[t % GK_SEQ4_SBK][c0] = d0; ((ACC *)P.dphi)[row + c0] = (ACC)d0; }
                 if (has1) { dph[t % GK_SEQ4_SBK][c1] = d1; ((ACC *)P.dphi)[row + c1] = (ACC)d1; }
                 if (lin) { dph[t % GK_SEQ4_SBK][c2] = d1; ((ACC *)P.dphi)[row + c2] = (ACC)d1; }
-                if (prof) { ck1 = clock64(); pc[2] += ck1 - ck0; ck0 = ck1; }
             }
         } else if (ur < RUP) {
-            if (prof) ck0 = clock64();
+            if (prof) ck0 = gk_clock();
             // Phi(old f) of node t+1 for the solver's next iteration
             if (u < PA && t + 1 < nb) phio[(t + 1) & 1][up] = up < Q ? foldC[(t + 1) * D + ua] * foldC[(t + 1) * D + ub] : foldC[(t + 1) * D + ua];
             if (t > 0) {
@@ -208,14 +210,14 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
                 if (up < Pn) { for (int j = s + 2 + ur; j < send; j += RUP) Gd[(size_t)j * PA + up] += xS(s, j) * d; }
                 else { for (int j = s + 2 + ur; j < send; j += RUP) Gd[(size_t)j * PA + up] += xA(s, j) * d; }
             }
-            if (prof) { ck1 = clock64(); pc[6] += ck1 - ck0; }
         }
-        if (prof) ck0 = clock64();
+        if (prof) { ck1 = gk_clock(); pc[0] += ck1 - ck0; ck0 = ck1; }
         __syncthreads();
-        if (prof) { ck1 = clock64(); pc[7] += ck1 - ck0; }
+        if (prof) { ck1 = gk_clock(); pc[7] += ck1 - ck0; }
         // flush: the sub-block [t+1-SBK, t] is complete -> every later row takes its 16 changes at once (registers hold the
         // column's changes; one read-modify-write of Gd per 16 FMAs).  The pair (t, t+1) stays with the solver's carry.
         if (t < nb && (t + 1) % GK_SEQ4_SBK == 0 && t + 1 < nb) {
+            if (prof) ck0 = gk_clock();
             constexpr int FR = GK_EIG_SEQ_THREADS / PA;
             const int fc = tid % PA, fr = tid / PA, s0 = t + 1 - GK_SEQ4_SBK;
             if (fr < FR) {
@@ -237,9 +239,10 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
                 }
             }
             __syncthreads();
+            if (prof) { ck1 = gk_clock(); pc[5] += ck1 - ck0; }
         }
     }
-    if (prof) { pc[3] = clock64() - lstart; pc[4] = lstart - kstart; }
+    if (prof) { pc[3] = gk_clock() - lstart; pc[4] = lstart - kstart; }
     if (prof && (tid == 0 || tid == 63)) for (int k = 0; k < 8; ++k) atomicAdd((unsigned long long *)P.prof + (tid ? 8 : 0) + k, (unsigned long long)pc[k]);
     // ---- block exit: G rows, features, column sums of F
     for (int t = tid; t < nb * PA; t += GK_EIG_SEQ_THREADS) P.G[(size_t)n0 * PA + t] += (double)Gd[t];
@@ -255,5 +258,5 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
         for (int i = 0; i < nb; ++i) s += diff[i * D + tid];
         P.glob[GK_EIG_GLOB_SUMF + tid] = s;
     }
-    if (prof && tid == 0) atomicAdd((unsigned long long *)P.prof + 5, (unsigned long long)(clock64() - kstart));
+    if (prof && tid == 0) atomicAdd((unsigned long long *)P.prof + 6, (unsigned long long)(gk_clock() - kstart));
 }
