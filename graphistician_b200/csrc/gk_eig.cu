@@ -3,7 +3,7 @@
 #include <string.h>
 #include <stdlib.h>
 #include <algorithm>
-#include "gk_eig_fast.cuh"
+#include "gk_eig_mf.cuh"
 
 struct gk_eig {
     gk_net *net = nullptr;
@@ -16,6 +16,7 @@ struct gk_eig {
     double *scal = nullptr;            // small device scalars (sum of omega, ...)
     double *out_prec = nullptr, *out_h = nullptr;
     double *G = nullptr, *spart = nullptr; void *dphi = nullptr;   // running-G sweep (gk_eig_fast.cuh): [ld][PA], [NB][PA], [64][PA]
+    double *mfMu = nullptr, *mfSig = nullptr, *mfLin = nullptr, *mfPhi = nullptr, *mfSmall = nullptr, *mfPart = nullptr;   // mean-field q (K11)
     long long *prof = nullptr;         // debug cycle counters of k_eig_seq3 (env GK_EIG_PROF=1)
     int use_fast = 1;                  // unsharded sweeps use the running-G form (GK_EIG_OPT_FAST_SWEEP)
     double mu0 = 0.0;
@@ -75,7 +76,8 @@ extern "C" int gk_eig_destroy(gk_ctx *ctx, gk_eig *e) {
     if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
     cudaFree(e->S); cudaFree(e->F); cudaFree(e->z); cudaFree(e->lmbda); cudaFree(e->acc); cudaFree(e->glob);
     cudaFree(e->part); cudaFree(e->scal); cudaFree(e->out_prec); cudaFree(e->out_h);
-    cudaFree(e->G); cudaFree(e->dphi); cudaFree(e->spart);
+    cudaFree(e->G); cudaFree(e->dphi); cudaFree(e->spart); cudaFree(e->prof);
+    cudaFree(e->mfMu); cudaFree(e->mfSig); cudaFree(e->mfLin); cudaFree(e->mfPhi); cudaFree(e->mfSmall); cudaFree(e->mfPart);
     delete e;
     return GK_OK;
 }
@@ -390,22 +392,21 @@ static int launch_seq4_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sig
     return GK_OK;
 }
 
+// one full contraction G[n] = sum_m X[m,n] Phi_m over the whole network (Phi from e->F, or given rows phi_given)
 template <typename T, int D>
-static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
+static int launch_gfull(gk_ctx *ctx, gk_eig *e, const double *phi_given, size_t *smem_push_out) {
     typedef typename gk_eacc<T>::type ACC;
     constexpr int PA = gk_edim<D>::PA, PH = gk_edim<D>::PH, NB = gk_eig_nb<T>::NB;
     gk_net *net = e->net;
     const int N = e->N, npad = net->ld, strips = npad / GK_EF_COLS;
     if (!e->G) {
         GK_CUDA(ctx, cudaMalloc(&e->G, (size_t)npad * GK_EIG_PA_MAX * 8));
-        GK_CUDA(ctx, cudaMalloc(&e->dphi, (size_t)GK_EIG_NBMAX * GK_EIG_PA_MAX * 8));       // U [NB][PA]
+        GK_CUDA(ctx, cudaMalloc(&e->dphi, (size_t)GK_EIG_NBMAX * GK_EIG_PA_MAX * 8));       // ACC [NB][PA]
         GK_CUDA(ctx, cudaMalloc(&e->spart, (size_t)64 * GK_EIG_PA_MAX * 8));
         if (getenv("GK_EIG_PROF")) GK_CUDA(ctx, cudaMalloc(&e->prof, 16 * 8));
     }
-    if (e->prof) {
-        GK_CUDA(ctx, cudaMemsetAsync(e->prof, 0, 16 * 8, ctx->stream));
-    }
-    // full contraction: row chunks so that the grid covers >= 2 waves of 2 CTAs/SM
+    if (e->prof) GK_CUDA(ctx, cudaMemsetAsync(e->prof, 0, 16 * 8, ctx->stream));
+    // row chunks so that the grid covers >= 2 waves of 2 CTAs/SM
     int nchunks = std::max(1, std::min(16, (4 * ctx->num_sms + strips - 1) / strips));
     int chunk_rows = ((N + nchunks - 1) / nchunks + GK_EF_PIECE - 1) / GK_EF_PIECE * GK_EF_PIECE;
     nchunks = (N + chunk_rows - 1) / chunk_rows;
@@ -422,23 +423,42 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
     }
     gk_time_begin(ctx, 3, (double)N * N * (sizeof(T) + 1.0));
     k_eig_gfull<T, D><<<dim3(strips, nchunks), GK_EF_THREADS, smem_full, ctx->stream>>>(
-        (const T *)e->S, net->Asym, net->ld, N, e->F, chunk_rows, npad, partial, e->probit);
+        (const T *)e->S, net->Asym, net->ld, N, e->F, phi_given, chunk_rows, npad, partial, e->probit);
     gk_time_end(ctx, 3);
     GK_CHECK_LAUNCH(ctx);
     const size_t per_chunk = (size_t)npad * PA;
     k_eig_greduce<ACC><<<(int)std::min<size_t>((per_chunk + 255) / 256, (size_t)ctx->num_sms * 8), 256, 0, ctx->stream>>>(
         partial, nchunks, per_chunk, e->G);
     GK_CHECK_LAUNCH(ctx);
+    if (smem_push_out) *smem_push_out = smem_push;
+    return GK_OK;
+}
+
+template <typename T, int D>
+static int launch_push(gk_ctx *ctx, gk_eig *e, int n0, int nb, size_t smem_push) {
+    typedef typename gk_eacc<T>::type ACC;
+    gk_net *net = e->net;
+    gk_time_begin(ctx, 3, (double)nb * e->N * (sizeof(T) + 1.0));
+    k_eig_push<T, D><<<net->ld / GK_EF_COLS, GK_EF_THREADS, smem_push, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, e->N,
+                                                                                    (const ACC *)e->dphi, n0, nb, e->G, e->probit);
+    gk_time_end(ctx, 3);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+template <typename T, int D>
+static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
+    constexpr int NB = gk_eig_nb<T>::NB;
+    const int N = e->N;
+    size_t smem_push = 0;
+    int rc0 = launch_gfull<T, D>(ctx, e, nullptr, &smem_push);
+    if (rc0) return rc0;
     for (int n0 = 0; n0 < N; n0 += NB) {
         const int nb = std::min(NB, N - n0);
         int rc = (sizeof(T) == 4 && !e->chol_f64) ? launch_seq4_ch<T, float, D>(ctx, e, n0, nb, inv_sigma_F)
                                                   : launch_seq4_ch<T, double, D>(ctx, e, n0, nb, inv_sigma_F);
         if (rc) return rc;
-        gk_time_begin(ctx, 3, (double)nb * N * (sizeof(T) + 1.0));
-        k_eig_push<T, D><<<strips, GK_EF_THREADS, smem_push, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, N, (const ACC *)e->dphi, n0, nb,
-                                                                           e->G, e->probit);
-        gk_time_end(ctx, 3);
-        GK_CHECK_LAUNCH(ctx);
+        if ((rc = launch_push<T, D>(ctx, e, n0, nb, smem_push))) return rc;
     }
     k_eig_gstats<D><<<64, 512, 0, ctx->stream>>>(e->G, e->F, N, e->glob, e->probit, e->spart);
     GK_CHECK_LAUNCH(ctx);
@@ -619,4 +639,171 @@ extern "C" int gk_eig_log_likelihood(gk_ctx *ctx, gk_eig *e, int link, double *l
     GK_CUDA(ctx, cudaMemcpyAsync(ll, e->scal + 1, 8, cudaMemcpyDeviceToHost, ctx->stream));
     GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     return GK_OK;
+}
+
+// ---------------------------------------------------------------------------------------------
+// K11: mean-field logistic eigenmodel (eigenmodel.py:998-1157).  Unsharded networks.
+// Device state of q: e->mfMu (N x D), e->mfSig (N x D x D), e->mfPhi (N x PA = E[ff^T] packed | lin | lin).
+// ---------------------------------------------------------------------------------------------
+static int mf_ensure(gk_ctx *ctx, gk_eig *e) {
+    if (e->net->row0 != 0 || e->net->nrows != e->net->N) return gk_fail(ctx, GK_EINVAL, "the mean-field eigenmodel path needs an unsharded network");
+    if (!e->mfMu) {
+        const size_t N = e->N, D = e->D;
+        GK_CUDA(ctx, cudaMalloc(&e->mfMu, N * D * 8));
+        GK_CUDA(ctx, cudaMalloc(&e->mfSig, N * D * D * 8));
+        GK_CUDA(ctx, cudaMalloc(&e->mfLin, N * D * 8));
+        GK_CUDA(ctx, cudaMalloc(&e->mfPhi, N * GK_EIG_PA_MAX * 8));
+        GK_CUDA(ctx, cudaMalloc(&e->mfSmall, 256 * 8));
+        const size_t nt = (N + GK_MFE_TILE - 1) / GK_MFE_TILE;
+        GK_CUDA(ctx, cudaMalloc(&e->mfPart, 2 * nt * nt * 8));
+    }
+    return GK_OK;
+}
+
+template <typename T, int D>
+static int mf_build_phi(gk_ctx *ctx, gk_eig *e, const double *mu, const double *Sig, const double *Flin) {
+    const size_t N = e->N;
+    GK_CUDA(ctx, cudaMemcpyAsync(e->mfMu, mu, N * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(e->mfSig, Sig, N * D * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    if (Flin) GK_CUDA(ctx, cudaMemcpyAsync(e->mfLin, Flin, N * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    k_eig_mf_phi<D><<<ctx->num_sms * 4, 256, 0, ctx->stream>>>(e->mfMu, e->mfSig, Flin ? e->mfLin : nullptr, e->N, e->mfPhi);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+template <typename T, int D>
+static int mf_omega_T(gk_ctx *ctx, gk_eig *e, const double *mu, const double *Sig, const double *wq, const double *lam, double mu0,
+                      double sig_mu0, int n_samples, uint64_t seed, double *sums) {
+    constexpr int Q = gk_edim<D>::Q;
+    int rc = mf_build_phi<T, D>(ctx, e, mu, Sig, nullptr);
+    if (rc) return rc;
+    GK_CUDA(ctx, cudaMemcpyAsync(e->mfSmall, wq, Q * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(e->mfSmall + 64, lam, D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    const int nt = (e->N + GK_MFE_TILE - 1) / GK_MFE_TILE;
+    gk_time_begin(ctx, 2, (double)e->N * e->N * sizeof(T));
+    k_eig_mf_omega<T, D><<<dim3(nt, nt), 256, 0, ctx->stream>>>((T *)e->S, e->net->ld, e->N, e->mfPhi, e->mfSmall, e->mfSmall + 64, mu0,
+                                                                 sig_mu0, n_samples, seed, e->mfPart);
+    gk_time_end(ctx, 2);
+    GK_CHECK_LAUNCH(ctx);
+    k_sum_partials<<<1, 1024, 0, ctx->stream>>>(e->mfPart, nt * nt, e->mfSmall + 128);
+    GK_CHECK_LAUNCH(ctx);
+    k_sum_partials<<<1, 1024, 0, ctx->stream>>>(e->mfPart + (size_t)nt * nt, nt * nt, e->mfSmall + 129);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaMemcpyAsync(sums, e->mfSmall + 128, 16, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    e->have_S = true; e->probit = 0;
+    return GK_OK;
+}
+
+extern "C" int gk_eig_mf_omega(gk_ctx *ctx, gk_eig *e, const double *mf_mu_F, const double *mf_Sigma_F, const double *E_llT,
+                               const double *E_lmbda, double mf_mu_mu0, double mf_sigma_mu0, int n_samples, uint64_t seed,
+                               double *sum_EO, double *sum_EO_FdotF) {
+    if (!ctx || !e || !mf_mu_F || !mf_Sigma_F || !E_llT || !E_lmbda) return GK_EINVAL;
+    if (n_samples < 1) return gk_fail(ctx, GK_EINVAL, "n_samples must be positive");
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = mf_ensure(ctx, e);
+    if (rc) return rc;
+    rc = gk_net_ensure_asym(ctx, e->net);
+    if (rc) return rc;
+    const int D = e->D;
+    double wq[GK_EIG_MAXD * (GK_EIG_MAXD + 1) / 2], sums[2];
+    for (int a = 0; a < D; ++a)
+        for (int b = a; b < D; ++b) wq[gk_qidx(D, a, b)] = (a == b ? 1.0 : 2.0) * 0.5 * (E_llT[a * D + b] + E_llT[b * D + a]);
+    rc = e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, D, mf_omega_T, ctx, e, mf_mu_F, mf_Sigma_F, wq, E_lmbda, mf_mu_mu0, mf_sigma_mu0, n_samples, seed, sums)
+                            : GK_EIG_SWITCH_D(double, D, mf_omega_T, ctx, e, mf_mu_F, mf_Sigma_F, wq, E_lmbda, mf_mu_mu0, mf_sigma_mu0, n_samples, seed, sums);
+    if (rc) return rc;
+    if (sum_EO) *sum_EO = sums[0];
+    if (sum_EO_FdotF) *sum_EO_FdotF = sums[1];
+    return GK_OK;
+}
+
+template <typename T, int D>
+static int mf_update_F_T(gk_ctx *ctx, gk_eig *e, double *mu, double *Sig, const double *Flin, const double *llT, const double *lam,
+                         double mu0, double sigma_F, double stepsize, double *out_prec, double *out_h) {
+    constexpr int NB = gk_eig_nb<T>::NB;
+    const size_t N = e->N;
+    gk_net *net = e->net;
+    int rc = mf_build_phi<T, D>(ctx, e, mu, Sig, Flin);
+    if (rc) return rc;
+    GK_CUDA(ctx, cudaMemcpyAsync(e->mfSmall, llT, D * D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(e->mfSmall + 64, lam, D * 8, cudaMemcpyHostToDevice, ctx->stream));
+    if (out_prec && !e->out_prec) GK_CUDA(ctx, cudaMalloc(&e->out_prec, N * D * D * 8));
+    if (out_h && !e->out_h) GK_CUDA(ctx, cudaMalloc(&e->out_h, N * D * 8));
+    // running column sums of the linear features (the "- sum_m f_m" of kappa + kappa^T = Asym - 1)
+    k_eig_colsum<<<1, 1024, 0, ctx->stream>>>(Flin ? e->mfLin : e->mfMu, e->N, D, e->glob + GK_EIG_GLOB_SUMF);
+    GK_CHECK_LAUNCH(ctx);
+    size_t smem_push = 0;
+    if ((rc = launch_gfull<T, D>(ctx, e, e->mfPhi, &smem_push))) return rc;
+    const size_t smem = gk_eig_mfseq_smem<T, D>();
+    static bool attr_set = false;
+    if (!attr_set) {
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_mf_seq<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        attr_set = true;
+    }
+    for (int n0 = 0; n0 < e->N; n0 += NB) {
+        const int nb = std::min(NB, e->N - n0);
+        gk_eig_mfseq_params P;
+        P.n0 = n0; P.nb = nb; P.N = e->N;
+        P.Sblk = (const T *)e->S + (size_t)n0 * net->ld + n0; P.ldS = net->ld;
+        P.Ablk = net->Asym + (size_t)n0 * net->ld + n0; P.ldA = net->ld;
+        P.G = e->G; P.Phi = e->mfPhi; P.mu = e->mfMu; P.Sig = e->mfSig; P.llT = e->mfSmall; P.lam = e->mfSmall + 64;
+        P.mu0 = mu0; P.inv_sigma_F = 1.0 / sigma_F; P.stepsize = stepsize; P.track = Flin ? 0 : 1;
+        P.dphi = e->dphi; P.glob = e->glob; P.out_prec = out_prec ? e->out_prec : nullptr; P.out_h = out_h ? e->out_h : nullptr;
+        gk_time_begin(ctx, 5, 0.0);
+        k_eig_mf_seq<T, D><<<1, 256, smem, ctx->stream>>>(P);
+        gk_time_end(ctx, 5);
+        GK_CHECK_LAUNCH(ctx);
+        if ((rc = launch_push<T, D>(ctx, e, n0, nb, smem_push))) return rc;
+    }
+    GK_CUDA(ctx, cudaMemcpyAsync(mu, e->mfMu, N * D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(Sig, e->mfSig, N * D * D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_prec) GK_CUDA(ctx, cudaMemcpyAsync(out_prec, e->out_prec, N * D * D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_h) GK_CUDA(ctx, cudaMemcpyAsync(out_h, e->out_h, N * D * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}
+
+extern "C" int gk_eig_mf_update_F(gk_ctx *ctx, gk_eig *e, double *mf_mu_F, double *mf_Sigma_F, const double *F_lin,
+                                  const double *E_llT, const double *E_lmbda, double E_mu0, double sigma_F, double stepsize,
+                                  double *out_prec, double *out_h) {
+    if (!ctx || !e || !mf_mu_F || !mf_Sigma_F || !E_llT || !E_lmbda) return GK_EINVAL;
+    if (!e->have_S || e->probit) return gk_fail(ctx, GK_EINVAL, "gk_eig_mf_update_F: call gk_eig_mf_omega or gk_eig_set_S first");
+    if (!(sigma_F > 0) || !(stepsize >= 0.0 && stepsize <= 1.0)) return gk_fail(ctx, GK_EINVAL, "bad sigma_F / stepsize");
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = mf_ensure(ctx, e);
+    if (rc) return rc;
+    const int D = e->D;
+    return e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, D, mf_update_F_T, ctx, e, mf_mu_F, mf_Sigma_F, F_lin, E_llT, E_lmbda, E_mu0, sigma_F, stepsize, out_prec, out_h)
+                              : GK_EIG_SWITCH_D(double, D, mf_update_F_T, ctx, e, mf_mu_F, mf_Sigma_F, F_lin, E_llT, E_lmbda, E_mu0, sigma_F, stepsize, out_prec, out_h);
+}
+
+template <typename T, int D>
+static int mf_pair_stats_T(gk_ctx *ctx, gk_eig *e, const double *mu, const double *Sig, double *stats) {
+    int rc = mf_build_phi<T, D>(ctx, e, mu, Sig, nullptr);
+    if (rc) return rc;
+    k_eig_colsum<<<1, 1024, 0, ctx->stream>>>(e->mfMu, e->N, D, e->glob + GK_EIG_GLOB_SUMF);
+    GK_CHECK_LAUNCH(ctx);
+    if ((rc = launch_gfull<T, D>(ctx, e, e->mfPhi, nullptr))) return rc;
+    k_eig_gstats_phi<D><<<64, 512, 0, ctx->stream>>>(e->G, e->mfPhi, e->N, e->glob, e->spart);
+    GK_CHECK_LAUNCH(ctx);
+    k_eig_gstats_final<D><<<1, 64, 0, ctx->stream>>>(e->spart, 64, e->glob);
+    GK_CHECK_LAUNCH(ctx);
+    double g[GK_EIG_GLOB_LEN];
+    GK_CUDA(ctx, cudaMemcpyAsync(g, e->glob, sizeof g, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int a = 0; a < D; ++a)
+        for (int b = 0; b < D; ++b) stats[a * D + b] = g[GK_EIG_GLOB_PQ + gk_qidx(D, std::min(a, b), std::max(a, b))];
+    for (int a = 0; a < D; ++a) { stats[D * D + a] = g[GK_EIG_GLOB_HS + a]; stats[D * D + D + a] = g[GK_EIG_GLOB_HK + a]; }
+    return GK_OK;
+}
+
+extern "C" int gk_eig_mf_pair_stats(gk_ctx *ctx, gk_eig *e, const double *mf_mu_F, const double *mf_Sigma_F, double *stats) {
+    if (!ctx || !e || !mf_mu_F || !mf_Sigma_F || !stats) return GK_EINVAL;
+    if (!e->have_S || e->probit) return gk_fail(ctx, GK_EINVAL, "gk_eig_mf_pair_stats: call gk_eig_mf_omega or gk_eig_set_S first");
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    int rc = mf_ensure(ctx, e);
+    if (rc) return rc;
+    const int D = e->D;
+    return e->dtype == GK_F32 ? GK_EIG_SWITCH_D(float, D, mf_pair_stats_T, ctx, e, mf_mu_F, mf_Sigma_F, stats)
+                              : GK_EIG_SWITCH_D(double, D, mf_pair_stats_T, ctx, e, mf_mu_F, mf_Sigma_F, stats);
 }

@@ -110,8 +110,8 @@ __device__ __forceinline__ void gk_ef_fold(ACC (&acc)[2][NP], ACC *__restrict__ 
 // ---------------------------------------------------------------------------------------------------
 template <typename T, int D>
 __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_gfull(const T *__restrict__ S, const uint8_t *__restrict__ Asym, int ld,
-                                                                 int N, const double *__restrict__ F, int chunk_rows, int npad,
-                                                                 typename gk_eacc<T>::type *__restrict__ partial, int probit) {
+                                                                 int N, const double *__restrict__ F, const double *__restrict__ PhiG, int chunk_rows,
+                                                                 int npad, typename gk_eacc<T>::type *__restrict__ partial, int probit) {
     typedef typename gk_eacc<T>::type ACC;
     constexpr int PA = gk_edim<D>::PA, PH = gk_edim<D>::PH;
     extern __shared__ __align__(16) unsigned char smem_raw[];
@@ -127,7 +127,9 @@ __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_gfull(const T *__restr
     for (int rp = r0; rp < r1; rp += GK_EF_PIECE) {
         const int mrows = min(GK_EF_PIECE, r1 - rp);
         __syncthreads();
-        if (tid < mrows) {
+        if (PhiG) {                                       // mean-field form: Phi rows given (E[f f^T] | E[f] | E[f])
+            for (int t = tid; t < mrows * PA; t += GK_EF_THREADS) phi[t] = (ACC)PhiG[(size_t)rp * PA + t];
+        } else if (tid < mrows) {
             double f[D];
 #pragma unroll
             for (int d = 0; d < D; ++d) f[d] = F[(size_t)(rp + tid) * D + d];

@@ -202,6 +202,39 @@ class DeviceEigenmodel:
         self.ctx.check(self.ctx.lib.gk_eig_get_S(self.ctx.h, self.h, ptr(S)))
         return S
 
+    # ---- K11 (mean field) ----------------------------------------------------------------------------
+    def mf_omega(self, mf_mu_F, mf_Sigma_F, E_llT, E_lmbda, mf_mu_mu0, mf_sigma_mu0, n_samples, seed):
+        """S <- E_O + E_O^T by Monte Carlo; returns (sum E_O over all N^2 entries, sum_{n != m} E_O * E_FdotF)."""
+        assert self.comm is None, "the mean-field eigenmodel path runs on single-rank networks"
+        args = [np.ascontiguousarray(a, dtype=np.float64) for a in (mf_mu_F, mf_Sigma_F, E_llT, E_lmbda)]
+        assert args[0].shape == (self.N, self.D) and args[1].shape == (self.N, self.D, self.D)
+        s0, s1 = ctypes.c_double(0.0), ctypes.c_double(0.0)
+        self.ctx.check(self.ctx.lib.gk_eig_mf_omega(self.ctx.h, self.h, *[ptr(a) for a in args], float(mf_mu_mu0),
+                                                   float(mf_sigma_mu0), int(n_samples), ctypes.c_uint64(int(seed)),
+                                                   ctypes.byref(s0), ctypes.byref(s1)))
+        return s0.value, s1.value
+
+    def mf_update_F(self, mf_mu_F, mf_Sigma_F, F_lin, E_llT, E_lmbda, E_mu0, sigma_F, stepsize=1.0, want_conditionals=False):
+        """Serial mean-field update of q(F).  Returns (mf_mu_F, mf_Sigma_F, prec or None, h or None)."""
+        assert self.comm is None, "the mean-field eigenmodel path runs on single-rank networks"
+        mu = np.array(mf_mu_F, dtype=np.float64, copy=True, order="C")
+        Sig = np.array(mf_Sigma_F, dtype=np.float64, copy=True, order="C")
+        lin = None if F_lin is None else np.ascontiguousarray(F_lin, dtype=np.float64)
+        llT = np.ascontiguousarray(E_llT, dtype=np.float64); lam = np.ascontiguousarray(E_lmbda, dtype=np.float64)
+        D = self.D
+        prec = np.empty((self.N, D, D)) if want_conditionals else None
+        h = np.empty((self.N, D)) if want_conditionals else None
+        self.ctx.check(self.ctx.lib.gk_eig_mf_update_F(self.ctx.h, self.h, ptr(mu), ptr(Sig), ptr(lin), ptr(llT), ptr(lam),
+                                                      float(E_mu0), float(sigma_F), float(stepsize), ptr(prec), ptr(h)))
+        return mu, Sig, prec, h
+
+    def mf_pair_stats(self, mf_mu_F, mf_Sigma_F):
+        mu = np.ascontiguousarray(mf_mu_F, dtype=np.float64); Sig = np.ascontiguousarray(mf_Sigma_F, dtype=np.float64)
+        D = self.D
+        st = np.zeros(D * D + 2 * D)
+        self.ctx.check(self.ctx.lib.gk_eig_mf_pair_stats(self.ctx.h, self.h, ptr(mu), ptr(Sig), ptr(st)))
+        return dict(Pq=st[:D * D].reshape(D, D), hS=st[D * D:D * D + D], hK=st[D * D + D:])
+
     def resample_F(self, sigma_F, normals, want_conditionals=False):
         """K4+K5.  Returns (F_new, stats dict, prec or None, h or None)."""
         z = np.ascontiguousarray(normals, dtype=np.float64)

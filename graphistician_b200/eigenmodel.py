@@ -198,9 +198,155 @@ class _GibbsLogisticEigenmodel(_LogisticEigenmodelBase):
         self.lmbda = np.random.multivariate_normal(post_cov.dot(h), post_cov)
 
 
-class LogisticEigenmodel(_GibbsLogisticEigenmodel):
-    """eigenmodel.py:1313 (Gibbs part; the mean-field mixin is a later row of SURVEY.md 8a)."""
-    pass
+class _MeanFieldLogisticEigenModel(_LogisticEigenmodelBase):
+    """eigenmodel.py:968-1311.  Fixed networks (E_A = A).  The N^2 work runs in libgk:
+      _meanfieldupdate_Omega  <- gk_eig_mf_omega      (:1055-1064; N_samples activations per element, on the device)
+      _meanfieldupdate_F      <- gk_eig_mf_update_F   (:1090-1124; serial in n)
+      mu0 / lmbda sums        <- the omega kernel's tile sums, gk_eig_mf_pair_stats (:1066-1088, 1126-1157)
+    `literal_h_features` (default True) keeps a reference quirk: _meanfieldupdate_F builds h_n from `self.F` (the Gibbs
+    sample, :1113-1114) rather than from mf_mu_F; False uses mf_mu_F, following the update."""
+    literal_h_features = True
+    mf_n_samples = 1000                      # :1061
+
+    def _mf_init(self):
+        """:969-985 (called by the concrete class after the Gibbs constructor)."""
+        N, D = self.N, self.D
+        self.mf_mu_Z = np.zeros((N, N)) if N <= 4096 else None     # never read by the reference's updates
+        self.mf_mu_mu0 = self.mu_mu_0
+        self.mf_sigma_mu0 = self.sigma_mu0
+        self.mf_mu_F = np.sqrt(self.sigma_F) * np.random.randn(N, D)
+        self.mf_Sigma_F = np.tile((self.sigma_F * np.eye(D))[None, :, :], [N, 1, 1])
+        if self.lmbda_given:
+            self.mf_mu_lmbda = self.lmbda.copy()
+            self.mf_Sigma_lmbda = 1e-16 * np.eye(D)
+        else:
+            self.mf_mu_lmbda = self.mu_lmbda.copy()
+            self.mf_Sigma_lmbda = self.sigma_lmbda * np.eye(D)
+        self._mf_seed = int(np.random.randint(0, 2 ** 31 - 1))
+        self._mf_calls = 0
+
+    def init_with_gibbs(self, gibbs_model):
+        """:988-996"""
+        self.mf_mu_lmbda = gibbs_model.lmbda.copy()
+        self.mf_Sigma_lmbda = 1e-4 * np.eye(self.D)
+        self.mf_mu_mu0 = gibbs_model.mu_0
+        self.mf_sigma_mu0 = 1e-4
+        self.mf_mu_F = gibbs_model.F.copy()
+        self.mf_Sigma_F = np.tile((1e-4 * np.eye(self.D))[None, :, :], [self.N, 1, 1])
+
+    # ---- the updates ----------------------------------------------------------------------------------------
+    def meanfieldupdate(self, network, stepsize_mu0=1.0):
+        """:998-1022 (order: Omega, mu0, F, lmbda)."""
+        network = as_network(network)
+        sums = self._meanfieldupdate_Omega(network)
+        self._meanfieldupdate_mu0(network, sums, stepsize=stepsize_mu0)
+        self._meanfieldupdate_F(network)
+        if not self.lmbda_given:
+            self._meanfieldupdate_lmbda(network)
+
+    def svi_step(self, network, minibatchfrac, stepsize):
+        """:1024-1053: the stepsize reaches the mu0 update only."""
+        self.meanfieldupdate(network, stepsize_mu0=stepsize)
+
+    def _meanfieldupdate_Omega(self, network):
+        """:1055-1064.  Leaves S = E_O + E_O^T on the device; returns (sum E_O, sum_{n != m} E_O * E_FdotF)."""
+        dev = self._device_state(network)
+        self._mf_calls += 1
+        return dev.mf_omega(self.mf_mu_F, self.mf_Sigma_F, self.mf_expected_llT(), self.mf_mu_lmbda, self.mf_mu_mu0,
+                            self.mf_sigma_mu0, self.mf_n_samples, (self._mf_seed + 7919 * self._mf_calls) % (2 ** 63))
+
+    def _sum_kappa(self, network):
+        """sum of kappa(E_A) = A - 1/2 over all N^2 entries (:1083)."""
+        net = network.device(self.dtype)
+        n_edge, _, _ = net.block_stats(np.zeros(self.N, np.int32), 1)
+        return float(n_edge[0, 0]) + float(np.count_nonzero(net.diagA)) - 0.5 * self.N * self.N
+
+    def _meanfieldupdate_mu0(self, network, sums, stepsize=1.0):
+        """:1066-1088"""
+        sum_EO, sum_EOF = sums
+        post_prec = 1.0 / self.sigma_mu0 + sum_EO
+        post_mean_dot_prec = self.mu_mu_0 / self.sigma_mu0 + self._sum_kappa(network) - sum_EOF
+        self.mf_sigma_mu0 = (1 - stepsize) * self.mf_sigma_mu0 + stepsize * 1.0 / post_prec
+        self.mf_mu_mu0 = (1 - stepsize) * self.mf_mu_mu0 + stepsize * self.mf_sigma_mu0 * post_mean_dot_prec
+
+    def _meanfieldupdate_F(self, network, stepsize=1.0, want_conditionals=False):
+        """:1090-1124"""
+        dev = self._device_state(network)
+        F_lin = self.F if self.literal_h_features else None
+        self.mf_mu_F, self.mf_Sigma_F, prec, h = dev.mf_update_F(
+            self.mf_mu_F, self.mf_Sigma_F, F_lin, self.mf_expected_llT(), self.mf_mu_lmbda, self.mf_mu_mu0, self.sigma_F,
+            stepsize, want_conditionals)
+        assert np.all(np.isfinite(self.mf_mu_F)) and np.all(np.isfinite(self.mf_Sigma_F))
+        return prec, h
+
+    def _meanfieldupdate_lmbda(self, network, stepsize=1.0):
+        """:1126-1157"""
+        dev = self._device_state(network)
+        st = dev.mf_pair_stats(self.mf_mu_F, self.mf_Sigma_F)
+        post_prec = 1.0 / self.sigma_lmbda * np.eye(self.D) + st["Pq"]
+        post_mean_dot_prec = self.mu_lmbda / self.sigma_lmbda + st["hK"] - self.mf_mu_mu0 * st["hS"]
+        self.mf_Sigma_lmbda = (1.0 - stepsize) * self.mf_Sigma_lmbda + stepsize * np.linalg.inv(post_prec)
+        self.mf_mu_lmbda = (1.0 - stepsize) * self.mf_mu_lmbda + stepsize * self.mf_Sigma_lmbda.dot(post_mean_dot_prec)
+
+    # ---- expectations (:1159-1248; N x N on the host: reporting only) --------------------------------------------
+    def mf_expected_mu(self):
+        E_mu = self.mf_mu_mu0 + (self.mf_mu_F * self.mf_mu_lmbda[None, :]).dot(self.mf_mu_F.T)
+        np.fill_diagonal(E_mu, self.mf_mu_mu0)
+        return E_mu
+
+    def mf_expected_mu0sq(self):
+        return self.mf_sigma_mu0 + self.mf_mu_mu0 ** 2
+
+    def mf_expected_ffT(self, n):
+        return self.mf_Sigma_F[n, :, :] + np.outer(self.mf_mu_F[n, :], self.mf_mu_F[n, :])
+
+    def mf_expected_llT(self):
+        return self.mf_Sigma_lmbda + np.outer(self.mf_mu_lmbda, self.mf_mu_lmbda)
+
+    def mf_expected_musq(self):
+        N, D = self.N, self.D
+        E = np.zeros((N, N)) + self.mf_expected_mu0sq()
+        E += 2 * self.mf_mu_mu0 * (self.mf_mu_F * self.mf_mu_lmbda[None, :]).dot(self.mf_mu_F.T)
+        ffT = (self.mf_Sigma_F + self.mf_mu_F[:, :, None] * self.mf_mu_F[:, None, :]).reshape(N, D * D)
+        E += (ffT * self.mf_expected_llT().reshape(D * D)[None, :]).dot(ffT.T)
+        np.fill_diagonal(E, self.mf_expected_mu0sq())
+        return E
+
+    def mf_variance_mu(self):
+        return self.mf_expected_musq() - self.mf_expected_mu() ** 2
+
+    def mf_sample_mus(self, N_samples=10):
+        E_mu = self.mf_expected_mu()[None, :, :]
+        std_mu = np.sqrt(self.mf_variance_mu())[None, :, :]
+        return E_mu + std_mu * np.random.randn(N_samples, self.N, self.N)
+
+    def mf_expected_log_p(self):
+        Ps = np.clip(logistic(self.mf_sample_mus()), 1e-16, 1 - 1e-16)
+        return np.log(Ps).mean(0)
+
+    def mf_expected_log_notp(self):
+        Ps = np.clip(logistic(self.mf_sample_mus()), 1e-16, 1 - 1e-16)
+        return np.log(1 - Ps).mean(0)
+
+    def expected_log_likelihood(self, network):
+        A = as_network(network).A
+        return (A * self.mf_expected_log_p() + (1 - A) * self.mf_expected_log_notp()).sum()
+
+    def resample_from_mf(self):
+        """:1300-1311"""
+        for n in range(self.N):
+            self.F[n, :] = np.random.multivariate_normal(self.mf_mu_F[n, :], self.mf_Sigma_F[n, :, :])
+        self.mu_0 = np.random.normal(self.mf_mu_mu0, np.sqrt(self.mf_sigma_mu0))
+        if not self.lmbda_given:
+            self.lmbda = np.random.multivariate_normal(self.mf_mu_lmbda, self.mf_Sigma_lmbda)
+
+
+class LogisticEigenmodel(_GibbsLogisticEigenmodel, _MeanFieldLogisticEigenModel):
+    """eigenmodel.py:1313."""
+
+    def __init__(self, N, D, **kwargs):
+        super(LogisticEigenmodel, self).__init__(N, D, **kwargs)
+        self._mf_init()
 
 
 # ------------------------------------------------------------------------------------------------------

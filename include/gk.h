@@ -190,6 +190,29 @@ int gk_latent_hmc_pass(gk_ctx *ctx, gk_latent *lat, double *acc_dev);
 int gk_latent_hmc_advance(gk_ctx *ctx, gk_latent *lat, const double *acc_dev);
 int gk_latent_hmc_end(gk_ctx *ctx, gk_latent *lat, double log_u, int *accepted, double *log_ratio);
 
+/* ---- K11: mean-field logistic eigenmodel ------------------------------------------------
+ * Unsharded networks.  q(f_n) = N(mf_mu_F[n], mf_Sigma_F[n]) (N x D, N x D x D row-major), q(lmbda) through E_lmbda (D) and
+ * E_llT (D x D), q(mu_0) = N(mf_mu_mu0, mf_sigma_mu0).
+ * gk_eig_mf_omega replaces eigenmodel.py:1055-1064 (_meanfieldupdate_Omega) fused with mf_expected_mu / mf_expected_musq /
+ * mf_sample_mus (:1177-1248): per directed entry n_samples activations z ~ N(E[mu], Var[mu]) from a counter-based generator
+ * keyed by (seed, tile, lane), E_O = 1/2 mean tanh(z/2)/z; stores S = E_O + E_O^T (zero diagonal) in the state's S buffer.
+ * sum_EO = sum of ALL N^2 entries of E_O (the precision term of :1076); sum_EO_FdotF = sum_{n != m} E_O[n,m] E_FdotF[n,m]
+ * (:1079-1083).  Both optional. */
+int gk_eig_mf_omega(gk_ctx *ctx, gk_eig *eig, const double *mf_mu_F, const double *mf_Sigma_F, const double *E_llT,
+                    const double *E_lmbda, double mf_mu_mu0, double mf_sigma_mu0, int n_samples, uint64_t seed,
+                    double *sum_EO, double *sum_EO_FdotF);
+/* gk_eig_mf_update_F replaces eigenmodel.py:1090-1124 (_meanfieldupdate_F), same serial semantics: node n's q is recomputed
+ * from the CURRENT q of every other node, in index order:  prec_n = I/sigma_F + E_llT o sum_m S[n,m] E[f_m f_m^T],
+ * h_n = E_lmbda o sum_m (A[n,m] + A[m,n] - 1 - E_mu0 S[n,m]) lin_m,  Sigma_n <- (1-stepsize) Sigma_n + stepsize prec_n^-1,
+ * mu_n <- (1-stepsize) mu_n + stepsize Sigma_n h_n.  lin = F_lin (N x D; the reference uses self.F, the Gibbs sample,
+ * :1113-1114) or, when F_lin == NULL, mf_mu_F itself as it is updated.  out_prec (N x D x D) / out_h (N x D) optional:
+ * the conditionals at the moment each node was updated.  S comes from gk_eig_mf_omega or gk_eig_set_S. */
+int gk_eig_mf_update_F(gk_ctx *ctx, gk_eig *eig, double *mf_mu_F, double *mf_Sigma_F, const double *F_lin, const double *E_llT,
+                       const double *E_lmbda, double E_mu0, double sigma_F, double stepsize, double *out_prec, double *out_h);
+/* pair sums over n1 < n2 of eigenmodel.py:1126-1157 (_meanfieldupdate_lmbda): stats = Pq[D*D] | hS[D] | hK[D] with
+ * Pq[a,b] = sum S E[f1 f1^T][a,b] E[f2 f2^T][a,b],  hS[a] = sum S mu1a mu2a,  hK[a] = sum (A12 + A21 - 1) mu1a mu2a. */
+int gk_eig_mf_pair_stats(gk_ctx *ctx, gk_eig *eig, const double *mf_mu_F, const double *mf_Sigma_F, double *stats);
+
 /* ---- K10: mean-field SBM ---------------------------------------------------------
  * Fixed networks only (E_A = A, E_W = W, E_WWT = W W^T: the reference's FixedGaussianNetwork); unsharded.
  * gk_mf_sbm_soft_stats replaces the C x C loops of stochastic_block_model.py:366-389 (mf_update_p) and :340-344 with

@@ -219,9 +219,46 @@ def make_mf_sbm():
     print("mf_sbm_small.npz")
 
 
+def make_mf_eigen():
+    """mf_eigen_small.npz: the literal loop nests of eigenmodel.py:1090-1157 (oracle/mf_eigen.py `*_loops`), small N.
+    Parity unpinned by the reference (eigenmodel.py cannot be imported); frozen so the oracle cannot drift."""
+    from oracle import mf_eigen as M
+    rng = np.random.RandomState(1357)
+    N, D = 14, 3
+    A = (rng.rand(N, N) < 0.3).astype(np.uint8)
+    mu = rng.randn(N, D) * 0.7
+    X = rng.randn(N, D, D) * 0.3
+    Sg = X @ X.transpose(0, 2, 1) + 0.1 * np.eye(D)
+    lam = rng.randn(D)
+    Y = rng.randn(D, D) * 0.2
+    SL = Y @ Y.T + 0.05 * np.eye(D)
+    mu0, s0 = -0.5, 0.2
+    Fg = rng.randn(N, D)
+    Em = M.expected_mu(mu0, mu, lam)
+    V = M.variance_mu(mu0, s0, mu, Sg, lam, SL)
+    z = rng.randn(50, N, N)
+    EO = M.expected_omega_mc(Em, V, z)
+    llT = M.expected_llT(lam, SL)
+    Af = A.astype(float)
+    out = dict(A=A, mu=mu, Sig=Sg, lam=lam, SigL=SL, mu0=mu0, s0=s0, Fg=Fg, E_mu=Em, Var_mu=V, z=z, E_O=EO,
+               E_O_quad=M.expected_omega_quad(Em, V))
+    m0 = M.meanfieldupdate_mu0(Af, EO, mu, lam, -1.2, 0.9, mu0, s0, 0.8)
+    out.update(mu0_new=m0[0], s0_new=m0[1], mu0_prec=m0[2], mu0_h=m0[3])
+    for tr in (0, 1):
+        for tag, st in (("full", 1.0), ("step", 0.4)):
+            r = M.meanfieldupdate_F_loops(Af, EO, Fg, mu, Sg, mu0, lam, llT, 1.5, st, bool(tr))
+            for nm, v in zip(("mu", "Sig", "prec", "h"), r):
+                out["F_%s_%s_tr%d" % (nm, tag, tr)] = v
+    r = M.meanfieldupdate_lmbda_loops(Af, EO, mu, Sg, mu0, 0.0, 2.0, lam, SL, 0.7)
+    out.update(lam_new=r[0], SigL_new=r[1], lam_prec=r[2], lam_h=r[3])
+    np.savez(os.path.join(HERE, "mf_eigen_small.npz"), **out)
+    print("mf_eigen_small.npz")
+
+
 if __name__ == "__main__":
     make_ref_internals()
     make_sbm()
     make_eigen()
     make_latent()
     make_mf_sbm()
+    make_mf_eigen()
