@@ -408,13 +408,14 @@ static int launch_gfull(gk_ctx *ctx, gk_eig *e, const double *phi_given, size_t 
     if (e->prof) GK_CUDA(ctx, cudaMemsetAsync(e->prof, 0, 16 * 8, ctx->stream));
     // row chunks so that the grid covers >= 2 waves of 2 CTAs/SM
     int nchunks = std::max(1, std::min(16, (4 * ctx->num_sms + strips - 1) / strips));
-    int chunk_rows = ((N + nchunks - 1) / nchunks + GK_EF_PIECE - 1) / GK_EF_PIECE * GK_EF_PIECE;
+    constexpr int PR = gk_ef_piece_rows<T>::R;
+    int chunk_rows = ((N + nchunks - 1) / nchunks + PR - 1) / PR * PR;
     nchunks = (N + chunk_rows - 1) / chunk_rows;
     ACC *partial = (ACC *)gk_scratch(ctx, 2, (size_t)nchunks * npad * PA * sizeof(ACC));
     if (!partial) return GK_ENOMEM;
     const size_t fold_elems = (size_t)128 * (2 * PH + 1);
-    const size_t smem_full = std::max((size_t)GK_EF_PIECE * PA, fold_elems) * sizeof(ACC);
-    const size_t smem_push = std::max((size_t)NB * PA, fold_elems) * sizeof(ACC);
+    const size_t smem_full = std::max((size_t)2 * PR * GK_EF_COLS * (sizeof(T) + 1) + (size_t)2 * PR * PA * sizeof(ACC), fold_elems * sizeof(ACC));
+    const size_t smem_push = std::max((size_t)NB * GK_EF_COLS * (sizeof(T) + 1) + (size_t)NB * PA * sizeof(ACC), fold_elems * sizeof(ACC));
     static bool attr_set = false;
     if (!attr_set) {
         GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_gfull<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full));

@@ -16,7 +16,6 @@
 
 #define GK_EF_THREADS 256
 #define GK_EF_COLS 128            // columns per CTA strip (2 per thread-column)
-#define GK_EF_PIECE 64            // rows of Phi staged in shared memory at a time
 
 template <typename T> struct gk_vec2;
 template <> struct gk_vec2<float> { typedef float2 type; };
@@ -38,7 +37,7 @@ __device__ __forceinline__ void gk_phi_row(const double *__restrict__ f, ACC *__
 // One thread = (column pair cp, half of the PA output columns, row group rg of 2).  Accumulates rows
 // [0, mrows) of a piece whose Phi rows sit in shared memory.  mg0 = global index of the piece's first row;
 // colg = global index of the thread's first column; a pair (m, col) counts iff m > mlow[e].
-template <typename T, int D, int HALF>
+template <typename T, int D, int HALF, bool SM = false>
 __device__ __forceinline__ void gk_ef_piece(const T *__restrict__ Sp, const uint8_t *__restrict__ Ap, size_t ld, int mrows,
                                             const typename gk_eacc<T>::type *__restrict__ phi, int rg, bool probit, int mg0,
                                             int colg, int mlow0, int mlow1,
@@ -54,7 +53,7 @@ __device__ __forceinline__ void gk_ef_piece(const T *__restrict__ Sp, const uint
             const int mm = m + 2 * u;
             const bool ok = mm < mrows;
             const int mc = ok ? mm : m;
-            const T2 sv = __ldg((const T2 *)(Sp + (size_t)mc * ld));
+            const T2 sv = SM ? *(const T2 *)(Sp + (size_t)mc * ld) : __ldg((const T2 *)(Sp + (size_t)mc * ld));
             const int mg = mg0 + mc;
             const bool k0 = ok && mg > mlow0, k1 = ok && mg > mlow1;
             if (probit) {
@@ -63,7 +62,7 @@ __device__ __forceinline__ void gk_ef_piece(const T *__restrict__ Sp, const uint
                 a[u][0] = k0 ? (ACC)sv.x : ACC(0);
                 a[u][1] = k1 ? (ACC)sv.y : ACC(0);
             } else {
-                const unsigned av = __ldg((const unsigned short *)(Ap + (size_t)mc * ld));
+                const unsigned av = SM ? *(const unsigned short *)(Ap + (size_t)mc * ld) : __ldg((const unsigned short *)(Ap + (size_t)mc * ld));
                 s[u][0] = k0 ? (ACC)sv.x : ACC(0);
                 s[u][1] = k1 ? (ACC)sv.y : ACC(0);
                 a[u][0] = k0 ? (ACC)(av & 0xffu) : ACC(0);
@@ -83,6 +82,31 @@ __device__ __forceinline__ void gk_ef_piece(const T *__restrict__ Sp, const uint
         }
     }
 }
+
+// ---- asynchronous staging of a [rows x GK_EF_COLS] tile of S (and of Asym) into shared memory (cp.async, 16 bytes) ----
+__device__ __forceinline__ void gk_cp16(void *smem, const void *gmem) {
+    const unsigned sa = (unsigned)__cvta_generic_to_shared(smem);
+    asm volatile("cp.async.cg.shared.global [%0], [%1], 16;" ::"r"(sa), "l"(gmem));
+}
+__device__ __forceinline__ void gk_cp_commit() { asm volatile("cp.async.commit_group;"); }
+__device__ __forceinline__ void gk_cp_wait_all() { asm volatile("cp.async.wait_group 0;" ::: "memory"); }
+
+template <typename T>
+__device__ __forceinline__ void gk_ef_stage(T *Ssm, uint8_t *Asm, const T *Sg, const uint8_t *Ag, size_t ld, int rows, bool probit,
+                                            int tid) {
+    constexpr int VS = GK_EF_COLS * sizeof(T) / 16, VA = GK_EF_COLS / 16;      // 16-byte vectors per tile row
+    for (int idx = tid; idx < rows * VS; idx += GK_EF_THREADS) {
+        const int r = idx / VS, v = idx - r * VS;
+        gk_cp16((char *)(Ssm + (size_t)r * GK_EF_COLS) + v * 16, (const char *)(Sg + (size_t)r * ld) + v * 16);
+    }
+    if (!probit)
+        for (int idx = tid; idx < rows * VA; idx += GK_EF_THREADS) {
+            const int r = idx / VA, v = idx - r * VA;
+            gk_cp16(Asm + (size_t)r * GK_EF_COLS + v * 16, Ag + (size_t)r * ld + v * 16);
+        }
+}
+
+template <typename T> struct gk_ef_piece_rows { static constexpr int R = sizeof(T) == 4 ? 64 : 32; };
 
 // fold the two row groups of a CTA through shared memory; on return the rg == 0 threads hold the sums
 template <typename ACC, int NP>
@@ -113,9 +137,12 @@ __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_gfull(const T *__restr
                                                                  int N, const double *__restrict__ F, const double *__restrict__ PhiG, int chunk_rows,
                                                                  int npad, typename gk_eacc<T>::type *__restrict__ partial, int probit) {
     typedef typename gk_eacc<T>::type ACC;
-    constexpr int PA = gk_edim<D>::PA, PH = gk_edim<D>::PH;
+    constexpr int PA = gk_edim<D>::PA, PH = gk_edim<D>::PH, PR = gk_ef_piece_rows<T>::R;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    ACC *phi = (ACC *)smem_raw;                                   // [GK_EF_PIECE][PA]; reused as fold scratch
+    // two stages of a [PR x 128] tile of S and of Asym (cp.async), two stages of Phi rows; the S area doubles as fold scratch
+    T *Ssm = (T *)smem_raw;                                       // [2][PR][128]
+    uint8_t *Asm = (uint8_t *)(Ssm + (size_t)2 * PR * GK_EF_COLS);   // [2][PR][128]
+    ACC *phis = (ACC *)(Asm + (size_t)2 * PR * GK_EF_COLS);       // [2][PR][PA]
     const int tid = threadIdx.x, cp = tid & 63, half = (tid >> 6) & 1, rg = tid >> 7;
     const int c0 = blockIdx.x * GK_EF_COLS, colg = c0 + 2 * cp;
     const int r0 = blockIdx.y * chunk_rows, r1 = min(N, r0 + chunk_rows);
@@ -124,10 +151,13 @@ __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_gfull(const T *__restr
     for (int e = 0; e < 2; ++e)
 #pragma unroll
         for (int p = 0; p < PH; ++p) acc[e][p] = ACC(0);
-    for (int rp = r0; rp < r1; rp += GK_EF_PIECE) {
-        const int mrows = min(GK_EF_PIECE, r1 - rp);
-        __syncthreads();
-        if (PhiG) {                                       // mean-field form: Phi rows given (E[f f^T] | E[f] | E[f])
+    auto stage = [&](int rp, int st) {
+        const int mrows = min(PR, r1 - rp);
+        gk_ef_stage<T>(Ssm + (size_t)st * PR * GK_EF_COLS, Asm + (size_t)st * PR * GK_EF_COLS, S + (size_t)rp * ld + c0,
+                       Asym + (size_t)rp * ld + c0, (size_t)ld, mrows, probit != 0, tid);
+        gk_cp_commit();
+        ACC *phi = phis + (size_t)st * PR * PA;
+        if (PhiG) {                                               // mean-field form: Phi rows given (E[f f^T] | E[f] | E[f])
             for (int t = tid; t < mrows * PA; t += GK_EF_THREADS) phi[t] = (ACC)PhiG[(size_t)rp * PA + t];
         } else if (tid < mrows) {
             double f[D];
@@ -135,12 +165,21 @@ __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_gfull(const T *__restr
             for (int d = 0; d < D; ++d) f[d] = F[(size_t)(rp + tid) * D + d];
             gk_phi_row<ACC, D>(f, phi + (size_t)tid * PA);
         }
-        __syncthreads();
-        const T *Sp = S + (size_t)rp * ld + colg;
-        const uint8_t *Ap = Asym + (size_t)rp * ld + colg;
-        if (half == 0) gk_ef_piece<T, D, 0>(Sp, Ap, (size_t)ld, mrows, phi, rg, probit != 0, rp, colg, -1, -1, acc);
-        else gk_ef_piece<T, D, 1>(Sp, Ap, (size_t)ld, mrows, phi, rg, probit != 0, rp, colg, -1, -1, acc);
+    };
+    if (r0 < r1) stage(r0, 0);
+    int k = 0;
+    for (int rp = r0; rp < r1; rp += PR, ++k) {
+        const int mrows = min(PR, r1 - rp), st = k & 1;
+        gk_cp_wait_all();
+        __syncthreads();                                          // piece k landed; everyone is done with piece k-1
+        if (rp + PR < r1) stage(rp + PR, st ^ 1);
+        const T *Sp = Ssm + (size_t)st * PR * GK_EF_COLS + 2 * cp;
+        const uint8_t *Ap = Asm + (size_t)st * PR * GK_EF_COLS + 2 * cp;
+        const ACC *phi = phis + (size_t)st * PR * PA;
+        if (half == 0) gk_ef_piece<T, D, 0, true>(Sp, Ap, (size_t)GK_EF_COLS, mrows, phi, rg, probit != 0, rp, colg, -1, -1, acc);
+        else gk_ef_piece<T, D, 1, true>(Sp, Ap, (size_t)GK_EF_COLS, mrows, phi, rg, probit != 0, rp, colg, -1, -1, acc);
     }
+    ACC *phi = (ACC *)smem_raw;                                   // fold scratch over the (now dead) S stages
     gk_ef_fold<ACC, PH>(acc, phi, tid);
     if (rg == 0) {
         const int p0 = half * PH, np = half == 0 ? PH : PA - PH;
@@ -171,13 +210,17 @@ __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_push(const T *__restri
                                                                 int N, const typename gk_eacc<T>::type *__restrict__ dphi, int n0,
                                                                 int nb, double *__restrict__ G, int probit) {
     typedef typename gk_eacc<T>::type ACC;
-    constexpr int PA = gk_edim<D>::PA, PH = gk_edim<D>::PH;
+    constexpr int PA = gk_edim<D>::PA, PH = gk_edim<D>::PH, NB = gk_eig_nb<T>::NB;
     extern __shared__ __align__(16) unsigned char smem_raw[];
-    ACC *phi = (ACC *)smem_raw;                                   // [nb <= 128][PA]; then fold scratch
+    // the whole [nb x 128] tile of S and Asym is staged at once (one exposure to HBM latency); the S area doubles as fold scratch
+    T *Ssm = (T *)smem_raw;                                       // [NB][128]
+    uint8_t *Asm = (uint8_t *)(Ssm + (size_t)NB * GK_EF_COLS);    // [NB][128]
+    ACC *phis = (ACC *)(Asm + (size_t)NB * GK_EF_COLS);           // [NB][PA]
     const int tid = threadIdx.x, cp = tid & 63, half = (tid >> 6) & 1, rg = tid >> 7;
     const int c0 = blockIdx.x * GK_EF_COLS, colg = c0 + 2 * cp;
-    for (int t = tid; t < nb * PA; t += GK_EF_THREADS) phi[t] = dphi[t];
-    __syncthreads();
+    gk_ef_stage<T>(Ssm, Asm, S + (size_t)n0 * ld + c0, Asym + (size_t)n0 * ld + c0, (size_t)ld, nb, probit != 0, tid);
+    gk_cp_commit();
+    for (int t = tid; t < nb * PA; t += GK_EF_THREADS) phis[t] = dphi[t];
     ACC acc[2][PH];
 #pragma unroll
     for (int e = 0; e < 2; ++e)
@@ -185,10 +228,13 @@ __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_push(const T *__restri
         for (int p = 0; p < PH; ++p) acc[e][p] = ACC(0);
     const bool inb0 = colg >= n0 && colg < n0 + nb, inb1 = colg + 1 >= n0 && colg + 1 < n0 + nb;
     const int mlow0 = inb0 ? colg : -1, mlow1 = inb1 ? colg + 1 : -1;
-    const T *Sp = S + (size_t)n0 * ld + colg;
-    const uint8_t *Ap = Asym + (size_t)n0 * ld + colg;
-    if (half == 0) gk_ef_piece<T, D, 0>(Sp, Ap, (size_t)ld, nb, phi, rg, probit != 0, n0, colg, mlow0, mlow1, acc);
-    else gk_ef_piece<T, D, 1>(Sp, Ap, (size_t)ld, nb, phi, rg, probit != 0, n0, colg, mlow0, mlow1, acc);
+    gk_cp_wait_all();
+    __syncthreads();
+    const T *Sp = Ssm + 2 * cp;
+    const uint8_t *Ap = Asm + 2 * cp;
+    if (half == 0) gk_ef_piece<T, D, 0, true>(Sp, Ap, (size_t)GK_EF_COLS, nb, phis, rg, probit != 0, n0, colg, mlow0, mlow1, acc);
+    else gk_ef_piece<T, D, 1, true>(Sp, Ap, (size_t)GK_EF_COLS, nb, phis, rg, probit != 0, n0, colg, mlow0, mlow1, acc);
+    ACC *phi = (ACC *)smem_raw;                                   // fold scratch over the (now dead) S tile
     gk_ef_fold<ACC, PH>(acc, phi, tid);
     if (rg == 0) {
         const int p0 = half * PH, np = half == 0 ? PH : PA - PH;
