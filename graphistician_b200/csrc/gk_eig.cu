@@ -192,7 +192,11 @@ extern "C" int gk_eig_pg_draw(gk_ctx *ctx, gk_eig *e, uint64_t seed, double *sum
 // Stores Z + Z^T (zero diagonal) in the S buffer; part[tile] = sum of this tile's Z[n,m], n != m.
 // ---------------------------------------------------------------------------------------------
 __device__ __forceinline__ double gk_hash_uniform(uint64_t seed, uint32_t sweep, uint32_t src, uint32_t dst) {
-    uint64_t x = seed + 0x9E3779B97F4A7C15ull * ((uint64_t)sweep + 1) + (((uint64_t)src << 32) | (uint64_t)dst);
+    // the (seed, sweep) key is mixed BEFORE the entry index enters: consecutive seeds must not alias neighbouring entries
+    // (seed + 1, dst) == (seed, dst + 1) would replay one iteration's uniforms in the next -- caught by the Geweke test)
+    uint64_t x = seed + 0x9E3779B97F4A7C15ull * ((uint64_t)sweep + 1);
+    x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
+    x ^= ((uint64_t)src << 32) | (uint64_t)dst;
     x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
     x += 0x9E3779B97F4A7C15ull;
     x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
