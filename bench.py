@@ -240,7 +240,7 @@ def setup_workload(args, rank):
         s_O = 4 if args.dtype == "f32" else 8
         return dict(N=N, data=d, model=model, network=network,
                     algo_bytes=1.0 * N * N * (2 * s_O + 1),       # write S + read S + read A
-                    h2d=N * N + N * D * 16 + 8 * D + 8, d2h=N * D * 8 + 8 * 68 + 8, dominant=(3, "k_eig_slab"),
+                    h2d=N * N + N * D * 16 + 8 * D + 8, d2h=N * D * 8 + 8 * 68 + 8, dominant=(3, "k_eig_gfull+k_eig_push"),
                     cpu_baseline=cpu_baseline_eigen,
                     config={"workload": "logistic_eigenmodel_pg_gibbs_sweep N=%d D=%d lmbda given (configs[2])" % (N, D),
                             "N": N, "D": D})
@@ -317,7 +317,8 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = kbytes / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
-    names = {0: "k_strip_stats", 1: "k_sbm_seq", 2: "k_eig_pg_tile", 3: "k_eig_slab", 4: "k_latent_pair", 5: "k_eig_seq"}
+    names = {0: "k_strip_stats", 1: "k_sbm_seq", 2: "k_eig_pg_tile", 3: "k_eig_gfull+k_eig_push", 4: "k_latent_pair",
+             5: "k_eig_seq4"}
     out = {
         "metric": METRIC, "value": (1 if rows else world) * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
