@@ -253,7 +253,7 @@ extern "C" int gk_sbm_sweep_begin(gk_ctx *ctx, gk_net *net, const int32_t *c, in
     GK_CUDA(ctx, cudaMemcpyAsync(sw->c, c, (size_t)N * 4, cudaMemcpyHostToDevice, ctx->stream));
     GK_CUDA(ctx, cudaMemcpyAsync(sw->sizes, sizes.data(), (size_t)K * 4, cudaMemcpyHostToDevice, ctx->stream));
     GK_CUDA(ctx, cudaMemcpyAsync(sw->u, uniforms, (size_t)N * 8, cudaMemcpyHostToDevice, ctx->stream));
-    GK_CUDA(ctx, cudaMemsetAsync(sw->nchanged, 0, 8, ctx->stream));
+    GK_CUDA(ctx, cudaMemsetAsync(sw->nchanged, 0, 64, ctx->stream));
     k_narrow_labels<<<(N + 255) / 256, 256, 0, ctx->stream>>>(sw->c, sw->c8, N);
     GK_CHECK_LAUNCH(ctx);
     GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));      // blob/sizes are host temporaries
@@ -285,8 +285,15 @@ static int launch_sample(gk_ctx *ctx, gk_net *net, gk_sweep *sw, int n0, int nb,
     P.c = sw->c; P.c8 = sw->c8; P.sizes = sw->sizes; P.lp = sw->lp; P.u = sw->u; P.T = sw->T;
     P.A = net->A; P.At = net->At; P.W = net->W; P.Wt = net->Wt;
     P.out_lp = sw->want_lp ? sw->out_lp : nullptr; P.nchanged = sw->nchanged;
+    P.prof = getenv("GK_SBM_PROF") != nullptr;
     gk_time_begin(ctx, 1, 0.0);
-    k_sbm_seq<T, B><<<1, GK_SEQ_THREADS, 0, ctx->stream>>>(P);
+    const size_t dyn = ((size_t)sw->K * (nb | 1) + nb) * 8 + (size_t)(nb + 15) / 16 * 16;
+    if (nb <= GK_SEQ_THREADS && dyn <= 208 * 1024) {          // conditionals of the block fit in shared memory
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_sbm_seq2<T, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
+        k_sbm_seq2<T, B><<<1, GK_SEQ_THREADS, dyn, ctx->stream>>>(P);
+    } else {
+        k_sbm_seq<T, B><<<1, GK_SEQ_THREADS, 0, ctx->stream>>>(P);
+    }
     gk_time_end(ctx, 1);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
@@ -326,6 +333,13 @@ extern "C" int gk_sbm_sweep_end(gk_ctx *ctx, gk_net *net, int32_t *c_out, double
     if (!ctx || !ctx->sweep) return GK_EINVAL;
     gk_sweep *sw = ctx->sweep;
     unsigned long long nch = 0;
+    if (getenv("GK_SBM_PROF")) {                               // phase clocks of k_sbm_seq2 (shares)
+        unsigned long long pc[7];
+        GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        GK_CUDA(ctx, cudaMemcpy(pc, sw->nchanged, sizeof pc, cudaMemcpyDeviceToHost));
+        fprintf(stderr, "[gk_sbm prof] moves %llu  draw %llu  bar1 %llu  tables+features %llu  bar2 %llu  push %llu  bar3 %llu\n",
+                pc[0], pc[1], pc[2], pc[3], pc[4], pc[5], pc[6]);
+    }
     if (c_out) GK_CUDA(ctx, cudaMemcpyAsync(c_out, sw->c, (size_t)sw->N * 4, cudaMemcpyDeviceToHost, ctx->stream));
     if (out_lp && sw->want_lp) GK_CUDA(ctx, cudaMemcpyAsync(out_lp, sw->out_lp, (size_t)sw->N * sw->K * 8, cudaMemcpyDeviceToHost, ctx->stream));
     GK_CUDA(ctx, cudaMemcpyAsync(&nch, sw->nchanged, 8, cudaMemcpyDeviceToHost, ctx->stream));

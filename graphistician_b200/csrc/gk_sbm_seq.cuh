@@ -43,6 +43,8 @@ __global__ void k_lp_from_stats(const double *__restrict__ stats, gk_tables Tb, 
     }
 }
 
+__device__ __forceinline__ long long gk_sbm_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory"); return t; }
+
 struct gk_seq_params {
     int n0, nb, K, N, ld, row0, sampler;
     int32_t *c; uint8_t *c8; int *sizes;       // global state (device)
@@ -51,7 +53,8 @@ struct gk_seq_params {
     gk_tables T;
     const uint8_t *A, *At; const void *W, *Wt; // local rows (must contain the block's rows)
     double *out_lp;                            // optional [N][K]
-    unsigned long long *nchanged;
+    unsigned long long *nchanged;              // [0] moves; [1..6] phase clocks when prof
+    int prof;
 };
 
 #define GK_SEQ_THREADS 1024
@@ -157,6 +160,159 @@ __global__ void __launch_bounds__(GK_SEQ_THREADS, 1) k_sbm_seq(gk_seq_params P) 
         __syncthreads();
     }
     if (tid == 0 && P.nchanged) atomicAdd(P.nchanged, changed);
+}
+
+__device__ __forceinline__ void gk_prefetch_l2(const void *p) { asm volatile("prefetch.global.L2 [%0];" ::"l"(p)); }
+
+// Shared-memory form of k_sbm_seq for blocks whose conditionals fit on chip (nb * K * 8 B <= ~190 KB): same speculative
+// windows and the same arithmetic, but lp, labels and uniforms of the block live in shared memory ([k][i], odd pitch),
+// a label change is pushed by ONE pass with a thread per later node (coalesced reads of row ns of A, A^T, W, W^T), and
+// the warp that finds the earliest change so far prefetches those row segments into L2 while the window finishes.
+// A sweep from random labels (every node moves) costs ~1/4 of the global-memory form; a converged chain is unchanged.
+template <typename T, int B>
+__global__ void __launch_bounds__(GK_SEQ_THREADS, 1) k_sbm_seq2(gk_seq_params P) {
+    constexpr int S = gk_sdim<B>::S;
+    extern __shared__ __align__(16) double seq_dyn[];
+    __shared__ __align__(16) double dL1[GK_MAX_K], dCO[S * GK_MAX_K], dCI[S * GK_MAX_K];
+    __shared__ double T0[GK_MAX_K], L1s[GK_MAX_K * GK_MAX_K];
+    __shared__ int s_first, ssz[GK_MAX_K];
+    __shared__ unsigned char s_new[4096];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, K = P.K, nb = P.nb;
+    const int pitch = nb | 1;
+    const bool prof = P.prof && tid == 0;
+    long long pc[8] = {0, 0, 0, 0, 0, 0, 0, 0}, tk = 0;
+    double *lp_s = seq_dyn, *u_s = lp_s + (size_t)K * pitch;
+    unsigned char *c_s = (unsigned char *)(u_s + nb);
+    for (int t = tid; t < nb * K; t += GK_SEQ_THREADS) lp_s[(t % K) * pitch + t / K] = P.lp[t];
+    for (int i = tid; i < nb; i += GK_SEQ_THREADS) {
+        const int n = P.n0 + i;
+        u_s[i] = n < P.N ? P.u[n] : 0.0;
+        c_s[i] = n < P.N ? P.c8[n] : 255;
+    }
+    for (int t = tid; t < K * K; t += GK_SEQ_THREADS) L1s[t] = P.T.L1[t];
+    for (int t = tid; t < S * GK_MAX_K; t += GK_SEQ_THREADS) { dCO[t] = 0.0; dCI[t] = 0.0; }
+    if (tid < GK_MAX_K) dL1[tid] = 0.0;
+    if (tid == 0) s_first = 0x7fffffff;
+    if (tid < K) ssz[tid] = P.sizes[tid];
+    __syncthreads();
+    if (tid < K) { double t = 0.0; for (int k2 = 0; k2 < K; ++k2) t += (double)ssz[k2] * L1s[tid * K + k2]; T0[tid] = t; }
+    __syncthreads();
+    const size_t esz = B * sizeof(T);
+    int cursor = 0, window = 64;
+    unsigned long long changed = 0;
+    while (cursor < nb) {
+        const int wend = min(nb, cursor + window);
+        if (prof) tk = gk_sbm_clock();
+        for (int i = cursor + warp; i < wend; i += GK_SEQ_WARPS) {
+            const int n = P.n0 + i;
+            if (n >= P.N) { if (lane == 0) s_new[i - cursor] = 255; continue; }
+            const int ci = c_s[i];
+            double v = lane < K ? lp_s[lane * pitch + i] + T0[lane] - L1s[lane * K + ci] : -1e300;
+            double mx = v;
+            for (int o = 16; o; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
+            double e = lane < K ? exp(v - mx) : 0.0;
+            int newc;
+            if (P.sampler == GK_SAMPLER_CUMSUM) {
+                double cum = e;
+                for (int o = 1; o < 32; o <<= 1) { double t = __shfl_up_sync(0xffffffffu, cum, o); if (lane >= o) cum += t; }
+                double tot = __shfl_sync(0xffffffffu, cum, K - 1);
+                double r = u_s[i] * tot;
+                newc = __popc(__ballot_sync(0xffffffffu, lane < K && r > cum));
+            } else {
+                double tot = e;
+                for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+                double cum = e / tot;
+                for (int o = 1; o < 32; o <<= 1) { double t = __shfl_up_sync(0xffffffffu, cum, o); if (lane >= o) cum += t; }
+                newc = __popc(__ballot_sync(0xffffffffu, lane < K && cum < u_s[i]));
+            }
+            newc = min(newc, K - 1);
+            if (P.out_lp && lane < K) P.out_lp[(size_t)n * K + lane] = v;
+            if (lane == 0) s_new[i - cursor] = (unsigned char)newc;
+            if (newc != ci) {
+                int prev = 0;
+                if (lane == 0) prev = atomicMin(&s_first, i);
+                prev = __shfl_sync(0xffffffffu, prev, 0);
+                if (i < prev) {                              // earliest mover so far: warm L2 with its row segments
+                    const size_t off = (size_t)(n - P.row0) * P.ld + P.n0;
+                    for (int b = lane * 128; b < nb; b += 32 * 128) { gk_prefetch_l2(P.A + off + b); gk_prefetch_l2(P.At + off + b); }
+                    if constexpr (B > 0)
+                        for (size_t b = (size_t)lane * 128; b < nb * esz; b += 32 * 128) {
+                            gk_prefetch_l2((const char *)P.W + off * esz + b); gk_prefetch_l2((const char *)P.Wt + off * esz + b);
+                        }
+                }
+            }
+        }
+        if (prof) { long long t = gk_sbm_clock(); pc[0] += t - tk; tk = t; }
+        __syncthreads();
+        const int first = s_first;
+        __syncthreads();
+        if (prof) { long long t = gk_sbm_clock(); pc[1] += t - tk; tk = t; }
+        if (first >= wend) {                       // nothing in the window moved: commit it all
+            cursor = wend; window = min(window * 2, 4096);
+            continue;
+        }
+        // commit nodes cursor..first; node `first` moves a -> b
+        const int ns = P.n0 + first, a = c_s[first], b = s_new[first - cursor];
+        if (tid < K) {
+            dL1[tid] = L1s[tid * K + b] - L1s[tid * K + a];
+            for (int s = 0; s < S; ++s) {
+                dCO[s * GK_MAX_K + tid] = P.T.COt[(size_t)(b * S + s) * K + tid] - P.T.COt[(size_t)(a * S + s) * K + tid];
+                dCI[s * GK_MAX_K + tid] = P.T.CIt[(size_t)(b * S + s) * K + tid] - P.T.CIt[(size_t)(a * S + s) * K + tid];
+            }
+        }
+        const size_t rowoff = (size_t)(ns - P.row0) * P.ld;
+        // features of the later nodes against ns (nb <= GK_SEQ_THREADS: one later node per thread); the loads are
+        // issued before the barrier that publishes the delta tables
+        const int i = first + 1 + tid, n = P.n0 + i;
+        const bool act = i < nb && n < P.N;
+        double xo[S], xi[S];
+        if (act) {
+            const bool eo = P.At[rowoff + n] != 0, ei = P.A[rowoff + n] != 0;
+            xo[0] = eo ? 1.0 : 0.0; xi[0] = ei ? 1.0 : 0.0;
+            if constexpr (B > 0) {
+                const T *wo = (const T *)P.Wt + (rowoff + n) * B, *wi = (const T *)P.W + (rowoff + n) * B;
+#pragma unroll
+                for (int bb = 0; bb < B; ++bb) { xo[1 + bb] = eo ? (double)wo[bb] : 0.0; xi[1 + bb] = ei ? (double)wi[bb] : 0.0; }
+#pragma unroll
+                for (int bb = 0; bb < B; ++bb)
+#pragma unroll
+                    for (int b2 = bb; b2 < B; ++b2) {
+                        xo[gk_sym_idx(B, bb, b2)] = xo[1 + bb] * xo[1 + b2];
+                        xi[gk_sym_idx(B, bb, b2)] = xi[1 + bb] * xi[1 + b2];
+                    }
+            }
+        }
+        if (prof) { long long t = gk_sbm_clock(); pc[2] += t - tk; tk = t; }
+        __syncthreads();
+        if (prof) { long long t = gk_sbm_clock(); pc[3] += t - tk; tk = t; }
+        if (act) {
+            for (int k = 0; k < K; k += 2) {
+                const double2 l1 = *(const double2 *)&dL1[k];
+                double d0 = l1.x, d1 = l1.y;
+#pragma unroll
+                for (int s = 0; s < S; ++s) {
+                    const double2 co = *(const double2 *)&dCO[s * GK_MAX_K + k], cin = *(const double2 *)&dCI[s * GK_MAX_K + k];
+                    d0 += xo[s] * co.x + xi[s] * cin.x;
+                    d1 += xo[s] * co.y + xi[s] * cin.y;
+                }
+                lp_s[k * pitch + i] += d0;
+                if (k + 1 < K) lp_s[(k + 1) * pitch + i] += d1;
+            }
+        }
+        if (tid == 0) {
+            P.c[ns] = b; P.c8[ns] = (uint8_t)b; c_s[first] = (unsigned char)b;
+            ssz[a] -= 1; ssz[b] += 1;
+            s_first = 0x7fffffff;
+        }
+        changed++;
+        cursor = first + 1; window = max(32, window / 2);
+        if (prof) { long long t = gk_sbm_clock(); pc[4] += t - tk; tk = t; }
+        __syncthreads();
+        if (prof) { long long t = gk_sbm_clock(); pc[5] += t - tk; tk = t; }
+    }
+    if (tid < K) P.sizes[tid] = ssz[tid];
+    if (tid == 0 && P.nchanged) atomicAdd(P.nchanged, changed);
+    if (prof) for (int q = 0; q < 6; ++q) atomicAdd(P.nchanged + 1 + q, (unsigned long long)pc[q]);
 }
 
 // K1: fold per-node in-edge statistics  stats[n1][bin = c[n2]][s]  into cells (c[n2], c[n1]).

@@ -48,6 +48,7 @@ class DeviceNetwork:
         dW = None if self.B == 0 else np.ascontiguousarray(diagW, dtype=np.float64)
         self.ctx.check(self.ctx.lib.gk_network_set_diag(self.ctx.h, self.h, ptr(dA), ptr(dW)))
         self.diagA, self.diagW = dA, dW
+        self._diag_feat = None
 
     def device_bytes(self):
         return int(self.ctx.lib.gk_network_device_bytes(self.h))
@@ -67,15 +68,21 @@ class DeviceNetwork:
     def diag_stats(self, c, K):
         """O(N) host-side diagonal statistics per block (composed with block_stats by the model classes)."""
         c = np.asarray(c)
-        e = self.diagA != 0
-        out = dict(d_cnt=np.bincount(c, minlength=K).astype(np.int64),
-                   d_edge=np.bincount(c[e], minlength=K).astype(np.int64),
-                   d_sum_w=np.zeros((K, self.B)), d_sum_ww=np.zeros((K, self.B, self.B)))
-        for b in range(self.B):
-            out["d_sum_w"][:, b] = np.bincount(c[e], weights=self.diagW[e, b], minlength=K)
-            for b2 in range(self.B):
-                out["d_sum_ww"][:, b, b2] = np.bincount(c[e], weights=self.diagW[e, b] * self.diagW[e, b2], minlength=K)
-        return out
+        B = self.B
+        if self._diag_feat is None:                      # the diagonal is fixed with the network: features made once
+            e = np.flatnonzero(self.diagA != 0)
+            X = np.ones((e.size, 1 + B + B * B))
+            if B:
+                w = self.diagW[e]
+                X[:, 1:1 + B] = w
+                X[:, 1 + B:] = (w[:, :, None] * w[:, None, :]).reshape(e.size, B * B)
+            self._diag_feat = (e, X)
+        e, X = self._diag_feat
+        onehot = np.zeros((K, e.size))
+        onehot[c[e], np.arange(e.size)] = 1.0
+        S = onehot.dot(X)
+        return dict(d_cnt=np.bincount(c, minlength=K).astype(np.int64), d_edge=np.rint(S[:, 0]).astype(np.int64),
+                    d_sum_w=S[:, 1:1 + B].copy(), d_sum_ww=S[:, 1 + B:].reshape(K, B, B).copy())
 
     # ---- K2 -------------------------------------------------------------------------------------
     def sbm_sweep(self, c, log_m, p, mu, sigma, uniforms, self_mode=_lib.SELF_ONCE, sampler=_lib.SAMPLER_CUMSUM,

@@ -31,3 +31,16 @@ for fam, name in ((6, "k_strip_soft"), (7, "k_mf_seq")):
 ctx.lib.gk_ctx_kernel_timing(ctx.h, 0)
 for nm, fn in (("mf_update_c", lambda: model.mf_update_c(net)), ("mf_update_p", lambda: model.mf_update_p(net))):
     t = time.time(); fn(); print(nm, "wall s", time.time() - t)
+
+# ---- mean-field logistic eigenmodel (a19) at the same N, D=8 ---------------------------------------------------
+from graphistician_b200.eigenmodel import LogisticEigenmodel  # noqa: E402
+
+del model, net, dev, W
+em = LogisticEigenmodel(N, 8)
+enet = FixedGaussianNetwork(A, None)
+em.meanfieldupdate(enet)
+for nm, fn in (("eig _meanfieldupdate_Omega (1000 draws/entry)", lambda: em._meanfieldupdate_Omega(enet)),
+               ("eig _meanfieldupdate_F", lambda: em._meanfieldupdate_F(enet)),
+               ("eig _meanfieldupdate_lmbda", lambda: em._meanfieldupdate_lmbda(enet)),
+               ("eig meanfieldupdate", lambda: em.meanfieldupdate(enet))):
+    t = time.time(); fn(); print(nm, "wall s", time.time() - t)
