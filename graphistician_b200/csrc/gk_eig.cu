@@ -166,11 +166,14 @@ extern "C" int gk_eig_pg_draw(gk_ctx *ctx, gk_eig *e, uint64_t seed, double *sum
     GK_CUDA(ctx, cudaSetDevice(ctx->device));
     dim3 grid((net->N + GK_PG_TILE - 1) / GK_PG_TILE, (net->nrows + GK_PG_TILE - 1) / GK_PG_TILE);
     const double bytes = (double)net->nrows * net->N * gk_esize(e->dtype);
+    const size_t pg_dyn = 8 * 2 * (GK_PG_TILE * GK_PG_TILE / 256) * 32 * sizeof(unsigned short);   // per-warp draw lists
+    GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_pg_tile<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pg_dyn));
+    GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_pg_tile<double>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)pg_dyn));
     gk_time_begin(ctx, 2, bytes);
     if (e->dtype == GK_F32)
-        k_eig_pg_tile<float><<<grid, 256, 0, ctx->stream>>>((float *)e->S, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
+        k_eig_pg_tile<float><<<grid, 256, pg_dyn, ctx->stream>>>((float *)e->S, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
     else
-        k_eig_pg_tile<double><<<grid, 256, 0, ctx->stream>>>((double *)e->S, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
+        k_eig_pg_tile<double><<<grid, 256, pg_dyn, ctx->stream>>>((double *)e->S, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
     gk_time_end(ctx, 2);
     GK_CHECK_LAUNCH(ctx);
     e->sweep++;

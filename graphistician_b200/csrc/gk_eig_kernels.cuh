@@ -57,8 +57,8 @@ __global__ void k_eig_asym(const uint8_t *__restrict__ A, const uint8_t *__restr
 // always GENERATED in its canonical orientation (smaller block index first) by per-lane generators keyed by
 // (seed, sweep, canonical tile, thread), so any rank regenerates exactly the same tile; it is then written to
 // the local rows directly, transposed, or both.  Tiles below the diagonal whose mirror image is local are
-// skipped.  Pass 1 (uniform across the warp): logits and proposal masses into shared memory.  Pass 2: each lane
-// drains its own queue of 16 entries x 2 draws (gk_pg1_step), so accepted lanes do not idle.
+// skipped.  Pass 1 (uniform across the warp): logits and proposal masses into shared memory.  Pass 2: the draws,
+// sorted by proposal piece so that a warp runs one code path at a time (see the comment in the kernel).
 // part[tile] = sum of the tile's pair draws (each unordered pair counted by exactly one CTA over all ranks)
 //              + its diagonal draws PG(1, mu_0).
 // ---------------------------------------------------------------------------------------------------
@@ -70,6 +70,7 @@ __global__ void __launch_bounds__(256) k_eig_pg_tile(T *__restrict__ S, int ld, 
     constexpr int TS = GK_PG_TILE, NQ = TS * TS / 256;
     __shared__ float fi[TS][GK_EIG_MAXD], fj[TS][GK_EIG_MAXD];
     __shared__ float tile[TS][TS + 1], massb[TS][TS + 1];
+    extern __shared__ unsigned short pglist_dyn[];            // [8 warps][2 * NQ * 32] left-piece draw lists
     __shared__ double red[8];
     const int tid = threadIdx.x;
     const int I = row0 + blockIdx.y * TS, J = blockIdx.x * TS;          // local row block, column block
@@ -105,30 +106,51 @@ __global__ void __launch_bounds__(256) k_eig_pg_tile(T *__restrict__ S, int ld, 
         }
         tile[i][j] = z; massb[i][j] = ms;
     }
-    // pass 2: drain the queue
+    // pass 2: piece-sorted draws (gk_pg.cuh).  Each entry needs 2 draws (1 on the diagonal).  2a: every lane decides the
+    // piece of its entries' draws and finishes the right-piece ones; left-piece draws are filed into this warp's list
+    // (small-Z codes from the front, inverse-Gaussian codes from the back).  2b / 2c: the lists are drained densely, item
+    // q by lane q % 32 with that lane's generator, so a tile is a pure function of (seed, sweep, canonical tile).
+    // massb is reused as the accumulator of the two draws once the masses have been consumed.
     gk_xoshiro g; g.seed(seed, (uint32_t)tid | ((uint32_t)sweep << 8), (uint32_t)cI, (uint32_t)cJ);
-    double local = 0.0;
-    int k = 0, need = 0;
-    bool in_left = false;
-    float Z = 0.f, mass = 0.f, accv = 0.f;
-    while (k < NQ) {
+    const int lane = tid & 31;
+    const unsigned lt = (1u << lane) - 1u;
+    unsigned short *lst = pglist_dyn + (tid >> 5) * (2 * NQ * 32);
+    int nA = 0, nB = 0;
+    for (int k = 0; k < NQ; ++k) {
         const int i = i0 + k * (256 / TS);
-        if (need == 0) {                                   // start the next entry
-            mass = massb[i][j];
-            if (mass < 0.f) { tile[i][j] = 0.f; ++k; continue; }
-            Z = 0.5f * fabsf(tile[i][j]);
-            need = (diag_tile && i == j) ? 1 : 2;
-            accv = 0.f; in_left = false;
+        const float mass = massb[i][j], Z = 0.5f * fabsf(tile[i][j]);
+        const int ndraw = mass < 0.f ? 0 : ((diag_tile && i == j) ? 1 : 2);
+        const bool small = Z < 1.0f / GK_PG_T;
+        float accv = 0.f;
+#pragma unroll
+        for (int q = 0; q < 2; ++q) {
+            const bool right = g.unif() < mass;             // mass < 0 for dead entries
+            const bool left = q < ndraw && !right;
+            if (q < ndraw && right) accv += 0.25f * gk_pg1_right(Z, g);
+            const unsigned mA = __ballot_sync(0xffffffffu, left && small), mB = __ballot_sync(0xffffffffu, left && !small);
+            const unsigned short code = (unsigned short)(i * TS + j);
+            if (left && small) lst[nA + __popc(mA & lt)] = code;
+            if (left && !small) lst[2 * NQ * 32 - 1 - nB - __popc(mB & lt)] = code;
+            nA += __popc(mA); nB += __popc(mB);
         }
-        float X;
-        if (gk_pg1_step(Z, mass, in_left, g, X)) {
-            accv += 0.25f * X;
-            if (--need == 0) {
-                if (diag_tile && i == j) { local += (double)accv; tile[i][j] = 0.f; }
-                else { tile[i][j] = accv; if (!swapped) local += (double)accv; }
-                ++k;
-            }
-        }
+        massb[i][j] = accv;
+    }
+    __syncwarp();
+    for (int q = lane; q < nA; q += 32) {
+        const int code = lst[q], i = code / TS, jj = code % TS;
+        atomicAdd(&massb[i][jj], 0.25f * gk_pg1_left_small(0.5f * fabsf(tile[i][jj]), g));
+    }
+    for (int q = lane; q < nB; q += 32) {
+        const int code = lst[2 * NQ * 32 - 1 - q], i = code / TS, jj = code % TS;
+        atomicAdd(&massb[i][jj], 0.25f * gk_pg1_left_ig(0.5f * fabsf(tile[i][jj]), g));
+    }
+    __syncwarp();
+    double local = 0.0;
+    for (int k = 0; k < NQ; ++k) {
+        const int i = i0 + k * (256 / TS);
+        const float accv = massb[i][j];                      // 0 for dead entries
+        if (diag_tile && i == j) { local += (double)accv; tile[i][j] = 0.f; }
+        else { tile[i][j] = accv; if (!swapped) local += (double)accv; }
     }
     __syncthreads();
     // write: own rows I.. (direct, or transposed when the canonical tile is the mirror image), mirror rows J..

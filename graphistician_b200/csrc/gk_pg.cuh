@@ -205,3 +205,65 @@ __device__ __forceinline__ bool gk_pg1_step(float Z, float mass, bool &in_left, 
     if (accept) X = x;
     return accept;
 }
+
+// ---- piece-sorted form (K3 tile kernel, pass 2) ----------------------------------------------------------
+// gk_pg1_step makes every lane walk through right piece / left piece (small Z) / left piece (inverse Gaussian) code
+// whether or not it needs it (ncu: 11 of 32 lanes active per instruction).  The tile kernel instead decides the
+// piece of every draw first (uniform work), finishes right-piece draws in place and files left-piece draws into two
+// per-warp lists that are then drained densely, one code path at a time.  The alternating-series test rejects
+// < 0.1 % of proposals; those restart through the generic step.
+__device__ __forceinline__ bool gk_pg_series_accept(float e, gk_xoshiro &g) {
+    const float u = g.unif();
+    float S = 1.0f - 3.0f * __expf(2.0f * e);
+    if (u <= S) return true;
+    for (int n = 2; n < 24; ++n) {
+        const float r = (float)(2 * n + 1) * __expf((float)(n * (n + 1)) * e);
+        if (n & 1) { S -= r; if (u <= S) return true; }
+        else { S += r; if (u > S) return false; }
+    }
+    return false;
+}
+
+__device__ __noinline__ float gk_pg1_generic(float Z, gk_xoshiro &g) {
+    const float mass = gk_pg_mass(Z);
+    bool in_left = false;
+    float X = 0.f;
+    while (!gk_pg1_step(Z, mass, in_left, g, X)) {}
+    return X;
+}
+
+// right (exponential) piece: one proposal, then the series test
+__device__ __forceinline__ float gk_pg1_right(float Z, gk_xoshiro &g) {
+    const float fz = 0.125f * GK_PI_F * GK_PI_F + 0.5f * Z * Z;
+    const float x = GK_PG_T + __fdividef(g.expon(), fz);
+    if (gk_pg_series_accept(-0.5f * GK_PI_F * GK_PI_F * x, g)) return x;
+    return gk_pg1_generic(Z, g);
+}
+
+// left piece, Z < 1/t: exponential-tail proposal for 1/sqrt(x) with inner rejection
+__device__ __forceinline__ float gk_pg1_left_small(float Z, gk_xoshiro &g) {
+    const float t = GK_PG_T;
+    float x;
+    for (;;) {
+        const float E1 = g.expon(), E2 = g.expon();
+        x = 1.0f + E1 * t;
+        x = __fdividef(t, x * x);
+        if (E1 * E1 <= 2.0f * E2 / t && g.unif() <= __expf(-0.5f * Z * Z * x)) break;
+    }
+    if (gk_pg_series_accept(__fdividef(-2.0f, x), g)) return x;
+    return gk_pg1_generic(Z, g);
+}
+
+// left piece, Z >= 1/t: inverse Gaussian(1/Z, 1) truncated to x <= t by rejection
+__device__ __forceinline__ float gk_pg1_left_ig(float Z, gk_xoshiro &g) {
+    const float t = GK_PG_T, mu = __fdividef(1.0f, Z), half_mu = 0.5f * mu;
+    float x;
+    do {
+        float Y = g.normal(); Y *= Y;
+        const float mu_Y = mu * Y;
+        x = mu + half_mu * mu_Y - half_mu * sqrtf(4.0f * mu_Y + mu_Y * mu_Y);
+        if (g.unif() > __fdividef(mu, mu + x)) x = __fdividef(mu * mu, x);
+    } while (x > t);
+    if (gk_pg_series_accept(__fdividef(-2.0f, x), g)) return x;
+    return gk_pg1_generic(Z, g);
+}
