@@ -15,6 +15,8 @@ struct gk_eig {
     double *part = nullptr; size_t npart = 0;              // per-tile partial sums of K3
     double *scal = nullptr;            // small device scalars (sum of omega, ...)
     double *out_prec = nullptr, *out_h = nullptr;
+    cudaStream_t s2 = nullptr; cudaEvent_t evE[2] = {nullptr, nullptr}, evR[2] = {nullptr, nullptr};   // push overlap (sweep_F_fast)
+    void *dphi2 = nullptr; int overlap_push = 1;
     double *G = nullptr, *spart = nullptr; void *dphi = nullptr;   // running-G sweep (gk_eig_fast.cuh): [ld][PA], [NB][PA], [64][PA]
     double *mfMu = nullptr, *mfSig = nullptr, *mfLin = nullptr, *mfPhi = nullptr, *mfSmall = nullptr, *mfPart = nullptr;   // mean-field q (K11)
     long long *prof = nullptr;         // debug cycle counters of k_eig_seq3 (env GK_EIG_PROF=1)
@@ -76,7 +78,9 @@ extern "C" int gk_eig_destroy(gk_ctx *ctx, gk_eig *e) {
     if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
     cudaFree(e->S); cudaFree(e->F); cudaFree(e->z); cudaFree(e->lmbda); cudaFree(e->acc); cudaFree(e->glob);
     cudaFree(e->part); cudaFree(e->scal); cudaFree(e->out_prec); cudaFree(e->out_h);
-    cudaFree(e->G); cudaFree(e->dphi); cudaFree(e->spart); cudaFree(e->prof);
+    cudaFree(e->G); cudaFree(e->dphi); cudaFree(e->dphi2); cudaFree(e->spart); cudaFree(e->prof);
+    if (e->s2) cudaStreamDestroy(e->s2);
+    for (int q = 0; q < 2; ++q) { if (e->evE[q]) cudaEventDestroy(e->evE[q]); if (e->evR[q]) cudaEventDestroy(e->evR[q]); }
     cudaFree(e->mfMu); cudaFree(e->mfSig); cudaFree(e->mfLin); cudaFree(e->mfPhi); cudaFree(e->mfSmall); cudaFree(e->mfPart);
     delete e;
     return GK_OK;
@@ -90,6 +94,7 @@ extern "C" int gk_eig_set_option(gk_ctx *ctx, gk_eig *e, int option, int value) 
     if (!ctx || !e) return GK_EINVAL;
     if (option == GK_EIG_OPT_CHOL_F64) { e->chol_f64 = value != 0; return GK_OK; }
     if (option == GK_EIG_OPT_FAST_SWEEP) { e->use_fast = value != 0; return GK_OK; }
+    if (option == GK_EIG_OPT_OVERLAP_PUSH) { e->overlap_push = value != 0; return GK_OK; }
     return gk_fail(ctx, GK_EINVAL, "unknown eigenmodel option %d", option);
 }
 
@@ -409,6 +414,12 @@ static int launch_gfull(gk_ctx *ctx, gk_eig *e, const double *phi_given, size_t 
     if (!e->G) {
         GK_CUDA(ctx, cudaMalloc(&e->G, (size_t)npad * GK_EIG_PA_MAX * 8));
         GK_CUDA(ctx, cudaMalloc(&e->dphi, (size_t)GK_EIG_NBMAX * GK_EIG_PA_MAX * 8));       // ACC [NB][PA]
+        GK_CUDA(ctx, cudaMalloc(&e->dphi2, (size_t)GK_EIG_NBMAX * GK_EIG_PA_MAX * 8));      // second buffer: blocks alternate
+        GK_CUDA(ctx, cudaStreamCreateWithFlags(&e->s2, cudaStreamNonBlocking));
+        for (int q = 0; q < 2; ++q) {
+            GK_CUDA(ctx, cudaEventCreateWithFlags(&e->evE[q], cudaEventDisableTiming));
+            GK_CUDA(ctx, cudaEventCreateWithFlags(&e->evR[q], cudaEventDisableTiming));
+        }
         GK_CUDA(ctx, cudaMalloc(&e->spart, (size_t)64 * GK_EIG_PA_MAX * 8));
         if (getenv("GK_EIG_PROF")) GK_CUDA(ctx, cudaMalloc(&e->prof, 16 * 8));
     }
@@ -443,12 +454,28 @@ static int launch_gfull(gk_ctx *ctx, gk_eig *e, const double *phi_given, size_t 
 }
 
 template <typename T, int D>
-static int launch_push(gk_ctx *ctx, gk_eig *e, int n0, int nb, size_t smem_push) {
+static int launch_push(gk_ctx *ctx, gk_eig *e, int n0, int nb, size_t smem_push, cudaStream_t st = nullptr, int skip_cb = -1) {
     typedef typename gk_eacc<T>::type ACC;
     gk_net *net = e->net;
-    gk_time_begin(ctx, 3, (double)nb * e->N * (sizeof(T) + 1.0));
+    cudaStream_t keep = ctx->stream;
+    if (st) ctx->stream = st;                                  // the timing events must sit on the launching stream
+    gk_time_begin(ctx, 3, (double)nb * (e->N - (skip_cb >= 0 ? GK_EF_COLS : 0)) * (sizeof(T) + 1.0));
     k_eig_push<T, D><<<net->ld / GK_EF_COLS, GK_EF_THREADS, smem_push, ctx->stream>>>((const T *)e->S, net->Asym, net->ld, e->N,
-                                                                                    (const ACC *)e->dphi, n0, nb, e->G, e->probit);
+                                                                                    (const ACC *)e->dphi, n0, nb, e->G, e->probit, skip_cb);
+    gk_time_end(ctx, 3);
+    ctx->stream = keep;
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+// the strip of the next node block only (see k_eig_push_cols)
+template <typename T, int D>
+static int launch_push_cols(gk_ctx *ctx, gk_eig *e, int n0, int nb, int c0, int ncols) {
+    typedef typename gk_eacc<T>::type ACC;
+    gk_net *net = e->net;
+    gk_time_begin(ctx, 3, (double)nb * ncols * (sizeof(T) + 1.0));
+    k_eig_push_cols<T, D><<<(ncols + GK_EPC_COLS - 1) / GK_EPC_COLS, 32 * GK_EPC_COLS, 0, ctx->stream>>>(
+        (const T *)e->S, net->Asym, net->ld, e->N, (const ACC *)e->dphi, n0, nb, e->G, e->probit, c0, ncols);
     gk_time_end(ctx, 3);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
@@ -461,12 +488,30 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
     size_t smem_push = 0;
     int rc0 = launch_gfull<T, D>(ctx, e, nullptr, &smem_push);
     if (rc0) return rc0;
+    int blk = 0;
     for (int n0 = 0; n0 < N; n0 += NB) {
         const int nb = std::min(NB, N - n0);
         int rc = (sizeof(T) == 4 && !e->chol_f64) ? launch_seq4_ch<T, float, D>(ctx, e, n0, nb, inv_sigma_F)
                                                   : launch_seq4_ch<T, double, D>(ctx, e, n0, nb, inv_sigma_F);
         if (rc) return rc;
-        if ((rc = launch_push<T, D>(ctx, e, n0, nb, smem_push))) return rc;
+        // Push of this block's change.  Only the strip holding the NEXT block's columns is needed before the next
+        // k_eig_seq4; every other strip goes to a second stream and runs under it.  Ordering: rest(b) after seq4(b)
+        // (evE); strip pushes and seq4 of later blocks after rest(b-1) (evR) -- so no two kernels ever touch the same
+        // rows of G at once, and the dphi buffer of block b is not rewritten (by seq4(b+2)) before rest(b) is done.
+        const int next0 = n0 + nb, q = blk & 1;
+        if (blk > 0 && e->overlap_push) GK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, e->evR[q ^ 1], 0));
+        if (!e->overlap_push || next0 >= N) {
+            if ((rc = launch_push<T, D>(ctx, e, n0, nb, smem_push))) return rc;
+        } else {
+            const int cbu = next0 / GK_EF_COLS;
+            GK_CUDA(ctx, cudaEventRecord(e->evE[q], ctx->stream));
+            GK_CUDA(ctx, cudaStreamWaitEvent(e->s2, e->evE[q], 0));
+            if ((rc = launch_push<T, D>(ctx, e, n0, nb, smem_push, e->s2, cbu))) return rc;
+            GK_CUDA(ctx, cudaEventRecord(e->evR[q], e->s2));
+            if ((rc = launch_push_cols<T, D>(ctx, e, n0, nb, cbu * GK_EF_COLS, std::min(GK_EF_COLS, e->net->ld - cbu * GK_EF_COLS)))) return rc;
+            std::swap(e->dphi, e->dphi2);
+        }
+        ++blk;
     }
     k_eig_gstats<D><<<64, 512, 0, ctx->stream>>>(e->G, e->F, N, e->glob, e->probit, e->spart);
     GK_CHECK_LAUNCH(ctx);

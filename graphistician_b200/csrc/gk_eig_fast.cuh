@@ -208,10 +208,11 @@ __global__ void k_eig_greduce(const ACC *__restrict__ partial, int nchunks, size
 template <typename T, int D>
 __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_push(const T *__restrict__ S, const uint8_t *__restrict__ Asym, int ld,
                                                                 int N, const typename gk_eacc<T>::type *__restrict__ dphi, int n0,
-                                                                int nb, double *__restrict__ G, int probit) {
+                                                                int nb, double *__restrict__ G, int probit, int skip_cb) {
     typedef typename gk_eacc<T>::type ACC;
     constexpr int PA = gk_edim<D>::PA, PH = gk_edim<D>::PH, NB = gk_eig_nb<T>::NB;
     extern __shared__ __align__(16) unsigned char smem_raw[];
+    if ((int)blockIdx.x == skip_cb) return;                      // that column strip is pushed by k_eig_push_cols
     // the whole [nb x 128] tile of S and Asym is staged at once (one exposure to HBM latency); the S area doubles as fold scratch
     T *Ssm = (T *)smem_raw;                                       // [NB][128]
     uint8_t *Asm = (uint8_t *)(Ssm + (size_t)NB * GK_EF_COLS);    // [NB][128]
@@ -242,6 +243,91 @@ __global__ void __launch_bounds__(GK_EF_THREADS, 2) k_eig_push(const T *__restri
 #pragma unroll
         for (int p = 0; p < PH; ++p)
             if (p < np) { out[p] += (double)acc[0][p]; out[PA + p] += (double)acc[1][p]; }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------------
+// k_eig_push_cols: the same update for a narrow column range [c0, c0+ncols) -- the columns of the NEXT node block,
+// which the next k_eig_seq4 needs at once, while k_eig_push covers every other strip on a second stream, overlapped
+// with that k_eig_seq4 (gk_eig.cu: sweep_F_fast).  One warp per column, lanes over the block's rows, 8 columns per
+// CTA so the strip is spread over 16 SMs and finishes in a few microseconds.
+// ---------------------------------------------------------------------------------------------------
+#define GK_EPC_COLS 8
+// recursive halving: after the steps LEN = 64, 32, 16, 8, 4 lane l holds the warp totals of entries 2l and 2l+1
+template <typename ACC, int LEN>
+__device__ __forceinline__ void gk_fold_step(ACC (&a)[64], int lane) {
+    constexpr int H = LEN / 2, O = LEN / 4;
+    const bool up = (lane & O) != 0;
+#pragma unroll
+    for (int p = 0; p < H; ++p) {
+        const ACC send = up ? a[p] : a[p + H];
+        const ACC keep = up ? a[p + H] : a[p];
+        a[p] = keep + __shfl_xor_sync(0xffffffffu, send, O);
+    }
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(32 * GK_EPC_COLS) k_eig_push_cols(const T *__restrict__ S, const uint8_t *__restrict__ Asym, int ld,
+                                                                     int N, const typename gk_eacc<T>::type *__restrict__ dphi,
+                                                                     int n0, int nb, double *__restrict__ G, int probit, int c0,
+                                                                     int ncols) {
+    typedef typename gk_eacc<T>::type ACC;
+    constexpr int Pn = gk_edim<D>::P, PA = gk_edim<D>::PA, NB = gk_eig_nb<T>::NB, R = NB / 32;
+    constexpr int VEC = 16 / sizeof(ACC);
+    static_assert(PA <= 64, "gk_fold_step holds 64 entries");
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    const int col = c0 + blockIdx.x * GK_EPC_COLS + w;
+    const bool live = w + (int)blockIdx.x * GK_EPC_COLS < ncols && col < N;
+    const int mlow = (col >= n0 && col < n0 + nb) ? col : -1;
+    ACC sv[R], av[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int m = lane + 32 * r, mg = n0 + m;
+        const bool keep = live && m < nb && mg > mlow;
+        ACC s = ACC(0), a = ACC(0);
+        if (keep) {
+            const ACC x = (ACC)__ldg(S + (size_t)mg * ld + col);
+            if (probit) { s = mg != col ? ACC(2) : ACC(0); a = x; }
+            else { s = x; a = (ACC)__ldg(Asym + (size_t)mg * ld + col); }
+        }
+        sv[r] = s; av[r] = a;
+    }
+    ACC acc[64];
+#pragma unroll
+    for (int p = 0; p < 64; ++p) acc[p] = ACC(0);
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const ACC *ph = dphi + (size_t)min(lane + 32 * r, nb - 1) * PA;        // rows >= nb carry zero weights
+        if constexpr (PA % VEC == 0 && sizeof(ACC) == 4) {
+#pragma unroll
+            for (int q = 0; q < PA / 4; ++q) {
+                const float4 v = __ldg((const float4 *)ph + q);
+                acc[4 * q + 0] += (4 * q + 0 < Pn ? sv[r] : av[r]) * v.x;
+                acc[4 * q + 1] += (4 * q + 1 < Pn ? sv[r] : av[r]) * v.y;
+                acc[4 * q + 2] += (4 * q + 2 < Pn ? sv[r] : av[r]) * v.z;
+                acc[4 * q + 3] += (4 * q + 3 < Pn ? sv[r] : av[r]) * v.w;
+            }
+        } else if constexpr (PA % VEC == 0 && sizeof(ACC) == 8) {
+#pragma unroll
+            for (int q = 0; q < PA / 2; ++q) {
+                const double2 v = __ldg((const double2 *)ph + q);
+                acc[2 * q + 0] += (2 * q + 0 < Pn ? sv[r] : av[r]) * v.x;
+                acc[2 * q + 1] += (2 * q + 1 < Pn ? sv[r] : av[r]) * v.y;
+            }
+        } else {
+#pragma unroll
+            for (int p = 0; p < PA; ++p) acc[p] += (p < Pn ? sv[r] : av[r]) * __ldg(ph + p);
+        }
+    }
+    gk_fold_step<ACC, 64>(acc, lane);
+    gk_fold_step<ACC, 32>(acc, lane);
+    gk_fold_step<ACC, 16>(acc, lane);
+    gk_fold_step<ACC, 8>(acc, lane);
+    gk_fold_step<ACC, 4>(acc, lane);
+    if (live) {
+        double *out = G + (size_t)col * PA;
+        if (2 * lane < PA) out[2 * lane] += (double)acc[0];
+        if (2 * lane + 1 < PA) out[2 * lane + 1] += (double)acc[1];
     }
 }
 

@@ -111,7 +111,10 @@ size_t gk_eig_device_bytes(gk_eig *eig);
 enum { GK_EIG_OPT_CHOL_F64 = 0,
        /* 1 (default): unsharded gk_eig_resample_F keeps a running contraction G for all nodes (one full pass + per-block
         * pushes); 0: re-contract a slab of S per node block (the form the row-sharded block API uses) */
-       GK_EIG_OPT_FAST_SWEEP = 1 };
+       GK_EIG_OPT_FAST_SWEEP = 1,
+       /* 1 (default): within the running-G sweep, the push of block b's change to all strips except the next block's
+        * runs on a second stream under the serial kernel of block b+1; 0: everything on the context stream */
+       GK_EIG_OPT_OVERLAP_PUSH = 2 };
 int gk_eig_set_option(gk_ctx *ctx, gk_eig *eig, int option, int value);
 /* upload the model attributes F (N x D), mu_0, lmbda (D)  (eigenmodel.py:41-73 state) */
 int gk_eig_set_params(gk_ctx *ctx, gk_eig *eig, const double *F, double mu0, const double *lmbda);

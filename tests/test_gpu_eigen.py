@@ -95,6 +95,30 @@ def test_feature_sweep_f32_storage(N, D, chol64):
     assert np.allclose(F_gpu, F_ref, rtol=1e-2, atol=2e-3)
 
 
+@pytest.mark.parametrize("dtype,N,D", [("f64", 450, 8), ("f32", 700, 3), ("f64", 129, 2)])
+def test_feature_sweep_push_overlap_is_equivalent(dtype, N, D):
+    """GK_EIG_OPT_OVERLAP_PUSH (second-stream push under the next block's serial kernel) and
+    GK_EIG_OPT_FAST_SWEEP = 0 (slab form) give the sweep of the plain single-stream running-G form."""
+    from graphistician_b200 import DeviceNetwork
+    from graphistician_b200.device import DeviceEigenmodel
+    A, O, F, lm, mu0, z = _problem(N, D, 77 + N)
+    outs = []
+    for fast, overlap in ((1, 1), (1, 0), (0, 0)):
+        net = DeviceNetwork(A, None, dtype=dtype)
+        eig = DeviceEigenmodel(net, D)
+        eig.set_option(1, fast)                    # GK_EIG_OPT_FAST_SWEEP
+        eig.set_option(2, overlap)                 # GK_EIG_OPT_OVERLAP_PUSH
+        eig.set_params(F, mu0, lm)
+        eig.set_S(O + O.T)
+        for _ in range(2):                         # two sweeps: the second starts from the first one's F
+            F_gpu, st, prec, h = eig.resample_F(1.1, z, want_conditionals=True)
+        outs.append((F_gpu, st["Pq"], st["hS"], st["hK"], prec, h))
+    tol = dict(rtol=1e-8, atol=1e-9) if dtype == "f64" else dict(rtol=2e-2, atol=5e-3)
+    for other in outs[1:]:
+        for a, b in zip(outs[0], other):
+            assert np.allclose(a, b, **tol)
+
+
 def test_pg_draw_symmetric_and_moments():
     from graphistician_b200 import DeviceNetwork
     from graphistician_b200.device import DeviceEigenmodel
