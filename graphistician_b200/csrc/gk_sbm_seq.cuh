@@ -26,7 +26,11 @@ __global__ void k_lp_from_stats(const double *__restrict__ stats, gk_tables Tb, 
         double v = 0.0;
         if (lane < K) {
             v = Tb.logm[lane] + Tb.selfc[lane];
-            for (int j = 0; j < KS; ++j) v += so[j] * Tb.COt[(size_t)j * K + lane] + si[j] * Tb.CIt[(size_t)j * K + lane];
+            // same summation order as the plain loop; unrolled so that the 4 loads of 8 terms are in flight together
+            // (the un-unrolled loop was one L1 round trip per term: 35 us per block, 3.6 % issue-active)
+            const double *co = Tb.COt + lane, *ci = Tb.CIt + lane;
+#pragma unroll 8
+            for (int j = 0; j < KS; ++j) v += __ldg(so + j) * __ldg(co + (size_t)j * K) + __ldg(si + j) * __ldg(ci + (size_t)j * K);
             if (diagA[n]) {
                 double x[S]; x[0] = 1.0;
 #pragma unroll
@@ -198,46 +202,50 @@ __global__ void __launch_bounds__(GK_SEQ_THREADS, 1) k_sbm_seq2(gk_seq_params P)
     if (tid < K) { double t = 0.0; for (int k2 = 0; k2 < K; ++k2) t += (double)ssz[k2] * L1s[tid * K + k2]; T0[tid] = t; }
     __syncthreads();
     const size_t esz = B * sizeof(T);
+    const int W = K <= 16 ? 16 : 32, npw = 32 / W, sub = lane / W, l = lane % W;
+    const unsigned hbits = W == 32 ? 0xffffffffu : 0xffffu, hmask = hbits << (W * sub);
     int cursor = 0, window = 64;
     unsigned long long changed = 0;
     while (cursor < nb) {
         const int wend = min(nb, cursor + window);
         if (prof) tk = gk_sbm_clock();
-        for (int i = cursor + warp; i < wend; i += GK_SEQ_WARPS) {
-            const int n = P.n0 + i;
-            if (n >= P.N) { if (lane == 0) s_new[i - cursor] = 255; continue; }
-            const int ci = c_s[i];
-            double v = lane < K ? lp_s[lane * pitch + i] + T0[lane] - L1s[lane * K + ci] : -1e300;
+        // K <= 16: two nodes per warp (one per 16-lane half) -- same shuffle trees, so the same bits as one per warp
+        for (int ib = cursor + npw * warp; ib < wend; ib += npw * GK_SEQ_WARPS) {
+            const int i = ib + sub, n = P.n0 + i;
+            const bool inw = i < wend, act = inw && n < P.N;
+            const int ci = act ? c_s[i] : 0;
+            double v = (act && l < K) ? lp_s[l * pitch + i] + T0[l] - L1s[l * K + ci] : -1e300;
             double mx = v;
-            for (int o = 16; o; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o));
-            double e = lane < K ? exp(v - mx) : 0.0;
-            int newc;
+            for (int o = W >> 1; o; o >>= 1) mx = fmax(mx, __shfl_xor_sync(0xffffffffu, mx, o, W));
+            double e = (act && l < K) ? exp(v - mx) : 0.0;
+            const double un = act ? u_s[i] : 0.0;
+            unsigned bal;
             if (P.sampler == GK_SAMPLER_CUMSUM) {
                 double cum = e;
-                for (int o = 1; o < 32; o <<= 1) { double t = __shfl_up_sync(0xffffffffu, cum, o); if (lane >= o) cum += t; }
-                double tot = __shfl_sync(0xffffffffu, cum, K - 1);
-                double r = u_s[i] * tot;
-                newc = __popc(__ballot_sync(0xffffffffu, lane < K && r > cum));
+                for (int o = 1; o < W; o <<= 1) { double t = __shfl_up_sync(0xffffffffu, cum, o, W); if (l >= o) cum += t; }
+                double tot = __shfl_sync(0xffffffffu, cum, K - 1, W);
+                double r = un * tot;
+                bal = __ballot_sync(0xffffffffu, l < K && r > cum);
             } else {
                 double tot = e;
-                for (int o = 16; o; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
+                for (int o = W >> 1; o; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o, W);
                 double cum = e / tot;
-                for (int o = 1; o < 32; o <<= 1) { double t = __shfl_up_sync(0xffffffffu, cum, o); if (lane >= o) cum += t; }
-                newc = __popc(__ballot_sync(0xffffffffu, lane < K && cum < u_s[i]));
+                for (int o = 1; o < W; o <<= 1) { double t = __shfl_up_sync(0xffffffffu, cum, o, W); if (l >= o) cum += t; }
+                bal = __ballot_sync(0xffffffffu, l < K && cum < un);
             }
-            newc = min(newc, K - 1);
-            if (P.out_lp && lane < K) P.out_lp[(size_t)n * K + lane] = v;
-            if (lane == 0) s_new[i - cursor] = (unsigned char)newc;
-            if (newc != ci) {
+            const int newc = min(__popc((bal >> (W * sub)) & hbits), K - 1);
+            if (act && P.out_lp && l < K) P.out_lp[(size_t)n * K + l] = v;
+            if (inw && l == 0) s_new[i - cursor] = act ? (unsigned char)newc : 255;
+            if (act && newc != ci) {                         // uniform over the half-warp
                 int prev = 0;
-                if (lane == 0) prev = atomicMin(&s_first, i);
-                prev = __shfl_sync(0xffffffffu, prev, 0);
+                if (l == 0) prev = atomicMin(&s_first, i);
+                prev = __shfl_sync(hmask, prev, 0, W);
                 if (i < prev) {                              // earliest mover so far: warm L2 with its row segments
                     const size_t off = (size_t)(n - P.row0) * P.ld + P.n0;
-                    for (int b = lane * 128; b < nb; b += 32 * 128) { gk_prefetch_l2(P.A + off + b); gk_prefetch_l2(P.At + off + b); }
+                    for (int bb = l * 128; bb < nb; bb += W * 128) { gk_prefetch_l2(P.A + off + bb); gk_prefetch_l2(P.At + off + bb); }
                     if constexpr (B > 0)
-                        for (size_t b = (size_t)lane * 128; b < nb * esz; b += 32 * 128) {
-                            gk_prefetch_l2((const char *)P.W + off * esz + b); gk_prefetch_l2((const char *)P.Wt + off * esz + b);
+                        for (size_t bb = (size_t)l * 128; bb < nb * esz; bb += W * 128) {
+                            gk_prefetch_l2((const char *)P.W + off * esz + bb); gk_prefetch_l2((const char *)P.Wt + off * esz + bb);
                         }
                 }
             }
@@ -305,7 +313,7 @@ __global__ void __launch_bounds__(GK_SEQ_THREADS, 1) k_sbm_seq2(gk_seq_params P)
             s_first = 0x7fffffff;
         }
         changed++;
-        cursor = first + 1; window = max(32, window / 2);
+        cursor = first + 1; window = max(32 * npw, window / 2);
         if (prof) { long long t = gk_sbm_clock(); pc[4] += t - tk; tk = t; }
         __syncthreads();
         if (prof) { long long t = gk_sbm_clock(); pc[5] += t - tk; tk = t; }

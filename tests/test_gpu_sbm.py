@@ -80,7 +80,8 @@ def _count_changes(A, W, c, m, p, mus, sig, u, mode, beta, sampler):
 
 
 @pytest.mark.parametrize("N,K,B,dtype,bn", [(50, 5, 2, "f64", 0), (200, 16, 2, "f64", 64), (333, 7, 1, "f64", 128),
-                                            (200, 16, 2, "f32", 0), (130, 3, 2, "f64", 64), (257, 32, 2, "f64", 0)])
+                                            (200, 16, 2, "f32", 0), (130, 3, 2, "f64", 64), (257, 32, 2, "f64", 0),
+                                            (300, 4, 1, "f32", 64), (500, 16, 2, "f32", 128), (512, 8, 1, "f64", 64)])
 def test_sweep_old_api_shared_c(N, K, B, dtype, bn):
     from graphistician_b200 import _lib
     A, W, c, m, p, mus, sig, u = _problem(7 * N + K, N, K, B)
