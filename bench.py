@@ -230,6 +230,9 @@ def setup_workload(args, rank):
                     algo_bytes=3.0 * N * N * (1 + B * s_W),       # K1 pass + K2 row pass + column pass
                     h2d=N * N * (1 + B * 4) + N * (1 + 8 * B) + N * 12 + 8 * K * K * (2 + B + B * B),
                     d2h=N * 4 + 8 * K * K * (1 + B + B * B) + 8, dominant=(0, "k_strip_stats"),
+                    # ncu --set full, dram read+write per launch averaged over the 17 launches of a sweep (16 block passes
+                    # at 306.15 MB, profiles/r1_sbm_full_v3.csv; the cell pass at 2441.7 MB, r1_sbm_strip_n16384_full.csv)
+                    traffic=(16 * 306.15e6 + 2441.67e6) / 17 if (N, K, B, args.dtype) == (16384, 16, 2, "f32") else None,
                     cpu_baseline=cpu_baseline_sbm,
                     config={"workload": "gaussian_sbm_gibbs_sweep N=%d K=%d B=%d (configs[1] model at the metric's N)" % (N, K, B),
                             "N": N, "K": K, "B": B})
@@ -241,6 +244,9 @@ def setup_workload(args, rank):
         return dict(N=N, data=d, model=model, network=network,
                     algo_bytes=1.0 * N * N * (2 * s_O + 1),       # write S + read S + read A
                     h2d=N * N + N * D * 16 + 8 * D + 8, d2h=N * D * 8 + 8 * 68 + 8, dominant=(3, "k_eig_gfull+k_eig_push"),
+                    # ncu --set full (profiles/r1_eig_n16384_full_v2.csv, r1_eig_full_v3.csv): gfull 1361.5 MB, 128 pushes at
+                    # 17.23 MB (10.5 MB of S/Asym + the G rows read and written), 127 strip pushes at 0.18 MB; per launch
+                    traffic=(1361.5e6 + 128 * 17.23e6 + 127 * 0.18e6) / 256 if (N, D, args.dtype) == (16384, 8, "f32") else None,
                     cpu_baseline=cpu_baseline_eigen,
                     config={"workload": "logistic_eigenmodel_pg_gibbs_sweep N=%d D=%d lmbda given (configs[2])" % (N, D),
                             "N": N, "D": D})
@@ -253,6 +259,7 @@ def setup_workload(args, rank):
                     algo_bytes=22.0 * N * N + 1.0 * N * N * (1 + Bw * 4),   # 11 + 11 pair passes + NIW statistics
                     h2d=N * N * (1 + Bw * 4) + N * dim * 8 + N * (1 + 8 * Bw), d2h=N * dim * 8 + 64,
                     dominant=(4, "k_latent_pair"), cpu_baseline=cpu_baseline_latent,
+                    traffic=139.6e6 if (N, args.dtype) == (16384, "f32") else None,   # profiles/r1_latent_n16384_full.csv
                     config={"workload": "latent_distance_hmc_gibbs_sweep + NIW weights N=%d dim=%d B=%d (configs[3])" % (N, dim, Bw),
                             "N": N, "dim": dim, "B": Bw})
     raise SystemExit("workload %s: not built yet" % args.workload)
@@ -330,6 +337,7 @@ def run_ours(args):
                 "d2h_bytes_per_step": int(d2h)},
         "roofline": {"bound": "hbm", "kernel": wl["dominant"][1], "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": wl.get("traffic"),
+                     "algorithmic_bytes_per_launch": (kbytes / kn) if kn else None,
                      "peak_source": "measured" if peaks else "fallback",
                      "launches_per_sweep": kn / 3.0, "kernel_ms_per_sweep": kms / 3.0,
                      "other_kernels_ms_per_sweep": {names[f]: fam[f][0] / 3.0 for f in fam if fam[f][1] and f != wl["dominant"][0]},
