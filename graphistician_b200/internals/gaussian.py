@@ -154,6 +154,36 @@ class Gaussian(object):
         chol = np.linalg.cholesky(sigma_mf)
         return -2 * np.log(np.diag(chol)).sum() + D * np.log(2) + psi((nu_mf - np.arange(D)) / 2.0).sum()
 
+    def get_vlb(self):
+        """NIW part of the variational bound, E_q[ln p(mu, Sigma)] + H[q(mu, Sigma)] = -KL(q || prior) -- what
+        pybasicbayes' ``Gaussian.get_vlb`` returns (Bishop 10.74 and 10.77 without the sum over components); the
+        reference calls it per block pair at stochastic_block_model.py:564-566."""
+        from scipy.special import gammaln, psi
+
+        def iw_log_partition(sigma, nu):
+            D = sigma.shape[0]
+            half_logdet = np.log(np.diag(np.linalg.cholesky(sigma))).sum()
+            return -(nu * half_logdet - (nu * D / 2.0 * np.log(2) + D * (D - 1) / 4.0 * np.log(np.pi)
+                                         + gammaln((nu - np.arange(D)) / 2.0).sum()))
+
+        def iw_entropy(sigma, nu):
+            D = sigma.shape[0]
+            half_logdet = np.log(np.diag(np.linalg.cholesky(sigma))).sum()
+            E_logdet_lmbda = psi((nu - np.arange(D)) / 2.0).sum() + D * np.log(2) - 2 * half_logdet
+            return iw_log_partition(sigma, nu) - (nu - D - 1) / 2.0 * E_logdet_lmbda + nu * D / 2.0
+
+        D = self.D
+        mu_mf, sigma_mf, kappa_mf, nu_mf = self._natural_to_standard(self.mf_natural_hypparam)
+        sigma_mf = 0.5 * (sigma_mf + sigma_mf.T)
+        llt = self._loglmbdatilde()
+        q_entropy = -0.5 * (llt + D * (np.log(kappa_mf / (2 * np.pi)) - 1)) + iw_entropy(sigma_mf, nu_mf)
+        dmu = mu_mf - self.mu_0
+        p_avgengy = 0.5 * (D * np.log(self.kappa_0 / (2 * np.pi)) + llt - D * self.kappa_0 / kappa_mf
+                           - self.kappa_0 * nu_mf * dmu.dot(np.linalg.solve(sigma_mf, dmu))) \
+            - iw_log_partition(self.sigma_0, self.nu_0) + (self.nu_0 - D - 1) / 2.0 * llt \
+            - 0.5 * nu_mf * np.trace(np.linalg.solve(sigma_mf, self.sigma_0))
+        return float(p_avgengy + q_entropy)
+
     def _resample_from_mf(self, rng=np.random):
         mu_n, sigma_n, kappa_n, nu_n = self._natural_to_standard(self.mf_natural_hypparam)
         self.sigma = invwishart_draw(0.5 * (sigma_n + sigma_n.T), nu_n, rng)

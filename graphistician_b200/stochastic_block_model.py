@@ -349,6 +349,33 @@ class _MeanFieldSBM(_StochasticBlockModelBase):
     def expected_log_likelihood(self, network):
         raise NotImplementedError()               # :531-532
 
+    def get_vlb(self):
+        """:536-568.  Host arithmetic over N*C + C*C terms, as in the reference (no N^2 work): cross entropies minus
+        negentropies of q(c), q(p), q(m), plus the weight models' NIW terms.  Like the reference it holds no data term."""
+        from scipy.special import gammaln
+        E_ln_m = self.mf_expected_log_m()
+        vlb = float(self.mf_m.dot(E_ln_m).sum())                                   # Discrete().negentropy(E_x, E_ln_p)
+        with np.errstate(divide="ignore", invalid="ignore"):
+            vlb -= float(np.nan_to_num((self.mf_m * np.log(self.mf_m)).sum(1)).sum())   # Discrete(mf_m[n]).negentropy()
+
+        def dirichlet_negentropy(gamma, E_ln_g):                                   # internals/distributions.py:327-340
+            return float(gammaln(gamma.sum(-1, keepdims=True)).sum() - gammaln(gamma).sum() + ((gamma - 1) * E_ln_g).sum())
+
+        E_ln_p = psi(self.mf_tau1) - psi(self.mf_tau0 + self.mf_tau1)
+        E_ln_notp = psi(self.mf_tau0) - psi(self.mf_tau0 + self.mf_tau1)
+        E_q = np.stack([E_ln_p, E_ln_notp], -1)
+        # Beta(tau1, tau0).negentropy(E_ln_p, E_ln_notp), literally: with scalar hyperparameters gamma has shape (1, 2), so
+        # the log normaliser enters once while the (gamma - 1) E[ln g] term broadcasts over all C x C cells
+        tau = np.concatenate((np.atleast_1d(self.tau1)[..., None], np.atleast_1d(self.tau0)[..., None]), -1).astype(float)
+        vlb += dirichlet_negentropy(tau, E_q)
+        vlb -= dirichlet_negentropy(np.stack([self.mf_tau1, self.mf_tau0], -1), E_q)   # Beta(mf_tau1, mf_tau0).negentropy()
+        vlb += dirichlet_negentropy(np.asarray(self.pi, float), E_ln_m)
+        vlb -= dirichlet_negentropy(np.asarray(self.mf_pi, float), E_ln_m)
+        for c1 in range(self.C):
+            for c2 in range(self.C):
+                vlb += self.weight_models[c1][c2].get_vlb()
+        return vlb
+
     def resample_from_mf(self):
         """:570-584"""
         self.m = np.random.dirichlet(self.mf_pi)

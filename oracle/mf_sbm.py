@@ -282,3 +282,72 @@ def mf_update_p(A, mf_m, tau1, tau0, mf_tau1, mf_tau0, stepsize=1.0):
     ms = mf_m.sum(0)
     n0 = np.outer(ms, ms) - n1
     return ((1.0 - stepsize) * mf_tau1 + stepsize * (tau1 + n1), (1.0 - stepsize) * mf_tau0 + stepsize * (tau0 + n0))
+
+
+# ---- variational lower bound (stochastic_block_model.py:536-568) ---------------------------------------------------
+def discrete_negentropy(p, E_x=None, E_ln_p=None):
+    """internals/distributions.py:36-50 (nan_to_num on the SUM: a vector with an exact zero gives 0)."""
+    E_x = p if E_x is None else E_x
+    with np.errstate(divide="ignore", invalid="ignore"):
+        E_ln_p = np.log(p) if E_ln_p is None else E_ln_p
+        return np.nan_to_num(E_x.dot(E_ln_p))
+
+
+def dirichlet_negentropy(gamma, E_ln_g=None):
+    """internals/distributions.py:327-340"""
+    from scipy.special import gammaln
+    gamma = np.asarray(gamma, dtype=np.float64)
+    if E_ln_g is None:
+        E_ln_g = psi(gamma) - psi(gamma.sum(axis=-1, keepdims=True))
+    return gammaln(gamma.sum(axis=-1, keepdims=True)).sum() - gammaln(gamma).sum() + ((gamma - 1) * E_ln_g).sum()
+
+
+def beta_negentropy(tau1, tau0, E_ln_p=None, E_ln_notp=None):
+    """internals/distributions.py:343-372 (gamma = [tau1, tau0] on a new last axis, after atleast_1d)."""
+    gamma = np.concatenate((np.atleast_1d(tau1)[..., None], np.atleast_1d(tau0)[..., None]), axis=-1)
+    E_ln_g = None
+    if E_ln_p is not None and E_ln_notp is not None:
+        E_ln_g = np.concatenate((E_ln_p[..., None], E_ln_notp[..., None]), axis=-1)
+    return dirichlet_negentropy(gamma, E_ln_g)
+
+
+def niw_vlb(mu_0, sigma_0, kappa_0, nu_0, mu_mf, sigma_mf, kappa_mf, nu_mf):
+    """pybasicbayes ``Gaussian.get_vlb`` (dependency absent from /root/reference: restated from Bishop 10.74 / 10.77,
+    parity unpinned by the reference; pinned instead by the identity  get_vlb = -KL(q || prior)  in tests/test_oracle_mf.py:
+    zero at q = prior and equal to a Monte Carlo estimate of E_q[ln p - ln q])."""
+    from scipy.special import gammaln
+    D = len(mu_0)
+
+    def logZ(sigma, nu):
+        hl = np.log(np.diag(np.linalg.cholesky(sigma))).sum()
+        return -(nu * hl - (nu * D / 2.0 * np.log(2) + D * (D - 1) / 4.0 * np.log(np.pi) + gammaln((nu - np.arange(D)) / 2.0).sum()))
+
+    hl = np.log(np.diag(np.linalg.cholesky(sigma_mf))).sum()
+    E_logdet_lmbda = psi((nu_mf - np.arange(D)) / 2.0).sum() + D * np.log(2) - 2 * hl
+    iw_entropy = logZ(sigma_mf, nu_mf) - (nu_mf - D - 1) / 2.0 * E_logdet_lmbda + nu_mf * D / 2.0
+    llt = loglmbdatilde(sigma_mf, nu_mf)
+    q_entropy = -0.5 * (llt + D * (np.log(kappa_mf / (2 * np.pi)) - 1)) + iw_entropy
+    d = mu_mf - mu_0
+    p_avg = 0.5 * (D * np.log(kappa_0 / (2 * np.pi)) + llt - D * kappa_0 / kappa_mf
+                   - kappa_0 * nu_mf * d.dot(np.linalg.solve(sigma_mf, d))) \
+        - logZ(sigma_0, nu_0) + (nu_0 - D - 1) / 2.0 * llt - 0.5 * nu_mf * np.trace(np.linalg.solve(sigma_mf, sigma_0))
+    return p_avg + q_entropy
+
+
+def sbm_vlb_loops(mf_m, pi, mf_pi, tau1, tau0, mf_tau1, mf_tau0, niw_terms):
+    """stochastic_block_model.py:536-568, statement by statement; niw_terms[c1][c2] = weight_models[c1][c2].get_vlb()."""
+    N, C = mf_m.shape
+    vlb = 0.0
+    E_ln_m = psi(mf_pi) - psi(mf_pi.sum())
+    for n in range(N):
+        vlb += discrete_negentropy(None, E_x=mf_m[n, :], E_ln_p=E_ln_m)
+        vlb -= discrete_negentropy(mf_m[n, :])
+    vlb += beta_negentropy(tau1, tau0, E_ln_p=psi(mf_tau1) - psi(mf_tau0 + mf_tau1),
+                           E_ln_notp=psi(mf_tau0) - psi(mf_tau0 + mf_tau1)).sum()
+    vlb -= beta_negentropy(mf_tau1, mf_tau0).sum()
+    vlb += dirichlet_negentropy(pi, E_ln_g=E_ln_m)
+    vlb -= dirichlet_negentropy(mf_pi)
+    for c1 in range(C):
+        for c2 in range(C):
+            vlb += niw_terms[c1][c2]
+    return vlb

@@ -215,6 +215,24 @@ def make_mf_sbm():
     nat0 = [[M.standard_to_natural(np.zeros(B), np.eye(B), 1.0, B + 2.0) for _ in range(C)] for _ in range(C)]
     nat = M.mf_update_weight_models_loops(Af, W, E_WWT, mf_m, nat0)
     out["w_nat"] = np.array(nat)
+    # get_vlb (stochastic_block_model.py:536-563) without the weight models' terms, by the reference's OWN Discrete /
+    # Beta / Dirichlet classes, statement by statement (scalar tau1 = tau0 = 1 and pi = 1, the class defaults)
+    pi0 = 1.0 * np.ones(C)
+    mf_m0 = mf_m.copy(); mf_m0[3] = np.array([0.0, 0.4, 0.6])       # an exact zero: Discrete.negentropy -> nan_to_num -> 0
+    for tag, mm in (("vlb_nogauss", mf_m), ("vlb_nogauss_zero", mf_m0)):
+        from scipy.special import psi as _psi
+        vlb = 0
+        E_ln_m = _psi(mf_pi) - _psi(mf_pi.sum())
+        for n in range(N):
+            vlb += dist.Discrete().negentropy(E_x=mm[n, :], E_ln_p=E_ln_m)
+            with np.errstate(divide="ignore", invalid="ignore"):
+                vlb -= dist.Discrete(mm[n, :]).negentropy()
+        vlb += dist.Beta(1.0, 1.0).negentropy(E_ln_p=(_psi(t1) - _psi(t0 + t1)), E_ln_notp=(_psi(t0) - _psi(t0 + t1))).sum()
+        vlb -= dist.Beta(t1, t0).negentropy().sum()
+        vlb += dist.Dirichlet(pi0).negentropy(E_ln_g=E_ln_m)
+        vlb -= dist.Dirichlet(mf_pi).negentropy()
+        out[tag] = float(vlb)
+    out["mf_m_zero"] = mf_m0
     np.savez(os.path.join(HERE, "mf_sbm_small.npz"), **out)
     print("mf_sbm_small.npz")
 
