@@ -288,6 +288,34 @@ class _MeanFieldLogisticEigenModel(_LogisticEigenmodelBase):
         self.mf_Sigma_lmbda = (1.0 - stepsize) * self.mf_Sigma_lmbda + stepsize * np.linalg.inv(post_prec)
         self.mf_mu_lmbda = (1.0 - stepsize) * self.mf_mu_lmbda + stepsize * self.mf_Sigma_lmbda.dot(post_mean_dot_prec)
 
+    def get_vlb(self):
+        """:1262-1298.  Prior and entropy terms of q(mu0), q(F), q(lmbda) -- N * D^2 host arithmetic, no N^2 work; the
+        reference leaves the likelihood term out (the entropy of q(omega) is unknown).  Gaussian.negentropy's constant is
+        -0.5 log 2 pi whatever D (internals/distributions.py:302), kept."""
+        D = self.D
+        c = -0.5 * np.log(2 * np.pi)
+
+        def cross(mu, sig_iso, E_x, E_xxT):           # Gaussian(mu, sig_iso I).negentropy(E_x, E_xxT)
+            return c - 0.5 * D * np.log(sig_iso) - 0.5 * np.trace(E_xxT) / sig_iso + E_x.dot(mu) / sig_iso - 0.5 * mu.dot(mu) / sig_iso
+
+        def own(mu, Sigma):                           # Gaussian(mu, Sigma).negentropy()
+            Si = np.linalg.inv(Sigma)
+            mm = np.outer(mu, mu)
+            return c - 0.5 * np.linalg.slogdet(Sigma)[1] - 0.5 * np.trace(Si.dot(Sigma + mm)) + mu.dot(Si).dot(mu) - 0.5 * np.trace(Si.dot(mm))
+
+        s0, m0 = self.sigma_mu0, self.mu_mu_0
+        vlb = c - 0.5 * np.log(s0) - 0.5 / s0 * self.mf_expected_mu0sq() + self.mf_mu_mu0 * m0 / s0 - 0.5 * m0 ** 2 / s0
+        qs, qm = self.mf_sigma_mu0, self.mf_mu_mu0
+        vlb -= c - 0.5 * np.log(qs) - 0.5 / qs * (qs + qm ** 2) + qm * qm / qs - 0.5 * qm ** 2 / qs
+        zero = np.zeros(D)
+        for n in range(self.N):
+            vlb += cross(zero, self.sigma_F, self.mf_mu_F[n], self.mf_expected_ffT(n))
+            vlb -= own(self.mf_mu_F[n], self.mf_Sigma_F[n])
+        if not self.lmbda_given:
+            vlb += cross(np.asarray(self.mu_lmbda, float), self.sigma_lmbda, self.mf_mu_lmbda, self.mf_expected_llT())
+            vlb -= own(self.mf_mu_lmbda, self.mf_Sigma_lmbda)
+        return float(vlb)
+
     # ---- expectations (:1159-1248; N x N on the host: reporting only) --------------------------------------------
     def mf_expected_mu(self):
         E_mu = self.mf_mu_mu0 + (self.mf_mu_F * self.mf_mu_lmbda[None, :]).dot(self.mf_mu_F.T)

@@ -174,3 +174,46 @@ def meanfieldupdate_lmbda(E_A, E_O, mf_mu_F, mf_Sigma_F, E_mu0, mu_lmbda, sigma_
     new_Sigma = (1.0 - stepsize) * mf_Sigma_lmbda + stepsize * np.linalg.inv(post_prec)
     new_mu = (1.0 - stepsize) * mf_mu_lmbda + stepsize * new_Sigma.dot(h)
     return new_mu, new_Sigma, post_prec, h
+
+
+# ---- variational lower bound (eigenmodel.py:1262-1298) ---------------------------------------------------------------
+def scalar_gaussian_negentropy(mu, sigmasq, E_x=None, E_xsq=None):
+    """internals/distributions.py:130-158 with the distribution's own parameters for mu / sigmasq."""
+    E_x = mu if E_x is None else E_x
+    E_xsq = sigmasq + mu ** 2 if E_xsq is None else E_xsq
+    H = -0.5 * np.log(2 * np.pi)
+    H += -0.5 * np.log(sigmasq)
+    H += -0.5 / sigmasq * E_xsq
+    H += 1.0 / sigmasq * E_x * mu
+    H += -0.5 / sigmasq * mu ** 2
+    return H
+
+
+def gaussian_negentropy(mu, Sigma, E_x=None, E_xxT=None):
+    """internals/distributions.py:278-308 with the distribution's own parameters (note -0.5 log 2 pi, not D times it)."""
+    E_x = mu if E_x is None else E_x
+    E_xxT = Sigma + np.outer(mu, mu) if E_xxT is None else E_xxT
+    Si = np.linalg.inv(Sigma)
+    H = -0.5 * np.log(2 * np.pi)
+    H += -0.5 * np.linalg.slogdet(Sigma)[1]
+    H += -0.5 * np.trace(Si.dot(E_xxT))
+    H += E_x.T.dot(Si).dot(mu)
+    H += -0.5 * np.trace(Si.dot(np.outer(mu, mu)))
+    return H
+
+
+def get_vlb_loops(mu_mu_0, sigma_mu0, sigma_F, mu_lmbda, sigma_lmbda, mf_mu_mu0, mf_sigma_mu0, mf_mu_F, mf_Sigma_F,
+                  mf_mu_lmbda, mf_Sigma_lmbda, lmbda_given=False):
+    """eigenmodel.py:1262-1298, statement by statement (prior / entropy terms only: the reference leaves out the
+    likelihood because the entropy of q(omega) is unknown)."""
+    N, D = mf_mu_F.shape
+    vlb = 0.0
+    vlb += scalar_gaussian_negentropy(mu_mu_0, sigma_mu0, E_x=mf_mu_mu0, E_xsq=mf_sigma_mu0 + mf_mu_mu0 ** 2)
+    vlb -= scalar_gaussian_negentropy(mf_mu_mu0, mf_sigma_mu0)
+    for n in range(N):
+        vlb += gaussian_negentropy(np.zeros(D), sigma_F * np.eye(D), E_x=mf_mu_F[n, :], E_xxT=mf_Sigma_F[n] + np.outer(mf_mu_F[n], mf_mu_F[n]))      # mf_expected_ffT(n), :1226-1232
+        vlb -= gaussian_negentropy(mf_mu_F[n, :], mf_Sigma_F[n, :, :])
+    if not lmbda_given:
+        vlb += gaussian_negentropy(mu_lmbda, sigma_lmbda * np.eye(D), E_x=mf_mu_lmbda, E_xxT=expected_llT(mf_mu_lmbda, mf_Sigma_lmbda))
+        vlb -= gaussian_negentropy(mf_mu_lmbda, mf_Sigma_lmbda)
+    return vlb

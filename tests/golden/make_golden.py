@@ -269,6 +269,19 @@ def make_mf_eigen():
                 out["F_%s_%s_tr%d" % (nm, tag, tr)] = v
     r = M.meanfieldupdate_lmbda_loops(Af, EO, mu, Sg, mu0, 0.0, 2.0, lam, SL, 0.7)
     out.update(lam_new=r[0], SigL_new=r[1], lam_prec=r[2], lam_h=r[3])
+    # get_vlb (eigenmodel.py:1262-1298) by the reference's OWN ScalarGaussian / Gaussian classes, statement by statement
+    _, dist = _import_reference_internals()
+    mu_mu_0, sigma_mu0, sigma_F, mu_lmbda, sigma_lmbda = -1.2, 0.9, 1.5, np.zeros(D), 2.0
+    vlb = 0
+    vlb += dist.ScalarGaussian(mu=mu_mu_0, sigmasq=sigma_mu0).negentropy(E_x=mu0, E_xsq=s0 + mu0 ** 2)
+    vlb -= dist.ScalarGaussian(mu=mu0, sigmasq=s0).negentropy()
+    for n in range(N):
+        vlb += dist.Gaussian(mu=np.zeros(D), Sigma=sigma_F * np.eye(D)).negentropy(E_x=mu[n, :], E_xxT=Sg[n] + np.outer(mu[n], mu[n]))
+        vlb -= dist.Gaussian(mu=mu[n, :], Sigma=Sg[n, :, :]).negentropy()
+    out["vlb_lmbda_given"] = float(vlb)
+    vlb += dist.Gaussian(mu=mu_lmbda, Sigma=sigma_lmbda * np.eye(D)).negentropy(E_x=lam, E_xxT=M.expected_llT(lam, SL))
+    vlb -= dist.Gaussian(mu=lam, Sigma=SL).negentropy()
+    out["vlb"] = float(vlb)
     np.savez(os.path.join(HERE, "mf_eigen_small.npz"), **out)
     print("mf_eigen_small.npz")
 
