@@ -225,7 +225,10 @@ extern "C" int gk_network_upload(gk_ctx *ctx, gk_net *net, const uint8_t *A_rows
             GK_CHECK_LAUNCH(ctx);
         }
     }
-    if (net->Asym) { cudaFree(net->Asym); net->Asym = nullptr; }
+    if (net->Asym) {                                     // a re-upload into a live handle: refresh A + A^T in place
+        int rc = gk_net_refresh_asym(ctx, net);
+        if (rc) return rc;
+    }
     GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));   // host buffers may be reused by the caller
     return GK_OK;
 }

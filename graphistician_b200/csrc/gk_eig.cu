@@ -31,14 +31,18 @@ struct gk_eig {
 
 #define GK_EIG_PA_MAX (GK_EIG_MAXD * (GK_EIG_MAXD + 1) / 2 + 2 * GK_EIG_MAXD)
 
+int gk_net_refresh_asym(gk_ctx *ctx, gk_net *net) {
+    k_eig_asym<<<ctx->num_sms * 8, 256, 0, ctx->stream>>>(net->A, net->At, net->Asym, net->nrows, net->N, net->ld, net->row0);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
 int gk_net_ensure_asym(gk_ctx *ctx, gk_net *net) {
     if (net->Asym) return GK_OK;
     size_t bytes = (size_t)net->nrows * net->ld;
     GK_CUDA(ctx, cudaMalloc(&net->Asym, bytes));
     net->bytes += bytes;
-    k_eig_asym<<<ctx->num_sms * 8, 256, 0, ctx->stream>>>(net->A, net->At, net->Asym, net->nrows, net->N, net->ld, net->row0);
-    GK_CHECK_LAUNCH(ctx);
-    return GK_OK;
+    return gk_net_refresh_asym(ctx, net);
 }
 
 extern "C" int gk_eig_create(gk_ctx *ctx, gk_net *net, int D, gk_eig **out) {

@@ -44,6 +44,7 @@ struct gk_net {
 };
 
 int gk_fail(gk_ctx *ctx, int code, const char *fmt, ...);
+int gk_net_refresh_asym(gk_ctx *ctx, gk_net *net);  // recomputes an existing net->Asym after a re-upload; gk_eig.cu
 int gk_net_ensure_asym(gk_ctx *ctx, gk_net *net);   // builds net->Asym = A + A^T (zero diagonal) once; gk_eig.cu
 void *gk_scratch(gk_ctx *ctx, int slot, size_t bytes);   // returns nullptr (and sets err) on failure
 

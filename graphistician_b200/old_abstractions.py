@@ -44,10 +44,14 @@ class FixedGaussianNetwork(WeightedDirectedNetwork):
         self.W = W
         self.B = 0 if W is None else W.shape[2]
         self._dev = {}
+        self._stale = set()
 
     def device(self, dtype="f32", ctx=None):
         """Device-resident copy (uploaded on first use; see SURVEY.md 8b 'Ownership': data is never mutated)."""
         key = (dtype, id(ctx))
+        if key in self._stale:
+            self._stale.discard(key)
+            self._dev[key].upload(self.A, self.W)
         if key not in self._dev:
             comm = getattr(self, "_comm", None)
             if comm is not None and comm.world > 1:
@@ -60,15 +64,28 @@ class FixedGaussianNetwork(WeightedDirectedNetwork):
     def shard(self, comm):
         """Row-shard the device copy over the ranks of ``comm`` (graphistician_b200.sharding.Comm): each rank then
         uploads only its rows, and every device pass of ``model.resample(network)`` becomes collective."""
-        self.invalidate()
+        self._drop()
         self._comm = comm
         return self
 
-    def invalidate(self):
-        """Drop device copies (call after mutating A or W in place)."""
+    def _drop(self):
+        """Free every device copy."""
         for d in self._dev.values():
             d.close()
         self._dev = {}
+        self._stale = set()
+
+    def invalidate(self):
+        """Call after mutating A or W in place: the next ``device()`` copies the host arrays to the device again.
+        Unsharded copies keep their device allocations (and the model-side state bound to them) and are refilled by
+        ``DeviceNetwork.upload``; sharded copies are dropped and rebuilt."""
+        from .device import DeviceNetwork
+        for key, d in list(self._dev.items()):
+            if type(d) is DeviceNetwork and d.nrows == d.N:
+                self._stale.add(key)
+            else:
+                d.close()
+                del self._dev[key]
 
     def __deepcopy__(self, memo):
         return FixedGaussianNetwork(self.A.copy(), None if self.W is None else self.W.copy())
@@ -129,7 +146,7 @@ def network_for(A, W=None):
         ref, net = ent
         if ref() is A:
             if W is not None and (net.W is None or net._W_id != id(W)):
-                net.invalidate()
+                net._drop()
                 net.__init__(A, W)
                 net._W_id = id(W)
             return net

@@ -227,3 +227,30 @@ def test_model_runs_with_device_rng():
     assert np.allclose(outs[0][0], outs[1][0], rtol=1e-6, atol=1e-9) and np.isclose(outs[0][1], outs[1][1], rtol=1e-9)
     ll0 = LogisticEigenmodel(N, D, p=0.3, lmbda=np.ones(D)).log_likelihood(A)
     assert model.log_likelihood(A) > ll0 - 50.0
+
+
+def test_invalidate_refills_the_device_copy_in_place():
+    """network.invalidate() after an in-place edit of A: same device handle, same allocations, new contents -- including
+    the derived A + A^T the eigenmodel kernels read (bench.py's e2e leg relies on this)."""
+    from graphistician_b200.device import DeviceEigenmodel, DeviceNetwork
+    from graphistician_b200.old_abstractions import FixedGaussianNetwork
+    N, D = 300, 4
+    A, O, F, lm, mu0, z = _problem(N, D, 123)
+    A2 = _problem(N, D, 456)[0]
+    net = FixedGaussianNetwork(A.copy(), None)
+    dev = net.device("f64")
+    eig = DeviceEigenmodel(dev, D)
+    eig.set_params(F, mu0, lm); eig.set_S(O + O.T)
+    first = eig.resample_F(1.0, z)[0]
+    net.A[...] = A2
+    net.invalidate()
+    assert net.device("f64") is dev
+    eig.set_params(F, mu0, lm); eig.set_S(O + O.T)
+    again = eig.resample_F(1.0, z)[0]
+    fresh_net = DeviceNetwork(A2, None, dtype="f64")
+    fresh = DeviceEigenmodel(fresh_net, D)
+    fresh.set_params(F, mu0, lm); fresh.set_S(O + O.T)
+    ref = fresh.resample_F(1.0, z)[0]
+    assert np.array_equal(again, ref) and not np.allclose(first, ref)
+    c = np.random.RandomState(0).randint(0, 3, N)
+    assert np.array_equal(dev.block_stats(c, 3)[0], fresh_net.block_stats(c, 3)[0])
