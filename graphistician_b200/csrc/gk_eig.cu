@@ -402,7 +402,19 @@ static int launch_seq4_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sig
     P.G = e->G; P.dphi = e->dphi; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h; P.probit = e->probit;
     P.prof = e->prof;
     gk_time_begin(ctx, 5, 0.0);
-    k_eig_seq4<T, CH, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
+    if (e->overlap_push) {
+        // programmatic dependent launch: the prologue (tile, feature and normal loads) may run while the preceding
+        // k_eig_push_cols is still in flight; the kernel waits (griddepcontrol.wait) before it reads G / the column sums
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(1); cfg.blockDim = dim3(GK_EIG_SEQ_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = ctx->stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        GK_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_eig_seq4<T, CH, D>, P));
+    } else {
+        k_eig_seq4<T, CH, D><<<1, GK_EIG_SEQ_THREADS, smem, ctx->stream>>>(P);
+    }
     gk_time_end(ctx, 5);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;

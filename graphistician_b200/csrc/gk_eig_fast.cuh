@@ -275,6 +275,7 @@ __global__ void __launch_bounds__(32 * GK_EPC_COLS) k_eig_push_cols(const T *__r
     constexpr int Pn = gk_edim<D>::P, PA = gk_edim<D>::PA, NB = gk_eig_nb<T>::NB, R = NB / 32;
     constexpr int VEC = 16 / sizeof(ACC);
     static_assert(PA <= 64, "gk_fold_step holds 64 entries");
+    asm volatile("griddepcontrol.launch_dependents;" ::: "memory");   // the next k_eig_seq4 may start its prologue now
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     const int col = c0 + blockIdx.x * GK_EPC_COLS + w;
     const bool live = w + (int)blockIdx.x * GK_EPC_COLS < ncols && col < N;

@@ -16,6 +16,9 @@
 // cycle counter the compiler may not move across memory operations or barriers (debug probes, env GK_EIG_PROF).
 // NB: on B200 %clock64 advanced ~0.58 ticks per SM cycle in these kernels (ncu sm__cycles_elapsed vs these counters), so the
 // probes give the SHARE of each phase, not SM cycles; each read also costs tens of cycles.
+// programmatic dependent launch (sm_90+): no-ops unless the kernel was launched with the stream-serialization attribute
+__device__ __forceinline__ void gk_pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void gk_pdl_launch_dependents() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 __device__ __forceinline__ long long gk_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory"); return t; }
 
 // factor prec = L L^T (packed upper, in the factorisation type) and draw f = L^-T (L^-1 h + z): right-looking
@@ -108,7 +111,8 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
     const long long kstart = P.prof ? gk_clock() : 0;
 
     // ---- block entry: in-block tiles of S / Asym (16-byte loads), G rows, features, normals
-    if (tid < D) sF0[tid] = P.glob[GK_EIG_GLOB_SUMF + tid];
+    //      (everything up to gk_pdl_wait() is independent of the kernels just before this one in the stream, so with a
+    //       programmatic launch it runs while k_eig_push_cols is still pushing the previous block's change)
     for (int idx = tid; idx < nb * (NB / VT); idx += GK_EIG_SEQ_THREADS) {
         const int i = idx / (NB / VT), v = idx - i * (NB / VT);
         *(int4 *)(Sb + (size_t)i * NB + v * VT) = __ldg((const int4 *)((const T *)P.Sblk + (size_t)i * P.ldS + v * VT));
@@ -122,6 +126,8 @@ __global__ void __launch_bounds__(GK_EIG_SEQ_THREADS, 1) k_eig_seq4(gk_eig_seq4_
         zc[t] = (CH)P.z[(size_t)n0 * D + t];
         foldC[t] = (C)P.F[(size_t)n0 * D + t];
     }
+    gk_pdl_wait();                                        // G and the running column sums come from the previous kernels
+    if (tid < D) sF0[tid] = P.glob[GK_EIG_GLOB_SUMF + tid];
     __syncthreads();
     for (int t = tid; t < nb * PA; t += GK_EIG_SEQ_THREADS) {
         const int i = t / PA, p = t - i * PA;
