@@ -1,18 +1,23 @@
 #!/usr/bin/env python
 """bench.py -- Gibbs sweeps/s of the B200 engine on BASELINE.json's metric, with roofline and CPU baseline.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--workload sbm|eigen|latent]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+                    [--workload all|sbm|eigen|latent|ais] [--shard chains|rows]
 
 A "step" is one full ``model.resample(network)`` Gibbs sweep on synthetic data (seed 1234, generators of
-SURVEY.md 8d).  Default workload: Gaussian SBM (configs[1] model: K=16, B=2) at the metric's N=16384.
-One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every field.
+SURVEY.md 8d).  The metric names two models -- "Gibbs sweeps/sec at N=16k (SBM, logistic eigenmodel)" -- so the
+default run (``--workload all``) times the Gaussian SBM (configs[1] model: K=16, B=2) at N=16384 as the top-level
+record and the logistic eigenmodel (configs[2]) and the latent-distance model (configs[3]) at N=16384 under
+``workloads``.  One JSON line on stdout (rank 0).  See DESIGN.md "Measurement" for every field.
 """
 import argparse
+import gc
 import json
 import os
 import sys
 import threading
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 import numpy as np
 
@@ -21,6 +26,8 @@ sys.path.insert(0, ROOT)
 
 METRIC = "gibbs_sweeps_per_sec"
 UNIT = "sweeps/s"
+FAMILY = {0: "k_strip_stats", 1: "k_sbm_seq", 2: "k_eig_pg_tile", 3: "k_eig_gfull+k_eig_push", 4: "k_latent_pair",
+          5: "k_eig_seq", 6: "k_strip_soft", 7: "k_mf_seq"}
 
 
 def parse_args():
@@ -29,9 +36,9 @@ def parse_args():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="sbm", choices=["sbm", "eigen", "latent"])
+    ap.add_argument("--workload", default="all", choices=["all", "sbm", "eigen", "latent", "ais"])
     ap.add_argument("--n", type=int, default=16384, help="nodes (metric: N=16k)")
-    ap.add_argument("--k", type=int, default=16, help="SBM blocks / eigenmodel latent dimension (8)")
+    ap.add_argument("--k", type=int, default=16, help="SBM blocks")
     ap.add_argument("--b", type=int, default=2, help="weight dimension")
     ap.add_argument("--d", type=int, default=8, help="eigenmodel latent dimension")
     ap.add_argument("--dtype", default="f32", choices=["f32", "f64"])
@@ -39,100 +46,174 @@ def parse_args():
                     help="N > 1: independent chains per GPU (weak scaling, default) or ONE chain with rows of A/W sharded "
                          "over the GPUs and NCCL all-reduces of the statistics (strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the mixing / f64 side records of the SBM workload")
     ap.add_argument("--cpu-nodes", type=int, default=0, help="nodes of the CPU-baseline sample (0 = auto)")
+    ap.add_argument("--ref-budget", type=float, default=70.0, help="reference arm: seconds of timed sweeps per workload")
+    ap.add_argument("--ais-particles", type=int, default=32)
     return ap.parse_args()
 
 
 # --------------------------------------------------------------------------------------------------
-# synthetic data: m ~ Dir(10), c ~ Cat(m), p ~ Beta(1,1), (mu,Sigma) ~ NIW(0,I,B+2,1)
+# host description (the CPU numbers are quoted with the cores they ran on)
 # --------------------------------------------------------------------------------------------------
-def pinned_empty(shape, dtype):
-    """Host buffer in pinned memory when CUDA is present (the e2e leg copies from it), else plain numpy."""
+def host_info():
+    info = {"cpu_count": os.cpu_count(), "affinity": len(os.sched_getaffinity(0)),
+            "OMP_NUM_THREADS": os.environ.get("OMP_NUM_THREADS")}
     try:
-        import torch
-        if torch.cuda.is_available():
-            t = torch.empty(tuple(shape), dtype=getattr(torch, np.dtype(dtype).name), pin_memory=True)
-            return t.numpy(), t
+        from threadpoolctl import threadpool_info
+        info["threadpools"] = [{"api": t.get("user_api"), "lib": t.get("internal_api"), "threads": t.get("num_threads")}
+                               for t in threadpool_info()]
     except Exception:
-        pass
+        info["threadpools"] = None
+    return info
+
+
+def usable_cores():
+    return max(1, len(os.sched_getaffinity(0)))
+
+
+# --------------------------------------------------------------------------------------------------
+# synthetic data.  Row chunks are filled by a thread pool, each chunk from its own PCG64 stream
+# keyed by (seed, rank, chunk), so the data do not depend on the number of threads.
+# --------------------------------------------------------------------------------------------------
+def pinned_empty(shape, dtype, pin=True):
+    """Host buffer in pinned memory when CUDA is present (the e2e leg copies from it), else plain numpy."""
+    if pin:
+        try:
+            import torch
+            if torch.cuda.is_available():
+                t = torch.empty(tuple(shape), dtype=getattr(torch, np.dtype(dtype).name), pin_memory=True)
+                return t.numpy(), t
+        except Exception:
+            pass
     return np.empty(shape, dtype), None
 
 
-def make_sbm_data(N, K, B, seed=1234, rank=0):
+def _fill_rows(N, fill, rows=512):
+    chunks = [(i, r0, min(N, r0 + rows)) for i, r0 in enumerate(range(0, N, rows))]
+    with ThreadPoolExecutor(max_workers=min(32, usable_cores())) as ex:
+        list(ex.map(lambda t: fill(*t), chunks))
+
+
+def _chunk_rng(seed, rank, chunk):
+    return np.random.Generator(np.random.PCG64(np.random.SeedSequence([seed, rank, chunk])))
+
+
+def sbm_truth(N, K, B, seed=1234, rank=0, signal=1.0):
+    """m ~ Dir(10), c ~ Cat(m), p ~ Beta(1,1), (mu,Sigma) ~ NIW(0,I,B+2,1).  ``signal`` < 1 shrinks the block
+    structure (p towards its mean, mu towards 0, Sigma towards I): the weak-signal dataset of the mixing record."""
+    from graphistician_b200.internals.gaussian import invwishart_draw
     rs = np.random.RandomState(seed + 7919 * rank)
     m = rs.dirichlet(10.0 * np.ones(K))
     c = rs.choice(K, p=m, size=N)
     p = rs.beta(1.0, 1.0, size=(K, K))
     mus = np.zeros((K, K, B)); sigmas = np.zeros((K, K, B, B))
-    from graphistician_b200.internals.gaussian import invwishart_draw
     for a in range(K):
         for b in range(K):
             sigmas[a, b] = invwishart_draw(np.eye(B), B + 2, rs)
             mus[a, b] = rs.multivariate_normal(np.zeros(B), sigmas[a, b])
-    g = np.random.Generator(np.random.PCG64(seed + 7919 * rank))
-    A, keepA = pinned_empty((N, N), np.uint8)
-    W, keepW = pinned_empty((N, N, B), np.float32)
-    chol = np.linalg.cholesky(sigmas)                        # K,K,B,B
-    rows = 1024
-    for r0 in range(0, N, rows):
-        r1 = min(N, r0 + rows)
-        cc = np.ix_(c[r0:r1], c)
-        A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < p[cc].astype(np.float32)
+    if signal != 1.0:
+        p = p.mean() + signal * (p - p.mean())
+        mus = signal * mus
+        sigmas = np.eye(B) + signal * (sigmas - np.eye(B))
+    return dict(c=c, m=m, p=p, mus=mus, sigmas=sigmas)
+
+
+def fill_sbm_data(A, W, truth, seed=1234, rank=0):
+    N = A.shape[0]
+    K, B = truth["p"].shape[0], truth["mus"].shape[2]
+    c = truth["c"]
+    p32 = truth["p"].astype(np.float32).ravel()
+    chol = np.linalg.cholesky(truth["sigmas"]).astype(np.float32).reshape(K * K, B, B)
+    mu32 = truth["mus"].astype(np.float32).reshape(K * K, B)
+
+    def fill(i, r0, r1):
+        g = _chunk_rng(seed, rank, i)
+        cell = (c[r0:r1, None] * K + c[None, :]).astype(np.int32)
+        A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < p32[cell]
         z = g.standard_normal((r1 - r0, N, B), dtype=np.float32)
-        W[r0:r1] = (np.einsum("ijab,ijb->ija", chol[cc].astype(np.float32), z) + mus[cc].astype(np.float32))
-    return dict(A=A, W=W, c=c, m=m, p=p, mus=mus, sigmas=sigmas, _keep=(keepA, keepW))
+        for a in range(B):
+            w = mu32[:, a][cell]
+            for b in range(a + 1):
+                w += chol[:, a, b][cell] * z[:, :, b]
+            W[r0:r1, :, a] = w
+    _fill_rows(N, fill)
 
 
-def make_eigen_data(N, D, seed=1234, rank=0, p=0.01):
+def make_sbm_data(N, K, B, seed=1234, rank=0, pin=True, signal=1.0):
+    truth = sbm_truth(N, K, B, seed, rank, signal)
+    A, keepA = pinned_empty((N, N), np.uint8, pin)
+    W, keepW = pinned_empty((N, N, B), np.float32, pin)
+    fill_sbm_data(A, W, truth, seed, rank)
+    return dict(truth, A=A, W=W, _keep=(keepA, keepW))
+
+
+def make_eigen_data(N, D, seed=1234, rank=0, p=0.01, pin=True):
     """F_true ~ N(0, I), lmbda = 1, mu_0 = Phi^-1(p) (eigenmodel.py:56), A ~ Bern(logistic(Mu))."""
     from scipy.stats import norm
-    g = np.random.Generator(np.random.PCG64(seed + 7919 * rank))
-    F = g.standard_normal((N, D)).astype(np.float32)
+    g0 = np.random.Generator(np.random.PCG64(seed + 7919 * rank))
+    F = g0.standard_normal((N, D)).astype(np.float32)
     mu0 = np.float32(norm.ppf(p))
-    A, keepA = pinned_empty((N, N), np.uint8)
-    rows = 1024
-    for r0 in range(0, N, rows):
-        r1 = min(N, r0 + rows)
+    A, keepA = pinned_empty((N, N), np.uint8, pin)
+
+    def fill(i, r0, r1):
+        g = _chunk_rng(seed, rank, i)
         eta = F[r0:r1] @ F.T + mu0
         eta[np.arange(r1 - r0), np.arange(r0, r1)] = mu0
         A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < 1.0 / (1.0 + np.exp(-eta))
+    _fill_rows(N, fill)
     return dict(A=A, W=None, F=F, mu0=float(mu0), _keep=(keepA,))
 
 
-def make_latent_data(N, dim, B=1, seed=1234, rank=0, sigma=2.0):
+def make_latent_data(N, dim, B=1, seed=1234, rank=0, sigma=2.0, pin=True):
     """L_true ~ sqrt(sigma) N(0, I) (adjacency.py:202), mu_0 = mu_self = 0,
     A ~ Bern(logistic(-||l_i - l_j||^2 + mu_0)), W ~ N(0, 1)."""
-    g = np.random.Generator(np.random.PCG64(seed + 7919 * rank))
-    L = (np.sqrt(sigma) * g.standard_normal((N, dim))).astype(np.float32)
-    A, keepA = pinned_empty((N, N), np.uint8)
-    W, keepW = pinned_empty((N, N, B), np.float32)
+    g0 = np.random.Generator(np.random.PCG64(seed + 7919 * rank))
+    L = (np.sqrt(sigma) * g0.standard_normal((N, dim))).astype(np.float32)
+    A, keepA = pinned_empty((N, N), np.uint8, pin)
+    W, keepW = pinned_empty((N, N, B), np.float32, pin)
     sq = (L * L).sum(1)
-    rows = 1024
-    for r0 in range(0, N, rows):
-        r1 = min(N, r0 + rows)
+
+    def fill(i, r0, r1):
+        g = _chunk_rng(seed, rank, i)
         eta = -(sq[r0:r1, None] + sq[None, :] - 2.0 * (L[r0:r1] @ L.T))
         A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < 1.0 / (1.0 + np.exp(-eta))
         W[r0:r1] = g.standard_normal((r1 - r0, N, B), dtype=np.float32)
+    _fill_rows(N, fill)
     return dict(A=A, W=W, L=L, _keep=(keepA, keepW))
 
 
-def build_latent_model(d, N, dim, B, dtype):
-    from graphistician_b200.networks import FactorizedNetworkDistribution
-    from graphistician_b200.adjacency import LatentDistanceAdjacencyDistribution
-    from graphistician_b200.weights import NIWGaussianWeightDistribution
-    from graphistician_b200.old_abstractions import network_for
-    np.random.seed(5678)
-    model = FactorizedNetworkDistribution(N, LatentDistanceAdjacencyDistribution, {"dim": dim, "sigma": 2.0, "dtype": dtype},
-                                          NIWGaussianWeightDistribution, {"B": B, "dtype": dtype})
-    return model, network_for(d["A"], d["W"])
+# --------------------------------------------------------------------------------------------------
+# workload descriptions shared by both arms: `config` is what the driver compares between the arms
+# --------------------------------------------------------------------------------------------------
+def workload_config(name, args):
+    N = args.n
+    if name == "sbm":
+        return {"workload": "gaussian_sbm_gibbs_sweep N=%d K=%d B=%d (configs[1] model at the metric's N)" % (N, args.k, args.b),
+                "N": N, "K": args.k, "B": args.b}
+    if name == "eigen":
+        return {"workload": "logistic_eigenmodel_pg_gibbs_sweep N=%d D=%d lmbda given (configs[2])" % (N, args.d),
+                "N": N, "D": args.d}
+    if name == "latent":
+        return {"workload": "latent_distance_hmc_gibbs_sweep + NIW weights N=%d dim=2 B=1 (configs[3])" % N,
+                "N": N, "dim": 2, "B": 1}
+    if name == "ais":
+        return {"workload": "ais_sbm_particle_sweep N=%d R=3 P=%d (configs[4])" % (N, args.ais_particles),
+                "N": N, "R": 3, "P": args.ais_particles}
+    raise SystemExit("unknown workload " + name)
 
 
-def build_eigen_model(d, N, D, dtype):
-    from graphistician_b200.eigenmodel import LogisticEigenmodel
-    from graphistician_b200.old_abstractions import FixedGaussianNetwork
-    np.random.seed(5678)
-    model = LogisticEigenmodel(N, D, p=0.01, sigma_F=1.0, sigma_mu0=1.0, lmbda=np.ones(D), dtype=dtype)
-    return model, FixedGaussianNetwork(d["A"], None)
+def algorithmic_bytes(name, args, dtype):
+    """bytes one sweep must move (s_A = 1; s_W = s_Omega = 4, or 8 in fp64 parity mode)."""
+    N = float(args.n)
+    s = 4 if dtype == "f32" else 8
+    if name == "sbm":
+        return 3.0 * N * N * (1 + args.b * s)              # K1 pass + K2 row pass + column pass
+    if name == "eigen":
+        return N * N * (2 * s + 1)                         # write S + read S + read A
+    if name == "latent":
+        return 22.0 * N * N + N * N * (1 + 1 * s)          # 11 + 11 pair passes + NIW statistics
+    raise SystemExit(name)
 
 
 # --------------------------------------------------------------------------------------------------
@@ -215,108 +296,133 @@ def build_sbm_model(d, N, K, B, dtype):
     from graphistician_b200.old_abstractions import FixedGaussianNetwork
     np.random.seed(5678)
     model = GaussianStochasticBlockModel(N, B, C=K, dtype=dtype)
-    network = FixedGaussianNetwork(d["A"], d["W"])
-    return model, network
+    return model, FixedGaussianNetwork(d["A"], d["W"])
 
 
-def setup_workload(args, rank):
+def build_eigen_model(d, N, D, dtype):
+    from graphistician_b200.eigenmodel import LogisticEigenmodel
+    from graphistician_b200.old_abstractions import FixedGaussianNetwork
+    np.random.seed(5678)
+    model = LogisticEigenmodel(N, D, p=0.01, sigma_F=1.0, sigma_mu0=1.0, lmbda=np.ones(D), dtype=dtype)
+    return model, FixedGaussianNetwork(d["A"], None)
+
+
+def build_latent_model(d, N, dim, B, dtype):
+    from graphistician_b200.networks import FactorizedNetworkDistribution
+    from graphistician_b200.adjacency import LatentDistanceAdjacencyDistribution
+    from graphistician_b200.weights import NIWGaussianWeightDistribution
+    from graphistician_b200.old_abstractions import network_for
+    np.random.seed(5678)
+    model = FactorizedNetworkDistribution(N, LatentDistanceAdjacencyDistribution, {"dim": dim, "sigma": 2.0, "dtype": dtype},
+                                          NIWGaussianWeightDistribution, {"B": B, "dtype": dtype})
+    return model, network_for(d["A"], d["W"])
+
+
+def ncu_traffic(kernel):
+    """dram read + write bytes per launch of `kernel` from the committed ncu --set full summaries
+    (profiles/traffic.json, written by profiles/summarize.py); None when no capture of this kernel is on file."""
+    try:
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))
+        ent = t.get(kernel)
+        return (ent["dram_bytes_per_launch"], ent["source"]) if ent else (None, None)
+    except Exception:
+        return None, None
+
+
+def setup_workload(name, args, rank, dtype):
     N, B = args.n, args.b
-    if args.workload == "sbm":
+    s = 4 if dtype == "f32" else 8
+    if name == "sbm":
         K = args.k
         d = make_sbm_data(N, K, B, rank=rank)
-        model, network = build_sbm_model(d, N, K, B, args.dtype)
-        s_W = 4 if args.dtype == "f32" else 8
+        model, network = build_sbm_model(d, N, K, B, dtype)
         return dict(N=N, data=d, model=model, network=network,
-                    algo_bytes=3.0 * N * N * (1 + B * s_W),       # K1 pass + K2 row pass + column pass
                     h2d=N * N * (1 + B * 4) + N * (1 + 8 * B) + N * 12 + 8 * K * K * (2 + B + B * B),
-                    d2h=N * 4 + 8 * K * K * (1 + B + B * B) + 8, dominant=(0, "k_strip_stats"),
-                    # ncu --set full, dram read+write per launch averaged over the 17 launches of a sweep (16 block passes
-                    # at 306.15 MB, profiles/r1_sbm_full_v3.csv; the cell pass at 2441.7 MB, r1_sbm_strip_n16384_full.csv)
-                    traffic=(16 * 306.15e6 + 2441.67e6) / 17 if (N, K, B, args.dtype) == (16384, 16, 2, "f32") else None,
-                    cpu_baseline=cpu_baseline_sbm,
-                    config={"workload": "gaussian_sbm_gibbs_sweep N=%d K=%d B=%d (configs[1] model at the metric's N)" % (N, K, B),
-                            "N": N, "K": K, "B": B})
-    if args.workload == "eigen":
+                    d2h=N * 4 + 8 * K * K * (1 + B + B * B) + 8, dominant=0, cpu_baseline=cpu_baseline_sbm)
+    if name == "eigen":
         D = args.d
         d = make_eigen_data(N, D, rank=rank)
-        model, network = build_eigen_model(d, N, D, args.dtype)
-        s_O = 4 if args.dtype == "f32" else 8
+        model, network = build_eigen_model(d, N, D, dtype)
         return dict(N=N, data=d, model=model, network=network,
-                    algo_bytes=1.0 * N * N * (2 * s_O + 1),       # write S + read S + read A
-                    h2d=N * N + N * D * 16 + 8 * D + 8, d2h=N * D * 8 + 8 * 68 + 8, dominant=(3, "k_eig_gfull+k_eig_push"),
-                    # ncu --set full (profiles/r1_eig_n16384_full_v2.csv, r1_eig_full_v3.csv): gfull 1361.5 MB, 128 pushes at
-                    # 17.23 MB (10.5 MB of S/Asym + the G rows read and written), 127 strip pushes at 0.18 MB; per launch
-                    traffic=(1361.5e6 + 128 * 17.23e6 + 127 * 0.18e6) / 256 if (N, D, args.dtype) == (16384, 8, "f32") else None,
-                    cpu_baseline=cpu_baseline_eigen,
-                    config={"workload": "logistic_eigenmodel_pg_gibbs_sweep N=%d D=%d lmbda given (configs[2])" % (N, D),
-                            "N": N, "D": D})
-    if args.workload == "latent":
+                    h2d=N * N + N * D * 16 + 8 * D + 8, d2h=N * D * 8 + 8 * 68 + 8, dominant=3,
+                    cpu_baseline=cpu_baseline_eigen)
+    if name == "latent":
         dim, Bw = 2, 1
         d = make_latent_data(N, dim, Bw, rank=rank)
-        model, network = build_latent_model(d, N, dim, Bw, args.dtype)
+        model, network = build_latent_model(d, N, dim, Bw, dtype)
         tup = (d["A"], d["W"])
         return dict(N=N, data=d, model=model, network=network, step=lambda: model.resample(tup),
-                    algo_bytes=22.0 * N * N + 1.0 * N * N * (1 + Bw * 4),   # 11 + 11 pair passes + NIW statistics
                     h2d=N * N * (1 + Bw * 4) + N * dim * 8 + N * (1 + 8 * Bw), d2h=N * dim * 8 + 64,
-                    dominant=(4, "k_latent_pair"), cpu_baseline=cpu_baseline_latent,
-                    traffic=139.6e6 if (N, args.dtype) == (16384, "f32") else None,   # profiles/r1_latent_n16384_full.csv
-                    config={"workload": "latent_distance_hmc_gibbs_sweep + NIW weights N=%d dim=%d B=%d (configs[3])" % (N, dim, Bw),
-                            "N": N, "dim": dim, "B": Bw})
-    raise SystemExit("workload %s: not built yet" % args.workload)
+                    dominant=4, cpu_baseline=cpu_baseline_latent)
+    raise SystemExit("workload %s: not built" % name)
 
 
-def run_ours(args):
-    import torch
-    from graphistician_b200 import _lib
-    rank, world, local = dist_setup(args)
-    if not torch.cuda.is_available():
-        raise SystemExit("bench.py: no CUDA device (this engine has no CPU fallback)")
-    torch.cuda.set_device(local)
-    dev = torch.device("cuda", local)
-    _lib.set_default_device(local)
-    ctx = _lib.default_context()
-    stream = torch.cuda.Stream(device=dev)
-    ctx.set_stream(stream.cuda_stream)
-    rows = args.shard == "rows" and world > 1
-    wl = setup_workload(args, 0 if rows else rank)
+class Runner:
+    """CUDA-event timing of `nsteps` sweeps on the ctx stream: barrier + synchronize on both sides, max over ranks."""
+
+    def __init__(self, args):
+        import torch
+        from graphistician_b200 import _lib
+        self.torch = torch
+        self.rank, self.world, self.local = dist_setup(args)
+        if not torch.cuda.is_available():
+            raise SystemExit("bench.py: no CUDA device (this engine has no CPU fallback)")
+        torch.cuda.set_device(self.local)
+        self.dev = torch.device("cuda", self.local)
+        _lib.set_default_device(self.local)
+        self.ctx = _lib.default_context()
+        self.stream = torch.cuda.Stream(device=self.dev)
+        self.ctx.set_stream(self.stream.cuda_stream)
+
+    def timed(self, step, nsteps, before=None):
+        torch = self.torch
+        barrier(self.world); torch.cuda.synchronize()
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        with torch.cuda.stream(self.stream):
+            e0.record(self.stream)
+            for _ in range(nsteps):
+                if before is not None:
+                    before()
+                step()
+            e1.record(self.stream)
+        torch.cuda.synchronize(); barrier(self.world)
+        return max_over_ranks(e0.elapsed_time(e1), self.world, self.dev)
+
+
+def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, first_sweep=False):
+    """One workload record: value (resident), e2e (host buffers), roofline of the dominant kernel family,
+    launches, clocks, and (rank 0, one GPU) the CPU baseline."""
+    wl = setup_workload(name, args, 0 if rows else R.rank, dtype)
+    model, network, d = wl["model"], wl["network"], wl["data"]
     if rows:                                                   # one chain, rows of A / W sharded over the ranks
         from graphistician_b200.sharding import Comm
-        torch.cuda.set_stream(stream)                          # libgk and NCCL share this stream
-        wl["network"].shard(Comm())
-    N, model, network, d, algo_bytes = wl["N"], wl["model"], wl["network"], wl["data"], wl["algo_bytes"]
+        R.torch.cuda.set_stream(R.stream)                      # libgk and NCCL share this stream
+        network.shard(Comm())
     step = wl.get("step") or (lambda: model.resample(network))
-
-    def timed(nsteps, e2e):
-        barrier(world); torch.cuda.synchronize()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        with torch.cuda.stream(stream):
-            e0.record(stream)
-            for _ in range(nsteps):
-                if e2e:
-                    network.invalidate()                        # host buffers -> device inside the timed region
-                step()
-            e1.record(stream)
-        torch.cuda.synchronize(); barrier(world)
-        return max_over_ranks(e0.elapsed_time(e1), world, dev)
-
-    timed(args.warmup, False)
-    sampler = ClockSampler(local); sampler.start()
-    l0 = ctx.launch_count()
-    ms = timed(args.steps, False)
-    launches = ctx.launch_count() - l0
+    algo_bytes = algorithmic_bytes(name, args, dtype)
+    rec = {}
+    if first_sweep:                                            # sweep 1 from the prior draw of the labels (data already resident)
+        network.device(dtype)
+        rec["first_sweep_ms"] = R.timed(step, 1)
+        rec["first_sweep_n_changed"] = int(getattr(model, "_n_changed", -1))
+        warmup = max(0, warmup - 1)
+    R.timed(step, warmup)
+    sampler = ClockSampler(R.local); sampler.start()
+    l0 = R.ctx.launch_count()
+    ms = R.timed(step, steps)
+    launches = R.ctx.launch_count() - l0
     clocks = sampler.result()
-    # e2e: same call, network re-uploaded from pinned host memory every step, state read back (c, m, p) every step
-    e2e_steps = max(3, min(args.steps, 5))
-    timed(1, True)
-    ms_e2e = timed(e2e_steps, True)
-    h2d, d2h = wl["h2d"], wl["d2h"]
+    # e2e: same call, network re-uploaded from pinned host memory every step, state read back every step
+    e2e_steps = max(3, min(steps, 5))
+    R.timed(step, 1, before=network.invalidate)
+    ms_e2e = R.timed(step, e2e_steps, before=network.invalidate)
     # per-kernel timing pass (CUDA events around every launch of each kernel family, on the ctx stream)
-    ctx.kernel_timing(True)
+    R.ctx.kernel_timing(True)
     for _ in range(3):
         step()
-    fam = {f: ctx.kernel_timing_read(f) for f in range(6)}
-    ctx.kernel_timing(False)
-    kms, kn, kbytes = fam[wl["dominant"][0]]
+    fam = {f: R.ctx.kernel_timing_read(f) for f in range(8)}
+    R.ctx.kernel_timing(False)
+    kms, kn, kbytes = fam[wl["dominant"]]
     peaks = {}
     try:
         peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
@@ -324,129 +430,134 @@ def run_ours(args):
         pass
     peak = float(peaks.get("hbm_gbs", 6650.0))
     achieved = kbytes / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
-    names = {0: "k_strip_stats", 1: "k_sbm_seq", 2: "k_eig_pg_tile", 3: "k_eig_gfull+k_eig_push", 4: "k_latent_pair",
-             5: "k_eig_seq4"}
-    out = {
-        "metric": METRIC, "value": (1 if rows else world) * args.steps / (ms * 1e-3), "unit": UNIT, "n_gpus": world,
-        "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
-        "scaling": "strong" if rows else "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
-        "config": dict(wl["config"], parallelism=("one chain, rows sharded x%d" if rows else "independent chains x%d") % world,
-                       l2="inputs (%.2f GB/sweep) exceed the 126 MB L2" % (algo_bytes / 1e9)),
-        "gpu_launches": int(launches), "clocks": clocks,
-        "e2e": {"value": (1 if rows else world) * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(h2d),
-                "d2h_bytes_per_step": int(d2h)},
-        "roofline": {"bound": "hbm", "kernel": wl["dominant"][1], "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": achieved / peak, "traffic": wl.get("traffic"),
+    mult = 1 if rows else R.world
+    kname = FAMILY[wl["dominant"]]
+    traffic, tsrc = ncu_traffic(kname)
+    rec.update({
+        "value": mult * steps / (ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": ms / steps, "dtype": dtype,
+        "config": workload_config(name, args), "gpu_launches": int(launches), "clocks": clocks,
+        "e2e": {"value": mult * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(wl["h2d"]),
+                "d2h_bytes_per_step": int(wl["d2h"])},
+        "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": traffic, "traffic_source": tsrc,
                      "algorithmic_bytes_per_launch": (kbytes / kn) if kn else None,
-                     "peak_source": "measured" if peaks else "fallback",
+                     "peak_source": "measured (MEASURED_PEAKS.json hbm_gbs)" if peaks else "fallback",
                      "launches_per_sweep": kn / 3.0, "kernel_ms_per_sweep": kms / 3.0,
-                     "other_kernels_ms_per_sweep": {names[f]: fam[f][0] / 3.0 for f in fam if fam[f][1] and f != wl["dominant"][0]},
-                     "sweep_algorithmic_GBps": algo_bytes / (ms / args.steps * 1e-3) / 1e9},
-    }
-    if args.workload == "sbm":
-        out["n_changed_last_sweep"] = int(getattr(model, "_n_changed", -1))
-    if rank == 0 and not args.no_cpu_baseline:
-        out["cpu_baseline"] = wl["cpu_baseline"](d, model, args)
-    if rank == 0:
+                     "other_kernels_ms_per_sweep": {FAMILY[f]: fam[f][0] / 3.0 for f in fam if fam[f][1] and f != wl["dominant"]},
+                     "sweep_algorithmic_bytes": algo_bytes,
+                     "sweep_algorithmic_GBps": algo_bytes / (ms / steps * 1e-3) / 1e9,
+                     "sweep_frac_of_peak": algo_bytes / (ms / steps * 1e-3) / 1e9 / peak},
+        "l2": "inputs (%.2f GB/sweep) exceed the 126 MB L2" % (algo_bytes / 1e9),
+    })
+    if name == "sbm":
+        rec["n_changed_last_sweep"] = int(getattr(model, "_n_changed", -1))
+        rec["regime"] = "stationary (planted blocks recovered during warm-up; see `mixing` for sweeps with movers)"
+    if cpu and R.rank == 0 and R.world == 1 and not args.no_cpu_baseline:
+        rec["cpu_baseline"] = wl["cpu_baseline"](d, model, args)
+    return rec, wl
+
+
+def sbm_mixing_record(args, R, wl, dtype):
+    """Sweeps WITH movers: the planted data are overwritten in place by a weak-signal draw of the same model
+    (block structure shrunk to 5 %: p within +-0.05 of its mean), where the labels never settle."""
+    d, network, N = wl["data"], wl["network"], args.n
+    truth = sbm_truth(N, args.k, args.b, seed=4321, rank=R.rank, signal=0.05)
+    fill_sbm_data(d["A"], d["W"], truth, seed=4321, rank=R.rank)
+    network.invalidate()
+    np.random.seed(8765)
+    from graphistician_b200.stochastic_block_model import GaussianStochasticBlockModel
+    model = GaussianStochasticBlockModel(N, args.b, C=args.k, dtype=dtype)
+    nch = []
+
+    def step():
+        model.resample(network)
+        nch.append(int(model._n_changed))
+    R.timed(step, 2)
+    del nch[:]
+    steps = 5
+    ms = R.timed(step, steps)
+    return {"dataset": "weak signal: p = mean + 0.05 (p - mean), mu x 0.05, Sigma = I + 0.05 (Sigma - I), seed 4321",
+            "ms_per_step": ms / steps, "value": R.world * steps / (ms * 1e-3), "unit": UNIT, "steps": steps,
+            "n_changed_per_sweep": nch, "us_per_move": 1e3 * (ms / steps) / max(1.0, float(np.mean(nch)))}
+
+
+def release(wl):
+    from graphistician_b200.old_abstractions import drop_cached_networks
+    try:
+        wl["network"]._drop()
+    except Exception:
+        pass
+    drop_cached_networks()
+    wl.clear()
+    gc.collect()
+
+
+def run_ours(args):
+    R = Runner(args)
+    rows = args.shard == "rows" and R.world > 1
+    names = ["sbm", "eigen", "latent"] if args.workload == "all" else [args.workload]
+    if names == ["ais"]:
+        return run_ais(args, R)
+    primary = names[0]
+    extras = args.workload == "all" and not args.no_extras and not rows
+    rec, wl = bench_workload(primary, args, R, args.dtype, args.steps, args.warmup, rows=rows,
+                             first_sweep=(primary == "sbm" and extras))
+    out = {"metric": METRIC, "value": rec["value"], "unit": UNIT, "n_gpus": R.world, "steps": args.steps,
+           "warmup": args.warmup, "ms_per_step": rec["ms_per_step"], "higher_is_better": True,
+           "scaling": "strong" if rows else "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
+           "config": rec["config"],
+           "parallelism": ("one chain, rows sharded x%d" if rows else "independent chains x%d") % R.world}
+    for k in ("l2", "gpu_launches", "clocks", "e2e", "roofline", "n_changed_last_sweep", "regime", "cpu_baseline"):
+        if k in rec:
+            out[k] = rec[k]
+    if primary == "sbm" and extras:
+        mixing = {"first_sweep_from_prior_labels_ms": rec.get("first_sweep_ms"),
+                  "first_sweep_n_changed": rec.get("first_sweep_n_changed")}
+        mixing["weak_signal"] = sbm_mixing_record(args, R, wl, args.dtype)
+        out["mixing"] = mixing
+    release(wl)
+    out["workloads"] = {}
+    for name in names[1:]:
+        r, w = bench_workload(name, args, R, args.dtype, args.steps, args.warmup, rows=rows)
+        out["workloads"][name] = r
+        release(w)
+    if primary == "sbm" and extras and args.dtype == "f32":       # the fp64-storage line beside the fp32 one
+        r, w = bench_workload("sbm", args, R, "f64", max(3, args.steps // 4), args.warmup, cpu=False)
+        out["workloads"]["sbm_f64"] = r
+        release(w)
+    out["host"] = host_info()
+    if R.rank == 0:
         print(json.dumps(out), flush=True)
-    if world > 1:
+    if R.world > 1:
         import torch.distributed as dist
         dist.destroy_process_group()
 
 
+def run_ais(args, R):
+    raise SystemExit("--workload ais: see profiles/bench_ais.py")
+
+
 # --------------------------------------------------------------------------------------------------
-# CPU baseline / reference arm: the oracle (vectorised T1 restatement of the reference's NumPy path), timed on the
-# host cores.  The reference itself cannot run (Python 2, missing modules and packages: SURVEY.md 8c), so kind="port".
+# CPU baseline of our arm: the oracle (vectorised T1 restatement of the reference's NumPy path) on a BOUNDED sample
+# of the same workload, one core, sample stated.  The reference itself cannot run (Python 2, missing modules and
+# packages: SURVEY.md 8c), so kind = "port".
 # --------------------------------------------------------------------------------------------------
-def cpu_baseline_sbm(d, model, args, nodes=None):
-    N = d["A"].shape[0]
-    nodes = nodes or args.cpu_nodes or min(N, 2048)
-    state = dict(c=np.asarray(model.c), m=np.asarray(model.m), p=np.clip(model.p, 1e-12, 1 - 1e-12),
-                 mus=model.mus, sigmas=model.sigmas)
-    from oracle import sbm
-    # block_pair_stats on a row subset needs square indexing: run it on the leading `nodes` rows only
-    A, W = d["A"], d["W"]
-    t0 = time.perf_counter()
-    _stats_rows(A, W, state["c"], len(state["m"]), nodes)
-    t_stats = time.perf_counter() - t0
-    gc = sbm.gaussian_coefficients(state["mus"], state["sigmas"])
-    logm = np.log(state["m"]); c = np.array(state["c"], dtype=np.int64).copy()
-    u = np.random.RandomState(1).rand(N)
-    t0 = time.perf_counter()
-    At = np.ascontiguousarray(A[:, :nodes].T); Wt = np.ascontiguousarray(W[:, :nodes].transpose(1, 0, 2))
-    for n1 in range(nodes):
-        lp = sbm.node_conditional(n1, A, W, c, logm, state["p"], gc, sbm.SELF_OLD, 1.0, At, Wt)
-        c[n1] = sbm.sample_discrete_from_log(lp, u[n1])
-    t_sweep = time.perf_counter() - t0
-    secs = (t_stats + t_sweep) * (N / float(nodes))
-    return {"value": 1.0 / secs, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": "oracle (vectorised NumPy restatement) on the first %d of %d nodes: K1 statistics over those rows "
-                      "+ their sequential conditionals/draws; %.1f s measured, scaled x%.1f to a full sweep"
-                      % (nodes, N, t_stats + t_sweep, N / float(nodes)),
-            "measured_s": t_stats + t_sweep}
+class _RowOffset:
+    """rows [lo, hi) of a transposed array addressed by their global row index (oracle.sbm.node_conditional's At / Wt)."""
+
+    def __init__(self, a, lo):
+        self.a, self.lo = a, lo
+
+    def __getitem__(self, idx):
+        return self.a[(idx[0] - self.lo,) + tuple(idx[1:])]
 
 
-def cpu_baseline_eigen(d, model, args, nodes=None):
-    """Oracle (port) of one logistic-eigenmodel sweep on a bounded sample: the C Devroye sampler (OpenMP, all
-    cores) for both Omega entries of the first `nodes` rows, then the per-node conditionals/draws of those nodes
-    (vectorised NumPy restatement of eigenmodel.py:876-908); scaled by N/nodes."""
-    from oracle import eigenmodel as eg, pg
-    A = d["A"]
-    N = A.shape[0]
-    nodes = nodes or args.cpu_nodes or min(N, 512)
-    F = np.asarray(model.F, dtype=np.float64); lm = np.asarray(model.lmbda, dtype=np.float64); mu0 = float(model.mu_0)
-    t0 = time.perf_counter()
-    O1 = pg.pgdraw_eigen(F, lm, mu0, seed=1, r0=0, r1=nodes)          # omega[n, :]
-    O2 = pg.pgdraw_eigen(F, lm, mu0, seed=2, r0=0, r1=nodes)          # omega[:, n]^T (Mu is symmetric)
-    t_pg = time.perf_counter() - t0
-    t0 = time.perf_counter()
-    S = O1 + O2
-    Asym = A[:nodes].astype(np.float64) + A[:, :nodes].T
-    R = Asym - 1.0 - mu0 * S
-    z = np.random.RandomState(1).randn(N, F.shape[1])
-    eg.resample_F(S, R, F, lm, model.sigma_F, z, nodes=nodes)
-    t_F = time.perf_counter() - t0
-    secs = (t_pg + t_F) * (N / float(nodes))
-    return {"value": 1.0 / secs, "unit": UNIT, "cores": pg.num_threads(), "kind": "port",
-            "sample": "oracle on the first %d of %d nodes: C Polya-gamma sampler (OpenMP x%d) for their 2N Omega entries "
-                      "(%.2f s) + sequential conditionals/draws in NumPy (%.2f s, 1 core); scaled x%.1f to a full sweep"
-                      % (nodes, N, pg.num_threads(), t_pg, t_F, N / float(nodes)),
-            "measured_s": t_pg + t_F}
-
-
-def cpu_baseline_latent(d, model, args, nodes=None):
-    """Oracle (port) of one latent-distance sweep on a bounded sample: the fused value + gradient of
-    adjacency.py:244-275 (vectorised NumPy, fp64) over the first `nodes` rows, for the 22 evaluations a sweep needs
-    (11 for L, 11 for mu_0), plus the K = 1 NIW statistics of those rows; scaled by N / nodes."""
-    from oracle import latent
-    A, W = d["A"], d["W"]
-    N = A.shape[0]
-    nodes = nodes or args.cpu_nodes or min(N, 256)
-    adj = model.adjacency
-    L = np.asarray(adj.L, dtype=np.float64)
-    Ar = A[:nodes].astype(np.float64); Atr = np.ascontiguousarray(A[:, :nodes].T).astype(np.float64)
-    t0 = time.perf_counter()
-    for _ in range(22):
-        latent.rows_value_and_grad(L, adj.mu_0, adj.mu_self, Ar, Atr, 0, adj.sigma)
-    e = A[:nodes] != 0
-    We = W[:nodes][e].astype(np.float64)
-    We.sum(0); We.T.dot(We)
-    secs = time.perf_counter() - t0
-    full = secs * (N / float(nodes))
-    return {"value": 1.0 / full, "unit": UNIT, "cores": 1, "kind": "port",
-            "sample": "oracle (vectorised NumPy restatement, fp64) on the first %d of %d rows: 22 value+gradient "
-                      "evaluations + NIW statistics; %.1f s measured, scaled x%.1f to a full sweep" % (nodes, N, secs, N / float(nodes)),
-            "measured_s": secs}
-
-
-def _stats_rows(A, W, c, K, nodes):
-    """K1 of the oracle (bincount over the fused cell index) restricted to the leading rows."""
-    from oracle import sbm
-    N = A.shape[0]
+def _stats_rows(A, W, c, K, lo, hi):
+    """K1 of the oracle (bincount over the fused cell index) restricted to rows [lo, hi)."""
     B = W.shape[2]
     c = np.asarray(c, dtype=np.int64)
-    for r0 in range(0, nodes, 256):
-        r1 = min(nodes, r0 + 256)
+    for r0 in range(lo, hi, 256):
+        r1 = min(hi, r0 + 256)
         Ar = (A[r0:r1] != 0)
         cell = (c[r0:r1, None] * K + c[None, :])
         Ar[np.arange(r1 - r0), np.arange(r0, r1)] = False
@@ -459,36 +570,196 @@ def _stats_rows(A, W, c, K, nodes):
                 np.bincount(ce, weights=We[:, b] * We[:, b2], minlength=K * K)
 
 
+def _sbm_nodes(A, W, state, lo, hi):
+    """K1 statistics over rows [lo, hi) + the sequential conditionals / draws of those nodes (oracle port)."""
+    from oracle import sbm
+    K = len(state["m"])
+    _stats_rows(A, W, state["c"], K, lo, hi)
+    gc_ = sbm.gaussian_coefficients(state["mus"], state["sigmas"])
+    logm = np.log(state["m"]); c = np.array(state["c"], dtype=np.int64).copy()
+    u = np.random.RandomState(1).rand(A.shape[0])
+    At = _RowOffset(np.ascontiguousarray(A[:, lo:hi].T), lo)
+    Wt = _RowOffset(np.ascontiguousarray(W[:, lo:hi].transpose(1, 0, 2)), lo)
+    for n1 in range(lo, hi):
+        lp = sbm.node_conditional(n1, A, W, c, logm, state["p"], gc_, sbm.SELF_OLD, 1.0, At, Wt)
+        c[n1] = sbm.sample_discrete_from_log(lp, u[n1])
+    return hi - lo
+
+
+def cpu_baseline_sbm(d, model, args, nodes=None):
+    N = d["A"].shape[0]
+    nodes = nodes or args.cpu_nodes or min(N, 2048)
+    state = dict(c=np.asarray(model.c), m=np.asarray(model.m), p=np.clip(model.p, 1e-12, 1 - 1e-12),
+                 mus=model.mus, sigmas=model.sigmas)
+    t0 = time.perf_counter()
+    _sbm_nodes(d["A"], d["W"], state, 0, nodes)
+    secs = time.perf_counter() - t0
+    full = secs * (N / float(nodes))
+    return {"value": 1.0 / full, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "oracle (vectorised NumPy restatement) on the first %d of %d nodes: K1 statistics over those rows "
+                      "+ their sequential conditionals/draws; %.1f s measured on 1 core, scaled x%.1f to a full sweep "
+                      "(the fully measured, all-cores number is the --impl reference arm)" % (nodes, N, secs, N / float(nodes)),
+            "measured_s": secs}
+
+
+def _eigen_nodes(A, F, lm, mu0, sigma_F, lo, hi, seed):
+    """Both Omega entries of rows [lo, hi) from the C Devroye sampler + the conditionals / draws of those nodes."""
+    from oracle import eigenmodel as eg, pg
+    N = A.shape[0]
+    O1 = pg.pgdraw_eigen(F, lm, mu0, seed=seed, r0=lo, r1=hi)              # omega[n, :]
+    O2 = pg.pgdraw_eigen(F, lm, mu0, seed=seed + 1, r0=lo, r1=hi)          # omega[:, n]^T (Mu is symmetric)
+    S = np.zeros((hi, N)); S[lo:hi] = O1 + O2                              # rows below lo are never read
+    R = np.zeros((hi, N))
+    R[lo:hi] = A[lo:hi].astype(np.float64) + A[:, lo:hi].T - 1.0 - mu0 * S[lo:hi]
+    z = np.random.RandomState(1).randn(N, F.shape[1])
+    eg.resample_F(S, R, F, lm, sigma_F, z, nodes=(lo, hi))
+    return hi - lo
+
+
+def cpu_baseline_eigen(d, model, args, nodes=None):
+    from oracle import pg
+    A = d["A"]
+    N = A.shape[0]
+    nodes = nodes or args.cpu_nodes or min(N, 512)
+    F = np.asarray(model.F, dtype=np.float64); lm = np.asarray(model.lmbda, dtype=np.float64)
+    t0 = time.perf_counter()
+    _eigen_nodes(A, F, lm, float(model.mu_0), model.sigma_F, 0, nodes, 1)
+    secs = time.perf_counter() - t0
+    full = secs * (N / float(nodes))
+    return {"value": 1.0 / full, "unit": UNIT, "cores": pg.num_threads(), "kind": "port",
+            "sample": "oracle on the first %d of %d nodes: C Polya-gamma sampler (OpenMP x%d) for their 2N Omega entries + "
+                      "sequential conditionals/draws in NumPy (1 core); %.2f s measured, scaled x%.1f to a full sweep"
+                      % (nodes, N, pg.num_threads(), secs, N / float(nodes)),
+            "measured_s": secs}
+
+
+def _latent_rows(A, W, L, mu0, mu_self, sigma, lo, hi):
+    """22 value + gradient evaluations of adjacency.py:244-275 restricted to rows [lo, hi) + their NIW statistics."""
+    from oracle import latent
+    for r0 in range(lo, hi, 128):
+        r1 = min(hi, r0 + 128)
+        Ar = A[r0:r1].astype(np.float64); Atr = np.ascontiguousarray(A[:, r0:r1].T).astype(np.float64)
+        for _ in range(22):
+            latent.rows_value_and_grad(L, mu0, mu_self, Ar, Atr, r0, sigma)
+        e = A[r0:r1] != 0
+        We = W[r0:r1][e].astype(np.float64)
+        We.sum(0); We.T.dot(We)
+    return hi - lo
+
+
+def cpu_baseline_latent(d, model, args, nodes=None):
+    A, W = d["A"], d["W"]
+    N = A.shape[0]
+    nodes = nodes or args.cpu_nodes or min(N, 256)
+    adj = model.adjacency
+    L = np.asarray(adj.L, dtype=np.float64)
+    t0 = time.perf_counter()
+    _latent_rows(A, W, L, adj.mu_0, adj.mu_self, adj.sigma, 0, nodes)
+    secs = time.perf_counter() - t0
+    full = secs * (N / float(nodes))
+    return {"value": 1.0 / full, "unit": UNIT, "cores": 1, "kind": "port",
+            "sample": "oracle (vectorised NumPy restatement, fp64) on the first %d of %d rows: 22 value+gradient "
+                      "evaluations + NIW statistics; %.1f s measured, scaled x%.1f to a full sweep" % (nodes, N, secs, N / float(nodes)),
+            "measured_s": secs}
+
+
+# --------------------------------------------------------------------------------------------------
+# reference arm: the reference's CPU path (the oracle port -- the reference is Python 2 and cannot run here) on ALL the
+# host cores, FULL sweeps measured wall-clock at the config size: the N nodes are spread over one forked worker per
+# usable core, every worker runs the per-node arithmetic of its contiguous node range from the same start state.
+# (The reference's own sweep is one serial loop; spreading it over the cores is the most favourable reading of "all
+# the host threads it can use".)  `steps` in the line is the number of sweeps actually timed inside --ref-budget.
+# --------------------------------------------------------------------------------------------------
+_SHARED = {}
+
+
+def _ref_task(task):
+    kind, lo, hi = task
+    s = _SHARED
+    if kind == "sbm":
+        return _sbm_nodes(s["A"], s["W"], s["state"], lo, hi)
+    if kind == "eigen":
+        return _eigen_nodes(s["A"], s["F"], s["lm"], s["mu0"], s["sigma_F"], lo, hi, 1 + 2 * lo)
+    if kind == "latent":
+        return _latent_rows(s["A"], s["W"], s["L"], 0.0, 0.0, s["sigma"], lo, hi)
+    raise ValueError(kind)
+
+
+def _ref_sweeps(kind, N, procs, args):
+    """Wall-clock seconds of full sweeps over all N nodes on `procs` forked workers; (times, warmup_done)."""
+    import multiprocessing as mp
+    per = max(8, (N + 8 * procs - 1) // (8 * procs))          # ~8 tasks per worker: load balance
+    tasks = [(kind, lo, min(N, lo + per)) for lo in range(0, N, per)]
+    ctx = mp.get_context("fork")
+    times = []
+    warm = 0
+    budget_t0 = time.perf_counter()
+    with ctx.Pool(procs) as pool:
+        for i in range(1 + args.steps):
+            t0 = time.perf_counter()
+            done = sum(pool.map(_ref_task, tasks, chunksize=1))
+            dt = time.perf_counter() - t0
+            assert done == N
+            if i == 0 and args.warmup > 0 and dt < 5.0:       # a cheap first sweep is the warm-up; a long one is kept
+                warm = 1
+                continue
+            times.append(dt)
+            if len(times) >= args.steps or time.perf_counter() - budget_t0 > args.ref_budget:
+                break
+    return times, warm
+
+
+def reference_workload(name, args, procs):
+    N = args.n
+    os.environ.setdefault("OMP_NUM_THREADS", "1")              # one worker per core; the C sampler stays single-threaded in each
+    _SHARED.clear()
+    if name == "sbm":
+        K, B = args.k, args.b
+        d = make_sbm_data(N, K, B, pin=False)
+        np.random.seed(5678)                                   # same start state as our arm's model (prior draw, seed 5678)
+        m = np.random.dirichlet(np.ones(K)); c = np.random.choice(K, p=m, size=N); p = np.random.beta(1.0, 1.0, size=(K, K))
+        _SHARED.update(A=d["A"], W=d["W"], state=dict(c=c, m=m, p=np.clip(p, 1e-12, 1 - 1e-12), mus=d["mus"], sigmas=d["sigmas"]))
+        what = "K1 statistics + sequential conditionals/draws of all %d nodes (oracle, vectorised NumPy)" % N
+    elif name == "eigen":
+        from oracle import pg
+        pg.build()
+        D = args.d
+        d = make_eigen_data(N, D, pin=False)
+        np.random.seed(5678)
+        F = np.random.randn(N, D)
+        _SHARED.update(A=d["A"], F=F, lm=np.ones(D), mu0=float(d["mu0"]), sigma_F=1.0)
+        what = "C Polya-gamma sampler for all 2 N^2 Omega entries + sequential conditionals/draws of all %d nodes" % N
+    elif name == "latent":
+        d = make_latent_data(N, 2, 1, pin=False)
+        np.random.seed(5678)
+        _SHARED.update(A=d["A"], W=d["W"], L=np.sqrt(2.0) * np.random.randn(N, 2), sigma=2.0)
+        what = "22 value+gradient evaluations over all %d rows + NIW statistics (oracle, vectorised NumPy, fp64)" % N
+    else:
+        raise SystemExit(name)
+    times, warm = _ref_sweeps(name, N, procs, args)
+    _SHARED.clear()
+    secs = float(np.mean(times))
+    return {"value": 1.0 / secs, "unit": UNIT, "steps": len(times), "warmup": warm, "ms_per_step": 1e3 * secs,
+            "dtype": args.dtype, "config": workload_config(name, args),
+            "cpu_baseline": {"value": 1.0 / secs, "unit": UNIT, "cores": procs, "kind": "port",
+                             "sample": "FULL sweeps, wall clock: %s, spread over %d forked workers (one per usable core); "
+                                       "%d sweep(s) timed: %s s" % (what, procs, len(times), ["%.2f" % t for t in times])},
+            "e2e": {"value": 1.0 / secs, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+
+
 def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    N, K, B = args.n, args.k, args.b
-    d = make_sbm_data(N, K, B)
-
-    class M:                                           # same initial state as our arm's model (prior draw, seed 5678)
-        pass
-    np.random.seed(5678)
-    rs = np.random
-    m = rs.dirichlet(np.ones(K)); c = rs.choice(K, p=m, size=N); p = rs.beta(1.0, 1.0, size=(K, K))
-    model = M(); model.c = c; model.m = m; model.p = p
-    model.mus = d["mus"]; model.sigmas = d["sigmas"]
-    nodes = args.cpu_nodes or min(N, 1024)
-    vals = []
-    for i in range(args.warmup + args.steps):
-        r = cpu_baseline_sbm(d, model, args, nodes)
-        if i >= args.warmup:
-            vals.append(r)
-        if sum(v["measured_s"] for v in vals) > 150:
-            break
-    v = float(np.mean([x["value"] for x in vals]))
-    out = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": len(vals),
-           "warmup": args.warmup, "ms_per_step": 1e3 / v, "higher_is_better": True, "scaling": "weak",
-           "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-           "config": {"workload": "gaussian_sbm_gibbs_sweep N=%d K=%d B=%d (configs[1] model at the metric's N)" % (N, K, B),
-                      "N": N, "K": K, "B": B},
-           "cpu_baseline": dict(vals[-1], value=v),
-           "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    procs = usable_cores()
+    names = ["sbm", "eigen", "latent"] if args.workload == "all" else [args.workload]
+    recs = {n: reference_workload(n, args, procs) for n in names}
+    r = recs[names[0]]
+    out = {"impl": "reference", "metric": METRIC, "value": r["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": r["steps"],
+           "warmup": r["warmup"], "ms_per_step": r["ms_per_step"], "higher_is_better": True, "scaling": "weak",
+           "vs_baseline": None, "dtype": args.dtype, "data": "synthetic", "config": r["config"],
+           "arithmetic": "fp64 NumPy on the same fp32 inputs", "cpu_baseline": r["cpu_baseline"], "e2e": r["e2e"],
+           "workloads": {n: recs[n] for n in names[1:]}, "host": host_info()}
     print(json.dumps(out), flush=True)
 
 

@@ -78,6 +78,7 @@ SIGNATURES = {
                                 ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl)]),
     "gk_eig_mf_update_F": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_dbl, c_dbl, c_dbl, c_vp, c_vp]),
     "gk_eig_mf_pair_stats": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "gk_eig_mf_probit_Z": (c_int, [c_vp, c_vp, c_vp, c_vp, c_dbl, c_int, ctypes.POINTER(c_dbl)]),
     "gk_mf_sbm_soft_stats": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
     "gk_mf_sbm_update_c": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_dbl, c_int, c_vp]),
     "gk_latent_hmc_end": (c_int, [c_vp, c_vp, c_dbl, ctypes.POINTER(c_int), ctypes.POINTER(c_dbl)]),

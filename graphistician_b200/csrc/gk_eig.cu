@@ -214,6 +214,16 @@ __device__ __forceinline__ double gk_hash_uniform(uint64_t seed, uint32_t sweep,
     x ^= x >> 30; x *= 0xBF58476D1CE4E5B9ull; x ^= x >> 27; x *= 0x94D049BB133111EBull; x ^= x >> 31;
     return ((double)(x >> 11) + 0.5) * (1.0 / 9007199254740992.0);
 }
+// E[z] of z ~ N(mu, 1) truncated to [0, inf) (edge) or (-inf, 0] (internals/utils.py:78-101, expected_truncnorm).  The reference's
+// normaliser is normal_cdf(ub) - normal_cdf(lb) of the RAW bounds (:93), i.e. 1/2 whatever mu: literal = that arithmetic,
+// E = mu +- 2 phi(mu); otherwise the truncated-normal mean E = mu +- phi(mu) / Phi(+-mu).
+__device__ __forceinline__ double gk_expected_truncnorm(double mu, bool edge, bool literal) {
+    const double phi = 0.39894228040143267794 * exp(-0.5 * mu * mu);
+    if (literal) return edge ? mu + 2.0 * phi : mu - 2.0 * phi;
+    const double cdf = 0.5 * erfc((edge ? -mu : mu) * 0.70710678118654752440);      // Phi(mu) or Phi(-mu)
+    const double r = phi / fmax(cdf, 1e-300);
+    return edge ? mu + r : mu - r;
+}
 __device__ __forceinline__ double gk_truncnorm(double mu, bool edge, double u) {
     const double c0 = 0.5 * erfc(mu * 0.70710678118654752440);          // Phi(0 - mu)
     const double cl = edge ? c0 : 0.0, cu = edge ? 1.0 : c0;
@@ -222,7 +232,8 @@ __device__ __forceinline__ double gk_truncnorm(double mu, bool edge, double u) {
     return mu - 1.41421356237309504880 * erfcinv(2.0 * cdf);
 }
 
-template <typename T>
+// MODE 0: draws (Gibbs, K7); 1 / 2: expectations (mean field, eigenmodel.py:519-534 mf_expected_Z; 1 = the reference's literal normaliser)
+template <typename T, int MODE>
 __global__ void __launch_bounds__(256) k_eig_tn_tile(T *__restrict__ S, const uint8_t *__restrict__ A, const uint8_t *__restrict__ At,
                                                      int ld, int row0, int nrows, int N, int D, const double *__restrict__ F,
                                                      const double *__restrict__ lmbda, double mu0, uint64_t seed, uint32_t sweep,
@@ -247,8 +258,14 @@ __global__ void __launch_bounds__(256) k_eig_tn_tile(T *__restrict__ S, const ui
         double mu = mu0;
 #pragma unroll
         for (int d = 0; d < GK_EIG_MAXD; ++d) mu += fi[i][d] * fj[j][d];
-        const double z1 = gk_truncnorm(mu, A[off] != 0, gk_hash_uniform(seed, sweep, (uint32_t)n, (uint32_t)m));
-        const double z2 = gk_truncnorm(mu, At[off] != 0, gk_hash_uniform(seed, sweep, (uint32_t)m, (uint32_t)n));
+        double z1, z2;
+        if constexpr (MODE == 0) {
+            z1 = gk_truncnorm(mu, A[off] != 0, gk_hash_uniform(seed, sweep, (uint32_t)n, (uint32_t)m));
+            z2 = gk_truncnorm(mu, At[off] != 0, gk_hash_uniform(seed, sweep, (uint32_t)m, (uint32_t)n));
+        } else {
+            z1 = gk_expected_truncnorm(mu, A[off] != 0, MODE == 1);
+            z2 = gk_expected_truncnorm(mu, At[off] != 0, MODE == 1);
+        }
         S[off] = (T)(z1 + z2);
         local += z1;
     }
@@ -265,9 +282,9 @@ extern "C" int gk_eig_tn_draw(gk_ctx *ctx, gk_eig *e, uint64_t seed, double *sum
     dim3 grid((net->N + GK_PG_TILE - 1) / GK_PG_TILE, (net->nrows + GK_PG_TILE - 1) / GK_PG_TILE);
     gk_time_begin(ctx, 2, (double)net->nrows * net->N * (gk_esize(e->dtype) + 2.0));
     if (e->dtype == GK_F32)
-        k_eig_tn_tile<float><<<grid, 256, 0, ctx->stream>>>((float *)e->S, net->A, net->At, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
+        k_eig_tn_tile<float, 0><<<grid, 256, 0, ctx->stream>>>((float *)e->S, net->A, net->At, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
     else
-        k_eig_tn_tile<double><<<grid, 256, 0, ctx->stream>>>((double *)e->S, net->A, net->At, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
+        k_eig_tn_tile<double, 0><<<grid, 256, 0, ctx->stream>>>((double *)e->S, net->A, net->At, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, seed, e->sweep, e->part);
     gk_time_end(ctx, 2);
     GK_CHECK_LAUNCH(ctx);
     e->sweep++;
@@ -276,6 +293,31 @@ extern "C" int gk_eig_tn_draw(gk_ctx *ctx, gk_eig *e, uint64_t seed, double *sum
     e->have_S = true; e->probit = 1;
     if (sum_z) {
         GK_CUDA(ctx, cudaMemcpyAsync(sum_z, e->scal, 8, cudaMemcpyDeviceToHost, ctx->stream));
+        GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    }
+    return GK_OK;
+}
+
+// Mean-field probit (eigenmodel.py:570-585 _meanfieldupdate_Z fused with :519-534 mf_expected_Z): E[Z] per directed entry
+// from mf_mu_Z = E[mu_0] + E[f_n]^T diag(E[lmbda]) E[f_m]; stores E[Z] + E[Z]^T in the S buffer (probit link).
+extern "C" int gk_eig_mf_probit_Z(gk_ctx *ctx, gk_eig *e, const double *mf_mu_F, const double *E_lmbda, double E_mu0,
+                                  int exact_normalizer, double *sum_EZ) {
+    if (!ctx || !e || !mf_mu_F || !E_lmbda) return GK_EINVAL;
+    int rc = gk_eig_set_params(ctx, e, mf_mu_F, E_mu0, E_lmbda);
+    if (rc) return rc;
+    gk_net *net = e->net;
+    dim3 grid((net->N + GK_PG_TILE - 1) / GK_PG_TILE, (net->nrows + GK_PG_TILE - 1) / GK_PG_TILE);
+    gk_time_begin(ctx, 2, (double)net->nrows * net->N * (gk_esize(e->dtype) + 2.0));
+#define GK_TN_E(T, M) k_eig_tn_tile<T, M><<<grid, 256, 0, ctx->stream>>>((T *)e->S, net->A, net->At, net->ld, net->row0, net->nrows, net->N, e->D, e->F, e->lmbda, e->mu0, 0ull, 0u, e->part)
+    if (e->dtype == GK_F32) { if (exact_normalizer) GK_TN_E(float, 2); else GK_TN_E(float, 1); }
+    else { if (exact_normalizer) GK_TN_E(double, 2); else GK_TN_E(double, 1); }
+    gk_time_end(ctx, 2);
+    GK_CHECK_LAUNCH(ctx);
+    k_sum_partials<<<1, 1024, 0, ctx->stream>>>(e->part, (int)e->npart, e->scal);
+    GK_CHECK_LAUNCH(ctx);
+    e->have_S = true; e->probit = 1;
+    if (sum_EZ) {
+        GK_CUDA(ctx, cudaMemcpyAsync(sum_EZ, e->scal, 8, cudaMemcpyDeviceToHost, ctx->stream));
         GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
     }
     return GK_OK;
@@ -818,6 +860,7 @@ static int mf_update_F_T(gk_ctx *ctx, gk_eig *e, double *mu, double *Sig, const 
         P.G = e->G; P.Phi = e->mfPhi; P.mu = e->mfMu; P.Sig = e->mfSig; P.llT = e->mfSmall; P.lam = e->mfSmall + 64;
         P.mu0 = mu0; P.inv_sigma_F = 1.0 / sigma_F; P.stepsize = stepsize; P.track = Flin ? 0 : 1;
         P.dphi = e->dphi; P.glob = e->glob; P.out_prec = out_prec ? e->out_prec : nullptr; P.out_h = out_h ? e->out_h : nullptr;
+        P.probit = e->probit;
         gk_time_begin(ctx, 5, 0.0);
         k_eig_mf_seq<T, D><<<1, 256, smem, ctx->stream>>>(P);
         gk_time_end(ctx, 5);
@@ -836,7 +879,7 @@ extern "C" int gk_eig_mf_update_F(gk_ctx *ctx, gk_eig *e, double *mf_mu_F, doubl
                                   const double *E_llT, const double *E_lmbda, double E_mu0, double sigma_F, double stepsize,
                                   double *out_prec, double *out_h) {
     if (!ctx || !e || !mf_mu_F || !mf_Sigma_F || !E_llT || !E_lmbda) return GK_EINVAL;
-    if (!e->have_S || e->probit) return gk_fail(ctx, GK_EINVAL, "gk_eig_mf_update_F: call gk_eig_mf_omega or gk_eig_set_S first");
+    if (!e->have_S) return gk_fail(ctx, GK_EINVAL, "gk_eig_mf_update_F: call gk_eig_mf_omega, gk_eig_mf_probit_Z or gk_eig_set_S first");
     if (!(sigma_F > 0) || !(stepsize >= 0.0 && stepsize <= 1.0)) return gk_fail(ctx, GK_EINVAL, "bad sigma_F / stepsize");
     GK_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = mf_ensure(ctx, e);
@@ -853,7 +896,7 @@ static int mf_pair_stats_T(gk_ctx *ctx, gk_eig *e, const double *mu, const doubl
     k_eig_colsum<<<1, 1024, 0, ctx->stream>>>(e->mfMu, e->N, D, e->glob + GK_EIG_GLOB_SUMF);
     GK_CHECK_LAUNCH(ctx);
     if ((rc = launch_gfull<T, D>(ctx, e, e->mfPhi, nullptr))) return rc;
-    k_eig_gstats_phi<D><<<64, 512, 0, ctx->stream>>>(e->G, e->mfPhi, e->N, e->glob, e->spart);
+    k_eig_gstats_phi<D><<<64, 512, 0, ctx->stream>>>(e->G, e->mfPhi, e->N, e->glob, e->spart, e->probit);
     GK_CHECK_LAUNCH(ctx);
     k_eig_gstats_final<D><<<1, 64, 0, ctx->stream>>>(e->spart, 64, e->glob);
     GK_CHECK_LAUNCH(ctx);
@@ -868,7 +911,7 @@ static int mf_pair_stats_T(gk_ctx *ctx, gk_eig *e, const double *mu, const doubl
 
 extern "C" int gk_eig_mf_pair_stats(gk_ctx *ctx, gk_eig *e, const double *mf_mu_F, const double *mf_Sigma_F, double *stats) {
     if (!ctx || !e || !mf_mu_F || !mf_Sigma_F || !stats) return GK_EINVAL;
-    if (!e->have_S || e->probit) return gk_fail(ctx, GK_EINVAL, "gk_eig_mf_pair_stats: call gk_eig_mf_omega or gk_eig_set_S first");
+    if (!e->have_S) return gk_fail(ctx, GK_EINVAL, "gk_eig_mf_pair_stats: call gk_eig_mf_omega, gk_eig_mf_probit_Z or gk_eig_set_S first");
     GK_CUDA(ctx, cudaSetDevice(ctx->device));
     int rc = mf_ensure(ctx, e);
     if (rc) return rc;

@@ -129,6 +129,7 @@ struct gk_eig_mfseq_params {
     void *dphi;                          // gk_eacc<T> [NB][PA]
     double *glob;                        // running column sums of the linear features at GK_EIG_GLOB_SUMF
     double *out_prec, *out_h;
+    int probit;                          // 1: S == 2 and the S buffer holds E[Z] + E[Z]^T (eigenmodel.py:587-650)
 };
 
 template <typename T, int D>
@@ -153,10 +154,12 @@ __global__ void __launch_bounds__(256, 1) k_eig_mf_seq(gk_eig_mfseq_params P) {
         const int i = idx / (NB / VT), v = idx - i * (NB / VT);
         *(int4 *)(Sb + (size_t)i * NB + v * VT) = __ldg((const int4 *)((const T *)P.Sblk + (size_t)i * P.ldS + v * VT));
     }
-    for (int idx = tid; idx < nb * (NB / 16); idx += 256) {
-        const int i = idx / (NB / 16), v = idx - i * (NB / 16);
-        *(int4 *)(Ab + (size_t)i * NB + v * 16) = __ldg((const int4 *)(P.Ablk + (size_t)i * P.ldA + v * 16));
-    }
+    const bool probit = P.probit != 0;
+    if (!probit)
+        for (int idx = tid; idx < nb * (NB / 16); idx += 256) {
+            const int i = idx / (NB / 16), v = idx - i * (NB / 16);
+            *(int4 *)(Ab + (size_t)i * NB + v * 16) = __ldg((const int4 *)(P.Ablk + (size_t)i * P.ldA + v * 16));
+        }
     for (int t = tid; t < nb * PA; t += 256) Gd[t] = 0.0;
     if (tid < D) sumF[tid] = P.glob[GK_EIG_GLOB_SUMF + tid];
     int pa = 0, pb = 0;
@@ -175,7 +178,7 @@ __global__ void __launch_bounds__(256, 1) k_eig_mf_seq(gk_eig_mfseq_params P) {
         } else if (tid >= 64 && tid < 64 + D) {
             const int a = tid - 64;
             const double lin = P.Phi[(size_t)n * PA + Q + a];
-            const double v = P.lam[a] * (gs[Pn + a] - (sumF[a] - lin) - P.mu0 * gs[Q + a]);
+            const double v = P.lam[a] * (gs[Pn + a] - (probit ? 0.0 : sumF[a] - lin) - P.mu0 * gs[Q + a]);
             hv[a] = v;
             if (P.out_h) P.out_h[(size_t)n * D + a] = v;
         }
@@ -233,7 +236,7 @@ __global__ void __launch_bounds__(256, 1) k_eig_mf_seq(gk_eig_mfseq_params P) {
         __syncthreads();
         for (int e = tid; e < (nb - t - 1) * PA; e += 256) {
             const int jr = e / PA, p = e - jr * PA, j = t + 1 + jr;
-            const double x = p < Pn ? (double)Sb[t * NB + j] : (double)Ab[t * NB + j];
+            const double x = p < Pn ? (probit ? 2.0 : (double)Sb[t * NB + j]) : (probit ? (double)Sb[t * NB + j] : (double)Ab[t * NB + j]);
             Gd[j * PA + p] += x * dps[p];
         }
         __syncthreads();
@@ -247,7 +250,7 @@ __global__ void __launch_bounds__(256, 1) k_eig_mf_seq(gk_eig_mfseq_params P) {
 //   hK[a]  = 1/2 sum_n Phi_n[P+a] (G[n][P+a] - (sumF[a] - Phi_n[P+a]))
 template <int D>
 __global__ void k_eig_gstats_phi(const double *__restrict__ G, const double *__restrict__ Phi, int N, const double *__restrict__ glob,
-                                 double *__restrict__ part) {
+                                 double *__restrict__ part, int probit) {
     constexpr int Pn = gk_edim<D>::P, PA = gk_edim<D>::PA;
     __shared__ double red[8][gk_edim<D>::PA];
     const int tid = threadIdx.x, p = tid % 64, g = tid / 64;
@@ -258,7 +261,7 @@ __global__ void k_eig_gstats_phi(const double *__restrict__ G, const double *__r
         const double sF = glob[GK_EIG_GLOB_SUMF + pa];
         for (int n = lo + g; n < hi; n += 8) {
             const double ph = Phi[(size_t)n * PA + p], gv = G[(size_t)n * PA + p];
-            s += p < Pn ? ph * gv : ph * (gv - (sF - ph));
+            s += p < Pn ? ph * gv : ph * (gv - (probit ? 0.0 : sF - ph));
         }
         red[g][p] = s;
     }

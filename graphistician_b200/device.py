@@ -221,6 +221,16 @@ class DeviceEigenmodel:
                                                    ctypes.byref(s0), ctypes.byref(s1)))
         return s0.value, s1.value
 
+    def mf_probit_Z(self, mf_mu_F, E_lmbda, E_mu0, exact_normalizer=False):
+        """Probit mean field: S buffer <- E[Z] + E[Z]^T (probit link); returns sum of E[Z] over n != m."""
+        assert self.comm is None, "the mean-field eigenmodel path runs on single-rank networks"
+        F = np.ascontiguousarray(mf_mu_F, dtype=np.float64); lam = np.ascontiguousarray(E_lmbda, dtype=np.float64)
+        assert F.shape == (self.N, self.D) and lam.shape == (self.D,)
+        s = ctypes.c_double(0.0)
+        self.ctx.check(self.ctx.lib.gk_eig_mf_probit_Z(self.ctx.h, self.h, ptr(F), ptr(lam), float(E_mu0),
+                                                      int(bool(exact_normalizer)), ctypes.byref(s)))
+        return s.value
+
     def mf_update_F(self, mf_mu_F, mf_Sigma_F, F_lin, E_llT, E_lmbda, E_mu0, sigma_F, stepsize=1.0, want_conditionals=False):
         """Serial mean-field update of q(F).  Returns (mf_mu_F, mf_Sigma_F, prec or None, h or None)."""
         assert self.comm is None, "the mean-field eigenmodel path runs on single-rank networks"

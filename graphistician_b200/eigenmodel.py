@@ -452,9 +452,152 @@ class _GibbsProbitEigenmodel(_ProbitEigenmodelBase):
             self.lmbda = np.random.multivariate_normal(self.mu_lmbda, self.sigma_lmbda * np.eye(self.D))
 
 
-class ProbitEigenmodel(_GibbsProbitEigenmodel):
-    """eigenmodel.py:772 (Gibbs part)."""
-    pass
+class _MeanFieldProbitEigenModel(_ProbitEigenmodelBase):
+    """eigenmodel.py:382-770.  Fixed networks (mf_A = A).  The N^2 work runs in libgk:
+      _meanfieldupdate_Z + mf_expected_Z  <- gk_eig_mf_probit_Z   (:570-585, 519-534; E[Z] per tile, never an N x N host array)
+      _meanfieldupdate_F                  <- gk_eig_mf_update_F   (:610-641, serial in n; probit link: S == 2, h from E[Z] - E[mu_0])
+      mu0 / lmbda sums                    <- the E[Z] kernel's tile sums, gk_eig_mf_pair_stats (:587-608, 643-674)
+    `literal_truncnorm_normalizer` (default True) keeps a reference quirk: expected_truncnorm normalises by
+    normal_cdf(ub) - normal_cdf(lb) of the RAW bounds (internals/utils.py:93), i.e. by 1/2 whatever mu; False uses the
+    truncated-normal mean."""
+    literal_truncnorm_normalizer = True
+
+    def _mf_init(self):
+        """:383-399 (called by the concrete class after the Gibbs constructor)."""
+        N, D = self.N, self.D
+        self.mf_mu_mu0 = self.mu_mu_0
+        self.mf_sigma_mu0 = self.sigma_mu0
+        self.mf_mu_F = np.sqrt(self.sigma_F) * np.random.randn(N, D)
+        self.mf_Sigma_F = np.tile((self.sigma_F * np.eye(D))[None, :, :], [N, 1, 1])
+        if self.lmbda_given:
+            self.mf_mu_lmbda = self.lmbda.copy()
+            self.mf_Sigma_lmbda = 1e-16 * np.eye(D)
+        else:
+            self.mf_mu_lmbda = self.mu_lmbda.copy()
+            self.mf_Sigma_lmbda = self.sigma_lmbda * np.eye(D)
+
+    init_with_gibbs = _MeanFieldLogisticEigenModel.init_with_gibbs            # :402-410, same body as :988-996
+
+    # ---- expectations (:472-568; N x N on the host: reporting only) ------------------------------------------------
+    mf_expected_mu = _MeanFieldLogisticEigenModel.mf_expected_mu
+    mf_expected_musq = _MeanFieldLogisticEigenModel.mf_expected_musq
+    mf_variance_mu = _MeanFieldLogisticEigenModel.mf_variance_mu
+    mf_expected_mu0sq = _MeanFieldLogisticEigenModel.mf_expected_mu0sq
+    mf_expected_ffT = _MeanFieldLogisticEigenModel.mf_expected_ffT
+    mf_expected_llT = _MeanFieldLogisticEigenModel.mf_expected_llT
+    resample_from_mf = _MeanFieldLogisticEigenModel.resample_from_mf          # :758-769
+
+    _mf_Z_snapshot = None
+
+    @property
+    def mf_mu_Z(self):
+        """The N x N array _meanfieldupdate_Z sets (:570-585), rebuilt on demand from the (E[mu_0], E[F], E[lmbda]) it
+        was computed from -- the device recomputes it per tile and never stores it.  Zeros before the first update (:388)."""
+        if self._mf_Z_snapshot is None:
+            return np.zeros((self.N, self.N))
+        mu0, F, lam = self._mf_Z_snapshot
+        Mu = mu0 + (F * lam[None, :]).dot(F.T)
+        np.fill_diagonal(Mu, mu0)
+        return Mu
+
+    def _truncnorm_mean(self, mu, edge):
+        phi = np.exp(-0.5 * mu * mu) / np.sqrt(2 * np.pi)
+        if self.literal_truncnorm_normalizer:
+            return np.where(edge, mu + 2.0 * phi, mu - 2.0 * phi)
+        from scipy.special import erfc
+        cdf = 0.5 * erfc(np.where(edge, -mu, mu) / np.sqrt(2.0))
+        r = phi / np.maximum(cdf, 1e-300)
+        return np.where(edge, mu + r, mu - r)
+
+    def mf_expected_Z(self, A):
+        """:519-534 for a fixed network (host, N x N: reporting / tests only)."""
+        return self._truncnorm_mean(self.mf_mu_Z, np.asarray(A) != 0)
+
+    def mf_expected_log_p(self):
+        from scipy.special import erfc
+        return np.log(1.0 - 0.5 * erfc(self.mf_mu_Z / np.sqrt(2.0)))          # :440-447
+
+    def mf_expected_log_notp(self):
+        from scipy.special import erfc
+        return np.log(0.5 * erfc(self.mf_mu_Z / np.sqrt(2.0)))                # :449-455
+
+    def expected_log_likelihood(self, network):
+        A = as_network(network).A
+        return (A * self.mf_expected_log_p() + (1 - A) * self.mf_expected_log_notp()).sum()
+
+    # ---- the updates --------------------------------------------------------------------------------------------
+    def meanfieldupdate(self, network):
+        """:412-438 (order: Z, mu0, F, lmbda).  E[Z] is computed once, from the q(mu_0), q(F), q(lmbda) at entry, and is
+        held fixed through the three updates, as the reference does (mf_mu_Z is set at :570-585 and not touched again)."""
+        network = as_network(network)
+        sum_EZ = self._meanfieldupdate_Z(network)
+        self._meanfieldupdate_mu0(sum_EZ)
+        self._meanfieldupdate_F(network)
+        if not self.lmbda_given:
+            self._meanfieldupdate_lmbda(network)
+
+    def _meanfieldupdate_Z(self, network):
+        """:570-585 + :519-534.  Leaves E[Z] + E[Z]^T on the device; returns the sum of E[Z] over n != m."""
+        dev = self._device_state(as_network(network))
+        self._mf_Z_snapshot = (float(self.mf_mu_mu0), self.mf_mu_F.copy(), self.mf_mu_lmbda.copy())
+        return dev.mf_probit_Z(self.mf_mu_F, self.mf_mu_lmbda, self.mf_mu_mu0, not self.literal_truncnorm_normalizer)
+
+    def _meanfieldupdate_mu0(self, sum_EZ):
+        """:587-608: Zcent = E[Z] - E[F] diag(E[lmbda]) E[F]^T off the diagonal."""
+        F, lam = self.mf_mu_F, self.mf_mu_lmbda
+        cs = F.sum(0)
+        sum_FLF = float(((cs * lam) * cs).sum() - ((F * lam) * F).sum())      # sum_{n != m} f_n^T Lambda f_m
+        post_prec = 1.0 / self.sigma_mu0 + self.N ** 2 - self.N
+        post_mean_dot_prec = self.mu_mu_0 / self.sigma_mu0 + sum_EZ - sum_FLF
+        self.mf_sigma_mu0 = 1.0 / post_prec
+        self.mf_mu_mu0 = self.mf_sigma_mu0 * post_mean_dot_prec
+
+    def _meanfieldupdate_F(self, network, want_conditionals=False):
+        """:610-641 (h built from mf_mu_F as it is updated, :632-633)."""
+        dev = self._device_state(network)
+        self.mf_mu_F, self.mf_Sigma_F, prec, h = dev.mf_update_F(
+            self.mf_mu_F, self.mf_Sigma_F, None, self.mf_expected_llT(), self.mf_mu_lmbda, self.mf_mu_mu0, self.sigma_F,
+            1.0, want_conditionals)
+        assert np.all(np.isfinite(self.mf_mu_F)) and np.all(np.isfinite(self.mf_Sigma_F))
+        return prec, h
+
+    def _meanfieldupdate_lmbda(self, network):
+        """:643-674"""
+        dev = self._device_state(network)
+        st = dev.mf_pair_stats(self.mf_mu_F, self.mf_Sigma_F)
+        post_prec = 1.0 / self.sigma_lmbda * np.eye(self.D) + st["Pq"]
+        post_mean_dot_prec = self.mu_lmbda / self.sigma_lmbda + st["hK"] - self.mf_mu_mu0 * st["hS"]
+        self.mf_Sigma_lmbda = np.linalg.inv(post_prec)
+        self.mf_mu_lmbda = self.mf_Sigma_lmbda.dot(post_mean_dot_prec)
+
+    def get_vlb(self, network=None):
+        """:688-756.  The prior / entropy terms of q(mu0), q(F), q(lmbda) are the logistic class's (:1262-1298, same code);
+        with a network, the E[ln p(z | mu)] - E[ln q(z)] terms of :694-727 are added (N x N host arithmetic, as in the
+        reference: get_vlb is a diagnostic, not on the sweep path)."""
+        vlb = _MeanFieldLogisticEigenModel.get_vlb(self)
+        if network is None:
+            return vlb
+        from scipy.special import erfc
+        A = np.asarray(as_network(network).A) != 0
+        mu = self.mf_mu_Z
+        phi = np.exp(-0.5 * mu * mu) / np.sqrt(2 * np.pi)
+        Zn = np.where(A, 1.0 - 0.5 * erfc(mu / np.sqrt(2.0)), 0.5 * erfc(mu / np.sqrt(2.0)))     # P(z in its half line)
+        Zn = np.maximum(Zn, 1e-300)
+        E_z = np.where(A, mu + phi / Zn, mu - phi / Zn)
+        E_zsq = 1.0 + mu * E_z                                # truncated at 0: E[z^2] = 1 + mu E[z]
+        E_mu, E_musq = self.mf_expected_mu(), self.mf_expected_musq()
+        c = -0.5 * np.log(2 * np.pi)
+        cross = c - 0.5 * E_zsq + E_z * E_mu - 0.5 * E_musq   # ScalarGaussian().negentropy(E_x, E_xsq, E_mu, E_musq), sigmasq = 1
+        own = c - 0.5 * (E_zsq - 2 * mu * E_z + mu * mu) - np.log(Zn)          # TruncatedScalarGaussian(mu, 1).negentropy()
+        return float(vlb + (cross - own).sum())
+
+
+class ProbitEigenmodel(_GibbsProbitEigenmodel, _MeanFieldProbitEigenModel):
+    """eigenmodel.py:772."""
+
+    def __init__(self, N, D, **kwargs):
+        super(ProbitEigenmodel, self).__init__(N, D, **kwargs)
+        self._mf_init()
 
 
 Eigenmodel = ProbitEigenmodel        # the name test/test_probit_eigenmodel_geweke.py:8 imports

@@ -74,12 +74,14 @@ class FixedGaussianNetwork(WeightedDirectedNetwork):
             d.close()
         self._dev = {}
         self._stale = set()
+        self.__dict__.pop("_sum_A", None)
 
     def invalidate(self):
         """Call after mutating A or W in place: the next ``device()`` copies the host arrays to the device again.
         Unsharded copies keep their device allocations (and the model-side state bound to them) and are refilled by
         ``DeviceNetwork.upload``; sharded copies are dropped and rebuilt."""
         from .device import DeviceNetwork
+        self.__dict__.pop("_sum_A", None)          # host-side caches of A go stale with it
         for key, d in list(self._dev.items()):
             if type(d) is DeviceNetwork and d.nrows == d.N:
                 self._stale.add(key)
@@ -126,35 +128,45 @@ class GaussianWeightedNetworkDistribution(object):
 
 # ------------------------------------------------------------------------------------------------------
 # new-API callers pass bare arrays -- ``adjacency.resample(A)``, ``weights.resample((A, W))``
-# (networks.py:69-71).  The device copy is found again through a small identity cache: one network object
-# per live host array A (upgraded in place when a W shows up for the same A).
+# (networks.py:69-71).  The device copy is found again through a small, BOUNDED identity cache: one network
+# object per host array A (upgraded in place when a W shows up for the same A).  The cache owns its entries
+# (a network holds A, so the id cannot be reused while the entry lives) and evicts the least recently used one,
+# freeing its device copies, once more than ``MAX_CACHED_NETWORKS`` distinct arrays have been seen -- a Geweke or
+# AIS loop that draws a fresh A every iteration therefore keeps a flat device footprint.
 # ------------------------------------------------------------------------------------------------------
-_NETWORKS = {}
+import collections
+
+MAX_CACHED_NETWORKS = 4
+_NETWORKS = collections.OrderedDict()
 
 
 def network_for(A, W=None):
     """The (cached) network object that owns the device copy of the host arrays A (N x N) and W (N x N x B).
     Data is treated as immutable, as the reference treats it (SURVEY.md 8b 'Ownership'); after an in-place edit
     of A or W call ``network_for(A, W).invalidate()``."""
-    import weakref
     if isinstance(A, WeightedDirectedNetwork):
         return A
     A = np.asarray(A)
     key = id(A)
-    ent = _NETWORKS.get(key)
-    if ent is not None:
-        ref, net = ent
-        if ref() is A:
-            if W is not None and (net.W is None or net._W_id != id(W)):
-                net._drop()
-                net.__init__(A, W)
-                net._W_id = id(W)
-            return net
-        del _NETWORKS[key]
+    net = _NETWORKS.get(key)
+    if net is not None and net.A is A:
+        _NETWORKS.move_to_end(key)
+        if W is not None and (net.W is None or net._W_id != id(W)):
+            net._drop()
+            net.__init__(A, W)
+            net._W_id = id(W)
+        return net
     net = FixedGaussianNetwork(A, W)
     net._W_id = id(W) if W is not None else None
-    try:
-        _NETWORKS[key] = (weakref.ref(A, lambda _r, k=key: _NETWORKS.pop(k, None)), net)
-    except TypeError:                      # not weak-referenceable: no caching
-        pass
+    _NETWORKS[key] = net
+    while len(_NETWORKS) > MAX_CACHED_NETWORKS:
+        _, old = _NETWORKS.popitem(last=False)
+        old._drop()
     return net
+
+
+def drop_cached_networks():
+    """Free every cached network's device copies (the cache is rebuilt on demand)."""
+    while _NETWORKS:
+        _, old = _NETWORKS.popitem(last=False)
+        old._drop()

@@ -216,6 +216,16 @@ int gk_eig_mf_update_F(gk_ctx *ctx, gk_eig *eig, double *mf_mu_F, double *mf_Sig
  * Pq[a,b] = sum S E[f1 f1^T][a,b] E[f2 f2^T][a,b],  hS[a] = sum S mu1a mu2a,  hK[a] = sum (A12 + A21 - 1) mu1a mu2a. */
 int gk_eig_mf_pair_stats(gk_ctx *ctx, gk_eig *eig, const double *mf_mu_F, const double *mf_Sigma_F, double *stats);
 
+/* Mean-field PROBIT eigenmodel (eigenmodel.py:382-770, _MeanFieldProbitEigenModel).  gk_eig_mf_probit_Z replaces
+ * _meanfieldupdate_Z (:570-585: mf_mu_Z = E[mu_0] + E[f_n]^T diag(E[lmbda]) E[f_m], diagonal = E[mu_0]) fused with mf_expected_Z
+ * (:519-534) and internals/utils.py:78-101 (expected_truncnorm) for a fixed network (mf_A = A): E[Z] of every directed entry is
+ * computed per tile, E[Z] + E[Z]^T (zero diagonal) is stored in the state's S buffer and the state switches to the probit link, so
+ * that gk_eig_mf_update_F then runs :610-641 (S == 2, h from E[Z] - E[mu_0]) and gk_eig_mf_pair_stats feeds :643-674.
+ * exact_normalizer = 0 keeps the reference's normaliser (utils.py:93 takes normal_cdf of the RAW bounds, i.e. 1/2 whatever mu:
+ * E = mu +- 2 phi(mu)); 1 = the truncated-normal mean mu +- phi(mu)/Phi(+-mu).  sum_EZ (optional) = sum of E[Z] over n != m (:598-604). */
+int gk_eig_mf_probit_Z(gk_ctx *ctx, gk_eig *eig, const double *mf_mu_F, const double *E_lmbda, double E_mu0,
+                       int exact_normalizer, double *sum_EZ);
+
 /* ---- K10: mean-field SBM ---------------------------------------------------------
  * Fixed networks only (E_A = A, E_W = W, E_WWT = W W^T: the reference's FixedGaussianNetwork); unsharded.
  * gk_mf_sbm_soft_stats replaces the C x C loops of stochastic_block_model.py:366-389 (mf_update_p) and :340-344 with

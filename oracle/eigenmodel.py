@@ -96,7 +96,9 @@ def resample_F(S, Ksym_minus_mu0S, F, lmbda, sigma_F, z, base_scale=None, nodes=
     F = F.copy()
     precs = np.zeros((N, D, D)); hs = np.zeros((N, D))
     llT = np.outer(lmbda, lmbda)
-    for n in range(N if nodes is None else nodes):       # nodes: bounded sample for the timed CPU baseline
+    # nodes: bounded sample for the timed CPU baseline -- a count (the first `nodes` nodes) or a (lo, hi) range
+    lo, hi = (0, N) if nodes is None else ((0, nodes) if np.isscalar(nodes) else nodes)
+    for n in range(lo, hi):
         s = S[n].copy(); s[n] = 0.0
         r = Ksym_minus_mu0S[n].copy(); r[n] = 0.0
         prec = np.eye(D) / sigma_F + (F.T * s).dot(F) * llT
