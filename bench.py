@@ -457,11 +457,12 @@ def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, fi
     return rec, wl
 
 
-def sbm_mixing_record(args, R, wl, dtype):
-    """Sweeps WITH movers: the planted data are overwritten in place by a weak-signal draw of the same model
-    (block structure shrunk to 5 %: p within +-0.05 of its mean), where the labels never settle."""
+def sbm_mixing_record(args, R, wl, dtype, signal):
+    """Sweeps WITH movers: the planted data are overwritten in place by a draw of the same model whose block structure
+    is shrunk to `signal` (0.05: p within +-0.05 of its mean -- the labels settle slowly; 0: no structure at all --
+    the labels never settle and almost every node moves in every sweep, the worst case of the serial kernel)."""
     d, network, N = wl["data"], wl["network"], args.n
-    truth = sbm_truth(N, args.k, args.b, seed=4321, rank=R.rank, signal=0.05)
+    truth = sbm_truth(N, args.k, args.b, seed=4321, rank=R.rank, signal=signal)
     fill_sbm_data(d["A"], d["W"], truth, seed=4321, rank=R.rank)
     network.invalidate()
     np.random.seed(8765)
@@ -476,7 +477,7 @@ def sbm_mixing_record(args, R, wl, dtype):
     del nch[:]
     steps = 5
     ms = R.timed(step, steps)
-    return {"dataset": "weak signal: p = mean + 0.05 (p - mean), mu x 0.05, Sigma = I + 0.05 (Sigma - I), seed 4321",
+    return {"dataset": "p = mean + s (p - mean), mu x s, Sigma = I + s (Sigma - I) with s = %g, seed 4321" % signal,
             "ms_per_step": ms / steps, "value": R.world * steps / (ms * 1e-3), "unit": UNIT, "steps": steps,
             "n_changed_per_sweep": nch, "us_per_move": 1e3 * (ms / steps) / max(1.0, float(np.mean(nch)))}
 
@@ -513,7 +514,8 @@ def run_ours(args):
     if primary == "sbm" and extras:
         mixing = {"first_sweep_from_prior_labels_ms": rec.get("first_sweep_ms"),
                   "first_sweep_n_changed": rec.get("first_sweep_n_changed")}
-        mixing["weak_signal"] = sbm_mixing_record(args, R, wl, args.dtype)
+        mixing["weak_signal"] = sbm_mixing_record(args, R, wl, args.dtype, 0.05)
+        mixing["no_signal"] = sbm_mixing_record(args, R, wl, args.dtype, 0.0)
         out["mixing"] = mixing
     release(wl)
     out["workloads"] = {}

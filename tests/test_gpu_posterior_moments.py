@@ -50,6 +50,7 @@ def test_sbm_posterior_moments():
     # GPU chain
     np.random.seed(11)
     model = GaussianStochasticBlockModel(N, B, C=C, dtype="f64")
+    model.c = c_true.copy()                  # both chains start in the main mode (the merged-block states are metastable)
     net = FixedGaussianNetwork(A, W)
     gpu = []
     for it in range(T + burn):
@@ -61,7 +62,7 @@ def test_sbm_posterior_moments():
     hyp = dict(pi=model.pi, tau0=model.tau0, tau1=model.tau1, niw=(wm.mu_0, wm.sigma_0, wm.kappa_0, wm.nu_0))
     rs = np.random.RandomState(22)
     m0 = rs.dirichlet(np.ones(C))
-    state = dict(c=rs.choice(C, p=m0, size=N), m=m0, p=rs.beta(1, 1, (C, C)), mus=np.zeros((C, C, B)),
+    state = dict(c=c_true.copy(), m=m0, p=rs.beta(1, 1, (C, C)), mus=np.zeros((C, C, B)),
                  sigmas=np.tile(np.eye(B), (C, C, 1, 1)))
     Af = A.astype(float)
     ref = []
