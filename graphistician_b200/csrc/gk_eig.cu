@@ -21,6 +21,7 @@ struct gk_eig {
     double *mfMu = nullptr, *mfSig = nullptr, *mfLin = nullptr, *mfPhi = nullptr, *mfSmall = nullptr, *mfPart = nullptr;   // mean-field q (K11)
     long long *prof = nullptr;         // debug cycle counters of k_eig_seq3 (env GK_EIG_PROF=1)
     int use_fast = 1;                  // unsharded sweeps use the running-G form (GK_EIG_OPT_FAST_SWEEP)
+    int use_seq5 = 1;                  // fp32 path: register-resident solver k_eig_seq5 (GK_EIG_OPT_SEQ5); 0 = k_eig_seq4
     double mu0 = 0.0;
     bool have_S = false;
     bool chol_f64 = false;             // f32 storage: factorise the D x D conditionals in fp32 unless set
@@ -99,6 +100,7 @@ extern "C" int gk_eig_set_option(gk_ctx *ctx, gk_eig *e, int option, int value) 
     if (option == GK_EIG_OPT_CHOL_F64) { e->chol_f64 = value != 0; return GK_OK; }
     if (option == GK_EIG_OPT_FAST_SWEEP) { e->use_fast = value != 0; return GK_OK; }
     if (option == GK_EIG_OPT_OVERLAP_PUSH) { e->overlap_push = value != 0; return GK_OK; }
+    if (option == GK_EIG_OPT_SEQ5) { e->use_seq5 = value != 0; return GK_OK; }
     return gk_fail(ctx, GK_EINVAL, "unknown eigenmodel option %d", option);
 }
 
@@ -462,6 +464,40 @@ static int launch_seq4_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sig
     return GK_OK;
 }
 
+// fp32 storage + fp32 factorisation: the register-resident solver of gk_eig_seq5.cuh (GK_EIG_OPT_SEQ5, default on)
+template <int D, bool PROF>
+static int launch_seq5_p(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sigma_F) {
+    const size_t smem = gk_eig_seq5_smem<D>();
+    GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq5<D, PROF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    gk_net *net = e->net;
+    gk_eig_seq4_params P;
+    P.n0 = n0; P.nb = nb; P.N = e->N;
+    P.Sblk = (const float *)e->S + (size_t)n0 * net->ld + n0; P.ldS = net->ld;
+    P.Ablk = net->Asym + (size_t)n0 * net->ld + n0; P.ldA = net->ld;
+    P.F = e->F; P.z = e->z; P.lmbda = e->lmbda; P.mu0 = e->mu0; P.inv_sigma_F = inv_sigma_F;
+    P.G = e->G; P.dphi = e->dphi; P.glob = e->glob; P.out_prec = e->out_prec; P.out_h = e->out_h; P.probit = e->probit;
+    P.prof = e->prof;
+    gk_time_begin(ctx, 5, 0.0);
+    if (e->overlap_push) {
+        cudaLaunchConfig_t cfg = {};
+        cfg.gridDim = dim3(1); cfg.blockDim = dim3(GK_SEQ5_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = ctx->stream;
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+        at[0].val.programmaticStreamSerializationAllowed = 1;
+        cfg.attrs = at; cfg.numAttrs = 1;
+        GK_CUDA(ctx, cudaLaunchKernelEx(&cfg, k_eig_seq5<D, PROF>, P));
+    } else {
+        k_eig_seq5<D, PROF><<<1, GK_SEQ5_THREADS, smem, ctx->stream>>>(P);
+    }
+    gk_time_end(ctx, 5);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+template <int D>
+static int launch_seq5(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sigma_F) {
+    return e->prof ? launch_seq5_p<D, true>(ctx, e, n0, nb, inv_sigma_F) : launch_seq5_p<D, false>(ctx, e, n0, nb, inv_sigma_F);
+}
+
 // one full contraction G[n] = sum_m X[m,n] Phi_m over the whole network (Phi from e->F, or given rows phi_given)
 template <typename T, int D>
 static int launch_gfull(gk_ctx *ctx, gk_eig *e, const double *phi_given, size_t *smem_push_out) {
@@ -549,8 +585,10 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
     int blk = 0;
     for (int n0 = 0; n0 < N; n0 += NB) {
         const int nb = std::min(NB, N - n0);
-        int rc = (sizeof(T) == 4 && !e->chol_f64) ? launch_seq4_ch<T, float, D>(ctx, e, n0, nb, inv_sigma_F)
-                                                  : launch_seq4_ch<T, double, D>(ctx, e, n0, nb, inv_sigma_F);
+        int rc;
+        if (sizeof(T) == 4 && !e->chol_f64 && e->use_seq5) rc = launch_seq5<D>(ctx, e, n0, nb, inv_sigma_F);
+        else rc = (sizeof(T) == 4 && !e->chol_f64) ? launch_seq4_ch<T, float, D>(ctx, e, n0, nb, inv_sigma_F)
+                                                   : launch_seq4_ch<T, double, D>(ctx, e, n0, nb, inv_sigma_F);
         if (rc) return rc;
         // Push of this block's change.  Only the strip holding the NEXT block's columns is needed before the next
         // k_eig_seq4; every other strip goes to a second stream and runs under it.  Ordering: rest(b) after seq4(b)
@@ -579,6 +617,11 @@ static int sweep_F_fast(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
         long long h[16];
         GK_CUDA(ctx, cudaMemcpyAsync(h, e->prof, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
         GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (e->use_seq5 && e->dtype == GK_F32 && !e->chol_f64)
+            fprintf(stderr, "[gk_eig seq5 prof] cycles/node: solver loop %.0f = build+factor %.0f, wait base %.0f, load+backsub+store %.0f, fence %.0f, arrive %.0f | finisher: wait f %.0f, phase %.0f (->dphi %.0f, ->tot %.0f, bar4 %.0f) | summer pre-sum %.0f\n",
+                    (double)h[0] / N, (double)h[2] / N, (double)h[1] / N, (double)h[3] / N, (double)h[4] / N, (double)h[5] / N, (double)h[8] / N, (double)h[9] / N,
+                    (double)h[11] / N, (double)h[12] / N, (double)h[13] / N, (double)h[10] / N);
+        else
         fprintf(stderr, "[gk_eig prof] cycles/node: solver busy %.0f barrier wait %.0f | updater(63) busy %.0f barrier wait %.0f\n",
                 (double)h[0] / N, (double)h[7] / N, (double)h[8] / N, (double)h[8 + 7] / N);
         fprintf(stderr, "[gk_eig prof] cycles/node: loop %.0f setup %.0f flush %.0f whole kernel %.0f\n", (double)h[3] / N, (double)h[4] / N, (double)h[5] / N, (double)h[6] / N);

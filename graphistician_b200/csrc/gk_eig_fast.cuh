@@ -333,6 +333,7 @@ __global__ void __launch_bounds__(32 * GK_EPC_COLS) k_eig_push_cols(const T *__r
 }
 
 #include "gk_eig_seq4.cuh"
+#include "gk_eig_seq5.cuh"
 
 // ---------------------------------------------------------------------------------------------------
 // k_eig_gstats: pair statistics of eigenmodel.py:910-965 from the all-new G (one CTA per node range, fixed order):

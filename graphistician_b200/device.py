@@ -49,6 +49,16 @@ class DeviceNetwork:
         self.ctx.check(self.ctx.lib.gk_network_set_diag(self.ctx.h, self.h, ptr(dA), ptr(dW)))
         self.diagA, self.diagW = dA, dW
         self._diag_feat = None
+        self._edge_count = None
+
+    def edge_count(self):
+        """Number of non-zero entries of A over this rank's rows, diagonal included: one K1 pass (K = 1) on the device,
+        cached until the next upload (so an in-place edit of A followed by invalidate() is seen)."""
+        if self._edge_count is None:
+            n_edge, _, _ = self.block_stats(np.zeros(self.N, np.int32), 1)
+            lo, hi = self.row0, self.row0 + self.nrows
+            self._edge_count = int(n_edge[0, 0]) + int(np.count_nonzero(self.diagA[lo:hi]))
+        return self._edge_count
 
     def device_bytes(self):
         return int(self.ctx.lib.gk_network_device_bytes(self.h))

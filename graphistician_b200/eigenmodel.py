@@ -102,6 +102,13 @@ class _EigenmodelBase(NetworkDistribution):
             self._dev = (net, DeviceEigenmodel(net, self.D))
         return self._dev[1]
 
+    def _edge_total(self, network):
+        """sum of A over all N^2 entries, counted on the device with the upload it belongs to (summed over row shards)."""
+        net = network.device(self.dtype)
+        if getattr(net, "comm", None) is not None:
+            return float(net.comm.allreduce_np(np.array([float(net.local.edge_count())]))[0])
+        return float(net.edge_count())
+
     def __deepcopy__(self, memo):
         cls = self.__class__
         new = cls.__new__(cls)
@@ -175,10 +182,8 @@ class _GibbsLogisticEigenmodel(_LogisticEigenmodelBase):
 
     def _mu0_conditional(self, network, sum_omega, st):
         """eigenmodel.py:914-927: (post_prec, post_mean_dot_prec)."""
-        if not hasattr(network, "_sum_A"):
-            network._sum_A = float(np.count_nonzero(network.A))
         post_prec = 1.0 / self.sigma_mu0 + sum_omega
-        sum_kappa = network._sum_A - 0.5 * self.N * self.N
+        sum_kappa = self._edge_total(network) - 0.5 * self.N * self.N
         h = self.mu_mu_0 / self.sigma_mu0 + sum_kappa - float(np.dot(self.lmbda, st["hS"]))
         return post_prec, h
 
@@ -257,9 +262,7 @@ class _MeanFieldLogisticEigenModel(_LogisticEigenmodelBase):
 
     def _sum_kappa(self, network):
         """sum of kappa(E_A) = A - 1/2 over all N^2 entries (:1083)."""
-        net = network.device(self.dtype)
-        n_edge, _, _ = net.block_stats(np.zeros(self.N, np.int32), 1)
-        return float(n_edge[0, 0]) + float(np.count_nonzero(net.diagA)) - 0.5 * self.N * self.N
+        return self._edge_total(network) - 0.5 * self.N * self.N
 
     def _meanfieldupdate_mu0(self, network, sums, stepsize=1.0):
         """:1066-1088"""

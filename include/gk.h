@@ -114,7 +114,10 @@ enum { GK_EIG_OPT_CHOL_F64 = 0,
        GK_EIG_OPT_FAST_SWEEP = 1,
        /* 1 (default): within the running-G sweep, the push of block b's change to all strips except the next block's
         * runs on a second stream under the serial kernel of block b+1; 0: everything on the context stream */
-       GK_EIG_OPT_OVERLAP_PUSH = 2 };
+       GK_EIG_OPT_OVERLAP_PUSH = 2,
+       /* 1 (default): with fp32 storage and fp32 factorisation the serial kernel is k_eig_seq5 (the solver warp keeps the
+        * previous node's features in registers, helper warps prepare the next conditional's base row); 0: k_eig_seq4 */
+       GK_EIG_OPT_SEQ5 = 3 };
 int gk_eig_set_option(gk_ctx *ctx, gk_eig *eig, int option, int value);
 /* upload the model attributes F (N x D), mu_0, lmbda (D)  (eigenmodel.py:41-73 state) */
 int gk_eig_set_params(gk_ctx *ctx, gk_eig *eig, const double *F, double mu0, const double *lmbda);
