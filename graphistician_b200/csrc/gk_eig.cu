@@ -468,6 +468,7 @@ static int launch_seq4_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sig
 template <int D, bool PROF>
 static int launch_seq5_p(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sigma_F) {
     const size_t smem = gk_eig_seq5_smem<D>();
+    { static int dbg_set = 0; if (!dbg_set) { dbg_set = 1; const char *ev = getenv("GK_SEQ5_DEBUG"); if (ev) { int v = atoi(ev); cudaMemcpyToSymbol(gk_seq5_debug, &v, sizeof v); } } }
     GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq5<D, PROF>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     gk_net *net = e->net;
     gk_eig_seq4_params P;

@@ -23,6 +23,7 @@
 #define GK_SEQ5_HELP 288                          // warps 1-3, 5-7, 9-11: 64 finishers + 224 summers
 #define GK_SEQ5_SRMAX 24                          // bound on the summers' row classes (192 threads / column quads)
 
+__device__ int gk_seq5_debug = 0;      // timing experiments only (env GK_SEQ5_DEBUG): 1 = summers skip their sums, 2 = finishers skip the reduction
 __device__ __forceinline__ void gk_bar_sync(int id, int n) { asm volatile("bar.sync %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 __device__ __forceinline__ void gk_bar_arrive(int id, int n) { asm volatile("bar.arrive %0, %1;" ::"r"(id), "r"(n) : "memory"); }
 // %clock64 read that cannot issue before `dep` (a value loaded after a barrier) has arrived: BAR.SYNC defers its blocking to the
@@ -33,6 +34,8 @@ __device__ __forceinline__ long long gk_clock_after(const float *smem_word) {
     asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) : "f"(dep) : "memory");
     return t;
 }
+// byte k of a packed word as a float without the (quarter-rate) I2F: 0x4B000000 | b is the float 2^23 + b
+__device__ __forceinline__ float gk_byte_to_float(unsigned w, int k) { return __uint_as_float(0x4B000000u | ((w >> (8 * k)) & 0xffu)) - 8388608.0f; }
 __device__ __forceinline__ float gk_rsq_fast(float x) { float r; asm("rsqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(x)); return r; }
 
 template <int D> struct gk_seq5_dim {
@@ -43,7 +46,7 @@ template <int D> struct gk_seq5_dim {
 template <int D>
 size_t gk_eig_seq5_smem() {
     constexpr int NB = 128, PA = gk_edim<D>::PA;
-    return (size_t)3 * NB * PA * 4 + (size_t)NB * ((PA + 3) / 4 * 4) * 4 + (size_t)NB * NB * 4 + (size_t)NB * NB + (size_t)3 * NB * D * 4 + 64;
+    return (size_t)2 * NB * PA * 4 + (size_t)NB * (gk_seq5_dim<D>::BROW > PA ? gk_seq5_dim<D>::BROW : PA) * 4 + (size_t)NB * ((PA + 3) / 4 * 4) * 4 + (size_t)NB * NB * 4 + (size_t)NB * NB + (size_t)3 * NB * D * 4 + 64;
 }
 
 // PROF = true compiles the %clock64 probes in (env GK_EIG_PROF); the production instantiation carries none of them
@@ -51,26 +54,29 @@ template <int D, bool PROF>
 __global__ void __launch_bounds__(GK_SEQ5_THREADS, 1) k_eig_seq5(gk_eig_seq4_params P) {
     constexpr int NB = 128, Q = gk_edim<D>::Q, Pn = gk_edim<D>::P, PA = gk_edim<D>::PA, BROW = gk_seq5_dim<D>::BROW;
     constexpr int PAp = (PA + 3) / 4 * 4, NQ = PAp / 4, SR = (GK_SEQ5_HELP - 64) / NQ < GK_SEQ5_SRMAX ? (GK_SEQ5_HELP - 64) / NQ : GK_SEQ5_SRMAX;   // dPhi row pitch, column quads, summer row classes
-    static_assert(PA + D <= 64, "one finisher thread per statistic column and running sum");
+    static_assert(PA + D + 2 <= 64, "one finisher thread per statistic column, per h entry, and two for x and coef");
     static_assert(SR >= 1 && SR <= GK_SEQ5_SRMAX, "summer row classes");
+    constexpr int CBP = BROW > PA ? BROW : PA;                 // pitch of the base-row constants
     constexpr bool HOMO = (Pn % 4 == 0) && (PA % 4 == 0);      // column quads never straddle the S / A boundary (D = 8)
     extern __shared__ __align__(16) unsigned char smem_raw[];
     float *Gb = (float *)smem_raw;                        // [NB][PA]  G rows at block entry (A-linear column: minus sum_m f_m + f_t)
     float *Gd = Gb + (size_t)NB * PA;                     // [NB][PA]  in-block changes sum_{s<j} X[s,j] dPhi_s
     float *dph = Gd + (size_t)NB * PA;                    // [NB][PAp] dPhi of the block's nodes (rows padded to float4)
-    float *pho = dph + (size_t)NB * PAp;                  // [NB][PA]  Phi(old f)
-    float *Sb = pho + (size_t)NB * PA;                    // [NB][NB]
+    float *Cb = dph + (size_t)NB * PAp;                   // [NB][CBP] constants of every node's base row (built at block entry)
+    float *Sb = Cb + (size_t)NB * CBP;                    // [NB][NB]
     float *zc = Sb + (size_t)NB * NB;                     // [NB][D]
     float *fnS = zc + (size_t)NB * D;                     // [NB][D]   new features
     float *foldC = fnS + (size_t)NB * D;                  // [NB][D]   features at block entry
     uint8_t *Ab = (uint8_t *)(foldC + (size_t)NB * D);    // [NB][NB]
     __shared__ __align__(16) float baseS[2][BROW];
     __shared__ __align__(16) float part[2 * GK_SEQ5_SRMAX * 64];     // [2][SR][PAp] partial sums of the summers (double-buffered by phase)
-    __shared__ float totS[72], lamS[D];
+    __shared__ float lamS[D];
     __shared__ double sF0[D];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nb = P.nb, n0 = P.n0;
     const bool probit = P.probit != 0;
     const float mu0 = (float)P.mu0, isf = (float)P.inv_sigma_F;
+    const int dbg = gk_seq5_debug;
+    const int nh1 = 64;                                       // barrier 1: the solver and the finishers only
 
     // ---- block entry (everything before gk_pdl_wait() is independent of the preceding kernels in the stream)
     for (int idx = tid; idx < nb * (NB / 4); idx += GK_SEQ5_THREADS) {
@@ -96,39 +102,31 @@ __global__ void __launch_bounds__(GK_SEQ5_THREADS, 1) k_eig_seq5(gk_eig_seq4_par
         if (p >= Pn && !probit) g -= sF0[p - Pn] - P.F[(size_t)(n0 + i) * D + (p - Pn)];
         Gb[t] = (float)g; Gd[t] = 0.f;
         if (p == 0) { for (int e = PA; e < PAp; ++e) dph[i * PAp + e] = 0.f; }
-        int a, b; gk_col_ab<D>(p, a, b);
-        pho[t] = p < Q ? foldC[i * D + a] * foldC[i * D + b] : foldC[i * D + a];
     }
     __syncthreads();
-    // operand of an in-block pair (s, j), s < j, for helper column p: S columns, A columns, running-sum columns
-    auto xcol = [&](int s, int j, int p) -> float {
-        if (p < Pn) return probit ? 2.f : Sb[s * NB + j];
-        if (p < PA) return probit ? Sb[s * NB + j] : (float)Ab[s * NB + j];
-        return 1.f;
-    };
-    // base row of node j from tot[p] = sum_{s <= j-2} X[s,j] dPhi_s[p] (and the running sums), written by 64 threads
-    auto make_base = [&](int j, int p, const float *tot) {
+    // constants of every node's base row: Cb[j] = [ k0 + k1 (Gb[j] - x_j Phi(old f_{j-1})) | lmbda (Gb_A - mu_0 Gb_S) - coef_j lmbda f_old_{j-1} | x_j | coef_j ]
+    // with x_j = X_S[j-1, j], coef_j = X_A[j-1, j] - mu_0 x_j - 1 (zero for j = 0): everything in base_j that does not depend on the draws
+    for (int t = tid; t < nb * BROW; t += GK_SEQ5_THREADS) {
+        const int j = t / BROW, p = t - j * BROW;
         const float xs = j > 0 ? (probit ? 2.f : Sb[(j - 1) * NB + j]) : 0.f;
         const float xa = j > 0 ? (probit ? Sb[(j - 1) * NB + j] : (float)Ab[(j - 1) * NB + j]) : 0.f;
         const float coef = j > 0 ? xa - mu0 * xs - (probit ? 0.f : 1.f) : 0.f;
-        float *row = baseS[j & 1];
+        float v = 0.f;
         if (p < Q) {
             int a, b; gk_col_ab<D>(p, a, b);
-            const float k1 = lamS[a] * lamS[b];
-            const float old = j > 0 ? xs * pho[(j - 1) * PA + p] : 0.f;
-            row[p] = (a == b ? isf : 0.f) + k1 * (Gb[j * PA + p] + tot[p] - old);
+            const float old = j > 0 ? xs * foldC[(j - 1) * D + a] * foldC[(j - 1) * D + b] : 0.f;
+            v = (a == b ? isf : 0.f) + lamS[a] * lamS[b] * (Gb[j * PA + p] - old);
         } else if (p < Q + D) {
             const int a = p - Q;
-            const float run = probit ? 0.f : tot[PA + a];
             const float fo = j > 0 ? foldC[(j - 1) * D + a] : 0.f;
-            row[p] = lamS[a] * (Gb[j * PA + Pn + a] + tot[Pn + a] - mu0 * (Gb[j * PA + Q + a] + tot[Q + a]) - run) - coef * lamS[a] * fo;
-        } else if (p == Q + D) row[p] = xs;
-        else if (p == Q + D + 1) row[p] = coef;
-    };
-    if (tid < 72) { totS[tid] = 0.f; }
+            v = lamS[a] * (Gb[j * PA + Pn + a] - mu0 * Gb[j * PA + Q + a]) - coef * lamS[a] * fo;
+        } else if (p == Q + D) v = xs;
+        else if (p == Q + D + 1) v = coef;
+        Cb[j * CBP + p] = v;
+    }
     for (int t = tid; t < 2 * GK_SEQ5_SRMAX * 64; t += GK_SEQ5_THREADS) part[t] = 0.f;
     __syncthreads();
-    if (tid < 64) { make_base(0, tid, totS); if (nb > 1) make_base(1, tid, totS); }
+    if (tid < BROW) { baseS[0][tid] = Cb[tid]; if (nb > 1) baseS[1][tid] = Cb[CBP + tid]; }   // base rows of nodes 0 and 1 carry no in-block sums
     __syncthreads();
 
     if (warp == 0) {
@@ -219,7 +217,7 @@ __global__ void __launch_bounds__(GK_SEQ5_THREADS, 1) k_eig_seq5(gk_eig_seq4_par
             // (bar.arrive / bar.sync order the prior shared-memory accesses of the participants: no fence needed)
             if (sprof) { c0 = gk_clock(); pf_ += c0 - ck; }
             __syncwarp();
-            gk_bar_arrive(1, 32 + GK_SEQ5_HELP);                    // f_t published
+            gk_bar_arrive(1, 32 + nh1);                    // f_t published
             if (sprof) { pr_ += gk_clock() - c0; }
         }
         if (sprof && lane == 0) { atomicAdd((unsigned long long *)P.prof + 0, (unsigned long long)(gk_clock() - l0)); atomicAdd((unsigned long long *)P.prof + 1, (unsigned long long)pcw);
@@ -229,88 +227,79 @@ __global__ void __launch_bounds__(GK_SEQ5_THREADS, 1) k_eig_seq5(gk_eig_seq4_par
         // ================= helpers =================
         const int u = (warp - 1 - (warp >> 2)) * 32 + lane;       // 0..287
         if (u < 64) {
-            // ---- finishers: one thread per statistic column (p < PA) or per running sum of feature changes (PA <= p < PA + D)
+            // ---- finishers: thread p < PA owns statistic column p (dPhi, the in-block sums; for p < Q also prec entry p of the
+            //      base row); thread PA + a owns h entry a of the base row (it needs columns Q+a and P+a and the running sum of
+            //      the block's feature changes, all of which it can form itself: no exchange between finishers); two threads
+            //      copy x and coef.  After f_s is published a finisher does: two loads of f, its partial sums, a few FMAs,
+            //      one store -- then hands barrier 2 to the solver.
             const int p = u;
-            const bool col = p < PA, runc = p >= PA && p < PA + D;
+            const bool col = p < PA, isq = p < Q, ish = p >= PA && p < PA + D, isx = p >= PA + D && p < PA + D + 2;
             int pa = 0, pb = 0;
             if (col) gk_col_ab<D>(p, pa, pb);
-            if (runc) pa = p - PA;
-            // X[s', j] of this thread's column as wS * S + wA * A + w1 (per-thread constants: no divergence)
-            const float wS = (p < Pn && !probit) || (p >= Pn && col && probit) ? 1.f : 0.f;
-            const float wA = (p >= Pn && col && !probit) ? 1.f : 0.f;
-            const float w1 = (p < Pn && probit) ? 2.f : 0.f;
-            auto xw = [&](int sp, int jj) -> float { return fmaf(wS, Sb[sp * NB + jj], fmaf(wA, (float)Ab[sp * NB + jj], w1)); };
+            if (ish) pa = pb = p - PA;
+            const int c1 = ish ? Q + pa : (col ? p : 0), c2 = Pn + pa;        // columns of the partial sums this thread reduces
+            const int brow = ish ? Q + pa : (isx ? Q + D + (p - PA - D) : p); // entry of the base row it writes
+            // X[s', j] of column c1 (and of c2 for the h threads) as wS * S + wA * A + w1: per-thread constants, no divergence
+            const bool c1S = c1 < Pn;
+            const float wS = (c1S && !probit) || (!c1S && probit) ? 1.f : 0.f, wA = (!c1S && !probit) ? 1.f : 0.f, w1 = (c1S && probit) ? 2.f : 0.f;
+            const float vS = probit ? 1.f : 0.f, vA = probit ? 0.f : 1.f;    // column c2 is an A column
+            float k1 = 0.f, lamh = 0.f;
+            if (isq) { k1 = lamS[pa] * lamS[pb]; }
+            if (ish) lamh = lamS[pa];
             float run = 0.f;
-            long long pc0 = 0, pc1 = 0, ck = 0, pcA = 0, pcB = 0, pcC = 0, c1 = 0;
+            long long pc0 = 0, pc1 = 0, ck = 0, pcA = 0, pcB = 0, pcC = 0, c1k = 0;
             const bool prof = PROF && P.prof != nullptr && u == 0;
-            // role in the base row: Q prec entries (own column only), D h entries (three columns of tot), x and coef
-            const bool isq = p < Q, ish = p >= Q && p < Q + D;
-            const int ha = ish ? p - Q : 0;
-            int qa = 0, qb = 0;
-            if (isq) gk_col_ab<D>(p, qa, qb);
-            const float k0 = (isq && qa == qb) ? isf : 0.f, k1 = isq ? lamS[qa] * lamS[qb] : 0.f, lamh = lamS[ha];
             for (int s = 0; s < nb; ++s) {
                 const int j = s + 2;
-                // ---- everything that does not depend on f_s is fetched / computed before the wait
-                const float xj = (col && j < nb) ? xw(s, j) : 0.f, x1 = (col && s + 1 < nb) ? xw(s, s + 1) : 0.f;
-                const float phs = col ? (p < Q ? pho[s * PA + p] : foldC[s * D + pa]) : (runc ? foldC[s * D + pa] : 0.f);
-                float pre = 0.f;
-                if (j < nb) {
-                    const float xs = probit ? 2.f : Sb[(j - 1) * NB + j];
-                    const float xa = probit ? Sb[(j - 1) * NB + j] : (float)Ab[(j - 1) * NB + j];
-                    const float coef = xa - mu0 * xs - (probit ? 0.f : 1.f);
-                    float *row = baseS[j & 1];
-                    if (isq) pre = k0 + k1 * (Gb[j * PA + p] - xs * pho[(j - 1) * PA + p]);
-                    else if (ish) pre = lamh * (Gb[j * PA + Pn + ha] - mu0 * Gb[j * PA + Q + ha]) - coef * lamh * foldC[(j - 1) * D + ha];
-                    else if (p == Q + D) row[p] = xs;            // (the solver finished with this buffer two phases ago)
-                    else if (p == Q + D + 1) row[p] = coef;
-                }
+                const bool haveJ = j < nb;
+                // ---- everything that does not depend on f_s is fetched before the wait
+                const int jj = haveJ ? j : s;                       // (a valid address when there is no node s + 2)
+                const float sx = Sb[s * NB + jj], ax = (float)Ab[s * NB + jj];
+                const float xj1 = fmaf(wS, sx, fmaf(wA, ax, w1)), xj2 = fmaf(vS, sx, vA * ax);
+                const int s1 = s + 1 < nb ? s + 1 : s;
+                const float x1 = fmaf(wS, Sb[s * NB + s1], fmaf(wA, (float)Ab[s * NB + s1], w1));
+                const float foa = foldC[s * D + pa], fob = foldC[s * D + pb];
+                const float phs = isq ? foa * fob : foa;
+                const float cpre = Cb[jj * CBP + brow];
+                if (isx && haveJ) baseS[j & 1][brow] = cpre;       // (the solver finished with this buffer two phases ago)
                 if (prof) ck = gk_clock();
                 __syncwarp();
-                gk_bar_sync(1, 32 + GK_SEQ5_HELP);                // f_s published
-                if (prof) { const long long c2 = gk_clock_after(fnS); pc0 += c2 - ck; ck = c2; }
+                gk_bar_sync(1, 32 + nh1);                // f_s published
+                if (prof) { const long long c2k = gk_clock_after(fnS); pc0 += c2k - ck; ck = c2k; }
                 const float fa = fnS[s * D + pa], fb = fnS[s * D + pb];
-                float ps[SR];
-                if (j < nb && col) {
-                    const float *pp = part + (size_t)(s & 1) * SR * PAp + p;
+                float t1 = 0.f, t2 = 0.f;
+                if (s >= 1 && !(dbg & 4)) gk_bar_sync(4, GK_SEQ5_HELP);      // the summers' sums of phase s - 1 are in shared memory
+                if (haveJ && !(dbg & 2)) {
+                    const float *pp = part + (size_t)(s & 1) * SR * PAp;
+                    float u0 = 0.f, u1 = 0.f, w0 = 0.f, w1s = 0.f;
 #pragma unroll
-                    for (int q = 0; q < SR; ++q) ps[q] = pp[q * PAp];
+                    for (int q = 0; q + 1 < SR; q += 2) { u0 += pp[q * PAp + c1]; u1 += pp[(q + 1) * PAp + c1]; }
+                    if (SR & 1) u0 += pp[(SR - 1) * PAp + c1];
+                    if (ish) {
+#pragma unroll
+                        for (int q = 0; q + 1 < SR; q += 2) { w0 += pp[q * PAp + c2]; w1s += pp[(q + 1) * PAp + c2]; }
+                        if (SR & 1) w0 += pp[(SR - 1) * PAp + c2];
+                    }
+                    t1 = u0 + u1; t2 = w0 + w1s;
                 }
-                const float d = p < Q ? fa * fb - phs : fa - phs;
+                const float d = isq ? fa * fb - phs : fa - phs;
                 if (col) dph[s * PAp + p] = d;
-                if (runc) run += d;
+                if (ish) run += d;
+                t1 = fmaf(xj1, d, t1); t2 = fmaf(xj2, d, t2);
+                if (haveJ) {
+                    if (isq) baseS[j & 1][brow] = fmaf(k1, t1, cpre);
+                    if (ish) baseS[j & 1][brow] = fmaf(lamh, t2 - mu0 * t1 - (probit ? 0.f : run), cpre);
+                }
                 // (bar.arrive / bar.sync order the prior shared-memory accesses of the participants: no fence needed)
                 __syncwarp();
-                gk_bar_arrive(3, GK_SEQ5_HELP);                   // dPhi_s is in shared memory: the summers may start
-                if (prof) { c1 = gk_clock(); pcA += c1 - ck; }
-                if (j < nb) {
-                    float tot = 0.f;
-                    if (col) {
-                        float t0 = 0.f, t1 = 0.f;
-#pragma unroll
-                        for (int q = 0; q + 1 < SR; q += 2) { t0 += ps[q]; t1 += ps[q + 1]; }
-                        if (SR & 1) t0 += ps[SR - 1];
-                        tot = fmaf(xj, d, t0 + t1);
-                        if (isq) baseS[j & 1][p] = fmaf(k1, tot, pre);      // prec entries need their own column only
-                        else totS[p] = tot;
-                    }
-                    if (runc) totS[PA + pa] = run;
-                    __syncwarp();
-                    if (prof) { const long long c2 = gk_clock(); pcB += c2 - c1; c1 = c2; }
-                    gk_bar_sync(4, 64);
-                    if (prof) { const long long c2 = gk_clock_after(totS); pcC += c2 - c1; c1 = c2; }
-                    if (ish) {
-                        const float run_a = probit ? 0.f : totS[PA + ha];
-                        baseS[j & 1][p] = fmaf(lamh, totS[Pn + ha] - mu0 * totS[Q + ha] - run_a, pre);
-                    }
-                    if (col) Gd[j * PA + p] = tot;
-                }
-                // Every phase but the last hands barrier 2 to the solver, base row or not: the solver may not publish f_{s+1}
-                // (a second arrival on barrier 1) before every helper has consumed the publication of f_s.
-                __syncwarp();
-                if (s + 1 < nb) gk_bar_arrive(2, 96);
+                if (s + 1 < nb) gk_bar_arrive(2, 96);             // base row of node s + 2 ready (and: f_s consumed, see the solver)
+                if (!(dbg & 4)) gk_bar_arrive(3, GK_SEQ5_HELP);                   // dPhi_s is in shared memory: the summers may start
+                if (prof) { c1k = gk_clock(); pcA += c1k - ck; }
+                if (!(dbg & 8)) {
+                if (col && haveJ) Gd[j * PA + p] = t1;
                 if (col && s + 1 < nb) Gd[(s + 1) * PA + p] += x1 * d;
-                if (prof) { const long long c2 = gk_clock(); pc1 += c2 - ck; ck = c2; }
+                }
+                if (prof) { const long long c2k = gk_clock(); pc1 += c2k - ck; ck = c2k; }
             }
             if (prof) { atomicAdd((unsigned long long *)P.prof + 8, (unsigned long long)pc0); atomicAdd((unsigned long long *)P.prof + 9, (unsigned long long)pc1);
                 atomicAdd((unsigned long long *)P.prof + 11, (unsigned long long)pcA); atomicAdd((unsigned long long *)P.prof + 12, (unsigned long long)pcB); atomicAdd((unsigned long long *)P.prof + 13, (unsigned long long)pcC); }
@@ -339,9 +328,8 @@ __global__ void __launch_bounds__(GK_SEQ5_THREADS, 1) k_eig_seq5(gk_eig_seq4_par
             for (int k = 0; k < NG; ++k)
 #pragma unroll
                 for (int e = 0; e < 4; ++e) dc[k][e] = make_float4(0.f, 0.f, 0.f, 0.f);
-            for (int s = 0; s < nb; ++s) {
+            for (int s = 0; s < ((dbg & 4) ? 0 : nb); ++s) {
                 __syncwarp();
-                gk_bar_sync(1, 32 + GK_SEQ5_HELP);                // f_s published
                 gk_bar_sync(3, GK_SEQ5_HELP);                     // dPhi_s stored by the finishers
                 if (prof) ck = gk_clock_after(dph);
                 if (active) {
@@ -356,7 +344,7 @@ __global__ void __launch_bounds__(GK_SEQ5_THREADS, 1) k_eig_seq5(gk_eig_seq4_par
                                 if (k == kg && ee == e) dc[k][ee] = dn;
                     }
                     const int jt = s + 3;                         // target of the NEXT phase; its terms s' <= s are all known now
-                    if (jt < nb) {
+                    if (jt < nb && !(dbg & 1)) {
                         float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
                         const float *srow = Sb + (size_t)jt * NB;     // symmetric in-block tiles: X[s', jt] = X[jt, s'] (contiguous in s')
                         const uint8_t *arow = Ab + (size_t)jt * NB;
@@ -386,7 +374,8 @@ __global__ void __launch_bounds__(GK_SEQ5_THREADS, 1) k_eig_seq5(gk_eig_seq4_par
                         *(float4 *)(part + ((size_t)((s + 1) & 1) * SR + r) * PAp + 4 * q) = make_float4(a0, a1, a2, a3);
                     }
                 }
-                // (bar.arrive / bar.sync order the prior shared-memory accesses of the participants: no fence needed)
+                __syncwarp();
+                if (s + 1 < nb) gk_bar_arrive(4, GK_SEQ5_HELP);    // sums for the next phase stored (bar.arrive orders the prior stores)
                 if (prof) { pc2 += gk_clock() - ck; }
             }
             if (prof) atomicAdd((unsigned long long *)P.prof + 10, (unsigned long long)pc2);
