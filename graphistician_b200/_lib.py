@@ -33,6 +33,7 @@ SIGNATURES = {
     "gk_block_stats": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
     "gk_sbm_sweep": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_dbl, c_vp, c_int,
                              c_vp, PI64]),
+    "gk_sbm_sweep_stats": (c_int, [c_vp, c_vp, c_int, c_vp, c_vp, c_vp, ctypes.POINTER(c_int)]),
     "gk_sbm_sweep_begin": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_int, c_int, c_dbl, c_vp]),
     "gk_sbm_partial_len": (c_sz, [c_vp, c_int]),
     "gk_sbm_block_partials": (c_int, [c_vp, c_vp, c_int, c_int, c_vp]),

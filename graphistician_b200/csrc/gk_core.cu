@@ -1,4 +1,5 @@
 // gk_core.cu -- context, error handling, timing, network upload and device-side transposes.
+#include <stdlib.h>
 #include <stdarg.h>
 #include <string.h>
 #include "gk_internal.cuh"
@@ -48,6 +49,7 @@ extern "C" int gk_ctx_create(int device, gk_ctx **out) {
     if (cudaGetDeviceProperties(&prop, device) == cudaSuccess) ctx->num_sms = prop.multiProcessorCount;
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return GK_ECUDA; }
     ctx->own_stream = true;
+    ctx->sbm_prof = getenv("GK_SBM_PROF") != nullptr;
     *out = ctx;
     return GK_OK;
 }
@@ -56,7 +58,7 @@ extern "C" void gk_ctx_destroy(gk_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
-    for (int i = 0; i < 8; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
+    for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (auto &f : ctx->fam) for (auto &p : f.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
@@ -165,6 +167,7 @@ extern "C" int gk_network_create(gk_ctx *ctx, int N, int B, int dev_dtype, int r
 }
 
 extern "C" int gk_network_destroy(gk_ctx *ctx, gk_net *net) {
+    if (ctx && ctx->last_cells.net == net) { ctx->last_cells.valid = false; ctx->last_cells.net = nullptr; }
     if (!net) return GK_OK;
     if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
     cudaFree(net->A); cudaFree(net->At); cudaFree(net->W); cudaFree(net->Wt);
@@ -197,6 +200,7 @@ static int upload_w(gk_ctx *ctx, gk_net *net, void *dst, const void *src, int w_
 
 extern "C" int gk_network_upload(gk_ctx *ctx, gk_net *net, const uint8_t *A_rows, const void *W_rows, int w_dtype,
                                  const uint8_t *At_rows, const void *Wt_rows) {
+    if (ctx && ctx->last_cells.net == net) ctx->last_cells.valid = false;      // statistics of the previous data
     if (!ctx || !net || !A_rows) return GK_EINVAL;
     if (net->B && !W_rows) return gk_fail(ctx, GK_EINVAL, "W required when B > 0");
     bool whole = net->row0 == 0 && net->nrows == net->N;

@@ -374,11 +374,9 @@ static int launch_slab(gk_ctx *ctx, gk_eig *e, int n0, int nb, double *acc) {
 template <typename T, typename CH, int D>
 static int launch_seq_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, const void *Sblk, int ldS, const uint8_t *Ablk, int ldA,
                          double inv_sigma_F, double *acc) {
-    static bool attr_set = false;
     const size_t smem = gk_eig_seq_smem<T, D>();
-    if (!attr_set) {
+    if (gk_attr_needed(ctx, (const void *)k_eig_seq<T, CH, D>)) {
         GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq<T, CH, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
     }
     gk_eig_seq_params P;
     P.n0 = n0; P.nb = nb; P.N = e->N; P.Sblk = Sblk; P.ldS = ldS; P.Ablk = Ablk; P.ldA = ldA;
@@ -431,11 +429,9 @@ static int sweep_F(gk_ctx *ctx, gk_eig *e, double inv_sigma_F) {
 // running-G form of the sweep (gk_eig_fast.cuh): one full contraction, then per node block { serial draws ; push }
 template <typename T, typename CH, int D>
 static int launch_seq4_ch(gk_ctx *ctx, gk_eig *e, int n0, int nb, double inv_sigma_F) {
-    static bool attr_set = false;
     const size_t smem = gk_eig_seq4_smem<T, CH, D>();
-    if (!attr_set) {
+    if (gk_attr_needed(ctx, (const void *)k_eig_seq4<T, CH, D>)) {
         GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_seq4<T, CH, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
     }
     gk_net *net = e->net;
     gk_eig_seq4_params P;
@@ -529,11 +525,9 @@ static int launch_gfull(gk_ctx *ctx, gk_eig *e, const double *phi_given, size_t 
     const size_t fold_elems = (size_t)128 * (2 * PH + 1);
     const size_t smem_full = std::max((size_t)2 * PR * GK_EF_COLS * (sizeof(T) + 1) + (size_t)2 * PR * PA * sizeof(ACC), fold_elems * sizeof(ACC));
     const size_t smem_push = std::max((size_t)NB * GK_EF_COLS * (sizeof(T) + 1) + (size_t)NB * PA * sizeof(ACC), fold_elems * sizeof(ACC));
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (gk_attr_needed(ctx, (const void *)k_eig_gfull<T, D>)) {
         GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_gfull<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full));
         GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_push<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_push));
-        attr_set = true;
     }
     gk_time_begin(ctx, 3, (double)N * N * (sizeof(T) + 1.0));
     k_eig_gfull<T, D><<<dim3(strips, nchunks), GK_EF_THREADS, smem_full, ctx->stream>>>(
@@ -890,10 +884,8 @@ static int mf_update_F_T(gk_ctx *ctx, gk_eig *e, double *mu, double *Sig, const 
     size_t smem_push = 0;
     if ((rc = launch_gfull<T, D>(ctx, e, e->mfPhi, &smem_push))) return rc;
     const size_t smem = gk_eig_mfseq_smem<T, D>();
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (gk_attr_needed(ctx, (const void *)k_eig_mf_seq<T, D>)) {
         GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_mf_seq<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        attr_set = true;
     }
     for (int n0 = 0; n0 < e->N; n0 += NB) {
         const int nb = std::min(NB, e->N - n0);

@@ -9,6 +9,7 @@
 
 #define GK_PAD 128            // columns of every N x N device array are padded to a multiple of this
 #define GK_NFAMILY 8
+#define GK_ATTR_STRIP 0                 // attr_done slots: 0..5 k_strip_stats<T,B>, 8.. eigen kernels, 32.. mean field
 
 struct gk_timing {
     double ms = 0.0; int64_t launches = 0; double bytes = 0.0;
@@ -25,9 +26,15 @@ struct gk_ctx {
     gk_timing fam[GK_NFAMILY];
     std::string err;
     // scratch (grown on demand, freed with the ctx)
-    void *scratch[8] = {nullptr}; size_t scratch_bytes[8] = {0};
+    void *scratch[12] = {nullptr}; size_t scratch_bytes[12] = {0};
+    // K1 statistics of the labels the last unsharded gk_sbm_sweep ended on (gk_sbm_sweep_stats)
+    struct { const void *net = nullptr; int K = 0, S = 0; bool valid = false; std::vector<double> cell; } last_cells;
     // state of an open sharded sweep
     struct gk_sweep *sweep = nullptr;
+    // cudaFuncSetAttribute is per device: remembered per context, never in function-local statics
+    bool attr_done[64] = {false};
+    std::vector<const void *> attr_funcs;     // kernels whose attributes this context has set
+    bool sbm_prof = false;                    // env GK_SBM_PROF, read once at context creation
 };
 
 struct gk_net {
@@ -44,6 +51,12 @@ struct gk_net {
 };
 
 int gk_fail(gk_ctx *ctx, int code, const char *fmt, ...);
+// true the first time this context sees kernel `f` (cudaFuncSetAttribute is per device, so the memo is per context)
+static inline bool gk_attr_needed(gk_ctx *ctx, const void *f) {
+    for (const void *g : ctx->attr_funcs) if (g == f) return false;
+    ctx->attr_funcs.push_back(f);
+    return true;
+}
 int gk_net_refresh_asym(gk_ctx *ctx, gk_net *net);  // recomputes an existing net->Asym after a re-upload; gk_eig.cu
 int gk_net_ensure_asym(gk_ctx *ctx, gk_net *net);   // builds net->Asym = A + A^T (zero diagonal) once; gk_eig.cu
 void *gk_scratch(gk_ctx *ctx, int slot, size_t bytes);   // returns nullptr (and sets err) on failure

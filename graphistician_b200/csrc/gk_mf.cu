@@ -64,10 +64,8 @@ static int soft_strip_to_stats(gk_ctx *ctx, gk_net *net, gk_mf_state *st, int n0
     P.ld = net->ld; P.row0 = net->row0; P.nrows = net->nrows; P.n0 = n0; P.nb_pad = nb_pad; P.dir_first = dir_first;
     P.mT = st->mT; P.K = K; P.Kp = st->Kp; P.KGp = st->KGp; P.chunk_rows = chunk_rows; P.nchunks = nchunks; P.partial = partial;
     size_t smem = (size_t)st->Kp * S * GK_SLOT_PITCH * sizeof(ACC);
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (gk_attr_needed(ctx, (const void *)k_strip_soft<T, B>)) {
         GK_CUDA(ctx, cudaFuncSetAttribute(k_strip_soft<T, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
-        attr_set = true;
     }
     double bytes = (double)net->nrows * (double)std::min(nb_pad, net->N - n0) * (1.0 + B * sizeof(T)) * ndirs;
     gk_time_begin(ctx, 6, bytes);
@@ -154,10 +152,8 @@ static int launch_mf_seq(gk_ctx *ctx, gk_net *net, gk_mf_state *st, const double
     P.stepsize = stepsize; P.out_lp = out_lp_dev;
     size_t smem = ((size_t)GK_MF_MAX_NB * (K + 4) + 2 * (size_t)KS * K + 2 * (size_t)K * K + 2 * K + 2 * (size_t)S * K) * 8;
     if (smem > 220 * 1024) return gk_fail(ctx, GK_EUNSUPPORTED, "K=%d, B=%d needs %zu bytes of shared memory", K, B, smem);
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (gk_attr_needed(ctx, (const void *)k_mf_seq<T, B>)) {
         GK_CUDA(ctx, cudaFuncSetAttribute(k_mf_seq<T, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 220 * 1024));
-        attr_set = true;
     }
     gk_time_begin(ctx, 7, 0.0);
     k_mf_seq<T, B><<<1, GK_MFSEQ_THREADS, smem, ctx->stream>>>(P);

@@ -13,6 +13,8 @@ struct gk_sweep {
     bool want_lp = false;
 };
 
+#define GK_LOG_ZERO (-1e10)
+#define GK_CELL_MOVER_CAP 1024            // sweeps that moved more nodes than this leave no K1 table behind (a full pass is cheaper)
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
 // sum_edges log N(w; mu, Sigma) = n*c0 + c1.sum_w + sum_{b<=b'} C2s[b,b'] sum_ww[b,b']   (B <= 2, closed form)
@@ -49,8 +51,10 @@ static int build_tables(gk_ctx *ctx, int K, int B, const double *log_m, const do
             if (p) {
                 double pv = p[k * K + k2];
                 if (!(pv >= 0.0 && pv <= 1.0)) return gk_fail(ctx, GK_EINVAL, "p[%d,%d]=%g outside [0,1]", k, k2, pv);
-                pv = std::min(std::max(pv, 1e-300), 1.0 - 1e-16);
-                double lg = log(pv), l1 = log1p(-pv);
+                // p == 0 / p == 1 are legal (stochastic_block_model.py:60): the reference's Bernoulli.log_probability nan_to_num's
+                // x log 0 to -1.8e308 (a hard exclusion) and 0 log 0 to 0 (internals/distributions.py:59-67).  A finite -1e10 does
+                // both here -- exp(-1e10) == 0 in fp64 and 0 * (-1e10) == 0 -- while the rank-one pushes of a move stay exact to 1e-6.
+                double lg = pv > 0.0 ? log(pv) : GK_LOG_ZERO, l1 = pv < 1.0 ? log1p(-pv) : GK_LOG_ZERO;
                 cs[0] += beta * (lg - l1);
                 l1m[(size_t)k * K + k2] = beta * l1;
             }
@@ -78,8 +82,8 @@ static int build_tables(gk_ctx *ctx, int K, int B, const double *log_m, const do
         selfc[k] = mult * l1m[(size_t)k * K + k];
         for (int s = 0; s < S; ++s) selfa[(size_t)s * K + k] = cell[((size_t)k * K + k) * S + s];
         if (p) {   // the adjacency part of s=0 is doubled in TWICE mode; the Gaussian part is not
-            double pv = std::min(std::max(p[k * K + k], 1e-300), 1.0 - 1e-16);
-            selfa[k] += (mult - 1.0) * beta * (log(pv) - log1p(-pv));
+            const double pv = p[k * K + k];
+            selfa[k] += (mult - 1.0) * beta * ((pv > 0.0 ? log(pv) : GK_LOG_ZERO) - (pv < 1.0 ? log1p(-pv) : GK_LOG_ZERO));
         }
     }
     return GK_OK;
@@ -114,11 +118,8 @@ static int launch_strip(gk_ctx *ctx, gk_net *net, const uint8_t *c8, int K, int 
     P.c8 = c8; P.K = K; P.chunk_rows = chunk_rows; P.nchunks = nchunks; P.partial = partial;
     int U = std::max(K, GK_STRIP_WARPS);
     size_t smem = (size_t)U * S * GK_SLOT_PITCH * sizeof(ACC) + (size_t)chunk_rows * 3 + 16;
-    static bool attr_set = false;
-    if (!attr_set) {
+    if (gk_attr_needed(ctx, (const void *)k_strip_stats<T, B>))     // per context (= per device), not per process
         GK_CUDA(ctx, cudaFuncSetAttribute(k_strip_stats<T, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
-        attr_set = true;
-    }
     double bytes = (double)net->nrows * (double)std::min(nb_pad, net->N - n0) * (1.0 + B * sizeof(T)) * ndirs;
     gk_time_begin(ctx, 0, bytes);
     k_strip_stats<T, B><<<dim3(strips, nchunks, ndirs), GK_STRIP_THREADS, smem, ctx->stream>>>(P);
@@ -285,7 +286,7 @@ static int launch_sample(gk_ctx *ctx, gk_net *net, gk_sweep *sw, int n0, int nb,
     P.c = sw->c; P.c8 = sw->c8; P.sizes = sw->sizes; P.lp = sw->lp; P.u = sw->u; P.T = sw->T;
     P.A = net->A; P.At = net->At; P.W = net->W; P.Wt = net->Wt;
     P.out_lp = sw->want_lp ? sw->out_lp : nullptr; P.nchanged = sw->nchanged;
-    P.prof = getenv("GK_SBM_PROF") != nullptr;
+    P.prof = ctx->sbm_prof;
     gk_time_begin(ctx, 1, 0.0);
     const size_t dyn = ((size_t)sw->K * (nb | 1) + nb) * 8 + (size_t)(nb + 15) / 16 * 16;
     if (nb <= GK_SEQ_THREADS && dyn <= 208 * 1024) {          // conditionals of the block fit in shared memory
@@ -333,7 +334,7 @@ extern "C" int gk_sbm_sweep_end(gk_ctx *ctx, gk_net *net, int32_t *c_out, double
     if (!ctx || !ctx->sweep) return GK_EINVAL;
     gk_sweep *sw = ctx->sweep;
     unsigned long long nch = 0;
-    if (getenv("GK_SBM_PROF")) {                               // phase clocks of k_sbm_seq2 (shares)
+    if (ctx->sbm_prof) {                               // phase clocks of k_sbm_seq2 (shares)
         unsigned long long pc[7];
         GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
         GK_CUDA(ctx, cudaMemcpy(pc, sw->nchanged, sizeof pc, cudaMemcpyDeviceToHost));
@@ -366,13 +367,81 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
     }
     int bn = block_nodes > 0 ? block_nodes : 1024;
     bn = std::max(GK_STRIP_COLS, bn / GK_STRIP_COLS * GK_STRIP_COLS);
+    // per-node statistics of the whole sweep stay resident ([N_pad][2][K*S] doubles): their in-edge half, folded with the labels
+    // the sweep ends on, IS the K1 table of the next resample() -- no third pass over A / W (gk_sbm_sweep_stats)
+    const int KS = K * sw->S;
+    const size_t n_pad = (size_t)(N + bn - 1) / bn * bn;
+    double *stats_all = (double *)gk_scratch(ctx, 3, n_pad * 2 * KS * 8);
+    if (!stats_all) return GK_ENOMEM;
+    const int CAP = GK_CELL_MOVER_CAP, nparts = 128;
+    size_t o_cell = 0, o_part = align_up((size_t)K * KS * 8, 256), o_cnt = o_part + align_up((size_t)nparts * K * KS * 8, 256),
+           o_list = o_cnt + 256, o_cold = o_list + align_up((size_t)CAP * 12, 256), tot = o_cold + align_up((size_t)N, 256);
+    char *cb = (char *)gk_scratch(ctx, 8, tot);
+    if (!cb) return GK_ENOMEM;
+    double *cell = (double *)(cb + o_cell), *cellpart = (double *)(cb + o_part);
+    int *mcnt = (int *)(cb + o_cnt), *mlist = (int *)(cb + o_list);
+    uint8_t *c_old8 = (uint8_t *)(cb + o_cold);
+    GK_CUDA(ctx, cudaMemcpyAsync(c_old8, sw->c8, (size_t)N, cudaMemcpyDeviceToDevice, ctx->stream));
+    ctx->last_cells.valid = false;
     for (int n0 = 0; n0 < N; n0 += bn) {
         int nb = std::min(bn, N - n0);
-        size_t len = gk_sbm_partial_len(ctx, nb);
-        double *stats = (double *)gk_scratch(ctx, 3, len * 8);
-        if (!stats) return GK_ENOMEM;
+        double *stats = stats_all + (size_t)n0 * 2 * KS;
         if ((rc = gk_sbm_block_partials(ctx, net, n0, nb, stats))) return rc;
         if ((rc = gk_sbm_block_sample(ctx, net, n0, nb, stats))) return rc;
     }
-    return gk_sbm_sweep_end(ctx, net, c_inout, out_lp, out_nchanged);
+    // K1 of the final labels: fold, then move the movers' out-edges from their old source class to the new one
+    GK_CUDA(ctx, cudaMemsetAsync(cell, 0, (size_t)K * KS * 8, ctx->stream));
+    GK_CUDA(ctx, cudaMemsetAsync(mcnt, 0, 4, ctx->stream));
+    k_cell_partial2<<<nparts, 128, (size_t)K * KS * 8, ctx->stream>>>(stats_all, sw->c8, N, K, KS, cellpart);
+    GK_CHECK_LAUNCH(ctx);
+    k_cell_final<<<(K * KS + 127) / 128, 128, 0, ctx->stream>>>(cellpart, nparts, K, sw->S, cell);
+    GK_CHECK_LAUNCH(ctx);
+    k_find_movers<<<std::min((N + 255) / 256, ctx->num_sms * 4), 256, 0, ctx->stream>>>(c_old8, sw->c8, N, CAP, mcnt, mlist);
+    GK_CHECK_LAUNCH(ctx);
+#define CALL_MOV(T, BB) (k_cell_movers<T, BB><<<std::min(CAP, ctx->num_sms * 4), 64, (size_t)KS * 64 * 8, ctx->stream>>>(net->A, net->W, net->ld, sw->c8, mcnt, mlist, CAP, bn, N, K, cell), GK_OK)
+    if ((size_t)KS * 64 * 8 > 48 * 1024) {
+        if (net->dtype == GK_F32) { if (net->B == 2) cudaFuncSetAttribute(k_cell_movers<float, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); else if (net->B == 1) cudaFuncSetAttribute(k_cell_movers<float, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); else cudaFuncSetAttribute(k_cell_movers<float, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); }
+        else { if (net->B == 2) cudaFuncSetAttribute(k_cell_movers<double, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); else if (net->B == 1) cudaFuncSetAttribute(k_cell_movers<double, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); else cudaFuncSetAttribute(k_cell_movers<double, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); }
+    }
+    rc = GK_DISPATCH_TB(net, CALL_MOV);
+    GK_CHECK_LAUNCH(ctx);
+    {
+        std::vector<double> &hc = ctx->last_cells.cell;
+        hc.resize((size_t)K * KS);
+        int nmov = 0;
+        GK_CUDA(ctx, cudaMemcpyAsync(hc.data(), cell, (size_t)K * KS * 8, cudaMemcpyDeviceToHost, ctx->stream));
+        GK_CUDA(ctx, cudaMemcpyAsync(&nmov, mcnt, 4, cudaMemcpyDeviceToHost, ctx->stream));
+        const int S_ = sw->S;
+        rc = gk_sbm_sweep_end(ctx, net, c_inout, out_lp, out_nchanged);      // synchronises the stream
+        if (rc) return rc;
+        ctx->last_cells.net = net; ctx->last_cells.K = K; ctx->last_cells.S = S_;
+        ctx->last_cells.valid = nmov <= CAP;
+        return GK_OK;
+    }
+}
+
+// K1 statistics (off-diagonal pairs, as gk_block_stats returns them) of the labels the last unsharded gk_sbm_sweep on `net`
+// ended on -- folded from the sweep's own per-node statistics, so resample() needs no separate pass over A / W.
+// *valid = 0 when there is nothing to return (no sweep yet, another network or K, or the sweep moved too many nodes).
+extern "C" int gk_sbm_sweep_stats(gk_ctx *ctx, gk_net *net, int K, int64_t *n_edge, double *sum_w, double *sum_ww, int *valid) {
+    if (!ctx || !net || !n_edge || !valid) return GK_EINVAL;
+    *valid = 0;
+    if (!ctx->last_cells.valid || ctx->last_cells.net != net || ctx->last_cells.K != K) return GK_OK;
+    const int B = net->B, S = ctx->last_cells.S;
+    const std::vector<double> &h = ctx->last_cells.cell;
+    for (int a = 0; a < K; ++a)
+        for (int b = 0; b < K; ++b) {
+            const double *cs = &h[((size_t)a * K + b) * S];
+            n_edge[a * K + b] = (int64_t)llround(cs[0]);
+            for (int i = 0; i < B; ++i) {
+                if (sum_w) sum_w[((size_t)a * K + b) * B + i] = cs[1 + i];
+                if (sum_ww)
+                    for (int j = 0; j < B; ++j) {
+                        int lo = std::min(i, j), hi = std::max(i, j);
+                        sum_ww[(((size_t)a * K + b) * B + i) * B + j] = cs[gk_sym_idx(B, lo, hi)];
+                    }
+            }
+        }
+    *valid = 1;
+    return GK_OK;
 }

@@ -353,6 +353,79 @@ __global__ void k_cell_final(const double *__restrict__ cellpart, int nparts, in
     }
 }
 
+// The same fold over the statistics a whole SWEEP left behind (one row per node: [N_pad][2][K*S], in-edge half used), with the
+// labels the sweep ended on: cell[(k_src, k_dst)] += sum_{n : c'[n] = k_dst} in_stats[n][k_src].  Exact for every pair whose source
+// kept its label after the target's block was entered; k_cell_movers corrects the others.
+__global__ void k_cell_partial2(const double *__restrict__ stats, const uint8_t *__restrict__ c8, int N, int K, int KS,
+                                double *__restrict__ cellpart) {
+    extern __shared__ double tbl[];                  // [K][KS]
+    for (int t = threadIdx.x; t < K * KS; t += blockDim.x) tbl[t] = 0.0;
+    __syncthreads();
+    const int per = (N + gridDim.x - 1) / gridDim.x;
+    const int lo = blockIdx.x * per, hi = min(N, lo + per);
+    for (int j = threadIdx.x; j < KS; j += blockDim.x)
+        for (int n = lo; n < hi; ++n) tbl[c8[n] * KS + j] += stats[((size_t)n * 2 + 1) * KS + j];
+    __syncthreads();
+    for (int t = threadIdx.x; t < K * KS; t += blockDim.x) cellpart[(size_t)blockIdx.x * K * KS + t] = tbl[t];
+}
+
+// nodes whose label changed during the sweep, in index order is not needed: (node, old, new) triples, count in cnt[0]
+__global__ void k_find_movers(const uint8_t *__restrict__ c_old, const uint8_t *__restrict__ c_new, int N, int cap,
+                              int *__restrict__ cnt, int *__restrict__ list) {
+    for (int n = blockIdx.x * blockDim.x + threadIdx.x; n < N; n += gridDim.x * blockDim.x)
+        if (c_old[n] != c_new[n]) {
+            const int i = atomicAdd(cnt, 1);
+            if (i < cap) { list[3 * i] = n; list[3 * i + 1] = c_old[n]; list[3 * i + 2] = c_new[n]; }
+        }
+}
+
+// Correction of the folded cell table for the sweep's movers.  Node m moved a -> b while its block [b0, b1) was drawn; every node
+// n < b1 (n != m) had its in-statistics taken when m still carried a, so x(m -> n) sits in cell (a, c'[n]) and belongs in (b, c'[n]).
+// One CTA per mover, 64 threads, each with a private [K][S] table in shared memory (no atomics, layout [entry][thread]); the
+// tables are summed in a fixed order and applied to the global cell table with atomics (the table is tiny and movers are few:
+// the host falls back to a full K1 pass when a sweep moved more than `cap` nodes).
+template <typename T, int B>
+__global__ void __launch_bounds__(64) k_cell_movers(const uint8_t *__restrict__ A, const void *__restrict__ Wv, int ld, const uint8_t *__restrict__ c8,
+                                                    const int *__restrict__ cnt, const int *__restrict__ list, int cap, int block_nodes,
+                                                    int N, int K, double *__restrict__ cell) {
+    constexpr int S = gk_sdim<B>::S;
+    extern __shared__ double priv[];                 // [K*S][64]
+    const int nm = min(cnt[0], cap), tid = threadIdx.x, KS = K * S;
+    const T *W = (const T *)Wv;
+    for (int i = blockIdx.x; i < nm; i += gridDim.x) {
+        const int m = list[3 * i], a = list[3 * i + 1], b = list[3 * i + 2];
+        const int b1 = min(N, (m / block_nodes + 1) * block_nodes);
+        for (int t = 0; t < KS; ++t) priv[t * 64 + tid] = 0.0;
+        const uint8_t *Ar = A + (size_t)m * ld;
+        const T *Wr = W + (size_t)m * ld * B;
+        for (int n = tid; n < b1; n += 64) {
+            if (n == m || !Ar[n]) continue;
+            double *pt = priv + (size_t)c8[n] * S * 64 + tid;
+            pt[0] += 1.0;
+            if constexpr (B > 0) {
+                double w[B];
+#pragma unroll
+                for (int q = 0; q < B; ++q) { w[q] = (double)Wr[(size_t)n * B + q]; pt[(1 + q) * 64] += w[q]; }
+#pragma unroll
+                for (int q = 0; q < B; ++q)
+#pragma unroll
+                    for (int q2 = q; q2 < B; ++q2) pt[gk_sym_idx(B, q, q2) * 64] += w[q] * w[q2];
+            }
+        }
+        __syncthreads();
+        for (int t = tid; t < KS; t += 64) {
+            double v = 0.0;
+            for (int j = 0; j < 64; ++j) v += priv[t * 64 + j];
+            if (v != 0.0) {
+                const int kd = t / S, sidx = t - kd * S;
+                atomicAdd(&cell[((size_t)a * K + kd) * S + sidx], -v);
+                atomicAdd(&cell[((size_t)b * K + kd) * S + sidx], v);
+            }
+        }
+        __syncthreads();
+    }
+}
+
 // c (int32) -> c8 and block sizes are prepared on the host; this just narrows the labels on the device
 __global__ void k_narrow_labels(const int32_t *__restrict__ c, uint8_t *__restrict__ c8, int N) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) c8[i] = (uint8_t)c[i];

@@ -113,6 +113,17 @@ class DeviceNetwork:
                                                  ctypes.byref(nch)))
         return c32.astype(np.int64), lp, int(nch.value)
 
+    def sbm_sweep_stats(self, K):
+        """K1 statistics of the labels the last ``sbm_sweep`` ended on, folded from that sweep's own per-node statistics
+        (no pass over A / W); None when the engine has none to offer (see include/gk.h gk_sbm_sweep_stats)."""
+        B = self.B
+        n_edge = np.zeros((K, K), np.int64)
+        sum_w = np.zeros((K, K, B)); sum_ww = np.zeros((K, K, B, B))
+        ok = ctypes.c_int(0)
+        self.ctx.check(self.ctx.lib.gk_sbm_sweep_stats(self.ctx.h, self.h, int(K), ptr(n_edge), ptr(sum_w) if B else None,
+                                                       ptr(sum_ww) if B else None, ctypes.byref(ok)))
+        return (n_edge, sum_w, sum_ww) if ok.value else None
+
     # ---- K10 (mean field) ------------------------------------------------------------------------
     def mf_soft_stats(self, mf_m):
         """Off-diagonal soft block-pair statistics mf_m^T (A o x) mf_m (fp64)."""

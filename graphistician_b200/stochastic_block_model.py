@@ -65,6 +65,15 @@ class _StochasticBlockModelBase(NetworkDistribution):
         self.weight_models = [[self._weight_class(self.B, **self.weight_hypers) for _ in range(self.C)]
                               for _ in range(self.C)]
 
+    def __deepcopy__(self, memo):
+        """copy_sample(): everything but the handle on the device network of the last sweep."""
+        new = self.__class__.__new__(self.__class__)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            if k != "_swept":
+                setattr(new, k, copy.deepcopy(v, memo))
+        return new
+
     # ---- N x N views (stochastic_block_model.py:104-113, 594-628) -------------------------------------
     @property
     def P(self):
@@ -122,7 +131,11 @@ class _StochasticBlockModelBase(NetworkDistribution):
     def _cell_stats(self, network):
         """Per-cell (n_edge, n_noedge, sum_w, sum_ww) with the diagonal inside cell (k,k) (old API)."""
         dev = network.device(self.dtype)
-        n_edge, sw, sww = dev.block_stats(self.c, self.C)
+        st = None
+        last = getattr(self, "_swept", None)          # (device network, labels) the last resample_c left behind
+        if last is not None and last[0] is dev and hasattr(dev, "sbm_sweep_stats") and np.array_equal(last[1], self.c):
+            st = dev.sbm_sweep_stats(self.C)          # folded from that sweep's own statistics: no third pass over A / W
+        n_edge, sw, sww = st if st is not None else dev.block_stats(self.c, self.C)
         d = dev.diag_stats(self.c, self.C)
         k = np.arange(self.C)
         n_edge[k, k] += d["d_edge"]
@@ -198,6 +211,7 @@ class _GibbsSBM(_StochasticBlockModelBase):
                                                self.sigmas if has_w else None, u, self_mode=_lib.SELF_ONCE,
                                                sampler=_lib.SAMPLER_CUMSUM, want_lp=want_lp)
         self.c = c
+        self._swept = (dev, c.copy())
         return lp
 
     def resample_m(self):

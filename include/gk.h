@@ -85,6 +85,14 @@ int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, const double
                  const double *p, const double *mu, const double *sigma, int self_mode, int sampler,
                  double beta, const double *uniforms, int block_nodes, double *out_lp, int64_t *out_nchanged);
 
+/* K1 statistics (off-diagonal pairs, exactly what gk_block_stats returns) of the labels the last unsharded gk_sbm_sweep on
+ * `net` ended on.  They are folded from the per-node statistics that sweep computed anyway (sum over the nodes of each
+ * destination block of their in-edge statistics, plus a correction over the rows of the nodes that moved), so the next
+ * resample() -- stochastic_block_model.py:221-250 run on the labels :252-302 just produced -- needs no separate pass over A / W.
+ * *valid = 0 when there is nothing to return (no sweep yet, another network or K, the network re-uploaded since, or a sweep
+ * that moved more than 1024 nodes, where a fresh gk_block_stats pass is cheaper). */
+int gk_sbm_sweep_stats(gk_ctx *ctx, gk_net *net, int K, int64_t *n_edge, double *sum_w, double *sum_ww, int *valid);
+
 /* Sharded form of the same sweep: per node block, every rank computes the partial
  * per-node statistics of its own rows, the host all-reduces them, every rank samples redundantly. */
 int gk_sbm_sweep_begin(gk_ctx *ctx, gk_net *net, const int32_t *c, int K, const double *log_m,

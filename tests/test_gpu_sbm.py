@@ -121,3 +121,57 @@ def test_peaked_posterior_stationary():
     c2, _, nch = net.sbm_sweep(c, np.log(m), p, mus, sig, u, want_lp=False)
     ref, _ = sbm.sbm_assign_sweep(A.astype(float), W, c, m, p, mus, sig, u, sbm.SELF_OLD)
     assert np.array_equal(c2, ref) and nch < 50
+
+
+@pytest.mark.parametrize("N,K,B,dtype,bn", [(700, 5, 2, "f64", 128), (1500, 4, 2, "f64", 0), (900, 16, 1, "f32", 256),
+                                            (640, 7, 0, "f32", 64), (2600, 8, 2, "f64", 0)])
+def test_sweep_leaves_the_next_k1_table(N, K, B, dtype, bn):
+    """gk_sbm_sweep_stats: the K1 statistics of the labels a sweep ends on, folded from the sweep's own per-node statistics plus
+    the movers' rows, equal a fresh gk_block_stats pass (counts bit-exact) -- for a first sweep from random labels (many movers),
+    the sweep after it (few), and with planted labels (none)."""
+    A, W, c, m, p, mus, sig, u = _problem(3 * N + K, N, K, B)
+    net, Wd = _net(A, W, dtype)
+    assert net.sbm_sweep_stats(K) is None                                # no sweep yet
+    rng = np.random.RandomState(N)
+    got_valid = 0
+    for it in range(3):
+        c, _, nch = net.sbm_sweep(c, np.log(m), p, mus if B else None, sig if B else None, rng.rand(N), block_nodes=bn)
+        st = net.sbm_sweep_stats(K)
+        if nch > 1024:
+            assert st is None                                            # too many movers: the host takes a fresh pass
+            continue
+        assert st is not None
+        got_valid += 1
+        n_edge, sw, sww = net.block_stats(c, K)
+        assert np.array_equal(st[0], n_edge)
+        if B:
+            tol = 1e-10 if dtype == "f64" else 2e-4
+            assert np.allclose(st[1], sw, rtol=tol, atol=tol * np.abs(sww).max())
+            assert np.allclose(st[2], sww, rtol=tol, atol=tol * np.abs(sww).max())
+    assert got_valid >= 1
+    assert net.sbm_sweep_stats(K + 1) is None                            # another K: nothing to offer
+
+
+def test_sweep_with_exact_zero_and_one_probabilities():
+    """p == 0 / p == 1 are legal (stochastic_block_model.py:58-60).  The reference's Bernoulli.log_probability turns an
+    impossible event into a hard exclusion (nan_to_num(-inf) = -1.8e308) and 0 * log 0 into 0 (internals/distributions.py:59-67):
+    the device tables must do the same, not soften it.  Labels against the literal loops."""
+    rng = np.random.RandomState(4)
+    N, K, B = 48, 3, 1
+    c = rng.randint(0, K, N)
+    m = np.array([0.3, 0.3, 0.4])
+    p = rng.beta(2, 2, (K, K))
+    p[0, 1] = 0.0
+    p[2, 2] = 1.0
+    mus = rng.randn(K, K, B); sig = np.tile(np.eye(B), (K, K, 1, 1)) * 1.3
+    A = (rng.rand(N, N) < p[np.ix_(c, c)]).astype(np.uint8)          # consistent with p under the starting labels ...
+    W = rng.randn(N, N, B) + mus[np.ix_(c, c)]
+    u = rng.rand(N)
+    c_ref, lp_ref = sbm.gibbs_sbm_resample_c_loops(A.astype(float), W, c, m, p, mus, sig, u)
+    net, _ = _net(A, W, "f64")
+    c_gpu, lp_gpu, _ = net.sbm_sweep(c, np.log(m), p, mus, sig, u, want_lp=True)
+    assert np.array_equal(c_gpu, c_ref)
+    excluded = lp_ref < -1e100                                         # ... so other labels hit impossible events
+    assert excluded.any() and (~excluded).any()
+    assert np.all(lp_gpu[excluded] < -1e9)                             # hard exclusions stay hard
+    assert np.allclose(lp_gpu[~excluded], lp_ref[~excluded], rtol=1e-9, atol=1e-6)
