@@ -12,7 +12,7 @@ from graphistician_b200 import _lib  # noqa: E402
 
 N = int(sys.argv[1]) if len(sys.argv) > 1 else 16384
 args = types.SimpleNamespace(n=N, k=16, b=2, d=8, dtype="f32", workload="sbm")
-wl = bench.setup_workload(args, 0)
+wl = bench.setup_workload("sbm", args, 0, "f32")
 model, network = wl["model"], wl["network"]
 ctx = _lib.default_context()
 for i in range(6):
