@@ -21,6 +21,7 @@ struct gk_eig {
     double *mfMu = nullptr, *mfSig = nullptr, *mfLin = nullptr, *mfPhi = nullptr, *mfSmall = nullptr, *mfPart = nullptr;   // mean-field q (K11)
     long long *prof = nullptr;         // debug cycle counters of k_eig_seq3 (env GK_EIG_PROF=1)
     int use_fast = 1;                  // unsharded sweeps use the running-G form (GK_EIG_OPT_FAST_SWEEP)
+    int use_tc = 1;                    // fp32, D = 8, logistic: the full contraction runs on tcgen05 + TMA (GK_EIG_OPT_TC)
     int use_seq5 = 1;                  // fp32 path: register-resident solver k_eig_seq5 (GK_EIG_OPT_SEQ5); 0 = k_eig_seq4
     double mu0 = 0.0;
     bool have_S = false;
@@ -101,6 +102,7 @@ extern "C" int gk_eig_set_option(gk_ctx *ctx, gk_eig *e, int option, int value) 
     if (option == GK_EIG_OPT_FAST_SWEEP) { e->use_fast = value != 0; return GK_OK; }
     if (option == GK_EIG_OPT_OVERLAP_PUSH) { e->overlap_push = value != 0; return GK_OK; }
     if (option == GK_EIG_OPT_SEQ5) { e->use_seq5 = value != 0; return GK_OK; }
+    if (option == GK_EIG_OPT_TC) { e->use_tc = value != 0; return GK_OK; }
     return gk_fail(ctx, GK_EINVAL, "unknown eigenmodel option %d", option);
 }
 
@@ -529,11 +531,31 @@ static int launch_gfull(gk_ctx *ctx, gk_eig *e, const double *phi_given, size_t 
         GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_gfull<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_full));
         GK_CUDA(ctx, cudaFuncSetAttribute(k_eig_push<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_push));
     }
+    bool on_tc = false;
+    if constexpr (sizeof(T) == 4 && D == 8) {
+        // tensor-core form (gk_eig_tc.cu): fp32 storage, logistic link, features given by F; needs the symmetry of an unsharded S
+        if (e->use_tc && !phi_given && !e->probit && net->row0 == 0 && net->nrows == N) {
+            const int tc_chunks = std::max(1, std::min(16, (2 * ctx->num_sms + strips - 1) / strips));
+            int tc_rows = ((N + tc_chunks - 1) / tc_chunks + 31) / 32 * 32;
+            const int tc_n = (N + tc_rows - 1) / tc_rows;
+            void *work = gk_scratch(ctx, 9, gk_tc_work_bytes(npad));
+            partial = (ACC *)gk_scratch(ctx, 2, (size_t)tc_n * npad * PA * sizeof(ACC));
+            if (!work || !partial) return GK_ENOMEM;
+            gk_time_begin(ctx, 3, (double)N * N * (sizeof(T) + 1.0));
+            int rc = gk_tc_gfull(ctx, (const float *)e->S, net->Asym, net->ld, N, e->F, work, (float *)partial, tc_n, tc_rows);
+            gk_time_end(ctx, 3);
+            if (rc) return rc;
+            nchunks = tc_n;
+            on_tc = true;
+        }
+    }
+    if (!on_tc) {
     gk_time_begin(ctx, 3, (double)N * N * (sizeof(T) + 1.0));
     k_eig_gfull<T, D><<<dim3(strips, nchunks), GK_EF_THREADS, smem_full, ctx->stream>>>(
         (const T *)e->S, net->Asym, net->ld, N, e->F, phi_given, chunk_rows, npad, partial, e->probit);
     gk_time_end(ctx, 3);
     GK_CHECK_LAUNCH(ctx);
+    }
     const size_t per_chunk = (size_t)npad * PA;
     k_eig_greduce<ACC><<<(int)std::min<size_t>((per_chunk + 255) / 256, (size_t)ctx->num_sms * 8), 256, 0, ctx->stream>>>(
         partial, nchunks, per_chunk, e->G);

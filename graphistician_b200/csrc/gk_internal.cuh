@@ -59,7 +59,11 @@ static inline bool gk_attr_needed(gk_ctx *ctx, const void *f) {
 }
 int gk_net_refresh_asym(gk_ctx *ctx, gk_net *net);  // recomputes an existing net->Asym after a re-upload; gk_eig.cu
 int gk_net_ensure_asym(gk_ctx *ctx, gk_net *net);   // builds net->Asym = A + A^T (zero diagonal) once; gk_eig.cu
-void *gk_scratch(gk_ctx *ctx, int slot, size_t bytes);   // returns nullptr (and sets err) on failure
+void *gk_scratch(gk_ctx *ctx, int slot, size_t bytes);
+// gk_eig_tc.cu: the full Omega . (F (x) F) contraction on tcgen05 tensor cores fed by TMA (fp32 storage, D = 8)
+size_t gk_tc_work_bytes(int npad);
+int gk_tc_gfull(gk_ctx *ctx, const float *S, const uint8_t *Asym, int ld, int N, const double *F, void *work, float *partial,
+                int nchunks, int chunk_rows);   // returns nullptr (and sets err) on failure
 
 #define GK_CUDA(ctx, call)                                                                     \
     do {                                                                                       \

@@ -125,7 +125,10 @@ enum { GK_EIG_OPT_CHOL_F64 = 0,
        GK_EIG_OPT_OVERLAP_PUSH = 2,
        /* 1 (default): with fp32 storage and fp32 factorisation the serial kernel is k_eig_seq5 (the solver warp keeps the
         * previous node's features in registers, helper warps prepare the next conditional's base row); 0: k_eig_seq4 */
-       GK_EIG_OPT_SEQ5 = 3 };
+       GK_EIG_OPT_SEQ5 = 3,
+       /* 1 (default): with fp32 storage, D = 8 and the logistic link the once-per-sweep contraction G = S . Phi runs on the
+        * tcgen05 tensor cores fed by TMA (tf32 operands, fp32 accumulation in tensor memory); 0: the FMA kernel k_eig_gfull */
+       GK_EIG_OPT_TC = 4 };
 int gk_eig_set_option(gk_ctx *ctx, gk_eig *eig, int option, int value);
 /* upload the model attributes F (N x D), mu_0, lmbda (D)  (eigenmodel.py:41-73 state) */
 int gk_eig_set_params(gk_ctx *ctx, gk_eig *eig, const double *F, double mu0, const double *lmbda);
