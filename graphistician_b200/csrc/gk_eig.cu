@@ -535,7 +535,13 @@ static int launch_gfull(gk_ctx *ctx, gk_eig *e, const double *phi_given, size_t 
     if constexpr (sizeof(T) == 4 && D == 8) {
         // tensor-core form (gk_eig_tc.cu): fp32 storage, logistic link, features given by F; needs the symmetry of an unsharded S
         if (e->use_tc && !phi_given && !e->probit && net->row0 == 0 && net->nrows == N) {
-            const int tc_chunks = std::max(1, std::min(16, (2 * ctx->num_sms + strips - 1) / strips));
+            // partner chunks: the grid (strips x chunks, 2 CTAs per SM) should fill whole waves
+            int tc_chunks = 1; double best = 1e30;
+            for (int c = 1; c <= 16; ++c) {
+                const double waves = (double)strips * c / (2.0 * ctx->num_sms), cost = ceil(waves - 1e-9) / waves * (1.0 + 0.004 * c);
+                if ((N + c - 1) / c >= 256 && cost < best - 1e-12) { best = cost; tc_chunks = c; }
+            }
+            if (const char *ev = getenv("GK_TC_CHUNKS")) tc_chunks = std::max(1, std::min(32, atoi(ev)));     // tuning experiments
             int tc_rows = ((N + tc_chunks - 1) / tc_chunks + 31) / 32 * 32;
             const int tc_n = (N + tc_rows - 1) / tc_rows;
             void *work = gk_scratch(ctx, 9, gk_tc_work_bytes(npad));
