@@ -73,6 +73,9 @@ SIGNATURES = {
                                       ctypes.POINTER(c_dbl), ctypes.POINTER(c_dbl)]),
     "gk_latent_hmc": (c_int, [c_vp, c_vp, c_int, c_dbl, c_int, c_vp, c_dbl, ctypes.POINTER(c_int), ctypes.POINTER(c_dbl)]),
     "gk_latent_hmc_begin": (c_int, [c_vp, c_vp, c_int, c_dbl, c_int, c_vp]),
+    "gk_latent_set_weight_mode": (c_int, [c_vp, c_vp, c_int, c_dbl]),
+    "gk_latent_weight_stats": (c_int, [c_vp, c_vp, c_vp]),
+    "gk_latent_weight_stats_pass": (c_int, [c_vp, c_vp, c_vp]),
     "gk_latent_hmc_pass": (c_int, [c_vp, c_vp, c_vp]),
     "gk_latent_hmc_advance": (c_int, [c_vp, c_vp, c_vp]),
     "gk_eig_mf_omega": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, c_dbl, c_dbl, c_int, ctypes.c_uint64,

@@ -20,6 +20,8 @@ struct gk_latent {
     void *LT = nullptr, *qT = nullptr;                 // compute-type shadows of L and q
     double *sc = nullptr, *acc = nullptr, *grad = nullptr;
     double sigma = 1.0, mu_self = 0.0;
+    bool wmode = false; double lam = 1.0;              // Gaussian-weight target (weights.py:613-901): mu_0 plays b, sigma plays eta
+    double scale() const { return (f64 || wmode) ? 1.0 : GK_LAT_SCALE_F32; }   // pre-scaling of the compute-type shadows
     long long nd = 0;                                  // number of self edges (sum of diag A)
     // open trajectory
     int target = -1, nsteps = 0, stage = 0; double step = 0.0;
@@ -46,16 +48,22 @@ __device__ __forceinline__ double lat_softplus(double x) { return fmax(x, 0.0) +
 __device__ __forceinline__ double lat_sigmoid(double x) { return 1.0 / (1.0 + exp(-x)); }
 
 struct gk_lat_fin {
-    const double *acc; double *sc; int N, dim; double sigma, mu_self, nd;
+    const double *acc; double *sc; int N, dim; double sigma, mu_self, nd; int wmode; double lam;
 };
 // value of adjacency.py:244-275 from the pair sum: diagonal (eta_ii = mu_0 + mu_self) and priors in closed form
 __device__ __forceinline__ double lat_value(const gk_lat_fin &f, double mu0, double sumsq, double *ll_out) {
+    if (f.wmode) {                                             // weights.py:697-731: Gaussian residuals, priors on L and b
+        const double ll = -0.5 * f.lam * f.acc[(size_t)f.N * f.dim + GK_LAT_ACC_SV];
+        if (ll_out) *ll_out = ll;
+        return ll - 0.5 * sumsq / f.sigma - 0.5 * mu0 * mu0;
+    }
     const double ed = mu0 + f.mu_self;
     const double ll = f.acc[(size_t)f.N * f.dim + GK_LAT_ACC_SV] + f.nd * ed - (double)f.N * lat_softplus(ed);
     if (ll_out) *ll_out = ll;
     return ll - 0.5 * sumsq / f.sigma - 0.5 * mu0 * mu0 - 0.5 * f.mu_self * f.mu_self;
 }
 __device__ __forceinline__ double lat_gmu0(const gk_lat_fin &f, double mu0) {
+    if (f.wmode) return f.lam * f.acc[(size_t)f.N * f.dim + GK_LAT_ACC_SW] - mu0;      // d lp / d b = Lambda sum A r - b
     return f.acc[(size_t)f.N * f.dim + GK_LAT_ACC_SW] + f.nd - (double)f.N * lat_sigmoid(mu0 + f.mu_self) - mu0;
 }
 
@@ -76,7 +84,7 @@ __global__ void __launch_bounds__(1024) k_lat_eval_finish(gk_lat_fin f, const do
         f.sc[SC_LP] = lat_value(f, mu0, ss, &ll);
         f.sc[SC_LL] = ll;
         f.sc[SC_GMU0] = lat_gmu0(f, mu0);
-        f.sc[SC_GMUSELF] = f.nd - (double)f.N * lat_sigmoid(mu0 + f.mu_self) - f.mu_self;
+        f.sc[SC_GMUSELF] = f.wmode ? 0.0 : f.nd - (double)f.N * lat_sigmoid(mu0 + f.mu_self) - f.mu_self;
     }
 }
 
@@ -192,7 +200,7 @@ static int lat_shadow(gk_ctx *ctx, gk_latent *l, const double *src, void *dst) {
     const size_t n = (size_t)l->N * l->dim;
     const int grid = (int)std::min<size_t>((n + 255) / 256, (size_t)ctx->num_sms * 4);
     if (l->f64) k_lat_shadow<double><<<grid, 256, 0, ctx->stream>>>(src, (double *)dst, n, 1.0);
-    else k_lat_shadow<float><<<grid, 256, 0, ctx->stream>>>(src, (float *)dst, n, GK_LAT_SCALE_F32);
+    else k_lat_shadow<float><<<grid, 256, 0, ctx->stream>>>(src, (float *)dst, n, l->scale());
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
 }
@@ -229,10 +237,40 @@ static void lat_launch(gk_ctx *ctx, const gk_lat_pass_params &P, bool value, boo
     else k_latent_pair<T, DIM, false, false><<<grid, GK_LAT_THREADS, 0, ctx->stream>>>(P);
 }
 
+template <typename T, int DIM>
+static void latw_launch(gk_ctx *ctx, const gk_latw_params &P, bool grad, int grid) {
+    if (grad) k_latw_rows<T, DIM, true><<<grid, GK_LATW_THREADS, 0, ctx->stream>>>(P);
+    else k_latw_rows<T, DIM, false><<<grid, GK_LATW_THREADS, 0, ctx->stream>>>(P);
+}
+
+// Gaussian-weight target: one row pass over this rank's rows of (A, W) and (A^T, W^T) at (Lq, *b) into acc_dev
+static int latw_pass(gk_ctx *ctx, gk_latent *l, const void *Lq, const double *b_dev, bool grad, double *acc_dev) {
+    gk_net *net = l->net;
+    gk_latw_params P;
+    P.A = net->A; P.At = net->At; P.W = net->W; P.Wt = net->Wt; P.ld = net->ld; P.row0 = net->row0; P.nrows = net->nrows; P.N = net->N;
+    P.Lq = Lq; P.b = b_dev; P.lam = l->lam; P.acc = acc_dev;
+    const int groups = (net->nrows + GK_LATW_ROWS - 1) / GK_LATW_ROWS;
+    const int grid = std::max(1, std::min(groups, 8 * ctx->num_sms));
+    gk_time_begin(ctx, 4, (double)net->nrows * net->N * (grad ? 2.0 : 1.0) * (1.0 + (l->f64 ? 8.0 : 4.0)));
+    if (l->f64) {
+        if (l->dim == 1) latw_launch<double, 1>(ctx, P, grad, grid);
+        else if (l->dim == 2) latw_launch<double, 2>(ctx, P, grad, grid);
+        else latw_launch<double, 3>(ctx, P, grad, grid);
+    } else {
+        if (l->dim == 1) latw_launch<float, 1>(ctx, P, grad, grid);
+        else if (l->dim == 2) latw_launch<float, 2>(ctx, P, grad, grid);
+        else latw_launch<float, 3>(ctx, P, grad, grid);
+    }
+    gk_time_end(ctx, 4);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
 // one pair pass over this rank's rows at (Lq, *mu0) into acc_dev (zeroed here)
 static int lat_pass(gk_ctx *ctx, gk_latent *l, const void *Lq, const double *mu0_dev, bool value, bool grad, double *acc_dev) {
     gk_net *net = l->net;
     GK_CUDA(ctx, cudaMemsetAsync(acc_dev, 0, lat_acc_len(l) * 8, ctx->stream));
+    if (l->wmode) return latw_pass(ctx, l, Lq, mu0_dev, grad, acc_dev);
     gk_lat_pass_params P;
     P.Asym = net->Asym; P.ld = net->ld; P.row0 = net->row0; P.nrows = net->nrows; P.N = net->N;
     P.Lq = Lq; P.mu0 = mu0_dev; P.acc = acc_dev; P.magic = 0x4B000000u;
@@ -257,6 +295,7 @@ static int lat_pass(gk_ctx *ctx, gk_latent *l, const void *Lq, const double *mu0
 
 static gk_lat_fin lat_fin(gk_latent *l, const double *acc) {
     gk_lat_fin f; f.acc = acc; f.sc = l->sc; f.N = l->N; f.dim = l->dim; f.sigma = l->sigma; f.mu_self = l->mu_self; f.nd = (double)l->nd;
+    f.wmode = l->wmode; f.lam = l->lam;
     return f;
 }
 
@@ -291,6 +330,38 @@ extern "C" int gk_latent_lp_grad(gk_ctx *ctx, gk_latent *l, double *ll, double *
     return gk_latent_eval_finish(ctx, l, nullptr, ll, lp, gradL, gmu0, gmuself);
 }
 
+// ---- Gaussian-weight target (weights.py:613-901) -------------------------------------------------------
+extern "C" int gk_latent_set_weight_mode(gk_ctx *ctx, gk_latent *l, int on, double lam) {
+    if (!ctx || !l) return GK_EINVAL;
+    if (l->target >= 0) return gk_fail(ctx, GK_EINVAL, "a trajectory is open");
+    if (on && l->net->B != 1) return gk_fail(ctx, GK_EUNSUPPORTED, "the distance model of the weights is one-dimensional (B = 1, weights.py:705); network has B=%d", l->net->B);
+    if (on && !(lam > 0)) return gk_fail(ctx, GK_EINVAL, "the precision of the weights must be positive");
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    const bool rescale = (on != 0) != l->wmode;
+    l->wmode = on != 0; if (on) l->lam = lam;
+    if (rescale) { int rc = lat_shadow(ctx, l, l->L, l->LT); if (rc) return rc; }
+    return GK_OK;
+}
+
+extern "C" int gk_latent_weight_stats_pass(gk_ctx *ctx, gk_latent *l, double *acc_dev) {
+    if (!ctx || !l || !l->wmode) return GK_EINVAL;
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    return lat_pass(ctx, l, l->LT, l->sc + SC_MU0, true, false, acc_dev ? acc_dev : l->acc);
+}
+
+extern "C" int gk_latent_weight_stats(gk_ctx *ctx, gk_latent *l, double *out3) {
+    if (!ctx || !l || !out3) return GK_EINVAL;
+    if (!l->wmode) return gk_fail(ctx, GK_EINVAL, "gk_latent_set_weight_mode first");
+    if (l->net->row0 != 0 || l->net->nrows != l->N) return gk_fail(ctx, GK_EINVAL, "gk_latent_weight_stats needs an unsharded network; use gk_latent_weight_stats_pass / all-reduce");
+    int rc = gk_latent_weight_stats_pass(ctx, l, nullptr);
+    if (rc) return rc;
+    double ex[GK_LAT_ACC_EXTRA];
+    GK_CUDA(ctx, cudaMemcpyAsync(ex, l->acc + (size_t)l->N * l->dim, sizeof ex, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    out3[0] = ex[GK_LAT_ACC_N]; out3[1] = ex[GK_LAT_ACC_SW]; out3[2] = ex[GK_LAT_ACC_SV];
+    return GK_OK;
+}
+
 // ---- HMC trajectory ---------------------------------------------------------------------------------
 extern "C" int gk_latent_hmc_begin(gk_ctx *ctx, gk_latent *l, int target, double step, int nsteps, const double *p0) {
     if (!ctx || !l || !p0) return GK_EINVAL;
@@ -323,7 +394,7 @@ extern "C" int gk_latent_hmc_advance(gk_ctx *ctx, gk_latent *l, const double *ac
     gk_lat_fin f = lat_fin(l, acc_dev ? acc_dev : l->acc);
     if (l->target == 0) {
         if (l->f64) k_lat_advance_L<double><<<1, 1024, 0, ctx->stream>>>(f, l->q, l->p, (double *)l->qT, l->step, kind, 1.0);
-        else k_lat_advance_L<float><<<1, 1024, 0, ctx->stream>>>(f, l->q, l->p, (float *)l->qT, l->step, kind, GK_LAT_SCALE_F32);
+        else k_lat_advance_L<float><<<1, 1024, 0, ctx->stream>>>(f, l->q, l->p, (float *)l->qT, l->step, kind, l->scale());
     } else {
         k_lat_advance_mu0<<<1, 32, 0, ctx->stream>>>(f, l->step, kind);
     }

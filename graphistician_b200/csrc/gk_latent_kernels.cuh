@@ -270,3 +270,116 @@ __global__ void __launch_bounds__(GK_LAT_THREADS, VALUE ? 2 : 3) k_latent_pair(g
         if (VALUE) atomicAdd(&P.acc[(size_t)N * DIM + GK_LAT_ACC_SV], b);
     }
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Gaussian-weight sibling (upstream weights.py:613-901, LatentDistanceGaussianWeightDistribution, B = 1):
+//   W_ij | A_ij = 1  ~  N(-||l_i - l_j||^2 + b, Sigma)          i != j
+//   :697-731  lp(L, b) = -1/2 Lambda sum_{i != j} A_ij r_ij^2 - sum L^2 / (2 eta) - b^2 / 2 ,   r_ij = W_ij + ||l_i - l_j||^2 - b
+//   :765-780  its autograd gradient inside hips' HMC (step 0.005, 10 leapfrog steps)
+//   :838-873  the conjugate b and Sigma updates need  n = sum A,  sum A r,  sum A r^2  over the same pairs
+// dlp/dl_i = -2 G_i - l_i / eta  with  G_i = Lambda sum_j (A_ij r_ij + A_ji r_ji)(l_i - l_j): W is not symmetric, so
+// the pass streams row i of (A, W) and row i of (A^T, W^T) -- 2 x 5 B per ordered pair -- and node i's gradient is a
+// row-local sum (no atomics; a row shard owns its nodes' gradients).  One warp per row, 8 rows per CTA sharing the
+// column tile of L in shared memory.
+// ---------------------------------------------------------------------------------------------------------------
+#define GK_LATW_THREADS 256
+#define GK_LATW_ROWS (GK_LATW_THREADS / 32)
+#define GK_LATW_TILE 1024
+#define GK_LAT_ACC_N 2
+
+struct gk_latw_params {
+    const uint8_t *A, *At;   // nrows x ld
+    const void *W, *Wt;      // nrows x ld of the compute type (B = 1)
+    int ld, row0, nrows, N;
+    const void *Lq;          // padded N x DIM of the compute type, UNSCALED
+    const double *b;         // device scalar: the evaluation point's offset b
+    double lam;              // 1 / Sigma
+    double *acc;             // N*DIM + GK_LAT_ACC_EXTRA doubles, zeroed by the caller
+};
+
+template <typename T> __device__ __forceinline__ void gk_load4(const T *p, T (&v)[4]);
+template <> __device__ __forceinline__ void gk_load4<float>(const float *p, float (&v)[4]) {
+    const float4 t = __ldcs((const float4 *)p); v[0] = t.x; v[1] = t.y; v[2] = t.z; v[3] = t.w;
+}
+template <> __device__ __forceinline__ void gk_load4<double>(const double *p, double (&v)[4]) {
+    const double2 t = __ldcs((const double2 *)p), u = __ldcs((const double2 *)p + 1); v[0] = t.x; v[1] = t.y; v[2] = u.x; v[3] = u.y;
+}
+
+template <typename T, int DIM, bool GRAD>
+__global__ void __launch_bounds__(GK_LATW_THREADS) k_latw_rows(gk_latw_params P) {
+    __shared__ T sL[GK_LATW_TILE * DIM];
+    __shared__ double sScal[GK_LATW_ROWS][3];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const T *__restrict__ Lq = (const T *)P.Lq;
+    const T *__restrict__ W = (const T *)P.W, *__restrict__ Wt = (const T *)P.Wt;
+    const int N = P.N;
+    const T b = (T)__ldg(P.b);
+    double s_n = 0.0, s_r = 0.0, s_rr = 0.0;
+    const int ngroups = (P.nrows + GK_LATW_ROWS - 1) / GK_LATW_ROWS;
+    for (int g = blockIdx.x; g < ngroups; g += gridDim.x) {
+        const int il = g * GK_LATW_ROWS + warp, i = P.row0 + il;
+        const bool live = il < P.nrows;
+        T li[DIM], gi[DIM];
+#pragma unroll
+        for (int d = 0; d < DIM; ++d) { li[d] = live ? Lq[(size_t)i * DIM + d] : T(0); gi[d] = T(0); }
+        T tn = T(0), tr = T(0), trr = T(0);
+        const size_t rowoff = (size_t)(live ? il : 0) * P.ld;
+        for (int j0 = 0; j0 < N; j0 += GK_LATW_TILE) {
+            __syncthreads();
+            for (int t = tid; t < GK_LATW_TILE * DIM; t += GK_LATW_THREADS) {
+                const int j = j0 + t / DIM;
+                sL[t] = j < N ? Lq[(size_t)j0 * DIM + t] : T(0);
+            }
+            __syncthreads();
+            if (!live) continue;
+            const int jend = min(N, j0 + GK_LATW_TILE);
+            for (int j = j0 + lane * 4; j < jend; j += 128) {
+                const uint32_t a_out = __ldcs((const uint32_t *)(P.A + rowoff + j));
+                T w_out[4];
+                gk_load4<T>(W + rowoff + j, w_out);
+                uint32_t a_in = 0u;
+                T w_in[4] = {T(0), T(0), T(0), T(0)};
+                if (GRAD) { a_in = __ldcs((const uint32_t *)(P.At + rowoff + j)); gk_load4<T>(Wt + rowoff + j, w_in); }
+#pragma unroll
+                for (int c = 0; c < 4; ++c) {
+                    const int jj = j + c;
+                    const bool ok = jj < N && jj != i;
+                    T dd[DIM], d2 = T(0);
+#pragma unroll
+                    for (int d = 0; d < DIM; ++d) { dd[d] = li[d] - sL[(jj - j0) * DIM + d]; d2 = fma(dd[d], dd[d], d2); }
+                    const T x = d2 - b;
+                    const T ao = ok && ((a_out >> (8 * c)) & 0xffu) ? T(1) : T(0);
+                    const T ro = ao * (w_out[c] + x);
+                    tn += ao; tr += ro; trr = fma(ro, ro, trr);
+                    if (GRAD) {
+                        const T ai = ok && ((a_in >> (8 * c)) & 0xffu) ? T(1) : T(0);
+                        const T coef = fma(ai, w_in[c] + x, ro);
+#pragma unroll
+                        for (int d = 0; d < DIM; ++d) gi[d] = fma(coef, dd[d], gi[d]);
+                    }
+                }
+            }
+        }
+        if (GRAD) {
+#pragma unroll
+            for (int d = 0; d < DIM; ++d) {
+                double v = (double)gi[d];
+                for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+                if (lane == 0 && live) P.acc[(size_t)i * DIM + d] = P.lam * v;
+            }
+        }
+        s_n += (double)tn; s_r += (double)tr; s_rr += (double)trr;
+    }
+    for (int o = 16; o; o >>= 1) {
+        s_n += __shfl_xor_sync(0xffffffffu, s_n, o); s_r += __shfl_xor_sync(0xffffffffu, s_r, o); s_rr += __shfl_xor_sync(0xffffffffu, s_rr, o);
+    }
+    if (lane == 0) { sScal[warp][0] = s_n; sScal[warp][1] = s_r; sScal[warp][2] = s_rr; }
+    __syncthreads();
+    if (tid == 0) {
+        double a = 0.0, c = 0.0, e = 0.0;
+        for (int w = 0; w < GK_LATW_ROWS; ++w) { a += sScal[w][0]; c += sScal[w][1]; e += sScal[w][2]; }
+        atomicAdd(&P.acc[(size_t)N * DIM + GK_LAT_ACC_N], a);
+        atomicAdd(&P.acc[(size_t)N * DIM + GK_LAT_ACC_SW], c);
+        atomicAdd(&P.acc[(size_t)N * DIM + GK_LAT_ACC_SV], e);
+    }
+}

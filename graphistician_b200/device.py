@@ -407,6 +407,22 @@ class DeviceLatent:
             self.ctx.check(lib.gk_latent_hmc_end(c, h, float(log_u), ctypes.byref(acc), ctypes.byref(ratio)))
         return bool(acc.value), ratio.value
 
+    def set_weight_mode(self, on, lam=1.0):
+        """Switch the passes to the Gaussian-weight target of weights.py:697-731 (set_params' mu_0 = b, sigma = eta)."""
+        self.ctx.check(self.ctx.lib.gk_latent_set_weight_mode(self.ctx.h, self.h, int(bool(on)), float(lam)))
+
+    def weight_stats(self):
+        """(n, sum r, sum r^2) over the off-diagonal edges, r = W + d^2 - b, at the current (L, b)."""
+        if self.comm is not None:
+            acc = ctypes.c_void_p(self._acc.data_ptr())
+            self.ctx.check(self.ctx.lib.gk_latent_weight_stats_pass(self.ctx.h, self.h, acc))
+            self.comm.allreduce_(self._acc)
+            ex = self._acc[self.N * self.dim:].cpu().numpy()
+            return float(ex[2]), float(ex[0]), float(ex[1])
+        out = np.zeros(3)
+        self.ctx.check(self.ctx.lib.gk_latent_weight_stats(self.ctx.h, self.h, ptr(out)))
+        return float(out[0]), float(out[1]), float(out[2])
+
     def close(self):
         self._finalizer()
 

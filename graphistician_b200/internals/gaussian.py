@@ -260,3 +260,34 @@ def niw_resample_batched(hyp, n, sum_x, sum_xxT, rng=np.random):
     z_off = rng.standard_normal(n.shape + (B * (B - 1) // 2,))
     z_mu = rng.standard_normal(n.shape + (B,))
     return niw_draw_batched(mu_n, sigma_n, kappa_n, nu_n, chi2, z_off, z_mu)
+
+
+class GaussianFixedMean(object):
+    """pybasicbayes.distributions.GaussianFixedMean as weights.py:638,863-867 uses it: Sigma ~ IW(lmbda_0, nu_0) around a
+    fixed mean; ``resample_from_stats(n, S)`` draws from IW(lmbda_0 + S, nu_0 + n), S = sum (x - mu)(x - mu)^T."""
+
+    def __init__(self, mu=None, sigma=None, nu_0=None, lmbda_0=None):
+        self.mu = None if mu is None else np.array(mu, dtype=np.float64)
+        self.sigma = None if sigma is None else np.array(sigma, dtype=np.float64)
+        self.nu_0 = nu_0
+        self.lmbda_0 = None if lmbda_0 is None else np.array(lmbda_0, dtype=np.float64)
+        if sigma is None and nu_0 is not None and lmbda_0 is not None:
+            self.resample()
+
+    @property
+    def D(self):
+        return self.mu.shape[0]
+
+    @property
+    def sigma_chol(self):
+        return np.linalg.cholesky(self.sigma)
+
+    def resample_from_stats(self, n, S, rng=np.random):
+        self.sigma = invwishart_draw(self.lmbda_0 + S, self.nu_0 + n, rng)
+        return self
+
+    def resample(self, data=None, rng=np.random):
+        if data is None or len(data) == 0:
+            return self.resample_from_stats(0, 0.0, rng)
+        d = np.asarray(data, dtype=np.float64).reshape(-1, self.D) - self.mu
+        return self.resample_from_stats(d.shape[0], d.T.dot(d), rng)

@@ -253,6 +253,54 @@ def sample_network(model, N):
     return (A, f, theta)
 
 
+def fit_network(A, model, x0=None, N_iter=1000, callback=None, verbose=False):
+    """internals/graph_models.py:546-594: Gibbs on (theta, f) given A; the inner ``for n: f[n] = sample_f(...)`` loop
+    is one sequential device sweep (``sample_fs``).  Returns (f_trace, theta_trace, lp_trace)."""
+    N = A.shape[0]
+    if x0 is None:
+        theta0 = model.sample_theta()
+        f0 = [model.sample_f(theta0) for _ in range(N)]
+    else:
+        (f0, theta0) = x0
+    f, theta = copy.deepcopy(f0), copy.deepcopy(theta0)
+    lp_trace = np.zeros(N_iter)
+    f_trace, theta_trace = [], []
+    for it in range(N_iter):
+        lp_trace[it] = model.logpr(A, f, theta)
+        if verbose:
+            print("Iteration %d. \tlog pr: %f" % (it, lp_trace[it]))
+        theta = model.sample_theta((A, f))
+        f = model.sample_fs(theta, A, f)
+        if callback is not None:
+            callback(f, theta)
+        f_trace.append(np.array(f))             # the reference appends the list it keeps mutating (:587); copies here
+        theta_trace.append(copy.deepcopy(theta))
+    return (f_trace, theta_trace, lp_trace)
+
+
+def geweke_test(N, model, N_iter=1000, callback=None, verbose=False):
+    """internals/graph_models.py:597-650: successive-conditional sampler theta | A, f ; f | A, theta ; A | f, theta.
+    A changes every iteration, so every iteration uploads a new network (N is small in the reference's use)."""
+    theta0 = model.sample_theta()
+    f0 = [model.sample_f(theta0) for _ in range(N)]
+    A = np.asarray(model.sample_A(f0, theta0))
+    f, theta = copy.deepcopy(f0), copy.deepcopy(theta0)
+    lp_trace = np.zeros(N_iter)
+    f_trace, theta_trace = [], []
+    for it in range(N_iter):
+        lp_trace[it] = model.logpr(A, f, theta)
+        if verbose:
+            print("Iteration %d. \tlog pr: %f" % (it, lp_trace[it]))
+        theta = model.sample_theta((A, f))
+        f = model.sample_fs(theta, A, f)
+        A = np.asarray(model.sample_A(f, theta))
+        if callback is not None:
+            callback(A, f, theta)
+        theta_trace.append(copy.deepcopy(theta))
+        f_trace.append(np.array(f))
+    return (f_trace, theta_trace, lp_trace)
+
+
 def estimate_marginal_likelihood(A, f0, theta0, model, N_samples=1000, B=100, steps_per_B=11, comm=None,
                                  return_weights=False):
     """AIS estimate of log p(A | model) (examples/demo_ais.py:10-62): B temperatures, ``steps_per_B`` Gibbs steps

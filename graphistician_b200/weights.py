@@ -330,3 +330,237 @@ class SBMGaussianWeightDistribution(GaussianWeightDistribution, GibbsSampling):
     def resample_m(self):
         """weights.py:493-498."""
         self.m = np.random.dirichlet(self.pi + np.bincount(self.c, minlength=self.C))
+
+
+class SBMGaussianWeightSharedCov(SBMGaussianWeightDistribution):
+    """weights.py:501-611: the SBM weight model with ONE covariance shared by all C x C cells.  Cell means are conjugate
+    given the covariance (GaussianFixedCov: prior N(mu_0, I), :523-526), the covariance is inverse-Wishart given the
+    residuals of all off-diagonal edges (GaussianFixedMean around 0: prior IW(Sigma_0, nu_0), :520-521, 545-549); the self
+    Gaussian keeps the parent's NIW model (:541-543).  Label sweep, m, predictive parameters and log likelihood are
+    inherited: the per-cell (mu, Sigma) tables repeat the shared covariance.
+
+    Device work per ``resample_mu_and_Sig``: the parent's single K1 pass (n, sum w, sum w w^T per cell); both conjugate
+    updates are host O(C^2 B^2) arithmetic on those statistics (the reference gathers W[mask] per cell and W - Mu, :530-549):
+      mean of cell (a, b):  precision = I + n Sigma^-1,  h = mu_0 + Sigma^-1 sum w
+      shared covariance:    S = sum over cells of  sum ww^T - mu sw^T - sw mu^T + n mu mu^T   over off-diagonal edges"""
+
+    def __init__(self, N, B=1, C=3, pi=10.0, mu_0=None, Sigma_0=None, nu_0=None, special_case_self_conns=True, dtype="f32"):
+        super(SBMGaussianWeightSharedCov, self).__init__(N, B=B, C=C, pi=pi, mu_0=mu_0, Sigma_0=Sigma_0, nu_0=nu_0,
+                                                         special_case_self_conns=special_case_self_conns, dtype=dtype)
+        from .internals.gaussian import GaussianFixedMean
+        self._prior_mu = np.zeros(B) if mu_0 is None else np.array(mu_0, dtype=np.float64)
+        Sigma_0 = np.eye(B) if Sigma_0 is None else np.array(Sigma_0, dtype=np.float64)
+        self._cov_model = GaussianFixedMean(mu=np.zeros(B), nu_0=(B + 2 if nu_0 is None else nu_0), lmbda_0=Sigma_0)
+        for c1 in range(self.C):
+            for c2 in range(self.C):          # GaussianFixedCov(mu_0, sigma_0 = I, sigma = shared): mean drawn from its prior
+                self._gaussians[c1][c2].mu = np.random.multivariate_normal(self._prior_mu, np.eye(B))
+        self._set_shared_cov()
+
+    def _set_shared_cov(self):
+        for row in self._gaussians:
+            for g in row:
+                g.sigma = self._cov_model.sigma.copy()
+
+    @property
+    def shared_sigma(self):
+        return self._cov_model.sigma
+
+    def initialize_from_prior(self):
+        self.m = np.random.dirichlet(self.pi)
+        self.c = np.random.choice(self.C, p=self.m, size=self.N)
+        self._cov_model.resample()
+        for row in self._gaussians:
+            for g in row:
+                g.mu = np.random.multivariate_normal(self._prior_mu, np.eye(self.B))
+        self._set_shared_cov()
+        if self.special_case_self_conns:
+            self._self_gaussian.resample()
+
+    def log_prior(self):
+        """weights.py:553-575: the Dirichlet on m and the assignment terms only (the Gaussian terms are commented out there)."""
+        return _dirichlet_logpdf(self.m, self.pi) + float(np.log(self.m)[self.c].sum())
+
+    def resample_mu_and_Sig(self, A, W, draws=None):
+        """weights.py:528-551.  ``draws`` (parity tests) = dict(z_mu = C*C x B standard normals) fixes the mean draws
+        through mean + chol(cov) z; the self Gaussian and the covariance draw from ``np.random``."""
+        n, sw, sww, d = self._cell_stats(A, W)
+        self._last_stats = (n, sw, sww, d)
+        B, C = self.B, self.C
+        Lam = np.linalg.inv(self._cov_model.sigma)
+        for c1 in range(C):
+            for c2 in range(C):
+                cov = np.linalg.inv(np.eye(B) + n[c1, c2] * Lam)
+                mean = cov.dot(self._prior_mu + Lam.dot(sw[c1, c2]))
+                if draws is not None:
+                    self._gaussians[c1][c2].mu = mean + np.linalg.cholesky(cov).dot(draws["z_mu"][c1 * C + c2])
+                else:
+                    self._gaussians[c1][c2].mu = np.random.multivariate_normal(mean, cov)
+        if self.special_case_self_conns:
+            self._self_gaussian.resample_from_stats(int(d["d_edge"].sum()), d["d_sum_w"].sum(0), d["d_sum_ww"].sum(0))
+        # residuals of the OFF-DIAGONAL edges around the new means (:545-549)
+        n, sw, sww = n.copy(), sw.copy(), sww.copy()
+        if not self.special_case_self_conns:
+            k = np.arange(C)
+            n[k, k] -= d["d_edge"]; sw[k, k] -= d["d_sum_w"]; sww[k, k] -= d["d_sum_ww"]
+        S = np.zeros((B, B))
+        for c1 in range(C):
+            for c2 in range(C):
+                mu = self._gaussians[c1][c2].mu
+                S += sww[c1, c2] - np.outer(mu, sw[c1, c2]) - np.outer(sw[c1, c2], mu) + n[c1, c2] * np.outer(mu, mu)
+        self._cov_model.resample_from_stats(int(n.sum()), 0.5 * (S + S.T))
+        self._set_shared_cov()
+
+
+class LatentDistanceGaussianWeightDistribution(GaussianWeightDistribution, GibbsSampling):
+    """weights.py:613-901:  l_n ~ N(0, eta I),  W_ij | A_ij = 1 ~ N(-||l_i - l_j||^2 + b, Sigma) for i != j (B = 1),
+    self weights from their own NIW Gaussian.
+
+    ``resample((A, W))`` keeps the reference's five moves (:757-763):
+      L      hips HMC, step 0.005, 10 leapfrog steps (:765-780): 11 row passes of k_latw_rows over (A, W) and (A^T, W^T)
+             on the device (gk_latent_set_weight_mode + gk_latent_hmc), momentum and log-uniform from np.random in hips' order
+      b      exact Gaussian conditional (:838-860) from one statistics pass: n, sum r, sum r^2 with r = W + d^2 - b
+      Sigma  inverse-Wishart given the residuals around the NEW b (:863-867): sum (r - delta)^2 from the same three numbers
+      self   NIW posterior draw from the diagonal statistics (:869-872)
+      eta    inverse gamma (:874-890)."""
+
+    def __init__(self, N, B=1, dim=2, b=0.5, sigma=None, Sigma_0=None, nu_0=None, mu_self=0.0, eta=0.01, dtype="f32"):
+        super(LatentDistanceGaussianWeightDistribution, self).__init__(N, B)
+        from .internals.gaussian import GaussianFixedMean
+        self.dim, self.b, self.eta, self.dtype = dim, b, eta, dtype
+        self.L = np.sqrt(eta) * np.random.randn(N, dim)
+        Sigma_0 = np.eye(B) if Sigma_0 is None else Sigma_0
+        nu_0 = B + 2 if nu_0 is None else nu_0
+        self.cov = GaussianFixedMean(mu=np.zeros(B), sigma=sigma, lmbda_0=Sigma_0, nu_0=nu_0)
+        self._self_gaussian = Gaussian(mu_0=mu_self * np.ones(B), sigma_0=Sigma_0, nu_0=nu_0, kappa_0=1.0)
+        self._dev = None
+
+    @property
+    def D(self):
+        return ((self.L[:, None, :] - self.L[None, :, :]) ** 2).sum(2)
+
+    @property
+    def Mu(self):
+        Mu = np.tile((-self.D + self.b)[:, :, None], (1, 1, self.B))
+        idx = np.arange(self.N)
+        Mu[idx, idx, :] = self._self_gaussian.mu
+        return Mu
+
+    @property
+    def Sigma(self):
+        Sig = np.tile(self.cov.sigma[None, None, :, :], (self.N, self.N, 1, 1))
+        idx = np.arange(self.N)
+        Sig[idx, idx] = self._self_gaussian.sigma
+        return Sig
+
+    def initialize_from_prior(self):
+        self.L = np.sqrt(self.eta) * np.random.randn(self.N, self.dim)
+        self.cov.resample()
+
+    def log_prior(self):
+        """weights.py:679-695 (note: the L term there is a standard normal, not N(0, eta))."""
+        from scipy.stats import norm, invgamma, invwishart
+        lp = invgamma.logpdf(self.eta, 1, 1)
+        lp += norm.logpdf(self.b, 0, 1)
+        lp += norm.logpdf(self.L, 0, 1).sum()
+        lp += invwishart.logpdf(self.cov.sigma, self.cov.nu_0, self.cov.lmbda_0)
+        lp += normal_inverse_wishart_log_prob(self._self_gaussian)
+        return lp
+
+    # ---- device state ----------------------------------------------------------------------------------
+    def _device_state(self, A, W):
+        from .device import DeviceLatent
+        assert self.B == 1, "the distance model of the weights is one-dimensional (weights.py:705)"
+        net = network_for(A, W).device(self.dtype)
+        if self._dev is None or self._dev[0] is not net:
+            if self._dev is not None:
+                self._dev[1].close()
+            self._dev = (net, DeviceLatent(net, self.dim))
+        dev = self._dev[1]
+        dev.set_weight_mode(True, 1.0 / float(self.cov.sigma[0, 0]))
+        dev.set_params(self.L, self.b, 0.0, self.eta)
+        return dev
+
+    def __deepcopy__(self, memo):
+        import copy
+        new = self.__class__.__new__(self.__class__)
+        memo[id(self)] = new
+        for k, v in self.__dict__.items():
+            setattr(new, k, None if k == "_dev" else copy.deepcopy(v, memo))
+        return new
+
+    def hmc_log_probability_and_grad(self, A, W):
+        """(lp, d lp / d L, d lp / d b) of weights.py:697-731 and of its autograd gradient."""
+        ll, lp, gL, gb, _ = self._device_state(A, W).lp_grad()
+        return lp, gL, gb
+
+    def log_likelihood(self, network):
+        """abstractions.py:257-274 with Mu / Sigma of :649-668: Gaussian log density of the off-diagonal edges from
+        (n, sum r, sum r^2) of one device pass, plus the self edges from the diagonal statistics."""
+        A, W = network
+        dev = self._device_state(A, W)
+        n, sr, srr = dev.weight_stats()
+        sig = float(self.cov.sigma[0, 0])
+        ll = -0.5 * srr / sig - 0.5 * n * np.log(2 * np.pi * sig)
+        d = dev.net.diag_stats(np.zeros(self.N, np.int32), 1)
+        if d["d_edge"].sum():
+            ll += self._self_gaussian.log_likelihood_from_stats(d["d_edge"].sum(), d["d_sum_w"].sum(0), d["d_sum_ww"].sum(0))
+        return float(ll)
+
+    def sample_predictive_parameters(self):
+        """weights.py:735-761, O(N) instead of an (N+1)^2 distance matrix."""
+        lnew = np.sqrt(self.eta) * np.random.randn(1, self.dim)
+        mu = -((self.L - lnew) ** 2).sum(1) + self.b
+        Mu_row = np.tile(np.concatenate((mu, [self.b]))[:, None], (1, self.B))
+        Mu_row[-1] = self._self_gaussian.mu
+        Lc = np.linalg.cholesky(self.cov.sigma)
+        L_row = np.tile(Lc[None, :, :], (self.N + 1, 1, 1))
+        L_row[-1] = np.linalg.cholesky(self._self_gaussian.sigma)
+        return Mu_row, Mu_row.copy(), L_row, L_row.copy()
+
+    # ---- Gibbs / HMC -----------------------------------------------------------------------------------
+    def resample(self, network, draws=None):
+        """weights.py:757-763.  ``draws`` (parity tests) = dict(L=(p0, log_u), b=z) injects the HMC and b draws."""
+        A, W = network
+        dev = self._device_state(A, W)
+        self._resample_L(dev, None if draws is None else draws.get("L"))
+        stats = dev.weight_stats()
+        delta = self._resample_b(stats, None if draws is None else draws.get("b"))
+        self._resample_cov(stats, delta)
+        self._resample_self_gaussian(dev)
+        self._resample_eta()
+
+    def _resample_L(self, dev, draws=None, stepsz=0.005, nsteps=10):
+        if draws is None:
+            p0 = np.random.randn(self.N, self.dim)
+            log_u = np.log(np.random.rand())
+        else:
+            p0, log_u = draws
+        accepted, self._last_L_ratio = dev.hmc(0, stepsz, nsteps, p0, log_u)
+        if accepted:
+            self.L = dev.get_params()[0]
+        return accepted
+
+    def _resample_b(self, stats, z=None):
+        """weights.py:838-860: X = W + D on the off-diagonal edges, sum X = sum r + n b."""
+        n, sr, srr = stats
+        sigma = float(self.cov.sigma[0, 0])
+        sigma_post = 1.0 / (1.0 + n / sigma)
+        mu_post = sigma_post * ((sr + n * self.b) / sigma)
+        b_old = self.b
+        self.b = mu_post + np.sqrt(sigma_post) * (np.random.randn() if z is None else z)
+        return self.b - b_old
+
+    def _resample_cov(self, stats, delta):
+        """weights.py:863-867: residuals around the new mean, sum (r - delta)^2 = sum r^2 - 2 delta sum r + n delta^2."""
+        n, sr, srr = stats
+        S = srr - 2.0 * delta * sr + n * delta * delta
+        self.cov.resample_from_stats(int(round(n)), np.array([[max(S, 0.0)]]))
+
+    def _resample_self_gaussian(self, dev):
+        d = dev.net.diag_stats(np.zeros(self.N, np.int32), 1)
+        self._self_gaussian.resample_from_stats(int(d["d_edge"].sum()), d["d_sum_w"].sum(0), d["d_sum_ww"].sum(0))
+
+    def _resample_eta(self):
+        """weights.py:874-890: eta ~ IG(1 + N dim / 2, 1 + sum L^2 / 2)."""
+        from scipy.stats import invgamma
+        self.eta = invgamma.rvs(a=1.0 + self.L.size / 2.0, scale=1.0 + (self.L ** 2).sum() / 2.0)

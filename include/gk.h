@@ -206,6 +206,17 @@ int gk_latent_hmc_begin(gk_ctx *ctx, gk_latent *lat, int target, double step, in
 int gk_latent_hmc_pass(gk_ctx *ctx, gk_latent *lat, double *acc_dev);
 int gk_latent_hmc_advance(gk_ctx *ctx, gk_latent *lat, const double *acc_dev);
 int gk_latent_hmc_end(gk_ctx *ctx, gk_latent *lat, double log_u, int *accepted, double *log_ratio);
+/* Gaussian-weight sibling of the same state: LatentDistanceGaussianWeightDistribution (weights.py:613-901, B = 1),
+ *   W_ij | A_ij = 1 ~ N(-||l_i - l_j||^2 + b, 1 / lam),  i != j.
+ * on = 1 switches every pass of this state (lp_grad, eval_*, hmc*) to the target of _hmc_log_probability
+ * (weights.py:697-731): lp = -lam/2 sum A_ij r_ij^2 - sum L^2 / (2 eta) - b^2 / 2 with r = W + d^2 - b; gk_latent_set_params'
+ * mu0 is then b, sigma is eta, mu_self is unused.  Replaces the autograd gradient inside _resample_L (:765-780). */
+int gk_latent_set_weight_mode(gk_ctx *ctx, gk_latent *lat, int on, double lam);
+/* Statistics of the conjugate updates _resample_b (:838-860) and _resample_cov (:863-867) at the current (L, b), one
+ * row pass over (A, W): out3 = { n = sum A_ij, sum A_ij r_ij, sum A_ij r_ij^2 } over i != j.  The sharded form is
+ * weight_stats_pass -> all-reduce(acc_dev) -> read acc_dev[N*dim + {2, 0, 1}]. */
+int gk_latent_weight_stats(gk_ctx *ctx, gk_latent *lat, double *out3);
+int gk_latent_weight_stats_pass(gk_ctx *ctx, gk_latent *lat, double *acc_dev);
 
 /* ---- K11: mean-field logistic eigenmodel ------------------------------------------------
  * Unsharded networks.  q(f_n) = N(mf_mu_F[n], mf_Sigma_F[n]) (N x D, N x D x D row-major), q(lmbda) through E_lmbda (D) and

@@ -122,3 +122,46 @@ def rows_value_and_grad(L, mu_0, mu_self, A_rows, At_rows, r0, sigma):
     gs = g + (At_rows - sig)                 # g_nj + g_jn (eta is symmetric)
     gL = -2.0 * np.einsum("rj,rjd->rd", gs, diff) - Lr / sigma
     return ll, gL, g.sum(), g[np.arange(R), r0 + np.arange(R)].sum()
+
+
+# ------------------------------------------------------------------------------------------------------------------
+# LatentDistanceGaussianWeightDistribution (weights.py:613-901, B = 1)
+# ------------------------------------------------------------------------------------------------------------------
+def weight_log_probability_and_grad(L, b, A, W, sigma_w, eta):
+    """weights.py:697-731 (_hmc_log_probability) and the gradient autograd derives from it.
+
+    Mu = -||l_i - l_j||^2 + b;  X = (W - Mu) A_offdiag;  lp = -1/2 sum X^2 / sigma_w - sum L^2 / (2 eta) - b^2 / 2.
+    With r = W + d^2 - b on the off-diagonal edges:  d lp / d l_n = -2/sigma_w sum_j (A_nj r_nj + A_jn r_jn)(l_n - l_j) - l_n / eta,
+    d lp / d b = sum A r / sigma_w - b.   W: N x N (the single weight dimension)."""
+    N = L.shape[0]
+    D2 = ((L[:, None, :] - L[None, :, :]) ** 2).sum(2)
+    Aoff = np.asarray(A, dtype=np.float64) * (1.0 - np.eye(N))
+    R = (W + D2 - b) * Aoff
+    lam = 1.0 / sigma_w
+    lp = np.sum(-0.5 * R ** 2 * lam) - 0.5 * np.sum(L * L / eta) - 0.5 * b ** 2
+    Rs = R + R.T
+    gL = -2.0 * lam * (Rs.sum(1)[:, None] * L - Rs.dot(L)) - L / eta
+    gb = lam * R.sum() - b
+    return lp, gL, gb
+
+
+def weight_stats(L, b, A, W):
+    """(n, sum r, sum r^2) over the off-diagonal edges: what weights.py:838-867 reduce W to."""
+    N = L.shape[0]
+    D2 = ((L[:, None, :] - L[None, :, :]) ** 2).sum(2)
+    e = (np.asarray(A) != 0) & ~np.eye(N, dtype=bool)
+    r = (W + D2 - b)[e]
+    return float(r.size), float(r.sum()), float((r * r).sum())
+
+
+def weight_resample_L(L, b, A, W, sigma_w, eta, draws, step=0.005, nsteps=10):
+    """weights.py:765-780: one hips HMC transition on L, fixed step 0.005, 10 leapfrog steps."""
+    lp = lambda Lq: weight_log_probability_and_grad(Lq, b, A, W, sigma_w, eta)[0]
+    dlp = lambda Lq: weight_log_probability_and_grad(Lq, b, A, W, sigma_w, eta)[1]
+    return hmc(lp, dlp, step, nsteps, L.copy(), draws, negative_log_prob=False)
+
+
+def weight_b_posterior(n, sum_x, sigma_w):
+    """weights.py:838-860: X = W + D ~ N(b, sigma_w) on the off-diagonal edges, b ~ N(0, 1)  ->  (mean, variance)."""
+    sigma_post = 1.0 / (1.0 + n / sigma_w)
+    return sigma_post * (sum_x / sigma_w), sigma_post

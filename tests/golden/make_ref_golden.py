@@ -457,8 +457,173 @@ def make_ref_mf_eigen(R):
     _save("ref_mf_eigen.npz", out)
 
 
+# --------------------------------------------------------------------------------------------------
+# predictive path (abstractions.py:141-182, 289-357; adjacency.py:102,183,291,562; weights.py:59,144,375)
+# --------------------------------------------------------------------------------------------------
+def make_ref_predictive(R):
+    rng = np.random.RandomState(20249)
+    N, C, B, M = 12, 3, 2, 7
+    A, W, c, m, p, mus, sig = _sbm_problem(rng, N, C, B)
+    Arow = (rng.rand(N + 1) < 0.4); Acol = (rng.rand(N + 1) < 0.4); Acol[-1] = Arow[-1]
+    Wrow = rng.randn(N + 1, B); Wcol = rng.randn(N + 1, B); Wcol[-1] = Wrow[-1]
+    out = dict(c=c, m=m, p=p, mus=mus, sigmas=sig, Arow=Arow, Acol=Acol, Wrow=Wrow, Wcol=Wcol, M=M)
+
+    def adj_record(tag, mdl):
+        np.random.seed(101)
+        pr, pc = mdl.sample_predictive_parameters()
+        out[tag + "_Prow"], out[tag + "_Pcol"] = np.array(pr, dtype=float), np.array(pc, dtype=float)
+        np.random.seed(102)
+        ar, ac = mdl.sample_predictive_distribution()
+        out[tag + "_Arow"], out[tag + "_Acol"] = np.array(ar), np.array(ac)
+        np.random.seed(103)
+        out[tag + "_pll"] = mdl.approx_predictive_ll(Arow, Acol, M=M)
+
+    def w_record(tag, mdl):
+        np.random.seed(111)
+        mr, mc, lr, lc = mdl.sample_predictive_parameters()
+        out[tag + "_Murow"], out[tag + "_Mucol"], out[tag + "_Lrow"], out[tag + "_Lcol"] = \
+            [np.array(x, dtype=float) for x in (mr, mc, lr, lc)]
+        np.random.seed(112)
+        try:                                             # abstractions.py:297-298 asserts on arrays: ValueError for B > 1
+            wr, wc = mdl.sample_predictive_distribution()
+            out[tag + "_Wrow"], out[tag + "_Wcol"] = wr, wc
+        except ValueError as e:
+            out[tag + "_dist_error"] = np.array(repr(e))
+        np.random.seed(113)
+        out[tag + "_pll"] = mdl.approx_predictive_ll(Arow, Acol, Wrow, Wcol, M=M)
+
+    adj_record("bern", R.adjacency.BernoulliAdjacencyDistribution(N, p=0.3))
+    for sc in (0, 1):
+        np.random.seed(5)
+        kw = dict(tau1_self=1.5, tau0_self=0.5) if sc else {}
+        bb = R.adjacency.BetaBernoulliAdjacencyDistribution(N, tau1=2.0, tau0=3.0, **kw)
+        bb.p = 0.35
+        if sc:
+            bb.p_self = 0.8
+        adj_record("bb%d" % sc, bb)
+    for sp in (1, 0):
+        np.random.seed(2)
+        mdl = R.adjacency.SBMAdjacencyDistribution(N, C=C, c=c.astype(int), m=m.copy(), p=p.copy(),
+                                                   special_case_self_conns=bool(sp))
+        adj_record("sbm%d" % sp, mdl)
+    np.random.seed(3)
+    ld = R.adjacency.LatentDistanceAdjacencyDistribution(N, dim=2, sigma=1.5, mu0=0.3, mu_self=-0.4)
+    ld.L = rng.randn(N, 2)
+    out["ld_L"] = ld.L.copy(); out["ld_sigma"] = ld.sigma; out["ld_mu0"] = ld.mu_0; out["ld_mu_self"] = ld.mu_self
+    adj_record("ld", ld)
+
+    np.random.seed(6)
+    fx = R.weights.FixedGaussianWeightDistribution(N, B, mus[0, 1].copy(), sig[0, 1].copy())
+    w_record("fixed", fx)
+    np.random.seed(6)
+    niw = R.weights.NIWGaussianWeightDistribution(N, B=B)
+    niw._gaussian.mu = mus[0, 0].copy(); niw._gaussian.sigma = sig[0, 0].copy()
+    niw._self_gaussian.mu = mus[1, 1].copy(); niw._self_gaussian.sigma = sig[1, 1].copy()
+    w_record("niw", niw)
+    for sp in (1, 0):
+        np.random.seed(7)
+        mdl = R.weights.SBMGaussianWeightDistribution(N, B=B, C=C, special_case_self_conns=bool(sp))
+        mdl.c = c.astype(int).copy(); mdl.m = m.copy()
+        for a in range(C):
+            for b in range(C):
+                mdl._gaussians[a][b].mu = mus[a, b].copy(); mdl._gaussians[a][b].sigma = sig[a, b].copy()
+        if sp:
+            mdl._self_gaussian.mu = mus[0, 1].copy(); mdl._self_gaussian.sigma = sig[1, 0].copy()
+        w_record("sbmw%d" % sp, mdl)
+    # B = 1: the only case in which the reference's sample_predictive_distribution runs
+    np.random.seed(8)
+    mdl = R.weights.SBMGaussianWeightDistribution(N, B=1, C=C, special_case_self_conns=True)
+    mdl.c = c.astype(int).copy(); mdl.m = m.copy()
+    for a in range(C):
+        for b in range(C):
+            mdl._gaussians[a][b].mu = mus[a, b, :1].copy(); mdl._gaussians[a][b].sigma = sig[a, b, :1, :1].copy()
+    mdl._self_gaussian.mu = mus[0, 1, :1].copy(); mdl._self_gaussian.sigma = sig[1, 0, :1, :1].copy()
+    np.random.seed(112)
+    wr, wc = mdl.sample_predictive_distribution()
+    out["sbmw_b1_Wrow"], out["sbmw_b1_Wcol"] = wr, wc
+    _save("ref_predictive.npz", out)
+
+
+# --------------------------------------------------------------------------------------------------
+# weights.py:501-901: shared-covariance SBM weights, latent-distance Gaussian weights
+# --------------------------------------------------------------------------------------------------
+def make_ref_latent_weights(R):
+    rng = np.random.RandomState(20250)
+    N, dim = 12, 2
+    np.random.seed(9)
+    mdl = R.weights.LatentDistanceGaussianWeightDistribution(N, B=1, dim=dim, b=-1.5, eta=0.8)
+    L0 = np.sqrt(0.8) * rng.randn(N, dim)
+    mdl.L = L0.copy()
+    mdl.cov.sigma = np.array([[0.6]])
+    mdl._self_gaussian.mu = np.array([0.4]); mdl._self_gaussian.sigma = np.array([[1.3]])
+    A = (rng.rand(N, N) < 0.6).astype(np.float64)
+    W = mdl.Mu + np.sqrt(0.6) * rng.randn(N, N, 1)
+    out = dict(A=A.astype(np.uint8), W=W, L=L0, b=-1.5, eta=0.8, sigma_w=0.6, self_mu=0.4, self_sigma=1.3)
+    Ls = [L0, L0 + 0.3 * rng.randn(N, dim), 0.1 * rng.randn(N, dim)]
+    bs = [-1.5, 0.7, 0.0]
+    lps, gLs, gbs = [], [], []
+    for Lq, bq in zip(Ls, bs):
+        lps.append(float(mdl._hmc_log_probability(Lq, bq, A, W)))
+        gLs.append(ref_shim._grad(lambda x: mdl._hmc_log_probability(x, bq, A, W))(Lq))
+        gbs.append(float(ref_shim._grad(lambda x: mdl._hmc_log_probability(Lq, x, A, W))(np.array(bq))))
+    out.update(eval_L=np.array(Ls), eval_b=np.array(bs), eval_lp=np.array(lps), eval_gL=np.array(gLs), eval_gb=np.array(gbs))
+    out["ll"] = mdl.log_likelihood((A, W)); out["log_prior"] = mdl.log_prior()
+    # _resample_L (:765-780) three times with the HMC draws injected, then _resample_b (:838-860) with np.random seeded
+    nsw = 3
+    pL = rng.randn(nsw, N, dim); lu = np.log(rng.rand(nsw))
+    REC.reset(); REC.hmc_draws = [(pL[s], lu[s]) for s in range(nsw)]
+    tr = []
+    for s in range(nsw):
+        mdl._resample_L(A, W)
+        tr.append(mdl.L.copy())
+    out.update(hmc_pL=pL, hmc_logu=lu, hmc_L=np.array(tr))
+    np.random.seed(123)
+    mdl._resample_b(A, W)
+    out["b_seed"] = 123; out["b_new"] = mdl.b
+    # _resample_cov (:863-867): the residuals handed to GaussianFixedMean.resample
+    mask = (~np.eye(N, dtype=bool)) & A.astype(bool)
+    resid = (W - mdl.Mu)[mask]
+    out["cov_n"] = resid.shape[0]; out["cov_S"] = float((resid ** 2).sum())
+    Mr, Mc, Lr, Lc = None, None, None, None
+    np.random.seed(321)
+    Mr, Mc, Lr, Lc = mdl.sample_predictive_parameters()
+    out.update(pred_seed=321, pred_Murow=Mr, pred_Mucol=Mc, pred_Lrow=Lr, pred_Lcol=Lc)
+    _save("ref_latent_weights.npz", out)
+
+
+def make_ref_shared_cov(R):
+    rng = np.random.RandomState(20251)
+    N, C, B = 13, 3, 2
+    A, W, c, m, p, mus, sig = _sbm_problem(rng, N, C, B)
+    out = dict(A=A.astype(np.uint8), W=W, c=c, m=m, mus=mus)
+    shared = _spd(rng, B)
+    out["shared"] = shared
+    for sp in (1, 0):
+        np.random.seed(7)
+        mdl = R.weights.SBMGaussianWeightSharedCov(N, B=B, C=C, special_case_self_conns=bool(sp))
+        mdl.c = c.astype(int).copy(); mdl.m = m.copy()
+        mdl._cov_model.sigma = shared.copy()
+        for a in range(C):
+            for b in range(C):
+                mdl._gaussians[a][b].mu = mus[a, b].copy(); mdl._gaussians[a][b].sigma = shared.copy()
+        out["ll_%d" % sp] = mdl.log_likelihood((A, W))
+        out["log_prior_%d" % sp] = mdl.log_prior()
+        with patched_numpy() as rec:
+            REC.reset()
+            np.random.seed(71 + sp)
+            mdl.resample_mu_and_Sig(A, W)
+        out["mvn_mean_%d" % sp] = np.array([q[0] for q in REC.mvn[:C * C]])
+        out["mvn_cov_%d" % sp] = np.array([q[1] for q in REC.mvn[:C * C]])
+        out["mus_new_%d" % sp] = np.array([[mdl._gaussians[a][b].mu for b in range(C)] for a in range(C)])
+        # what the covariance update saw: residuals of the off-diagonal edges around the new means
+        Aoff = A.astype(bool) & ~np.eye(N, dtype=bool)
+        resid = (W - mdl.Mu)[Aoff]
+        out["cov_n_%d" % sp] = resid.shape[0]; out["cov_S_%d" % sp] = resid.T.dot(resid)
+    _save("ref_shared_cov.npz", out)
+
+
 if __name__ == "__main__":
     R = ref_shim.load_reference()
-    which = sys.argv[1:] or ["sbm", "adjacency", "latent", "weights", "eigen", "ais", "mf_sbm", "mf_eigen"]
+    which = sys.argv[1:] or ["sbm", "adjacency", "latent", "weights", "eigen", "ais", "mf_sbm", "mf_eigen", "predictive", "latent_weights", "shared_cov"]
     for w in which:
         globals()["make_ref_" + w](R)

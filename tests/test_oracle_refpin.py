@@ -170,6 +170,31 @@ def test_latent_resample_chain_is_the_references():
         assert np.isclose(step, g["sweep_step"][s]) and np.isclose(rate, g["sweep_rate"][s])
 
 
+def test_latent_weight_lp_gradient_and_moves_are_the_references():
+    """weights.py:697-731 evaluated by the reference (gradients = complex step THROUGH its code), three _resample_L
+    transitions (:765-780) with injected draws, the b posterior (:838-860) and the residual statistics of :863-867."""
+    g = load("ref_latent_weights.npz")
+    A, W = g["A"].astype(float), g["W"][:, :, 0]
+    sw, eta = float(g["sigma_w"]), float(g["eta"])
+    for i in range(len(g["eval_lp"])):
+        lp, gL, gb = lt.weight_log_probability_and_grad(g["eval_L"][i], float(g["eval_b"][i]), A, W, sw, eta)
+        assert np.isclose(lp, g["eval_lp"][i], rtol=1e-12)
+        assert np.allclose(gL, g["eval_gL"][i], rtol=1e-9, atol=1e-10) and np.isclose(gb, g["eval_gb"][i], rtol=1e-9)
+    L = g["L"].copy()
+    for s in range(len(g["hmc_logu"])):
+        L = lt.weight_resample_L(L, float(g["b"]), A, W, sw, eta, (g["hmc_pL"][s], float(g["hmc_logu"][s])))
+        assert np.allclose(L, g["hmc_L"][s], rtol=1e-9, atol=1e-11), s
+    n, sr, srr = lt.weight_stats(L, float(g["b"]), A, W)
+    mean, var = lt.weight_b_posterior(n, sr + n * float(g["b"]), sw)
+    np.random.seed(int(g["b_seed"]))
+    b_new = mean + np.sqrt(var) * np.random.randn()
+    assert np.isclose(b_new, float(g["b_new"]), rtol=1e-12)
+    n2, sr2, srr2 = lt.weight_stats(L, b_new, A, W)
+    assert n2 == int(g["cov_n"]) and np.isclose(srr2, float(g["cov_S"]), rtol=1e-12)
+    d = b_new - float(g["b"])
+    assert np.isclose(srr - 2 * d * sr + n * d * d, srr2, rtol=1e-10)          # the identity the host class uses
+
+
 # ---------------------------------------------------------------------------------------------- eigenmodel Gibbs
 @pytest.mark.parametrize("given", [0, 1])
 def test_logistic_eigenmodel_sweep_is_the_references(given):
