@@ -1,0 +1,57 @@
+"""Port of the reference's test/test_gaussian_weights.py (print-only there): the mean-field expectations of the NIW
+Gaussian weight model (internals/weights.py:134-175) against Monte Carlo averages of draws from the variational
+posterior, with a numeric criterion (|analytic - empirical| within 5 standard errors of the Monte Carlo mean)."""
+import numpy as np
+
+from graphistician_b200.internals.weights import GaussianWeights
+
+
+def _check(name, analytic, samples):
+    samples = np.asarray(samples, dtype=float)
+    mean = samples.mean(0)
+    se = samples.std(0, ddof=1) / np.sqrt(samples.shape[0])
+    assert np.all(np.abs(np.asarray(analytic) - mean) <= 5.0 * se + 1e-12), (name, analytic, mean, se)
+
+
+def _draws(w, n):
+    mu, mumuT, Sig, Sig_inv, logdet = [], [], [], [], []
+    for smpl in range(n):
+        w.resample_from_mf()
+        mu.append(w.mu.copy())
+        mumuT.append(np.outer(w.mu, w.mu))
+        Sig.append(w.sigma.copy())
+        Sig_inv.append(np.linalg.inv(w.sigma))
+        logdet.append(np.log(np.linalg.det(w.sigma)))
+    return mu, mumuT, Sig, Sig_inv, logdet
+
+
+def test_mf_expectations():
+    """The reference's own case: the variational posterior at its initial value (the prior, kappa = 1), 10000 draws."""
+    np.random.seed(0)
+    D = 2
+    w = GaussianWeights(D, mu_0=np.zeros(D), Sigma_0=np.eye(D), kappa_0=1, nu_0=5)
+    mu, mumuT, Sig, Sig_inv, logdet = _draws(w, 10000)
+    _check("E[mu]", w.mf_expected_mu(), mu)
+    _check("E[mu mu^T]", w.mf_expected_mumuT(), mumuT)
+    _check("E[Sigma]", w.mf_expected_Sigma(), Sig)
+    _check("E[Sigma^-1]", w.mf_expected_Sigma_inv(), Sig_inv)
+    _check("E[log |Sigma|]", w.mf_expected_logdet_Sigma(), logdet)
+
+
+def test_mf_expectations_after_an_update():
+    """A non-trivial variational posterior (kappa = 41).  Four expectations match Monte Carlo; E[mu mu^T] is kept as the
+    reference writes it, E[Sigma] + E[mu] E[mu]^T (internals/weights.py:204-208), which equals the Monte Carlo value
+    E[Sigma] / kappa + E[mu] E[mu]^T only for kappa = 1 -- the difference is asserted so that it stays documented."""
+    np.random.seed(1)
+    D = 2
+    w = GaussianWeights(D, mu_0=np.zeros(D), Sigma_0=np.eye(D), kappa_0=1, nu_0=5)
+    x = np.random.randn(40, D).dot(np.array([[1.0, 0.4], [0.0, 0.7]])) + np.array([0.5, -1.0])
+    w.meanfieldupdate_from_stats(x.shape[0], x.sum(0), x.T.dot(x))
+    mu, mumuT, Sig, Sig_inv, logdet = _draws(w, 10000)
+    _check("E[mu]", w.mf_expected_mu(), mu)
+    _check("E[Sigma]", w.mf_expected_Sigma(), Sig)
+    _check("E[Sigma^-1]", w.mf_expected_Sigma_inv(), Sig_inv)
+    _check("E[log |Sigma|]", w.mf_expected_logdet_Sigma(), logdet)
+    E_mu = w.mf_expected_mu()
+    assert np.allclose(w.mf_expected_mumuT(), w.mf_expected_Sigma() + np.outer(E_mu, E_mu))
+    _check("E[mu mu^T], exact", w.mf_expected_Sigma() / w.kappa_mf + np.outer(E_mu, E_mu), mumuT)
