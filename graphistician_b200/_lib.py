@@ -54,6 +54,8 @@ SIGNATURES = {
     "gk_eig_tn_draw": (c_int, [c_vp, c_vp, ctypes.c_uint64, ctypes.POINTER(c_dbl)]),
     "gk_eig_set_Zsym": (c_int, [c_vp, c_vp, c_vp]),
     "gk_truncnorm_draw": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_sz]),
+    "gk_truncnorm_draw_static": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_sz]),
+    "gk_truncnorm_static_max": (c_sz, []),
     "gk_eig_sweep_begin": (c_int, [c_vp, c_vp, c_dbl, c_vp]),
     "gk_eig_acc_len": (c_sz, [c_vp]),
     "gk_eig_block_nodes": (c_int, [c_vp]),

@@ -351,6 +351,48 @@ extern "C" int gk_truncnorm_draw(gk_ctx *ctx, const double *mu, const uint8_t *e
     return GK_OK;
 }
 
+// The same map with NO allocation on the call path (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA-graph capture, tight serving loops).  The staging scratch that
+// gk_truncnorm_draw takes from the context's cudaMalloc'd slots lives in a file-scope device array instead; every GPU that
+// loads the library holds these GK_TN_STATIC_BYTES (1.6 MB) until exit.  Layout: mu | u | out (GK_TN_STATIC_MAX doubles each) | edge.
+// In HOST code `gk_tn_static` is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress, once per
+// device, with that device current.  All calls on a device share the array and it keeps the previous call's contents; nothing
+// in it has to start at zero (out[0, n) is fully overwritten before it is read back) -- but two calls that overlap on the
+// GPU (two contexts / streams of one device) race on it.
+#define GK_TN_STATIC_MAX 65536
+#define GK_TN_STATIC_BYTES ((size_t)GK_TN_STATIC_MAX * 25)
+static __device__ __align__(256) unsigned char gk_tn_static[GK_TN_STATIC_BYTES];
+#define GK_TN_MAX_DEVICES 64
+static void *gk_tn_static_ptr[GK_TN_MAX_DEVICES];      // per device: address of that device's copy of gk_tn_static
+
+extern "C" size_t gk_truncnorm_static_max(void) { return GK_TN_STATIC_MAX; }
+
+extern "C" int gk_truncnorm_draw_static(gk_ctx *ctx, const double *mu, const uint8_t *edge, const double *u, double *out, size_t n) {
+    if (!ctx || !mu || !edge || !u || !out) return GK_EINVAL;
+    if (n > GK_TN_STATIC_MAX)
+        return gk_fail(ctx, GK_EINVAL, "gk_truncnorm_draw_static: n=%zu exceeds the static scratch of %d entries (use gk_truncnorm_draw, which allocates)",
+                       n, GK_TN_STATIC_MAX);
+    if (n == 0) return GK_OK;
+    if (ctx->device < 0 || ctx->device >= GK_TN_MAX_DEVICES) return gk_fail(ctx, GK_EUNSUPPORTED, "device %d: static scratch is tracked for %d devices", ctx->device, GK_TN_MAX_DEVICES);
+    GK_CUDA(ctx, cudaSetDevice(ctx->device));
+    if (!gk_tn_static_ptr[ctx->device]) {                      // set-up, once per device, with that device current
+        void *p = nullptr;
+        GK_CUDA(ctx, cudaGetSymbolAddress(&p, gk_tn_static));
+        if (!p) return gk_fail(ctx, GK_ECUDA, "cudaGetSymbolAddress(gk_tn_static) returned a null address");
+        gk_tn_static_ptr[ctx->device] = p;
+    }
+    char *buf = (char *)gk_tn_static_ptr[ctx->device];
+    double *dmu = (double *)buf, *du = dmu + GK_TN_STATIC_MAX, *dout = du + GK_TN_STATIC_MAX; uint8_t *da = (uint8_t *)(dout + GK_TN_STATIC_MAX);
+    GK_CUDA(ctx, cudaMemcpyAsync(dmu, mu, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(du, u, n * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemcpyAsync(da, edge, n, cudaMemcpyHostToDevice, ctx->stream));
+    k_truncnorm<<<(int)std::min<size_t>((n + 255) / 256, (size_t)ctx->num_sms * 8), 256, 0, ctx->stream>>>(dmu, da, du, dout, n);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaMemcpyAsync(out, dout, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}
+
 // ---------------------------------------------------------------------------------------------
 // K4 + K5 (+ K6 statistics): the sequential feature sweep
 // ---------------------------------------------------------------------------------------------

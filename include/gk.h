@@ -150,6 +150,14 @@ int gk_eig_tn_draw(gk_ctx *ctx, gk_eig *eig, uint64_t seed, double *sum_z);
 int gk_eig_set_Zsym(gk_ctx *ctx, gk_eig *eig, const double *Zsym_rows);
 /* the truncated-normal map by itself, uniforms supplied: out[i] = sample_truncnorm(mu[i], lb/ub from edge[i]; u[i]) */
 int gk_truncnorm_draw(gk_ctx *ctx, const double *mu, const uint8_t *edge, const double *u, double *out, size_t n);
+/* No counterpart in the reference.  The same map as gk_truncnorm_draw for
+ * callers that cannot call cudaMalloc (CUDA-graph capture, tight serving loops): the staging scratch is a file-scope static
+ * device array, so the call allocates nothing (no cudaMalloc / cudaFree, no allocating library routine).  n is limited to
+ * gk_truncnorm_static_max() = 65536 entries (1.6 MB held by every GPU that loads the library, until exit); larger n is
+ * refused with GK_EINVAL and a message.  All calls on one device share the array, which keeps the previous call's
+ * contents (nothing in it needs clearing: out[0, n) is overwritten before it is read): calls that overlap on the GPU race. */
+int gk_truncnorm_draw_static(gk_ctx *ctx, const double *mu, const uint8_t *edge, const double *u, double *out, size_t n);
+size_t gk_truncnorm_static_max(void);
 /* K4+K5: replaces eigenmodel.py:876-908 (_resample_F), same serial semantics: node n is drawn from
  * N(prec_n^-1 h_n, prec_n^-1) given the NEW features of m < n and the OLD ones of m > n, with the fixed map
  * f = L^-T (L^-1 h + z), prec = L L^T, z = normals[n] (N x D standard normals supplied by the caller).
