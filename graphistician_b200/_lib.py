@@ -88,6 +88,17 @@ SIGNATURES = {
     "gk_mf_sbm_soft_stats": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp]),
     "gk_mf_sbm_update_c": (c_int, [c_vp, c_vp, c_vp, c_int, c_vp, c_vp, c_vp, c_vp, c_vp, c_dbl, c_int, c_vp]),
     "gk_latent_hmc_end": (c_int, [c_vp, c_vp, c_dbl, ctypes.POINTER(c_int), ctypes.POINTER(c_dbl)]),
+    "gk_ais_create": (c_int, [c_vp, c_int, c_int, c_int, ctypes.POINTER(c_vp)]),
+    "gk_ais_destroy": (c_int, [c_vp, c_vp]),
+    "gk_ais_device_bytes": (c_sz, [c_vp]),
+    "gk_ais_upload_rows": (c_int, [c_vp, c_vp, c_vp, c_int, c_int, c_int]),
+    "gk_ais_upload_network": (c_int, [c_vp, c_vp, c_vp]),
+    "gk_ais_nnz": (c_int, [c_vp, c_vp, PI64]),
+    "gk_ais_set_labels": (c_int, [c_vp, c_vp, c_vp, c_int]),
+    "gk_ais_get_labels": (c_int, [c_vp, c_vp, c_vp]),
+    "gk_ais_counts": (c_int, [c_vp, c_vp, c_int, c_vp, c_vp]),
+    "gk_ais_sweep": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_uint64, c_vp, c_vp]),
+    "gk_ais_run": (c_int, [c_vp, c_vp, c_int, c_dbl, c_dbl, c_vp, c_int, c_int, c_vp, ctypes.c_uint64, c_vp]),
 }
 
 _lib = None

@@ -1,0 +1,746 @@
+// gk_ais.cu -- AIS over bit-packed adjacency matrices, batched over particles.
+//
+// Replaces the body of the AIS driver loop of examples/demo_ais.py:10-62 for P co-resident particles:
+//   StochasticBlockModel.sample_theta   internals/graph_models.py:337-371  (tempered Beta / Dirichlet posteriors: the
+//                                       R x R edge counts per particle are kept current on the device)
+//   naive_sample_f for n = 0..N-1       internals/graph_models.py:261-297  (beta-weighted conditional, the diagonal entry
+//                                       counted in both directions, hips log_sum_exp_sample)
+//   log_lkhd                            internals/graph_models.py:42-48    (from the same R x R counts)
+//
+// Layout: A and A^T bit-packed, one row = nw 32-bit words (N padded to 1024 bits); per particle and class a bit mask of
+// the nodes carrying that label.  A node's class counts are then popc(row & mask): one row of A streamed once serves
+// every co-resident particle (k_ais_rowcnt), and the serial part of the sweep is one warp per particle (k_ais_seq)
+// which corrects the block-entry counts by the nodes of its own 1024-node block that have already moved.
+#include <math.h>
+#include <string.h>
+#include "gk_internal.cuh"
+
+#define AIS_NB 1024              // nodes per sequential block = 32 words: lane <-> word in k_ais_seq
+#define AIS_MAXR 8
+#define AIS_CW 512               // words of a row per column chunk of k_ais_rowcnt (16 per lane)
+#define AIS_QG 32                // mask rows (particle, class) per CTA of k_ais_rowcnt: lane q owns count q
+#define AIS_RW 4                 // rows per warp
+#define AIS_WARPS 8
+#define AIS_LOG0 (-1e10)         // log 0 of the conditional tables (as gk_sbm.cu: exp underflows to 0, 0 * finite = 0)
+
+struct gk_ais {
+    int N = 0, Npad = 0, nw = 0, P = 0, R = 0;
+    uint32_t *Ab = nullptr, *Atb = nullptr;   // Npad x nw
+    uint2 *deg = nullptr;                     // Npad: (out-degree, in-degree), diagonal included
+    uint32_t *mask = nullptr;                 // P x R x nw
+    uint8_t *z = nullptr;                     // P x Npad
+    uint32_t *cnt = nullptr;                  // P x AIS_NB x 2 x (R-1): block-entry class counts of the current node block
+    long long *cell = nullptr;                // P x R x R edge counts, diagonal included
+    long long *sz = nullptr;                  // P x R
+    long long *nchg = nullptr;                // P
+    double *tab = nullptr;                    // P x (1 + R + 2 R R): beta, log pi, log B, log(1-B)
+    double *u = nullptr;                      // P x Npad uniforms of the sweep: injected, or k_ais_uniforms (allocated on first use)
+    cudaStream_t s2 = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // second particle group
+    double *lp = nullptr;                     // P x N x R conditionals (allocated on first use)
+    bool packed = false, degrees = false, labelled = false;
+    uint32_t sweep = 0;
+    size_t bytes = 0;
+};
+
+// ---------------------------------------------------------------------------------------------------------------
+// packing
+// ---------------------------------------------------------------------------------------------------------------
+// rows [row0, row0+nrows) of a u8 matrix -> words of A's rows; one warp per (row, 32-column group) via ballot
+__global__ void k_ais_pack_rows(const uint8_t *__restrict__ src, size_t lds, int N, int nrows, int row0, uint32_t *__restrict__ Ab, int nw) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const long long nwarp = ((long long)gridDim.x * blockDim.x) >> 5;
+    const int wN = (N + 31) >> 5;
+    for (long long t = warp; t < (long long)nrows * wN; t += nwarp) {
+        const int r = (int)(t / wN), w = (int)(t % wN);
+        const int c = w * 32 + lane;
+        const unsigned bit = c < N ? (src[(size_t)r * lds + c] != 0) : 0u;
+        const unsigned word = __ballot_sync(0xffffffffu, bit);
+        if (lane == 0) Ab[(size_t)(row0 + r) * nw + w] = word;
+    }
+}
+// the same rows as bit COLUMNS of A^T: thread per column c, 32 source rows -> one word of At[c]
+__global__ void k_ais_pack_cols(const uint8_t *__restrict__ src, size_t lds, int N, int nrows, int row0, uint32_t *__restrict__ Atb, int nw) {
+    const int c = blockIdx.x * blockDim.x + threadIdx.x;
+    const int g = blockIdx.y;                                   // group of 32 source rows
+    if (c >= N) return;
+    unsigned word = 0;
+    for (int k = 0; k < 32; ++k) {
+        const int r = g * 32 + k;
+        if (r < nrows && src[(size_t)r * lds + c] != 0) word |= 1u << k;
+    }
+    Atb[(size_t)c * nw + (row0 >> 5) + g] = word;
+}
+__global__ void k_ais_degrees(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, int Npad, int nw, uint2 *__restrict__ deg) {
+    const int lane = threadIdx.x & 31;
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= Npad) return;
+    unsigned so = 0, si = 0;
+    for (int w = lane; w < nw; w += 32) { so += __popc(Ab[(size_t)row * nw + w]); si += __popc(Atb[(size_t)row * nw + w]); }
+    so = __reduce_add_sync(0xffffffffu, so); si = __reduce_add_sync(0xffffffffu, si);
+    if (lane == 0) deg[row] = make_uint2(so, si);
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// labels -> class masks and class sizes
+// ---------------------------------------------------------------------------------------------------------------
+__global__ void k_ais_masks(const uint8_t *__restrict__ z, int Npad, int nw, int N, int P, int R, uint32_t *__restrict__ mask) {
+    const int lane = threadIdx.x & 31;
+    const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (warp >= (long long)P * nw) return;
+    const int p = (int)(warp / nw), w = (int)(warp % nw);
+    const int n = w * 32 + lane;
+    const int lab = n < N ? z[(size_t)p * Npad + n] : 255;
+    for (int r = 0; r < R; ++r) {
+        const unsigned word = __ballot_sync(0xffffffffu, lab == r);
+        if (lane == 0) mask[((size_t)p * R + r) * nw + w] = word;
+    }
+}
+__global__ void k_ais_sizes(const uint32_t *__restrict__ mask, int nw, int PR, long long *__restrict__ sz) {
+    const int lane = threadIdx.x & 31;
+    const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    if (row >= PR) return;
+    unsigned s = 0;
+    for (int w = lane; w < nw; w += 32) s += __popc(mask[(size_t)row * nw + w]);
+    s = __reduce_add_sync(0xffffffffu, s);
+    if (lane == 0) sz[row] = s;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K2a: class counts of a block of rows for every (particle, class) mask:  cnt[dir][i][q] = popc(row_i & mask_q)
+// ---------------------------------------------------------------------------------------------------------------
+// carry-save adder: h:l = a + b + c bitwise
+#define AIS_CSA(h, l, a, b, c) { const uint32_t _u = (a) ^ (b); h = ((a) & (b)) | (_u & (c)); l = _u ^ (c); }
+
+// population count of sixteen words a[k] & m[k] with 5 POPC instead of 16 (Harley-Seal: 15 carry-save adders)
+__device__ __forceinline__ unsigned ais_popc16(const uint32_t *a, const uint4 m0, const uint4 m1, const uint4 m2, const uint4 m3) {
+    const uint32_t x0 = a[0] & m0.x, x1 = a[1] & m0.y, x2 = a[2] & m0.z, x3 = a[3] & m0.w;
+    const uint32_t x4 = a[4] & m1.x, x5 = a[5] & m1.y, x6 = a[6] & m1.z, x7 = a[7] & m1.w;
+    const uint32_t x8 = a[8] & m2.x, x9 = a[9] & m2.y, x10 = a[10] & m2.z, x11 = a[11] & m2.w;
+    const uint32_t x12 = a[12] & m3.x, x13 = a[13] & m3.y, x14 = a[14] & m3.z, x15 = a[15] & m3.w;
+    uint32_t ones, twos, fours, eights, sixteens, t0, t1, f0, f1, e0, e1;
+    AIS_CSA(t0, ones, x0, x1, x2);
+    AIS_CSA(t1, ones, ones, x3, x4);
+    AIS_CSA(f0, twos, t0, t1, 0u);
+    AIS_CSA(t0, ones, ones, x5, x6);
+    AIS_CSA(t1, ones, ones, x7, x8);
+    AIS_CSA(f1, twos, twos, t0, t1);
+    AIS_CSA(e0, fours, f0, f1, 0u);
+    AIS_CSA(t0, ones, ones, x9, x10);
+    AIS_CSA(t1, ones, ones, x11, x12);
+    AIS_CSA(f0, twos, twos, t0, t1);
+    AIS_CSA(t0, ones, ones, x13, x14);
+    AIS_CSA(t1, ones, ones, x15, 0u);
+    AIS_CSA(f1, twos, twos, t0, t1);
+    AIS_CSA(e1, fours, fours, f0, f1);
+    AIS_CSA(sixteens, eights, e0, e1, 0u);
+    return 16u * __popc(sixteens) + 8u * __popc(eights) + 4u * __popc(fours) + 2u * __popc(twos) + __popc(ones);
+}
+
+// grid (row tiles of AIS_WARPS*AIS_RW rows, mask groups of AIS_QG, 2 directions); dynamic shared memory AIS_QG*AIS_CW words
+__global__ void __launch_bounds__(AIS_WARPS * 32)
+k_ais_rowcnt(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, const uint32_t *__restrict__ mask, int nw, int R,
+             int n0, int qbeg, int Q, uint32_t *__restrict__ cnt) {
+    extern __shared__ uint4 s_m4[];                                   // [AIS_QG][AIS_CW/4]
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int q0 = qbeg + blockIdx.y * AIS_QG;
+    const uint32_t *bits = blockIdx.z ? Atb : Ab;
+    const int row_base = blockIdx.x * (AIS_WARPS * AIS_RW) + warp * AIS_RW;
+    unsigned acc[AIS_RW];
+#pragma unroll
+    for (int r = 0; r < AIS_RW; ++r) acc[r] = 0;
+    const int nq = min(AIS_QG, Q - q0);
+    for (int c0 = 0; c0 < nw; c0 += AIS_CW) {
+        __syncthreads();
+        // mask rows of this group: q -> (particle q / (R-1), class q % (R-1)) -> mask row p * R + r
+        for (int t = tid; t < AIS_QG * (AIS_CW / 4); t += AIS_WARPS * 32) {
+            const int q = t / (AIS_CW / 4), w4 = t % (AIS_CW / 4);
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (q < nq && c0 + w4 * 4 < nw) {
+                const int qq = q0 + q, p = qq / (R - 1), r = qq % (R - 1);
+                v = *reinterpret_cast<const uint4 *>(mask + ((size_t)p * R + r) * nw + c0 + w4 * 4);
+            }
+            s_m4[t] = v;
+        }
+        __syncthreads();
+#pragma unroll
+        for (int rr = 0; rr < AIS_RW; ++rr) {
+            const int i = row_base + rr;
+            uint32_t a[16];
+#pragma unroll
+            for (int k = 0; k < 4; ++k) {
+                const int w = c0 + k * 128 + lane * 4;
+                uint4 v = make_uint4(0, 0, 0, 0);
+                if (i < AIS_NB && w < nw) v = *reinterpret_cast<const uint4 *>(bits + (size_t)(n0 + i) * nw + w);
+                a[4 * k] = v.x; a[4 * k + 1] = v.y; a[4 * k + 2] = v.z; a[4 * k + 3] = v.w;
+            }
+            for (int q = 0; q < nq; ++q) {
+                const uint4 *m = s_m4 + q * (AIS_CW / 4) + lane;
+                unsigned s = ais_popc16(a, m[0], m[32], m[64], m[96]);
+                s = __reduce_add_sync(0xffffffffu, s);
+                if (lane == q) acc[rr] += s;
+            }
+        }
+    }
+#pragma unroll
+    for (int rr = 0; rr < AIS_RW; ++rr) {
+        const int i = row_base + rr;
+        if (i < AIS_NB && lane < nq) {          // cnt[particle][node][direction][class]: one contiguous record per (particle, node)
+            const int qq = q0 + lane, p = qq / (R - 1), r = qq % (R - 1);
+            cnt[(((size_t)p * AIS_NB + i) * 2 + blockIdx.z) * (R - 1) + r] = acc[rr];
+        }
+    }
+}
+
+// fold the out-direction counts of a block into the R x R cell table (set-up and the recompute check only)
+__global__ void k_ais_fold_cells(const uint32_t *__restrict__ cnt, const uint2 *__restrict__ deg, const uint8_t *__restrict__ z,
+                                 int Npad, int N, int n0, int R, long long *__restrict__ cell) {
+    const int p = blockIdx.x;
+    __shared__ unsigned long long s_cell[AIS_MAXR * AIS_MAXR];
+    for (int t = threadIdx.x; t < R * R; t += blockDim.x) s_cell[t] = 0;
+    __syncthreads();
+    for (int i = threadIdx.x; i < AIS_NB; i += blockDim.x) {
+        const int n = n0 + i;
+        if (n >= N) break;
+        const int a = z[(size_t)p * Npad + n];
+        unsigned rest = deg[n].x;
+        for (int r = 0; r < R - 1; ++r) {
+            const unsigned v = cnt[(((size_t)p * AIS_NB + i) * 2) * (R - 1) + r];
+            rest -= v;
+            if (v) atomicAdd(&s_cell[a * R + r], (unsigned long long)v);
+        }
+        if (rest) atomicAdd(&s_cell[a * R + R - 1], (unsigned long long)rest);
+    }
+    __syncthreads();
+    for (int t = threadIdx.x; t < R * R; t += blockDim.x) cell[(size_t)p * R * R + t] += (long long)s_cell[t];
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// K2b: the serial part.  One warp per particle walks the 1024 nodes of the block in index order.
+// ---------------------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint64_t ais_mix(uint64_t x) {
+    x += 0x9E3779B97F4A7C15ull; x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull; x = (x ^ (x >> 27)) * 0x94D049BB133111EBull;
+    return x ^ (x >> 31);
+}
+__device__ __forceinline__ double ais_uniform(uint64_t key, uint32_t n) {
+    return (double)(ais_mix(key + n) >> 11) * (1.0 / 9007199254740992.0);
+}
+
+// the sweep's uniforms, one per (particle, node), when the caller injects none
+__global__ void k_ais_uniforms(double *__restrict__ u, int P, int N, int Npad, uint64_t seed, uint32_t sweep) {
+    const long long t = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= (long long)P * Npad) return;
+    const int p = (int)(t / Npad), n = (int)(t % Npad);
+    const uint64_t key = ais_mix(ais_mix(seed ^ ((uint64_t)sweep << 32)) + (uint64_t)p * 0xD1B54A32D192ED03ull);
+    u[t] = n < N ? ais_uniform(key, (uint32_t)n) : 0.0;
+}
+
+struct AisSeqParams {
+    const uint32_t *Ab, *Atb, *cnt; const uint2 *deg;
+    uint32_t *mask; uint8_t *z;
+    long long *cell, *sz, *nchg;
+    const double *tab, *u; double *lp;
+    int N, Npad, nw, n0, p0;
+};
+
+template <int R> struct AisNode { uint32_t ao, ai, ce[2 * (R - 1)]; uint2 dg; int a; double u; };
+
+template <int R> struct AisCursor {                 // the six streams a particle's warp reads, advanced by one node per step
+    const uint32_t *ao, *ai, *ce; const uint2 *dg; const uint8_t *z; const double *u; size_t nw;
+    __device__ __forceinline__ void load(AisNode<R> &nd) {
+        nd.ao = *ao; nd.ai = *ai; nd.dg = *dg; nd.a = *z; nd.u = *u;
+        if (R == 3) { const uint4 v = *reinterpret_cast<const uint4 *>(ce); nd.ce[0] = v.x; nd.ce[1] = v.y; nd.ce[2] = v.z; nd.ce[3] = v.w; }
+        else {
+#pragma unroll
+            for (int r = 0; r < 2 * (R - 1); ++r) nd.ce[r] = ce[r];
+        }
+        ao += nw; ai += nw; ce += 2 * (R - 1); ++dg; ++z; ++u;
+    }
+};
+
+template <int R>
+__global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
+    const int p = P.p0 + blockIdx.x, lane = threadIdx.x;
+    constexpr int TS = 1 + R + 2 * R * R;
+    __shared__ double s_tab[TS];
+    __shared__ int s_cell[R * R];                    // change of the cell table over this block
+    for (int t = lane; t < TS; t += 32) s_tab[t] = P.tab[(size_t)p * TS + t];
+    for (int t = lane; t < R * R; t += 32) s_cell[t] = 0;
+    __syncwarp();
+    const double beta = s_tab[0];
+    const double *lpi = s_tab + 1, *lB = s_tab + 1 + R, *l1B = s_tab + 1 + R + R * R;
+    uint32_t E[R], C[R];
+    int sz[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        E[r] = P.mask[((size_t)p * R + r) * P.nw + (P.n0 >> 5) + lane];
+        C[r] = E[r];
+        sz[r] = (int)P.sz[p * R + r];
+    }
+    const int nb = min(AIS_NB, P.N - P.n0);
+    int nchg = 0;
+    AisCursor<R> cs;
+    cs.nw = (size_t)P.nw;
+    cs.ao = P.Ab + (size_t)P.n0 * P.nw + (P.n0 >> 5) + lane;
+    cs.ai = P.Atb + (size_t)P.n0 * P.nw + (P.n0 >> 5) + lane;
+    cs.ce = P.cnt + (size_t)p * AIS_NB * 2 * (R - 1);
+    cs.dg = P.deg + P.n0;
+    cs.z = P.z + (size_t)p * P.Npad + P.n0;
+    cs.u = P.u + (size_t)p * P.Npad + P.n0;
+    AisNode<R> cur, nxt, nx2;
+    cs.load(cur); cs.load(nxt); cs.load(nx2);        // rows beyond the block exist (Npad rows, cnt has a 3-record tail): harmless reads
+    for (int i = 0; i < nb; ++i) {
+        AisNode<R> nx3;
+        cs.load(nx3);
+        // counts of node n's out- and in-neighbours per class under the CURRENT labels: block-entry counts plus what the
+        // nodes of this block that already moved changed (nothing while no node of the block has moved: C == E)
+        int co[R], ci[R];
+        {
+            int so = 0, si = 0;
+#pragma unroll
+            for (int r = 0; r < R - 1; ++r) { co[r] = (int)cur.ce[r]; ci[r] = (int)cur.ce[R - 1 + r]; }
+            if (nchg) {
+#pragma unroll
+                for (int r = 0; r < R - 1; ++r) {
+                    const int d_o = __popc(cur.ao & C[r]) - __popc(cur.ao & E[r]) + 32;
+                    const int d_i = __popc(cur.ai & C[r]) - __popc(cur.ai & E[r]) + 32;
+                    const unsigned red = __reduce_add_sync(0xffffffffu, (unsigned)d_o | ((unsigned)d_i << 16));
+                    co[r] += (int)(red & 0xffffu) - 1024;
+                    ci[r] += (int)(red >> 16) - 1024;
+                }
+            }
+#pragma unroll
+            for (int r = 0; r < R - 1; ++r) { so += co[r]; si += ci[r]; }
+            co[R - 1] = (int)cur.dg.x - so;
+            ci[R - 1] = (int)cur.dg.y - si;
+        }
+        const int a = cur.a;
+        const int self = (__shfl_sync(0xffffffffu, cur.ao, i >> 5) >> (i & 31)) & 1;      // A[n, n]
+        // the node itself is excluded here and re-added, as candidate k, in both directions (internals/graph_models.py:275-293)
+        double dco[R], dci[R], dsz[R];
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            const int me = (r == a);
+            co[r] -= me & self; ci[r] -= me & self;
+            dco[r] = (double)co[r]; dci[r] = (double)ci[r]; dsz[r] = (double)(sz[r] - me);
+        }
+        double lp[R];
+        double mx = -1.7976931348623157e308;
+#pragma unroll
+        for (int k = 0; k < R; ++k) {
+            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                s0 = fma(dco[r], lB[k * R + r], s0);  s1 = fma(dsz[r] - dco[r], l1B[k * R + r], s1);
+                s2 = fma(dci[r], lB[r * R + k], s2);  s3 = fma(dsz[r] - dci[r], l1B[r * R + k], s3);
+            }
+            const double sf = 2.0 * (self ? lB[k * R + k] : l1B[k * R + k]);
+            lp[k] = lpi[k] + beta * (((s0 + s1) + (s2 + s3)) + sf);
+            mx = fmax(mx, lp[k]);
+        }
+        // hips log_sum_exp_sample: first index whose normalised cdf reaches u.  Decided in fp32 when u is clearly inside
+        // a cell of the cdf (error of the fp32 cdf < 1e-5 of its total), else by the fp64 arithmetic of the reference.
+        int b = 0;
+        {
+            float ef[R], totf = 0.f;
+#pragma unroll
+            for (int k = 0; k < R; ++k) { ef[k] = __expf((float)(lp[k] - mx)); totf += ef[k]; }
+            const float thr = (float)cur.u * totf, band = 1e-4f * totf;
+            float cumf = 0.f; bool sure = true;
+#pragma unroll
+            for (int k = 0; k < R - 1; ++k) { cumf += ef[k]; b += (cumf < thr); sure = sure && (fabsf(cumf - thr) > band); }
+            if (!sure) {
+                double e[R], tot = 0.0, cum = 0.0;
+#pragma unroll
+                for (int k = 0; k < R; ++k) { e[k] = exp(lp[k] - mx); tot += e[k]; }
+                b = 0;
+#pragma unroll
+                for (int k = 0; k < R; ++k) { cum += e[k] / tot; b += (cum < cur.u); }
+                b = min(b, R - 1);
+            }
+        }
+        if (P.lp && lane < R) {
+            double v = lp[0];
+#pragma unroll
+            for (int k = 1; k < R; ++k) if (lane == k) v = lp[k];
+            P.lp[((size_t)p * P.N + P.n0 + i) * R + lane] = v;
+        }
+        if (b != a) {
+            ++nchg;
+            const uint32_t bit = (lane == (i >> 5)) ? (1u << (i & 31)) : 0u;
+#pragma unroll
+            for (int r = 0; r < R; ++r) {
+                if (r == a) { C[r] &= ~bit; sz[r] -= 1; }
+                if (r == b) { C[r] |= bit; sz[r] += 1; }
+            }
+            if (lane == 0) {
+                P.z[(size_t)p * P.Npad + P.n0 + i] = (uint8_t)b;
+#pragma unroll
+                for (int r = 0; r < R; ++r) {
+                    s_cell[a * R + r] -= co[r]; s_cell[b * R + r] += co[r];          // edges n -> class r change their source class
+                    s_cell[r * R + a] -= ci[r]; s_cell[r * R + b] += ci[r];          // edges class r -> n change their target class
+                }
+                s_cell[a * R + a] -= self; s_cell[b * R + b] += self;
+            }
+        }
+        cur = nxt; nxt = nx2; nx2 = nx3;
+    }
+    __syncwarp();
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        P.mask[((size_t)p * R + r) * P.nw + (P.n0 >> 5) + lane] = C[r];
+        if (lane == 0) P.sz[p * R + r] = sz[r];
+    }
+    for (int t = lane; t < R * R; t += 32) P.cell[(size_t)p * R * R + t] += s_cell[t];
+    if (lane == 0) P.nchg[p] += nchg;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// host side
+// ---------------------------------------------------------------------------------------------------------------
+static int ais_check(gk_ctx *ctx, gk_ais *a) {
+    if (!ctx || !a) return GK_EINVAL;
+    cudaSetDevice(ctx->device);
+    return GK_OK;
+}
+
+extern "C" int gk_ais_create(gk_ctx *ctx, int N, int P, int R, gk_ais **out) {
+    if (!ctx || !out || N < 1 || P < 1) return GK_EINVAL;
+    *out = nullptr;
+    if (R < 1 || R > AIS_MAXR) return gk_fail(ctx, GK_EUNSUPPORTED, "gk_ais_create: R = %d outside 1..%d (template instantiations)", R, AIS_MAXR);
+    cudaSetDevice(ctx->device);
+    gk_ais *a = new gk_ais();
+    a->N = N; a->P = P; a->R = R;
+    a->Npad = (N + AIS_NB - 1) / AIS_NB * AIS_NB;
+    a->nw = a->Npad / 32;
+    const size_t bits = ((size_t)a->Npad + 4) * a->nw * 4;       // + 4 rows: the serial kernel's read-ahead
+    struct { void **p; size_t n; } allocs[] = {
+        {(void **)&a->Ab, bits}, {(void **)&a->Atb, bits}, {(void **)&a->deg, ((size_t)a->Npad + 4) * 8},
+        {(void **)&a->mask, (size_t)P * R * a->nw * 4}, {(void **)&a->z, (size_t)P * a->Npad + 4},
+        {(void **)&a->cnt, ((size_t)P * AIS_NB + 4) * 2 * (R > 1 ? R - 1 : 1) * 4},
+        {(void **)&a->u, ((size_t)P * a->Npad + 4) * 8}, {(void **)&a->cell, (size_t)P * R * R * 8},
+        {(void **)&a->sz, (size_t)P * R * 8}, {(void **)&a->nchg, (size_t)P * 8},
+        {(void **)&a->tab, (size_t)P * (1 + R + 2 * R * R) * 8}};
+    for (auto &al : allocs) {
+        if (cudaMalloc(al.p, al.n) != cudaSuccess) {
+            for (auto &f : allocs) if (*f.p) cudaFree(*f.p);
+            delete a;
+            return gk_fail(ctx, GK_ENOMEM, "gk_ais_create: cudaMalloc(%zu) failed", al.n);
+        }
+        cudaMemsetAsync(*al.p, 0, al.n, ctx->stream);
+        a->bytes += al.n;
+    }
+    if (cudaStreamCreateWithFlags(&a->s2, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaEventCreateWithFlags(&a->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
+        cudaEventCreateWithFlags(&a->ev_join, cudaEventDisableTiming) != cudaSuccess)
+        return gk_fail(ctx, GK_ECUDA, "gk_ais_create: stream / event creation failed");
+    *out = a;
+    return GK_OK;
+}
+
+extern "C" int gk_ais_destroy(gk_ctx *ctx, gk_ais *a) {
+    if (ais_check(ctx, a)) return GK_EINVAL;
+    cudaStreamSynchronize(ctx->stream);
+    if (a->s2) { cudaStreamSynchronize(a->s2); cudaStreamDestroy(a->s2); }
+    if (a->ev_fork) cudaEventDestroy(a->ev_fork);
+    if (a->ev_join) cudaEventDestroy(a->ev_join);
+    void *ptrs[] = {a->Ab, a->Atb, a->deg, a->mask, a->z, a->cnt, a->cell, a->sz, a->nchg, a->tab, a->u, a->lp};
+    for (void *p : ptrs) if (p) cudaFree(p);
+    delete a;
+    return GK_OK;
+}
+
+extern "C" size_t gk_ais_device_bytes(gk_ais *a) { return a ? a->bytes : 0; }
+
+static int ais_pack(gk_ctx *ctx, gk_ais *a, const uint8_t *src, size_t lds, int row0, int nrows) {
+    k_ais_pack_rows<<<ctx->num_sms * 8, 256, 0, ctx->stream>>>(src, lds, a->N, nrows, row0, a->Ab, a->nw);
+    GK_CHECK_LAUNCH(ctx);
+    dim3 g((a->N + 255) / 256, (nrows + 31) / 32);
+    k_ais_pack_cols<<<g, 256, 0, ctx->stream>>>(src, lds, a->N, nrows, row0, a->Atb, a->nw);
+    GK_CHECK_LAUNCH(ctx);
+    a->packed = true; a->degrees = false;
+    return GK_OK;
+}
+
+extern "C" int gk_ais_upload_rows(gk_ctx *ctx, gk_ais *a, const uint8_t *A_rows, int row0, int nrows, int src_on_device) {
+    if (ais_check(ctx, a) || !A_rows) return GK_EINVAL;
+    if (row0 < 0 || nrows < 1 || row0 + nrows > a->N || (row0 & 31))
+        return gk_fail(ctx, GK_EINVAL, "gk_ais_upload_rows: rows [%d, %d) must lie in [0, N) and start on a multiple of 32", row0, row0 + nrows);
+    const uint8_t *src = A_rows;
+    if (!src_on_device) {
+        void *tmp = gk_scratch(ctx, 0, (size_t)nrows * a->N);
+        if (!tmp) return GK_ENOMEM;
+        GK_CUDA(ctx, cudaMemcpyAsync(tmp, A_rows, (size_t)nrows * a->N, cudaMemcpyHostToDevice, ctx->stream));
+        src = (const uint8_t *)tmp;
+    }
+    int rc = ais_pack(ctx, a, src, (size_t)a->N, row0, nrows);
+    if (rc) return rc;
+    if (!src_on_device) GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));     // the caller may reuse its buffer
+    return GK_OK;
+}
+
+extern "C" int gk_ais_upload_network(gk_ctx *ctx, gk_ais *a, gk_net *net) {
+    if (ais_check(ctx, a) || !net) return GK_EINVAL;
+    if (net->N != a->N || net->row0 != 0 || net->nrows != net->N)
+        return gk_fail(ctx, GK_EINVAL, "gk_ais_upload_network: needs an unsharded network of the same N");
+    return ais_pack(ctx, a, net->A, (size_t)net->ld, 0, a->N);
+}
+
+static int ais_degrees(gk_ctx *ctx, gk_ais *a) {
+    if (a->degrees) return GK_OK;
+    if (!a->packed) return gk_fail(ctx, GK_EINVAL, "gk_ais: no adjacency rows uploaded yet");
+    k_ais_degrees<<<(a->Npad * 32 + 255) / 256, 256, 0, ctx->stream>>>(a->Ab, a->Atb, a->Npad, a->nw, a->deg);
+    GK_CHECK_LAUNCH(ctx);
+    a->degrees = true;
+    return GK_OK;
+}
+
+extern "C" int gk_ais_nnz(gk_ctx *ctx, gk_ais *a, int64_t *nnz) {
+    if (ais_check(ctx, a) || !nnz) return GK_EINVAL;
+    int rc = ais_degrees(ctx, a); if (rc) return rc;
+    std::vector<uint2> d(a->Npad);
+    GK_CUDA(ctx, cudaMemcpyAsync(d.data(), a->deg, (size_t)a->Npad * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    int64_t s = 0; for (const uint2 &v : d) s += v.x;
+    *nnz = s;
+    return GK_OK;
+}
+
+// block-entry counts of node block n0 for the particles [p0, p1), on `st`
+static int ais_rowcnt(gk_ctx *ctx, gk_ais *a, int n0, int p0, int p1, cudaStream_t st) {
+    const int qbeg = p0 * (a->R - 1), Q = p1 * (a->R - 1);
+    if (Q == qbeg) return GK_OK;
+    const size_t sm = (size_t)AIS_QG * AIS_CW * 4;
+    if (gk_attr_needed(ctx, (const void *)k_ais_rowcnt))
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_ais_rowcnt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    dim3 g(AIS_NB / (AIS_WARPS * AIS_RW), (Q - qbeg + AIS_QG - 1) / AIS_QG, 2);
+    const bool timed = st == ctx->stream;
+    if (timed) gk_time_begin(ctx, 0, 2.0 * AIS_NB * a->nw * 4.0);
+    k_ais_rowcnt<<<g, AIS_WARPS * 32, sm, st>>>(a->Ab, a->Atb, a->mask, a->nw, a->R, n0, qbeg, Q, a->cnt);
+    if (timed) gk_time_end(ctx, 0);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
+// cell table and class sizes of the current labels from scratch
+static int ais_recount(gk_ctx *ctx, gk_ais *a) {
+    int rc = ais_degrees(ctx, a); if (rc) return rc;
+    const int PR = a->P * a->R;
+    k_ais_sizes<<<(PR * 32 + 255) / 256, 256, 0, ctx->stream>>>(a->mask, a->nw, PR, a->sz);
+    GK_CHECK_LAUNCH(ctx);
+    GK_CUDA(ctx, cudaMemsetAsync(a->cell, 0, (size_t)a->P * a->R * a->R * 8, ctx->stream));
+    for (int n0 = 0; n0 < a->N; n0 += AIS_NB) {
+        if ((rc = ais_rowcnt(ctx, a, n0, 0, a->P, ctx->stream))) return rc;
+        k_ais_fold_cells<<<a->P, 256, 0, ctx->stream>>>(a->cnt, a->deg, a->z, a->Npad, a->N, n0, a->R, a->cell);
+        GK_CHECK_LAUNCH(ctx);
+    }
+    return GK_OK;
+}
+
+extern "C" int gk_ais_set_labels(gk_ctx *ctx, gk_ais *a, const int32_t *z, int broadcast) {
+    if (ais_check(ctx, a) || !z) return GK_EINVAL;
+    const int np = broadcast ? 1 : a->P;
+    std::vector<uint8_t> h((size_t)a->P * a->Npad, 0);
+    for (int p = 0; p < a->P; ++p)
+        for (int n = 0; n < a->N; ++n) {
+            const int v = z[(size_t)(p % np) * a->N + n];
+            if (v < 0 || v >= a->R) return gk_fail(ctx, GK_EINVAL, "gk_ais_set_labels: label %d of node %d outside [0, %d)", v, n, a->R);
+            h[(size_t)p * a->Npad + n] = (uint8_t)v;
+        }
+    GK_CUDA(ctx, cudaMemcpyAsync(a->z, h.data(), h.size(), cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    const long long warps = (long long)a->P * a->nw;
+    k_ais_masks<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, ctx->stream>>>(a->z, a->Npad, a->nw, a->N, a->P, a->R, a->mask);
+    GK_CHECK_LAUNCH(ctx);
+    a->labelled = true;
+    return ais_recount(ctx, a);
+}
+
+extern "C" int gk_ais_get_labels(gk_ctx *ctx, gk_ais *a, int32_t *z) {
+    if (ais_check(ctx, a) || !z) return GK_EINVAL;
+    std::vector<uint8_t> h((size_t)a->P * a->Npad);
+    GK_CUDA(ctx, cudaMemcpyAsync(h.data(), a->z, h.size(), cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    for (int p = 0; p < a->P; ++p)
+        for (int n = 0; n < a->N; ++n) z[(size_t)p * a->N + n] = h[(size_t)p * a->Npad + n];
+    return GK_OK;
+}
+
+extern "C" int gk_ais_counts(gk_ctx *ctx, gk_ais *a, int recompute, int64_t *n_edge, int64_t *sizes) {
+    if (ais_check(ctx, a)) return GK_EINVAL;
+    if (!a->labelled) return gk_fail(ctx, GK_EINVAL, "gk_ais_counts: call gk_ais_set_labels first");
+    if (recompute) { int rc = ais_recount(ctx, a); if (rc) return rc; }
+    if (n_edge) GK_CUDA(ctx, cudaMemcpyAsync(n_edge, a->cell, (size_t)a->P * a->R * a->R * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (sizes) GK_CUDA(ctx, cudaMemcpyAsync(sizes, a->sz, (size_t)a->P * a->R * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}
+
+template <int R> static void ais_launch_seq(int np, cudaStream_t st, const AisSeqParams &prm) {
+    k_ais_seq<R><<<np, 32, 0, st>>>(prm);
+}
+
+// One sweep.  The particles are split in two groups on two streams so that one group's serial kernel (one warp per
+// particle) runs beside the other group's counting pass (which fills the rest of the machine).
+static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool inject, uint64_t seed, bool want_lp) {
+    const int R = a->R;
+    int rc = ais_degrees(ctx, a); if (rc) return rc;
+    GK_CUDA(ctx, cudaMemcpyAsync(a->tab, tab_host, (size_t)a->P * (1 + R + 2 * R * R) * 8, cudaMemcpyHostToDevice, ctx->stream));
+    GK_CUDA(ctx, cudaMemsetAsync(a->nchg, 0, (size_t)a->P * 8, ctx->stream));
+    a->sweep++;
+    if (R == 1) return GK_OK;
+    if (!inject) {
+        const long long tot = (long long)a->P * a->Npad;
+        k_ais_uniforms<<<(unsigned)((tot + 255) / 256), 256, 0, ctx->stream>>>(a->u, a->P, a->N, a->Npad, seed, a->sweep);
+        GK_CHECK_LAUNCH(ctx);
+    }
+    AisSeqParams prm;
+    prm.Ab = a->Ab; prm.Atb = a->Atb; prm.deg = a->deg; prm.cnt = a->cnt; prm.mask = a->mask; prm.z = a->z;
+    prm.cell = a->cell; prm.sz = a->sz; prm.nchg = a->nchg; prm.tab = a->tab; prm.u = a->u;
+    prm.lp = want_lp ? a->lp : nullptr;
+    prm.N = a->N; prm.Npad = a->Npad; prm.nw = a->nw;
+    const int ngroups = (a->P >= 16 && !ctx->timing) ? 2 : 1;          // kernel timing brackets need one stream
+    const int split = ngroups == 2 ? (a->P + 1) / 2 : a->P;
+    if (ngroups == 2) {
+        GK_CUDA(ctx, cudaEventRecord(a->ev_fork, ctx->stream));
+        GK_CUDA(ctx, cudaStreamWaitEvent(a->s2, a->ev_fork, 0));
+    }
+    for (int n0 = 0; n0 < a->N; n0 += AIS_NB) {
+        prm.n0 = n0;
+        for (int g = 0; g < ngroups; ++g) {
+            const int p0 = g ? split : 0, p1 = g ? a->P : split;
+            cudaStream_t st = g ? a->s2 : ctx->stream;
+            if ((rc = ais_rowcnt(ctx, a, n0, p0, p1, st))) return rc;
+            prm.p0 = p0;
+            if (!g) gk_time_begin(ctx, 1, 0.0);
+            switch (R) {
+                case 2: ais_launch_seq<2>(p1 - p0, st, prm); break;
+                case 3: ais_launch_seq<3>(p1 - p0, st, prm); break;
+                case 4: ais_launch_seq<4>(p1 - p0, st, prm); break;
+                case 5: ais_launch_seq<5>(p1 - p0, st, prm); break;
+                case 6: ais_launch_seq<6>(p1 - p0, st, prm); break;
+                case 7: ais_launch_seq<7>(p1 - p0, st, prm); break;
+                default: ais_launch_seq<8>(p1 - p0, st, prm); break;
+            }
+            if (!g) gk_time_end(ctx, 1);
+            GK_CHECK_LAUNCH(ctx);
+        }
+    }
+    if (ngroups == 2) {
+        GK_CUDA(ctx, cudaEventRecord(a->ev_join, a->s2));
+        GK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, a->ev_join, 0));
+    }
+    return GK_OK;
+}
+
+static inline double ais_log(double x) { return x > 0.0 ? fmax(log(x), AIS_LOG0) : AIS_LOG0; }
+
+// tab[p] = (beta, log pi[R], log B[R x R], log(1 - B)[R x R])
+static void ais_fill_tab(double *tab, int R, double beta, const double *log_pi, const double *B) {
+    tab[0] = beta;
+    for (int r = 0; r < R; ++r) tab[1 + r] = log_pi[r];
+    for (int t = 0; t < R * R; ++t) { tab[1 + R + t] = ais_log(B[t]); tab[1 + R + R * R + t] = ais_log(1.0 - B[t]); }
+}
+
+extern "C" int gk_ais_sweep(gk_ctx *ctx, gk_ais *a, const double *log_pi, const double *B, const double *beta,
+                            const double *uniforms, uint64_t seed, double *out_lp, int64_t *out_nchanged) {
+    if (ais_check(ctx, a) || !log_pi || !B || !beta) return GK_EINVAL;
+    if (!a->labelled) return gk_fail(ctx, GK_EINVAL, "gk_ais_sweep: call gk_ais_set_labels first");
+    const int R = a->R, TS = 1 + R + 2 * R * R;
+    std::vector<double> tab((size_t)a->P * TS);
+    for (int p = 0; p < a->P; ++p) ais_fill_tab(&tab[(size_t)p * TS], R, beta[p], log_pi + (size_t)p * R, B + (size_t)p * R * R);
+    if (uniforms) {
+        GK_CUDA(ctx, cudaMemcpy2DAsync(a->u, (size_t)a->Npad * 8, uniforms, (size_t)a->N * 8, (size_t)a->N * 8, a->P,
+                                       cudaMemcpyHostToDevice, ctx->stream));
+    }
+    if (out_lp && !a->lp) { GK_CUDA(ctx, cudaMalloc(&a->lp, (size_t)a->P * a->N * R * 8)); a->bytes += (size_t)a->P * a->N * R * 8; }
+    int rc = ais_sweep_device(ctx, a, tab.data(), uniforms != nullptr, seed, out_lp != nullptr);
+    if (rc) return rc;
+    if (out_lp) GK_CUDA(ctx, cudaMemcpyAsync(out_lp, a->lp, (size_t)a->P * a->N * R * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out_nchanged) GK_CUDA(ctx, cudaMemcpyAsync(out_nchanged, a->nchg, (size_t)a->P * 8, cudaMemcpyDeviceToHost, ctx->stream));
+    GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    return GK_OK;
+}
+
+// ---- host random numbers of gk_ais_run (xoshiro256**, Marsaglia-Tsang gamma) ----------------------------------------
+struct AisRng {
+    uint64_t s[4];
+    explicit AisRng(uint64_t seed) { for (auto &v : s) { seed += 0x9E3779B97F4A7C15ull; uint64_t x = seed; x = (x ^ (x >> 30)) * 0xBF58476D1CE4E5B9ull; x = (x ^ (x >> 27)) * 0x94D049BB133111EBull; v = x ^ (x >> 31); } }
+    static uint64_t rotl(uint64_t x, int k) { return (x << k) | (x >> (64 - k)); }
+    uint64_t next() { const uint64_t r = rotl(s[1] * 5, 7) * 9, t = s[1] << 17; s[2] ^= s[0]; s[3] ^= s[1]; s[1] ^= s[2]; s[0] ^= s[3]; s[2] ^= t; s[3] = rotl(s[3], 45); return r; }
+    double uniform() { return ((double)(next() >> 11) + 0.5) * (1.0 / 9007199254740992.0); }
+    double normal() { const double u1 = uniform(), u2 = uniform(); return sqrt(-2.0 * log(u1)) * cos(6.283185307179586 * u2); }
+    double gamma(double k) {
+        if (k < 1.0) return gamma(k + 1.0) * pow(uniform(), 1.0 / k);
+        const double d = k - 1.0 / 3.0, c = 1.0 / sqrt(9.0 * d);
+        for (;;) {
+            double x, v;
+            do { x = normal(); v = 1.0 + c * x; } while (v <= 0.0);
+            v = v * v * v;
+            const double u = uniform();
+            if (u < 1.0 - 0.0331 * x * x * x * x || log(u) < 0.5 * x * x + d * (1.0 - v + log(v))) return d * v;
+        }
+    }
+    double beta(double a, double b) { const double x = gamma(a), y = gamma(b); return x / (x + y); }
+};
+
+extern "C" int gk_ais_run(gk_ctx *ctx, gk_ais *a, int model, double b0, double b1, const double *alpha0, int n_temps,
+                          int steps_per_temp, const int32_t *f0, uint64_t seed, double *log_weights) {
+    if (ais_check(ctx, a) || !log_weights || n_temps < 2 || steps_per_temp < 1) return GK_EINVAL;
+    if (model != GK_AIS_ER && model != GK_AIS_SBM) return gk_fail(ctx, GK_EINVAL, "gk_ais_run: model %d", model);
+    const int P = a->P, R = a->R, TS = 1 + R + 2 * R * R;
+    AisRng rng(seed);
+    for (int p = 0; p < P; ++p) log_weights[p] = 0.0;
+    const double NN = (double)a->N * (double)a->N;
+    if (model == GK_AIS_ER) {
+        // internals/graph_models.py:168-182: rho ~ Beta(a + beta nnz, b + beta (N^2 - nnz)); no features
+        int64_t nnz = 0;
+        int rc = gk_ais_nnz(ctx, a, &nnz); if (rc) return rc;
+        for (int p = 0; p < P; ++p)
+            for (int b = 1; b < n_temps; ++b) {
+                const double beta = (double)b / (n_temps - 1), prev = (double)(b - 1) / (n_temps - 1);
+                double rho = 0.5;
+                for (int s = 0; s < steps_per_temp; ++s) rho = rng.beta(b1 + beta * nnz, b0 + beta * (NN - nnz));
+                log_weights[p] += (beta - prev) * (nnz * ais_log(rho) + (NN - nnz) * ais_log(1.0 - rho));
+            }
+        return GK_OK;
+    }
+    if (!alpha0 || !f0) return GK_EINVAL;
+    int rc = gk_ais_set_labels(ctx, a, f0, 1); if (rc) return rc;
+    std::vector<int64_t> cell((size_t)P * R * R), sz((size_t)P * R);
+    std::vector<double> tab((size_t)P * TS), Bm((size_t)P * R * R), lpi((size_t)P * R);
+    if ((rc = gk_ais_counts(ctx, a, 0, cell.data(), sz.data()))) return rc;
+    for (int b = 1; b < n_temps; ++b) {
+        const double beta = (double)b / (n_temps - 1), prev = (double)(b - 1) / (n_temps - 1);
+        for (int s = 0; s < steps_per_temp; ++s) {
+            // sample_theta (internals/graph_models.py:337-371): pi ~ Dir(alpha0 + sizes), untempered;
+            // B[r1, r2] ~ Beta(b1 + beta edges, b0 + beta non-edges), stored as float32 (:353)
+            for (int p = 0; p < P; ++p) {
+                double tot = 0.0;
+                for (int r = 0; r < R; ++r) { lpi[p * R + r] = rng.gamma(alpha0[r] + (double)sz[p * R + r]); tot += lpi[p * R + r]; }
+                for (int r = 0; r < R; ++r) lpi[p * R + r] = ais_log(lpi[p * R + r] / tot);
+                for (int r1 = 0; r1 < R; ++r1)
+                    for (int r2 = 0; r2 < R; ++r2) {
+                        const double e = (double)cell[(p * R + r1) * R + r2], np = (double)sz[p * R + r1] * (double)sz[p * R + r2];
+                        Bm[(p * R + r1) * R + r2] = (double)(float)rng.beta(b1 + beta * e, b0 + beta * (np - e));
+                    }
+                ais_fill_tab(&tab[(size_t)p * TS], R, beta, &lpi[p * R], &Bm[(size_t)p * R * R]);
+            }
+            if ((rc = ais_sweep_device(ctx, a, tab.data(), false, seed, false))) return rc;
+            if ((rc = gk_ais_counts(ctx, a, 0, cell.data(), sz.data()))) return rc;
+        }
+        // logpr(beta_b) - logpr(beta_{b-1}) at the same (f, theta): (beta_b - beta_{b-1}) log_lkhd (demo_ais.py:49-52)
+        for (int p = 0; p < P; ++p) {
+            double ll = 0.0;
+            for (int r1 = 0; r1 < R; ++r1)
+                for (int r2 = 0; r2 < R; ++r2) {
+                    const double e = (double)cell[(p * R + r1) * R + r2], np = (double)sz[p * R + r1] * (double)sz[p * R + r2];
+                    const double Bv = Bm[(p * R + r1) * R + r2];
+                    if (e > 0) ll += e * ais_log(Bv);
+                    if (np - e > 0) ll += (np - e) * ais_log(1.0 - Bv);
+                }
+            log_weights[p] += (beta - prev) * ll;
+        }
+    }
+    return GK_OK;
+}

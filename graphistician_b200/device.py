@@ -443,3 +443,96 @@ def truncnorm_draw(mu, edge, u, ctx=None):
     out = np.empty_like(mu)
     ctx.check(ctx.lib.gk_truncnorm_draw(ctx.h, ptr(mu), ptr(e8), ptr(uu), ptr(out), mu.size))
     return out
+
+
+class DeviceAIS:
+    """P co-resident AIS particles over one bit-packed adjacency matrix: the device side of
+    ``internals.graph_models.estimate_marginal_likelihood_batched`` (examples/demo_ais.py:10-62, internals/graph_models.py
+    :261-297, 337-371).  A: N x N {0,1} host array, an unsharded DeviceNetwork, or None (rows are then supplied with
+    ``upload_rows``, host arrays or device pointers)."""
+
+    def __init__(self, A, P, R, ctx=None, N=None):
+        self.ctx = ctx or _lib.default_context()
+        if isinstance(A, DeviceNetwork):
+            self.N = A.N
+        elif A is not None:
+            A = _as_u8(A)
+            self.N = int(A.shape[0])
+            assert A.shape == (self.N, self.N)
+        else:
+            self.N = int(N)
+        self.P, self.R = int(P), int(R)
+        h = ctypes.c_void_p()
+        self.ctx.check(self.ctx.lib.gk_ais_create(self.ctx.h, self.N, self.P, self.R, ctypes.byref(h)))
+        self.h = h
+        self._finalizer = weakref.finalize(self, _destroy_ais, self.ctx, h)
+        if isinstance(A, DeviceNetwork):
+            self.ctx.check(self.ctx.lib.gk_ais_upload_network(self.ctx.h, self.h, A.h))
+        elif A is not None:
+            step = max(32, (1 << 28) // self.N // 32 * 32)              # <= 256 MB of rows per staging copy
+            for r0 in range(0, self.N, step):
+                self.upload_rows(A[r0:r0 + step], r0)
+
+    def upload_rows(self, rows, row0, device_ptr=None, nrows=None):
+        """rows [row0, row0 + nrows) of A as a host uint8 array, or ``device_ptr`` (int) to nrows x N uint8 on the device."""
+        if device_ptr is not None:
+            self.ctx.check(self.ctx.lib.gk_ais_upload_rows(self.ctx.h, self.h, ctypes.c_void_p(device_ptr), int(row0), int(nrows), 1))
+            return
+        r8 = _as_u8(rows)
+        self.ctx.check(self.ctx.lib.gk_ais_upload_rows(self.ctx.h, self.h, ptr(r8), int(row0), int(r8.shape[0]), 0))
+
+    def device_bytes(self):
+        return int(self.ctx.lib.gk_ais_device_bytes(self.h))
+
+    def nnz(self):
+        v = ctypes.c_int64()
+        self.ctx.check(self.ctx.lib.gk_ais_nnz(self.ctx.h, self.h, ctypes.byref(v)))
+        return int(v.value)
+
+    def set_labels(self, z):
+        z32 = np.ascontiguousarray(z, dtype=np.int32)
+        assert z32.shape in ((self.N,), (self.P, self.N))
+        self.ctx.check(self.ctx.lib.gk_ais_set_labels(self.ctx.h, self.h, ptr(z32), int(z32.ndim == 1)))
+
+    def get_labels(self):
+        z = np.zeros((self.P, self.N), np.int32)
+        self.ctx.check(self.ctx.lib.gk_ais_get_labels(self.ctx.h, self.h, ptr(z)))
+        return z
+
+    def counts(self, recompute=False):
+        """(n_edge[P, R, R], sizes[P, R]) as int64, diagonal included."""
+        n_edge = np.zeros((self.P, self.R, self.R), np.int64)
+        sizes = np.zeros((self.P, self.R), np.int64)
+        self.ctx.check(self.ctx.lib.gk_ais_counts(self.ctx.h, self.h, int(recompute), ptr(n_edge), ptr(sizes)))
+        return n_edge, sizes
+
+    def sweep(self, log_pi, B, beta, uniforms=None, seed=0, want_lp=False):
+        """One exact sequential feature sweep of every particle.  Returns (n_changed[P], lp[P, N, R] or None)."""
+        P, R = self.P, self.R
+        lpi = np.ascontiguousarray(np.broadcast_to(np.asarray(log_pi, np.float64), (P, R)))
+        Bm = np.ascontiguousarray(np.broadcast_to(np.asarray(B, np.float64), (P, R, R)))
+        bt = np.ascontiguousarray(np.broadcast_to(np.asarray(beta, np.float64), (P,)))
+        u = None if uniforms is None else np.ascontiguousarray(uniforms, dtype=np.float64)
+        assert u is None or u.shape == (P, self.N)
+        lp = np.zeros((P, self.N, R)) if want_lp else None
+        nchg = np.zeros(P, np.int64)
+        self.ctx.check(self.ctx.lib.gk_ais_sweep(self.ctx.h, self.h, ptr(lpi), ptr(Bm), ptr(bt), ptr(u),
+                                                 ctypes.c_uint64(int(seed) & (2 ** 64 - 1)), ptr(lp), ptr(nchg)))
+        return nchg, lp
+
+    def run(self, model, b0, b1, alpha0, n_temps, steps_per_temp, f0=None, seed=0):
+        """gk_ais_run: the whole AIS ladder for the P particles; returns log_weights[P]."""
+        w = np.zeros(self.P)
+        a0 = None if alpha0 is None else np.ascontiguousarray(alpha0, dtype=np.float64)
+        f32 = None if f0 is None else np.ascontiguousarray(f0, dtype=np.int32)
+        self.ctx.check(self.ctx.lib.gk_ais_run(self.ctx.h, self.h, int(model), float(b0), float(b1), ptr(a0), int(n_temps),
+                                               int(steps_per_temp), ptr(f32), ctypes.c_uint64(int(seed) & (2 ** 64 - 1)), ptr(w)))
+        return w
+
+    def close(self):
+        self._finalizer()
+
+
+def _destroy_ais(ctx, h):
+    if getattr(ctx, "h", None):
+        ctx.lib.gk_ais_destroy(ctx.h, h)

@@ -328,3 +328,73 @@ def estimate_marginal_likelihood(A, f0, theta0, model, N_samples=1000, B=100, st
         log_weights = comm.allreduce_np(log_weights)
     log_Z = -np.log(N_samples) + logsumexp(log_weights)
     return (log_Z, log_weights) if return_weights else log_Z
+
+
+def estimate_marginal_likelihood_batched(A, f0, theta0, model, N_samples=1000, B=100, steps_per_B=11, particles=None,
+                                         comm=None, return_weights=False, device_uniforms=None, seeds=None, dev=None):
+    """``estimate_marginal_likelihood`` (examples/demo_ais.py:10-62) with the particles CO-RESIDENT on the device
+    (SURVEY.md row a17 / config 5): A is bit-packed once (N^2 / 8 bytes, plus its transpose), every streamed row of A
+    serves all particles of a batch (``DeviceAIS``: gk_ais_sweep), the serial feature sweeps of the particles run side by
+    side, and the R x R edge counts that ``sample_theta`` (internals/graph_models.py:337-371) and ``log_lkhd`` (:42-48) need
+    are kept current by the sweep itself.
+
+    Random numbers: the reference consumes ONE global stream particle after particle, which a batch cannot reproduce;
+    here particle m owns ``np.random.RandomState(seeds[m])`` (seeds drawn from the global ``np.random`` unless given) and
+    consumes it exactly as the reference's loop body does: Dirichlet, R^2 Betas row-major, then the N uniforms of the
+    feature sweep.  ``device_uniforms`` (default for N > 8192) replaces those N uniforms per sweep by the device's
+    counter-based stream.  With ``comm`` the particles m = rank, rank + world, ... run on this rank (no data-path
+    collective, one gather of the log weights)."""
+    from ..device import DeviceAIS
+    betas = np.linspace(0, 1, B)
+    rank, world = (comm.rank, comm.world) if comm is not None else (0, 1)
+    if seeds is None:
+        seeds = np.random.randint(0, 2 ** 31 - 1, size=N_samples)
+    mine = list(range(rank, N_samples, world))
+    log_weights = np.zeros(N_samples)
+    N = A.shape[0] if A is not None else dev.N
+    if device_uniforms is None:
+        device_uniforms = N > 8192
+    is_er = isinstance(model, ErdosRenyiNetwork)
+    R = 1 if is_er else model.R
+    P = len(mine) if particles is None else min(int(particles), max(1, len(mine)))
+    for lo in range(0, len(mine), max(P, 1)):
+        batch = mine[lo:lo + P]
+        rs = [np.random.RandomState(int(seeds[m])) for m in batch]
+        if dev is None or dev.P != len(batch) or dev.R != R:
+            dev = DeviceAIS(A, len(batch), R)
+        w = np.zeros(len(batch))
+        if is_er:
+            nnz = float(dev.nnz())
+            for k, r in enumerate(rs):
+                for b in range(1, B):
+                    for s in range(steps_per_B):
+                        rho = model.rho if model.rho is not None else r.beta(model.a + betas[b] * nnz, model.b + betas[b] * (N ** 2 - nnz))
+                    w[k] += (betas[b] - betas[b - 1]) * (nnz * np.log(rho) + (N ** 2 - nnz) * np.log(1 - rho))
+        else:
+            dev.set_labels(np.asarray(f0, dtype=np.int32))
+            n_edge, sizes = dev.counts()
+            Bm = np.zeros((len(batch), R, R)); lpi = np.zeros((len(batch), R))
+            for b in range(1, B):
+                beta = betas[b]
+                for s in range(steps_per_B):
+                    u = None if device_uniforms else np.zeros((len(batch), N))
+                    for k, r in enumerate(rs):
+                        # sample_theta (:337-371): pi ~ Dir(alpha0 + sizes) untempered; B ~ Beta(b1 + beta e, b0 + beta (pairs - e)) as float32
+                        lpi[k] = np.log(r.dirichlet(model.alpha0 + sizes[k]))
+                        n_pair = np.outer(sizes[k], sizes[k])
+                        Bm[k] = r.beta(model.b1 + beta * n_edge[k], model.b0 + beta * (n_pair - n_edge[k])).astype(np.float32)
+                        if u is not None:
+                            u[k] = r.rand(N)
+                    dev.sweep(lpi, Bm, beta, uniforms=u, seed=int(seeds[batch[0]]))
+                    n_edge, sizes = dev.counts()
+                for k in range(len(batch)):
+                    n_pair = np.outer(sizes[k], sizes[k])
+                    with np.errstate(divide="ignore", invalid="ignore"):
+                        t1 = np.where(n_edge[k] > 0, n_edge[k] * np.log(Bm[k]), 0.0)
+                        t0 = np.where(n_pair - n_edge[k] > 0, (n_pair - n_edge[k]) * np.log(1 - Bm[k]), 0.0)
+                    w[k] += (beta - betas[b - 1]) * float(np.sum(t1 + t0))
+        log_weights[batch] = w
+    if comm is not None and world > 1:
+        log_weights = comm.allreduce_np(log_weights)
+    log_Z = -np.log(N_samples) + logsumexp(log_weights)
+    return (log_Z, log_weights) if return_weights else log_Z

@@ -279,6 +279,47 @@ int gk_mf_sbm_update_c(gk_ctx *ctx, gk_net *net, double *mf_m_inout, int K, cons
                        const double *base_out, const double *base_in, const double *coef_out, const double *coef_in,
                        double stepsize, int block_nodes, double *out_lp);
 
+/* ---- AIS over a bit-packed adjacency matrix, batched over particles -------------------
+ * Replaces the body of the driver loop of examples/demo_ais.py:10-62 for P co-resident particles.  A and A^T are held
+ * bit-packed (N^2/8 bytes each); each particle keeps its labels as R class bit-masks, so the class counts of node n are
+ * popc(row_n & mask) and one streamed row of A serves every particle.  R <= 8 (template instantiations). */
+typedef struct gk_ais gk_ais;
+enum { GK_AIS_ER = 0,   /* internals/graph_models.py:105-182 (ErdosRenyiNetwork)     */
+       GK_AIS_SBM = 1   /* internals/graph_models.py:185-371 (StochasticBlockModel)  */ };
+int gk_ais_create(gk_ctx *ctx, int N, int P, int R, gk_ais **out);
+int gk_ais_destroy(gk_ctx *ctx, gk_ais *ais);
+size_t gk_ais_device_bytes(gk_ais *ais);
+/* rows [row0, row0 + nrows) of the {0,1} uint8 matrix A (nrows x N, row0 a multiple of 32; the `A` of
+ * estimate_marginal_likelihood, demo_ais.py:10) -> the bit-packed rows of A and bit columns of A^T.  src_on_device != 0:
+ * A_rows is a device pointer. */
+int gk_ais_upload_rows(gk_ctx *ctx, gk_ais *ais, const uint8_t *A_rows, int row0, int nrows, int src_on_device);
+/* the same from the uint8 copy an unsharded gk_net already holds on the device */
+int gk_ais_upload_network(gk_ctx *ctx, gk_ais *ais, gk_net *net);
+/* sum(A) over all N^2 entries: nnz_A of ErdosRenyiNetwork.sample_theta (internals/graph_models.py:178) */
+int gk_ais_nnz(gk_ctx *ctx, gk_ais *ais, int64_t *nnz);
+/* labels z (P x N, or N when broadcast != 0: `f, theta = copy.deepcopy((f0, theta0))`, demo_ais.py:22); builds the class
+ * masks, class sizes and the R x R edge-count table of every particle */
+int gk_ais_set_labels(gk_ctx *ctx, gk_ais *ais, const int32_t *z, int broadcast);
+int gk_ais_get_labels(gk_ctx *ctx, gk_ais *ais, int32_t *z);
+/* n_edge[P x R x R] = sum(A[np.ix_(z == r1, z == r2)]) (diagonal included, internals/graph_models.py:364-367 and the
+ * N^2 loop of log_lkhd :42-48), sizes[P x R] = sum(z == r) (:347-349).  recompute = 0: the tables the sweeps keep
+ * current (exact integer updates per move); 1: a fresh pass over A. */
+int gk_ais_counts(gk_ctx *ctx, gk_ais *ais, int recompute, int64_t *n_edge, int64_t *sizes);
+/* `for n in arange(N): f[n] = model.sample_f(theta, (n, A, f), beta)` (demo_ais.py:44-46 -> naive_sample_f,
+ * internals/graph_models.py:261-297) for every particle: exact serial semantics per particle, particles in parallel.
+ * log_pi[P x R], B[P x R x R] (theta of each particle), beta[P]; uniforms[P x N] = the uniform log_sum_exp_sample draws
+ * for node n, or NULL: a counter-based stream keyed by (seed, sweep number, particle, node).  out_lp (P x N x R,
+ * optional): ln_pi_post of each node at the moment it was drawn.  out_nchanged (P, optional). */
+int gk_ais_sweep(gk_ctx *ctx, gk_ais *ais, const double *log_pi, const double *B, const double *beta,
+                 const double *uniforms, uint64_t seed, double *out_lp, int64_t *out_nchanged);
+/* The whole of estimate_marginal_likelihood (demo_ais.py:10-62) for the P particles of this state, all starting at f0
+ * (N labels; unused for GK_AIS_ER): n_temps temperatures linspace(0, 1, n_temps), steps_per_temp x (sample_theta, feature
+ * sweep) per temperature, log_weights[p] = sum_b (beta_b - beta_{b-1}) log_lkhd.  Beta(b1 + beta edges, b0 + beta non-edges)
+ * (ER: x = (b1, b0)), Dirichlet(alpha0[R] + sizes); the O(R^2) conjugate draws run on the host from a xoshiro256** stream
+ * seeded by `seed` (the Python shell draws the seed from np.random); the caller forms log Z = -log(P) + logsumexp. */
+int gk_ais_run(gk_ctx *ctx, gk_ais *ais, int model, double b0, double b1, const double *alpha0, int n_temps,
+               int steps_per_temp, const int32_t *f0, uint64_t seed, double *log_weights);
+
 #ifdef __cplusplus
 }
 #endif
