@@ -49,7 +49,8 @@ def parse_args():
     ap.add_argument("--no-extras", action="store_true", help="skip the mixing / f64 side records of the SBM workload")
     ap.add_argument("--cpu-nodes", type=int, default=0, help="nodes of the CPU-baseline sample (0 = auto)")
     ap.add_argument("--ref-budget", type=float, default=70.0, help="reference arm: seconds of timed sweeps per workload")
-    ap.add_argument("--ais-particles", type=int, default=32)
+    ap.add_argument("--ais-particles", type=int, default=128, help="co-resident AIS particles per GPU")
+    ap.add_argument("--ais-n", type=int, default=65536, help="nodes of the AIS workload (configs[4]: N=65536)")
     return ap.parse_args()
 
 
@@ -198,8 +199,8 @@ def workload_config(name, args):
         return {"workload": "latent_distance_hmc_gibbs_sweep + NIW weights N=%d dim=2 B=1 (configs[3])" % N,
                 "N": N, "dim": 2, "B": 1}
     if name == "ais":
-        return {"workload": "ais_sbm_particle_sweep N=%d R=3 P=%d (configs[4])" % (N, args.ais_particles),
-                "N": N, "R": 3, "P": args.ais_particles}
+        return {"workload": "ais_sbm_particle_sweep N=%d R=3 P=%d per GPU (configs[4])" % (args.ais_n, args.ais_particles),
+                "N": args.ais_n, "R": 3, "P": args.ais_particles}
     raise SystemExit("unknown workload " + name)
 
 
@@ -523,6 +524,8 @@ def run_ours(args):
         r, w = bench_workload(name, args, R, args.dtype, args.steps, args.warmup, rows=rows)
         out["workloads"][name] = r
         release(w)
+    if args.workload == "all" and not rows:                        # config 5 beside the sweeps: batched AIS particle sweeps
+        out["workloads"]["ais"] = bench_ais(args, R, max(3, args.steps // 2), args.warmup)
     if primary == "sbm" and extras and args.dtype == "f32":       # the fp64-storage line beside the fp32 one
         r, w = bench_workload("sbm", args, R, "f64", max(3, args.steps // 4), args.warmup, cpu=False)
         out["workloads"]["sbm_f64"] = r
@@ -535,8 +538,201 @@ def run_ours(args):
         dist.destroy_process_group()
 
 
+AIS_UNIT = "particle-sweeps/s"
+
+
+def ais_truth(N, R=3, seed=1234):
+    """config 5: SBM truth R = 3, alpha0 = 10, b0 = b1 = 1 (examples/demo_ais.py:76-80), seed 1234."""
+    rng = np.random.RandomState(seed)
+    pi = rng.dirichlet(10 * np.ones(R))
+    z = rng.choice(R, size=N, p=pi)
+    Bt = rng.beta(1.0, 1.0, (R, R))
+    return z, Bt, pi
+
+
+def _ais_cpu_nodes(N, R, z_true, Bt, z, Bm, pi, beta, lo, hi, seed=3):
+    """naive_sample_f (internals/graph_models.py:261-297) for nodes [lo, hi): the count form of oracle.sbm.node_conditional
+    (SELF_AIS) on rows / columns of A generated for those nodes only (a 4.3 GB host matrix is never built)."""
+    from oracle import sbm
+    rng = np.random.RandomState(seed + lo)
+    logB, log1mB = np.log(Bm), np.log1p(-Bm)
+    z = np.array(z, dtype=np.int64)
+    for n in range(lo, hi):
+        a_out = rng.rand(N) < Bt[z_true[n], z_true]
+        a_in = rng.rand(N) < Bt[z_true, z_true[n]]
+        a11 = bool(a_out[n]); a_in[n] = a11
+        others = np.ones(N, bool); others[n] = False
+        sz = np.bincount(z[others], minlength=R).astype(np.float64)
+        co = np.bincount(z[a_out & others], minlength=R).astype(np.float64)
+        ci = np.bincount(z[a_in & others], minlength=R).astype(np.float64)
+        lp = np.log(pi) + beta * (logB.dot(co) + log1mB.dot(sz - co) + logB.T.dot(ci) + log1mB.T.dot(sz - ci))
+        k = np.arange(R)
+        lp += 2.0 * beta * (logB[k, k] if a11 else log1mB[k, k])
+        z[n] = sbm.log_sum_exp_sample(lp, rng.rand())
+    return hi - lo
+
+
+def cpu_baseline_ais(args, N, R, nodes=None):
+    nodes = nodes or args.cpu_nodes or 4096
+    z_true, Bt, pi = ais_truth(N, R)
+    z = np.random.RandomState(1).randint(0, R, N)
+    t0 = time.perf_counter()
+    _ais_cpu_nodes(N, R, z_true, Bt, z, np.clip(Bt, 1e-6, 1 - 1e-6), pi, 0.5, 0, nodes)
+    gen0 = time.perf_counter()
+    rng = np.random.RandomState(0)
+    for n in range(nodes):                                    # the data generation of the sample, timed alone and subtracted
+        rng.rand(N) < Bt[z_true[n], z_true]; rng.rand(N) < Bt[z_true, z_true[n]]
+    gen = time.perf_counter() - gen0
+    secs = max(1e-9, (gen0 - t0) - gen)
+    full = secs * (N / float(nodes))
+    return {"value": 1.0 / full, "unit": AIS_UNIT, "cores": 1, "kind": "port",
+            "sample": "oracle count form of naive_sample_f (vectorised NumPy) on the first %d of %d nodes of ONE particle; %.2f s "
+                      "measured on 1 core (generation of the sample's rows excluded), scaled x%.1f to a full feature sweep"
+                      % (nodes, N, secs, N / float(nodes)), "measured_s": secs}
+
+
+def _ais_device(args, R, P):
+    """DeviceAIS holding config 5's matrix: A is generated on the device, 2048 rows at a time; the first chunk also goes
+    through the host-buffer path (pinned uint8 rows -> gk_ais_upload_rows) to measure it."""
+    import torch
+    from graphistician_b200.device import DeviceAIS
+    N, Rk = args.ais_n, 3
+    z_true, Bt, pi = ais_truth(N, Rk)
+    g = torch.Generator(device=R.dev); g.manual_seed(1234 + R.rank)
+    dev = DeviceAIS(None, P, Rk, N=N)
+    zt = torch.from_numpy(z_true).to(R.dev); Btt = torch.from_numpy(Bt).float().to(R.dev)
+    rows_per = 2048
+    t_up, chunk_bytes = 0.0, 0
+    for r0 in range(0, N, rows_per):
+        Pm = Btt[zt[r0:r0 + rows_per]][:, zt]
+        rows = (torch.rand(Pm.shape, device=R.dev, generator=g) < Pm).to(torch.uint8).contiguous()
+        torch.cuda.synchronize()
+        if r0 == 0:
+            host_chunk = rows.cpu().pin_memory()
+            t0 = time.perf_counter()
+            dev.upload_rows(host_chunk.numpy(), 0)
+            dev.ctx.synchronize()
+            t_up, chunk_bytes = time.perf_counter() - t0, host_chunk.numel()
+        dev.upload_rows(None, r0, device_ptr=rows.data_ptr(), nrows=rows.shape[0])
+        dev.ctx.synchronize()
+        del rows, Pm
+    return dev, t_up, chunk_bytes
+
+
+def bench_ais(args, R, steps, warmup, cpu=True, scan=(8, 32, 512)):
+    """config 5: P co-resident AIS particles per GPU over one bit-packed N = 65536 adjacency matrix; a step = one batched
+    feature sweep (every particle's exact sequential sweep).  Particles are partitioned over the ranks (no data-path
+    collective), so the N-GPU value is the sum of the ranks' particle-sweeps."""
+    N, Rk, P = args.ais_n, 3, args.ais_particles
+    dev, t_up, chunk_bytes = _ais_device(args, R, P)
+    rng = np.random.RandomState(5678 + R.rank)
+    dev.set_labels(rng.randint(0, Rk, N))
+    model_b0 = model_b1 = 1.0; alpha0 = 10 * np.ones(Rk)
+    state = {"beta_i": 0}
+    betas = np.linspace(0, 1, 100)[1:]
+
+    def theta():
+        """sample_theta of every particle from the counts the device keeps (internals/graph_models.py:337-371)."""
+        n_edge, sizes = dev.counts()
+        beta = betas[state["beta_i"] % len(betas)]
+        lpi = np.log(np.stack([rng.dirichlet(alpha0 + sizes[k]) for k in range(P)]))
+        n_pair = sizes[:, :, None] * sizes[:, None, :]
+        Bm = rng.beta(model_b1 + beta * n_edge, model_b0 + beta * (n_pair - n_edge)).astype(np.float32).astype(np.float64)
+        return lpi, Bm, beta
+
+    lpi, Bm, beta = theta()
+
+    def step_resident():                                       # the device part alone, theta fixed
+        dev.sweep(lpi, Bm, beta, seed=7)
+
+    def step_e2e():                                            # one AIS step as the driver runs it: counts -> theta draws -> sweep
+        state["beta_i"] += 1
+        l, b, be = theta()
+        dev.sweep(l, b, be, seed=7)
+
+    R.timed(step_resident, warmup)
+    sampler = ClockSampler(R.local); sampler.start()
+    l0 = R.ctx.launch_count()
+    ms = R.timed(step_resident, steps)
+    launches = R.ctx.launch_count() - l0
+    clocks = sampler.result()
+    e2e_steps = max(3, min(steps, 8))
+    R.timed(step_e2e, 1)
+    ms_e2e = R.timed(step_e2e, e2e_steps)
+    R.ctx.kernel_timing(True)
+    for _ in range(3):
+        step_resident()
+    fam0, fam1 = R.ctx.kernel_timing_read(0), R.ctx.kernel_timing_read(1)
+    R.ctx.kernel_timing(False)
+    e1, s1 = dev.counts(); e2, s2 = dev.counts(recompute=True)
+    assert np.array_equal(e1, e2) and np.array_equal(s1, s2), "AIS cell table drifted"
+    peaks = {}
+    try:
+        peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+    except Exception:
+        pass
+    peak = float(peaks.get("hbm_gbs", 6650.0))
+    algo = 2.0 * N * N / 8.0                                   # SURVEY.md 8d: bit-packed row + column pass, shared by the P particles
+    kms = fam0[0] / 3.0
+    achieved = algo / (kms * 1e-3) / 1e9 if kms > 0 else 0.0
+    word_ops = 2.0 * N * (N / 32.0) * P * (Rk - 1)
+    rec = {
+        "value": R.world * P * steps / (ms * 1e-3), "unit": AIS_UNIT, "steps": steps, "ms_per_step": ms / steps, "dtype": "u32/f64",
+        "config": {"workload": "ais_sbm_particle_sweep N=%d R=3 P=%d per GPU (configs[4])" % (N, P), "N": N, "R": Rk, "P": P},
+        "gpu_launches": int(launches), "clocks": clocks,
+        "particles_total": R.world * P, "device_bytes": dev.device_bytes(),
+        "e2e": {"value": R.world * P * e2e_steps / (ms_e2e * 1e-3), "unit": AIS_UNIT,
+                "h2d_bytes_per_step": int(P * (1 + Rk + 2 * Rk * Rk) * 8), "d2h_bytes_per_step": int(P * (Rk * Rk + Rk + 1) * 8),
+                "what": "counts D2H -> Dirichlet / Beta draws of every particle on the host -> tables H2D -> batched sweep; A stays "
+                        "resident (it is the data of the whole AIS run)",
+                "upload_rows_host_GBps": (chunk_bytes / t_up / 1e9) if t_up > 0 else None},
+        "roofline": {"bound": "hbm", "kernel": "k_ais_rowcnt", "achieved": achieved, "peak": peak, "unit": "GB/s",
+                     "frac": achieved / peak, "traffic": ncu_traffic("k_ais_rowcnt")[0],
+                     "algorithmic_bytes_per_launch": algo / ((N + 1023) // 1024),
+                     "launches_per_sweep": fam0[1] / 3.0, "kernel_ms_per_sweep": kms,
+                     "other_kernels_ms_per_sweep": {"k_ais_seq": fam1[0] / 3.0},
+                     "note": "one streamed row of A serves all P particles, so the pass is bound by the integer pipe, not by HBM: "
+                             "%.3g AND-popcount word operations per sweep = %.3g /s (Harley-Seal: 5 POPC + 46 LOP3 per 16 words); "
+                             "the kernel-timing pass serialises the two particle groups that the timed sweeps overlap"
+                             % (word_ops, word_ops / (kms * 1e-3) if kms > 0 else 0.0),
+                     "sweep_algorithmic_bytes": algo, "sweep_frac_of_peak": algo / (ms / steps * 1e-3) / 1e9 / peak},
+        "l2": "A and A^T bit-packed (%.2f GB) exceed the 126 MB L2" % (2 * N * N / 8 / 1e9),
+        "data": "synthetic SBM, R=3, generated on the device in 2048-row chunks (the 4.3 GB uint8 matrix never exists on the host)",
+    }
+    if cpu and R.rank == 0 and R.world == 1 and not args.no_cpu_baseline:
+        rec["cpu_baseline"] = cpu_baseline_ais(args, N, Rk)
+    dev.close()
+    rec["particle_scan"] = {str(P): {"value": rec["value"], "ms_per_step": rec["ms_per_step"]}}
+    for Ps in scan:                                            # SURVEY.md 8d config 5: P swept per GPU (resident sweeps only)
+        if Ps == P or R.world > 1:
+            continue
+        dv, _, _ = _ais_device(args, R, Ps)
+        dv.set_labels(rng.randint(0, Rk, N))
+        n_edge, sizes = dv.counts()
+        lp_s = np.log(np.stack([rng.dirichlet(alpha0 + sizes[k]) for k in range(Ps)]))
+        n_pair = sizes[:, :, None] * sizes[:, None, :]
+        B_s = rng.beta(1.0 + beta * n_edge, 1.0 + beta * (n_pair - n_edge)).astype(np.float32).astype(np.float64)
+        st = lambda: dv.sweep(lp_s, B_s, beta, seed=7)
+        R.timed(st, 2)
+        ms_s = R.timed(st, 3)
+        rec["particle_scan"][str(Ps)] = {"value": Ps * 3 / (ms_s * 1e-3), "ms_per_step": ms_s / 3}
+        dv.close()
+    return rec
+
+
 def run_ais(args, R):
-    raise SystemExit("--workload ais: see profiles/bench_ais.py")
+    rec = bench_ais(args, R, args.steps, args.warmup)
+    out = {"metric": "AIS particle-sweeps/sec at N=%d (configs[4])" % args.ais_n, "value": rec["value"], "unit": AIS_UNIT,
+           "n_gpus": R.world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": rec["ms_per_step"],
+           "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": rec["dtype"], "data": rec["data"],
+           "parallelism": "particles partitioned x%d, no data-path collective" % R.world}
+    out.update({k: rec[k] for k in rec if k not in out})
+    out["host"] = host_info()
+    if R.rank == 0:
+        print(json.dumps(out), flush=True)
+    if R.world > 1:
+        import torch.distributed as dist
+        dist.destroy_process_group()
 
 
 # --------------------------------------------------------------------------------------------------
@@ -711,6 +907,42 @@ def _ref_sweeps(kind, N, procs, args):
     return times, warm
 
 
+def _ais_ref_task(task):
+    lo, hi, N, R = task
+    z_true, Bt, pi = ais_truth(N, R)
+    z = np.random.RandomState(1).randint(0, R, N)
+    t0 = time.perf_counter()
+    _ais_cpu_nodes(N, R, z_true, Bt, z, np.clip(Bt, 1e-6, 1 - 1e-6), pi, 0.5, lo, hi)
+    t1 = time.perf_counter()
+    rng = np.random.RandomState(0)
+    for n in range(lo, hi):
+        rng.rand(N) < Bt[z_true[n], z_true]; rng.rand(N) < Bt[z_true, z_true[n]]
+    return (t1 - t0) - (time.perf_counter() - t1)
+
+
+def reference_ais(args, procs):
+    """--impl reference --workload ais: the oracle's count form of naive_sample_f on a bounded sample of nodes, one
+    forked worker per usable core, scaled to full feature sweeps (a particle's sweep is serial; particles are independent,
+    so `procs` cores run `procs` particles side by side)."""
+    import multiprocessing as mp
+    N, R, per = args.ais_n, 3, 1024
+    tasks = [(k * per, (k + 1) * per, N, R) for k in range(procs)]
+    t0 = time.perf_counter()
+    with mp.get_context("fork").Pool(procs) as pool:
+        secs = pool.map(_ais_ref_task, tasks, chunksize=1)
+    wall = time.perf_counter() - t0
+    per_sweep = float(np.mean(secs)) * (N / float(per))        # one particle's full sweep on one core
+    value = procs / per_sweep
+    cfg = workload_config("ais", args)
+    return {"impl": "reference", "metric": "AIS particle-sweeps/sec at N=%d (configs[4])" % N, "value": value, "unit": AIS_UNIT,
+            "n_gpus": args.gpus, "steps": 1, "warmup": 0, "ms_per_step": 1e3 * per_sweep / procs, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
+            "cpu_baseline": {"value": value, "unit": AIS_UNIT, "cores": procs, "kind": "port",
+                             "sample": "%d nodes of one particle's feature sweep per core on %d cores (oracle count form, NumPy), "
+                                       "%.1f s wall; scaled x%d to full sweeps, %d particles side by side" % (per, procs, wall, N // per, procs)},
+            "e2e": {"value": value, "unit": AIS_UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "host": host_info()}
+
+
 def reference_workload(name, args, procs):
     N = args.n
     os.environ.setdefault("OMP_NUM_THREADS", "1")              # one worker per core; the C sampler stays single-threaded in each
@@ -754,6 +986,9 @@ def run_reference(args):
     if rank != 0:
         return
     procs = usable_cores()
+    if args.workload == "ais":
+        print(json.dumps(reference_ais(args, procs)), flush=True)
+        return
     names = ["sbm", "eigen", "latent"] if args.workload == "all" else [args.workload]
     recs = {n: reference_workload(n, args, procs) for n in names}
     r = recs[names[0]]

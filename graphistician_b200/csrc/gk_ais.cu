@@ -243,27 +243,51 @@ struct AisSeqParams {
     int N, Npad, nw, n0, p0;
 };
 
-template <int R> struct AisNode { uint32_t ao, ai, ce[2 * (R - 1)]; uint2 dg; int a; double u; };
+#define AIS_RING 8                // nodes of read-ahead of the serial kernel (cp.async ring in shared memory)
 
-template <int R> struct AisCursor {                 // the six streams a particle's warp reads, advanced by one node per step
-    const uint32_t *ao, *ai, *ce; const uint2 *dg; const uint8_t *z; const double *u; size_t nw;
-    __device__ __forceinline__ void load(AisNode<R> &nd) {
-        nd.ao = *ao; nd.ai = *ai; nd.dg = *dg; nd.a = *z; nd.u = *u;
-        if (R == 3) { const uint4 v = *reinterpret_cast<const uint4 *>(ce); nd.ce[0] = v.x; nd.ce[1] = v.y; nd.ce[2] = v.z; nd.ce[3] = v.w; }
-        else {
-#pragma unroll
-            for (int r = 0; r < 2 * (R - 1); ++r) nd.ce[r] = ce[r];
-        }
-        ao += nw; ai += nw; ce += 2 * (R - 1); ++dg; ++z; ++u;
-    }
-};
+__device__ __forceinline__ void ais_cp4(uint32_t *smem, const uint32_t *g) {
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g) : "memory");
+}
+__device__ __forceinline__ void ais_cp_commit() { asm volatile("cp.async.commit_group;" ::: "memory"); }
+template <int N_> __device__ __forceinline__ void ais_cp_wait() { asm volatile("cp.async.wait_group %0;" ::"n"(N_) : "memory"); }
 
+template <int R> static constexpr size_t ais_seq_smem() {
+    return (size_t)AIS_NB * (2 * (R - 1) * 4 + 8 + 8) + (size_t)AIS_RING * 2 * 32 * 4;
+}
+
+// One warp per particle.  The block's small per-node records (entry counts, degrees, uniforms) are staged in shared memory
+// once; the node's words of A / A^T (one per lane) come through an AIS_RING-deep cp.async ring, so that no register
+// scoreboard ties a node's arithmetic to loads issued for later nodes.
 template <int R>
 __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
     const int p = P.p0 + blockIdx.x, lane = threadIdx.x;
-    constexpr int TS = 1 + R + 2 * R * R;
+    constexpr int TS = 1 + R + 2 * R * R, CE = 2 * (R - 1);
+    extern __shared__ __align__(16) unsigned char s_dyn[];
+    uint32_t *s_ce = reinterpret_cast<uint32_t *>(s_dyn);                 // [AIS_NB][CE]
+    uint2 *s_dg = reinterpret_cast<uint2 *>(s_ce + AIS_NB * CE);          // [AIS_NB]
+    double *s_u = reinterpret_cast<double *>(s_dg + AIS_NB);              // [AIS_NB]
+    uint32_t *s_ring = reinterpret_cast<uint32_t *>(s_u + AIS_NB);        // [AIS_RING][2][32]
     __shared__ double s_tab[TS];
     __shared__ int s_cell[R * R];                    // change of the cell table over this block
+    const int nb = min(AIS_NB, P.N - P.n0);
+    const uint32_t *gAo = P.Ab + (size_t)P.n0 * P.nw + (P.n0 >> 5) + lane;
+    const uint32_t *gAi = P.Atb + (size_t)P.n0 * P.nw + (P.n0 >> 5) + lane;
+#pragma unroll
+    for (int k = 0; k < AIS_RING - 1; ++k) {         // read-ahead of the first nodes' words
+        if (k < nb) { ais_cp4(s_ring + (k * 2) * 32 + lane, gAo + (size_t)k * P.nw); ais_cp4(s_ring + (k * 2 + 1) * 32 + lane, gAi + (size_t)k * P.nw); }
+        ais_cp_commit();
+    }
+    {
+        const uint4 *g = reinterpret_cast<const uint4 *>(P.cnt + (size_t)p * AIS_NB * CE);
+        uint4 *d = reinterpret_cast<uint4 *>(s_ce);
+        for (int t = lane; t < AIS_NB * CE / 4; t += 32) d[t] = g[t];
+        const uint4 *g2 = reinterpret_cast<const uint4 *>(P.deg + P.n0);
+        uint4 *d2 = reinterpret_cast<uint4 *>(s_dg);
+        for (int t = lane; t < AIS_NB / 2; t += 32) d2[t] = g2[t];
+        const uint4 *g3 = reinterpret_cast<const uint4 *>(P.u + (size_t)p * P.Npad + P.n0);
+        uint4 *d3 = reinterpret_cast<uint4 *>(s_u);
+        for (int t = lane; t < AIS_NB / 2; t += 32) d3[t] = g3[t];
+    }
     for (int t = lane; t < TS; t += 32) s_tab[t] = P.tab[(size_t)p * TS + t];
     for (int t = lane; t < R * R; t += 32) s_cell[t] = 0;
     __syncwarp();
@@ -277,21 +301,31 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
         C[r] = E[r];
         sz[r] = (int)P.sz[p * R + r];
     }
-    const int nb = min(AIS_NB, P.N - P.n0);
     int nchg = 0;
-    AisCursor<R> cs;
-    cs.nw = (size_t)P.nw;
-    cs.ao = P.Ab + (size_t)P.n0 * P.nw + (P.n0 >> 5) + lane;
-    cs.ai = P.Atb + (size_t)P.n0 * P.nw + (P.n0 >> 5) + lane;
-    cs.ce = P.cnt + (size_t)p * AIS_NB * 2 * (R - 1);
-    cs.dg = P.deg + P.n0;
-    cs.z = P.z + (size_t)p * P.Npad + P.n0;
-    cs.u = P.u + (size_t)p * P.Npad + P.n0;
-    AisNode<R> cur, nxt, nx2;
-    cs.load(cur); cs.load(nxt); cs.load(nx2);        // rows beyond the block exist (Npad rows, cnt has a 3-record tail): harmless reads
     for (int i = 0; i < nb; ++i) {
-        AisNode<R> nx3;
-        cs.load(nx3);
+        {
+            const int k = i + AIS_RING - 1;
+            if (k < nb) {
+                const int slot = k & (AIS_RING - 1);
+                ais_cp4(s_ring + (slot * 2) * 32 + lane, gAo + (size_t)k * P.nw);
+                ais_cp4(s_ring + (slot * 2 + 1) * 32 + lane, gAi + (size_t)k * P.nw);
+            }
+            ais_cp_commit();
+            ais_cp_wait<AIS_RING - 1>();
+        }
+        struct { uint32_t ao, ai, ce[CE]; uint2 dg; int a; double u; } cur;
+        cur.ao = s_ring[((i & (AIS_RING - 1)) * 2) * 32 + lane];
+        cur.ai = s_ring[((i & (AIS_RING - 1)) * 2 + 1) * 32 + lane];
+#pragma unroll
+        for (int r = 0; r < CE; ++r) cur.ce[r] = s_ce[i * CE + r];
+        cur.dg = s_dg[i];
+        cur.u = s_u[i];
+        {   // the node's current label: the class whose mask holds bit i (the node has not been drawn yet in this sweep)
+            int al = 0;
+#pragma unroll
+            for (int r = 1; r < R; ++r) al += r * (int)((C[r] >> (i & 31)) & 1u);
+            cur.a = __shfl_sync(0xffffffffu, al, i >> 5);
+        }
         // counts of node n's out- and in-neighbours per class under the CURRENT labels: block-entry counts plus what the
         // nodes of this block that already moved changed (nothing while no node of the block has moved: C == E)
         int co[R], ci[R];
@@ -383,7 +417,6 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
                 s_cell[a * R + a] -= self; s_cell[b * R + b] += self;
             }
         }
-        cur = nxt; nxt = nx2; nx2 = nx3;
     }
     __syncwarp();
 #pragma unroll
@@ -576,8 +609,11 @@ extern "C" int gk_ais_counts(gk_ctx *ctx, gk_ais *a, int recompute, int64_t *n_e
     return GK_OK;
 }
 
-template <int R> static void ais_launch_seq(int np, cudaStream_t st, const AisSeqParams &prm) {
-    k_ais_seq<R><<<np, 32, 0, st>>>(prm);
+template <int R> static int ais_launch_seq(gk_ctx *ctx, int np, cudaStream_t st, const AisSeqParams &prm) {
+    if (gk_attr_needed(ctx, (const void *)k_ais_seq<R>))
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_ais_seq<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ais_seq_smem<R>()));
+    k_ais_seq<R><<<np, 32, ais_seq_smem<R>(), st>>>(prm);
+    return GK_OK;
 }
 
 // One sweep.  The particles are split in two groups on two streams so that one group's serial kernel (one warp per
@@ -614,15 +650,16 @@ static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool
             prm.p0 = p0;
             if (!g) gk_time_begin(ctx, 1, 0.0);
             switch (R) {
-                case 2: ais_launch_seq<2>(p1 - p0, st, prm); break;
-                case 3: ais_launch_seq<3>(p1 - p0, st, prm); break;
-                case 4: ais_launch_seq<4>(p1 - p0, st, prm); break;
-                case 5: ais_launch_seq<5>(p1 - p0, st, prm); break;
-                case 6: ais_launch_seq<6>(p1 - p0, st, prm); break;
-                case 7: ais_launch_seq<7>(p1 - p0, st, prm); break;
-                default: ais_launch_seq<8>(p1 - p0, st, prm); break;
+                case 2: rc = ais_launch_seq<2>(ctx, p1 - p0, st, prm); break;
+                case 3: rc = ais_launch_seq<3>(ctx, p1 - p0, st, prm); break;
+                case 4: rc = ais_launch_seq<4>(ctx, p1 - p0, st, prm); break;
+                case 5: rc = ais_launch_seq<5>(ctx, p1 - p0, st, prm); break;
+                case 6: rc = ais_launch_seq<6>(ctx, p1 - p0, st, prm); break;
+                case 7: rc = ais_launch_seq<7>(ctx, p1 - p0, st, prm); break;
+                default: rc = ais_launch_seq<8>(ctx, p1 - p0, st, prm); break;
             }
             if (!g) gk_time_end(ctx, 1);
+            if (rc) return rc;
             GK_CHECK_LAUNCH(ctx);
         }
     }
