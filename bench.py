@@ -46,6 +46,7 @@ def parse_args():
                     help="N > 1: independent chains per GPU (weak scaling, default) or ONE chain with rows of A/W sharded "
                          "over the GPUs and NCCL all-reduces of the statistics (strong scaling)")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="N > 1: skip the row-sharded (strong scaling) sub-record")
     ap.add_argument("--no-extras", action="store_true", help="skip the mixing / f64 side records of the SBM workload")
     ap.add_argument("--cpu-nodes", type=int, default=0, help="nodes of the CPU-baseline sample (0 = auto)")
     ap.add_argument("--ref-budget", type=float, default=70.0, help="reference arm: seconds of timed sweeps per workload")
@@ -390,7 +391,7 @@ class Runner:
         return max_over_ranks(e0.elapsed_time(e1), self.world, self.dev)
 
 
-def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, first_sweep=False):
+def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, first_sweep=False, e2e=True):
     """One workload record: value (resident), e2e (host buffers), roofline of the dominant kernel family,
     launches, clocks, and (rank 0, one GPU) the CPU baseline."""
     wl = setup_workload(name, args, 0 if rows else R.rank, dtype)
@@ -408,6 +409,13 @@ def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, fi
         rec["first_sweep_n_changed"] = int(getattr(model, "_n_changed", -1))
         warmup = max(0, warmup - 1)
     R.timed(step, warmup)
+    extra_warm = 0
+    if name == "sbm" and not rows and R.world > 1:
+        # the ranks' chains run on different data and may take different numbers of sweeps to recover the planted blocks; the
+        # timed region is a max over ranks, so every rank is brought to the stationary regime (n_changed = 0) first
+        while extra_warm < 12 and max_over_ranks(float(getattr(model, "_n_changed", 0)), R.world, R.dev) > 0:
+            R.timed(step, 1)
+            extra_warm += 1
     sampler = ClockSampler(R.local); sampler.start()
     l0 = R.ctx.launch_count()
     ms = R.timed(step, steps)
@@ -415,8 +423,10 @@ def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, fi
     clocks = sampler.result()
     # e2e: same call, network re-uploaded from pinned host memory every step, state read back every step
     e2e_steps = max(3, min(steps, 5))
-    R.timed(step, 1, before=network.invalidate)
-    ms_e2e = R.timed(step, e2e_steps, before=network.invalidate)
+    ms_e2e = float("nan")
+    if e2e:
+        R.timed(step, 1, before=network.invalidate)
+        ms_e2e = R.timed(step, e2e_steps, before=network.invalidate)
     # per-kernel timing pass (CUDA events around every launch of each kernel family, on the ctx stream)
     R.ctx.kernel_timing(True)
     for _ in range(3):
@@ -437,8 +447,8 @@ def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, fi
     rec.update({
         "value": mult * steps / (ms * 1e-3), "unit": UNIT, "steps": steps, "ms_per_step": ms / steps, "dtype": dtype,
         "config": workload_config(name, args), "gpu_launches": int(launches), "clocks": clocks,
-        "e2e": {"value": mult * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(wl["h2d"]),
-                "d2h_bytes_per_step": int(wl["d2h"])},
+        "e2e": ({"value": mult * e2e_steps / (ms_e2e * 1e-3), "unit": UNIT, "h2d_bytes_per_step": int(wl["h2d"]),
+                 "d2h_bytes_per_step": int(wl["d2h"])} if e2e else None),
         "roofline": {"bound": "hbm", "kernel": kname, "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "traffic": traffic, "traffic_source": tsrc,
                      "algorithmic_bytes_per_launch": (kbytes / kn) if kn else None,
@@ -451,7 +461,8 @@ def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, fi
         "l2": "inputs (%.2f GB/sweep) exceed the 126 MB L2" % (algo_bytes / 1e9),
     })
     if name == "sbm":
-        rec["n_changed_last_sweep"] = int(getattr(model, "_n_changed", -1))
+        rec["n_changed_last_sweep"] = int(max_over_ranks(float(getattr(model, "_n_changed", -1)), R.world, R.dev))
+        rec["extra_warmup_sweeps"] = extra_warm
         rec["regime"] = "stationary (planted blocks recovered during warm-up; see `mixing` for sweeps with movers)"
     if cpu and R.rank == 0 and R.world == 1 and not args.no_cpu_baseline:
         rec["cpu_baseline"] = wl["cpu_baseline"](d, model, args)
@@ -524,6 +535,15 @@ def run_ours(args):
         r, w = bench_workload(name, args, R, args.dtype, args.steps, args.warmup, rows=rows)
         out["workloads"][name] = r
         release(w)
+    if R.world > 1 and not rows and args.workload == "all" and not args.no_strong:
+        # ONE chain with the rows of A / W sharded over the ranks (north_star configs 3 / 4) beside the replicas:
+        # statistics all-reduced with NCCL in-stream, the sequential draws on the owner of each node block
+        out["strong"] = {"scaling": "strong", "parallelism": "one chain, rows sharded x%d" % R.world, "workloads": {}}
+        R.torch.cuda.set_stream(R.stream)
+        for name in ("latent", "eigen", "sbm"):
+            r, w = bench_workload(name, args, R, args.dtype, max(3, args.steps // 2), args.warmup, rows=True, cpu=False, e2e=False)
+            out["strong"]["workloads"][name] = {k: r[k] for k in ("value", "unit", "steps", "ms_per_step", "config", "gpu_launches", "roofline")}
+            release(w)
     if args.workload == "all" and not rows:                        # config 5 beside the sweeps: batched AIS particle sweeps
         out["workloads"]["ais"] = bench_ais(args, R, max(3, args.steps // 2), args.warmup)
     if primary == "sbm" and extras and args.dtype == "f32":       # the fp64-storage line beside the fp32 one

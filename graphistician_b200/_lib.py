@@ -40,6 +40,8 @@ SIGNATURES = {
     "gk_sbm_block_sample": (c_int, [c_vp, c_vp, c_int, c_int, c_vp]),
     "gk_sbm_get_block": (c_int, [c_vp, c_int, c_int, c_vp]),
     "gk_sbm_set_block": (c_int, [c_vp, c_int, c_int, c_vp]),
+    "gk_sbm_export_block_dev": (c_int, [c_vp, c_int, c_int, c_vp]),
+    "gk_sbm_import_block_dev": (c_int, [c_vp, c_int, c_int, c_vp]),
     "gk_sbm_sweep_end": (c_int, [c_vp, c_vp, c_vp, c_vp, PI64]),
     "gk_eig_create": (c_int, [c_vp, c_vp, c_int, ctypes.POINTER(c_vp)]),
     "gk_eig_destroy": (c_int, [c_vp, c_vp]),
@@ -99,6 +101,12 @@ SIGNATURES = {
     "gk_ais_counts": (c_int, [c_vp, c_vp, c_int, c_vp, c_vp]),
     "gk_ais_sweep": (c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_vp, ctypes.c_uint64, c_vp, c_vp]),
     "gk_ais_run": (c_int, [c_vp, c_vp, c_int, c_dbl, c_dbl, c_vp, c_int, c_int, c_vp, ctypes.c_uint64, c_vp]),
+    "gk_comm_unique_id": (c_int, [c_vp, c_vp]),
+    "gk_comm_init": (c_int, [c_vp, c_vp, c_int, c_int]),
+    "gk_comm_destroy": (c_int, [c_vp]),
+    "gk_comm_rank": (c_int, [c_vp]),
+    "gk_comm_world": (c_int, [c_vp]),
+    "gk_comm_allreduce": (c_int, [c_vp, c_vp, c_sz]),
 }
 
 _lib = None
@@ -164,6 +172,19 @@ class Context:
         ms, n, b = c_dbl(), c_i64(), c_dbl()
         self.check(self.lib.gk_ctx_kernel_timing_read(self.h, family, ctypes.byref(ms), ctypes.byref(n), ctypes.byref(b)))
         return ms.value, n.value, b.value
+
+    def init_comm(self, comm):
+        """Give this context the engine's own NCCL communicator over the ranks of ``comm`` (sharding.Comm): rank 0 draws
+        the id, the host broadcasts it, every rank joins.  From then on libgk issues the collectives of the row-sharded
+        sweeps itself, in-stream (include/gk.h 'the engine's own communicator')."""
+        if getattr(self, "native_world", 1) > 1 or comm.world < 2:
+            return
+        uid = np.zeros(128, np.uint8)
+        if comm.rank == 0:
+            self.check(self.lib.gk_comm_unique_id(self.h, ptr(uid)))
+        uid = np.ascontiguousarray(comm.broadcast_np(uid, 0), dtype=np.uint8)
+        self.check(self.lib.gk_comm_init(self.h, ptr(uid), int(comm.rank), int(comm.world)))
+        self.native_world = comm.world
 
     def close(self):
         if getattr(self, "h", None):

@@ -58,6 +58,7 @@ extern "C" void gk_ctx_destroy(gk_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
+    gk_comm_release(ctx);
     for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (auto &f : ctx->fam) for (auto &p : f.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);

@@ -705,7 +705,36 @@ extern "C" int gk_eig_resample_F(gk_ctx *ctx, gk_eig *e, double sigma_F, const d
     if (!e->have_S) return gk_fail(ctx, GK_EINVAL, "gk_eig_resample_F: call gk_eig_pg_draw or gk_eig_set_S first");
     if (!(sigma_F > 0)) return gk_fail(ctx, GK_EINVAL, "sigma_F must be positive");
     gk_net *net = e->net;
-    if (net->row0 != 0 || net->nrows != net->N) return gk_fail(ctx, GK_EINVAL, "gk_eig_resample_F needs an unsharded network; use the block form");
+    if (net->row0 != 0 || net->nrows != net->N) {
+        // Row shards with the engine's own communicator: per node block, slab partials on every rank -> NCCL all-reduce ->
+        // the owner of the block's rows draws it -> NCCL broadcast of the block's features; the pair statistics, which
+        // accumulate on whichever rank drew a block, are summed at the end.  All in-stream, no host round trips.
+        if (!ctx->comm) return gk_fail(ctx, GK_EINVAL, "gk_eig_resample_F on a row-sharded network needs gk_comm_init (or use the block form)");
+        if (out_prec || out_h) return gk_fail(ctx, GK_EUNSUPPORTED, "per-node conditionals are available on single-rank networks only");
+        const int world = gk_comm_world(ctx), rank = gk_comm_rank(ctx);
+        int rc = gk_eig_sweep_begin(ctx, e, sigma_F, normals);
+        if (rc) return rc;
+        const int bn = gk_eig_block_nodes(e);
+        double *acc = (double *)gk_scratch(ctx, 10, gk_eig_acc_len(e) * 8);
+        double *fblk = (double *)gk_scratch(ctx, 11, (size_t)bn * e->D * 8);
+        if (!acc || !fblk) return GK_ENOMEM;
+        for (int rk = 0; rk < world; ++rk) {
+            int s0, s1;
+            gk_comm_row_range(e->N, rk, world, &s0, &s1);
+            if (rk == rank && (s0 != net->row0 || s1 != net->row0 + net->nrows))
+                return gk_fail(ctx, GK_EINVAL, "rank %d of %d must hold rows [%d, %d)", rank, world, s0, s1);
+            for (int n0 = s0; n0 < s1; n0 += bn) {
+                const int nb = std::min(bn, s1 - n0);
+                if ((rc = gk_eig_block_partials(ctx, e, n0, nb, acc))) return rc;
+                if ((rc = gk_comm_allreduce_f64(ctx, acc, gk_eig_acc_len(e)))) return rc;
+                if (rank == rk && (rc = gk_eig_block_sample(ctx, e, n0, nb, acc, fblk))) return rc;
+                if ((rc = gk_comm_broadcast(ctx, fblk, (size_t)nb * e->D * 8, rk))) return rc;
+                if (rank != rk && (rc = gk_eig_set_block(ctx, e, n0, nb, fblk))) return rc;
+            }
+        }
+        if ((rc = gk_comm_allreduce_f64(ctx, e->glob + GK_EIG_GLOB_PQ, GK_EIG_GLOB_LEN - GK_EIG_GLOB_PQ))) return rc;
+        return gk_eig_sweep_end(ctx, e, F_out, stats);
+    }
     GK_CUDA(ctx, cudaSetDevice(ctx->device));
     const size_t N = e->N; const int D = e->D;
     GK_CUDA(ctx, cudaMemcpyAsync(e->z, normals, N * D * 8, cudaMemcpyHostToDevice, ctx->stream));

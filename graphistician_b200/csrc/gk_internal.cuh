@@ -16,7 +16,9 @@ struct gk_timing {
     std::vector<std::pair<cudaEvent_t, cudaEvent_t>> pending; std::vector<double> pending_bytes;
 };
 
+struct gk_comm;
 struct gk_ctx {
+    gk_comm *comm = nullptr;                  // the engine's own NCCL communicator (gk_comm.cu), or none
     int device = 0;
     cudaStream_t stream = nullptr;
     bool own_stream = false;
@@ -51,6 +53,14 @@ struct gk_net {
 };
 
 int gk_fail(gk_ctx *ctx, int code, const char *fmt, ...);
+// gk_comm.cu: in-stream collectives on the context's communicator (no-ops for a world of one)
+void gk_comm_release(gk_ctx *ctx);
+int gk_comm_allreduce_f64(gk_ctx *ctx, double *buf_dev, size_t n);
+int gk_comm_allreduce_i64(gk_ctx *ctx, long long *buf_dev, size_t n);
+int gk_comm_broadcast(gk_ctx *ctx, void *buf_dev, size_t bytes, int root);
+void gk_comm_row_range(int N, int rank, int world, int *r0, int *r1);
+extern "C" int gk_comm_rank(gk_ctx *ctx);
+extern "C" int gk_comm_world(gk_ctx *ctx);
 // true the first time this context sees kernel `f` (cudaFuncSetAttribute is per device, so the memo is per context)
 static inline bool gk_attr_needed(gk_ctx *ctx, const void *f) {
     for (const void *g : ctx->attr_funcs) if (g == f) return false;

@@ -422,11 +422,15 @@ extern "C" int gk_latent_hmc_end(gk_ctx *ctx, gk_latent *l, double log_u, int *a
 extern "C" int gk_latent_hmc(gk_ctx *ctx, gk_latent *l, int target, double step, int nsteps, const double *p0, double log_u,
                              int *accepted, double *log_ratio) {
     if (!ctx || !l) return GK_EINVAL;
-    if (l->net->row0 != 0 || l->net->nrows != l->N) return gk_fail(ctx, GK_EINVAL, "gk_latent_hmc needs an unsharded network; use the begin/pass/advance/end form");
+    const bool sharded = l->net->row0 != 0 || l->net->nrows != l->N;
+    if (sharded && !ctx->comm)
+        return gk_fail(ctx, GK_EINVAL, "gk_latent_hmc on a row-sharded network needs gk_comm_init (or use the begin/pass/advance/end form)");
     int rc = gk_latent_hmc_begin(ctx, l, target, step, nsteps, p0);
     if (rc) return rc;
     for (int s = 0; s <= nsteps; ++s) {
-        if ((rc = gk_latent_hmc_pass(ctx, l, nullptr)) || (rc = gk_latent_hmc_advance(ctx, l, nullptr))) { l->target = -1; return rc; }
+        // row shards: the accumulator of this rank's pair pass is summed over the ranks in-stream (NCCL) before the update
+        if ((rc = gk_latent_hmc_pass(ctx, l, nullptr)) || (sharded && (rc = gk_comm_allreduce_f64(ctx, l->acc, lat_acc_len(l)))) ||
+            (rc = gk_latent_hmc_advance(ctx, l, nullptr))) { l->target = -1; return rc; }
     }
     return gk_latent_hmc_end(ctx, l, log_u, accepted, log_ratio);
 }

@@ -330,6 +330,21 @@ extern "C" int gk_sbm_set_block(gk_ctx *ctx, int n0, int nb, const int32_t *c_in
     return GK_OK;
 }
 
+// device-side forms of get / set for the row-sharded sweep: the labels of a node block go owner -> NCCL broadcast -> the
+// other ranks without touching the host (no stream synchronisation)
+extern "C" int gk_sbm_export_block_dev(gk_ctx *ctx, int n0, int nb, int32_t *lab_dev) {
+    if (!ctx || !ctx->sweep || !lab_dev || n0 < 0 || nb <= 0 || n0 + nb > ctx->sweep->N) return GK_EINVAL;
+    GK_CUDA(ctx, cudaMemcpyAsync(lab_dev, ctx->sweep->c + n0, (size_t)nb * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+    return GK_OK;
+}
+extern "C" int gk_sbm_import_block_dev(gk_ctx *ctx, int n0, int nb, const int32_t *lab_dev) {
+    if (!ctx || !ctx->sweep || !lab_dev || n0 < 0 || nb <= 0 || n0 + nb > ctx->sweep->N) return GK_EINVAL;
+    gk_sweep *sw = ctx->sweep;
+    k_set_block<<<(nb + 255) / 256, 256, 0, ctx->stream>>>(sw->c, sw->c8, sw->sizes, lab_dev, n0, nb);
+    GK_CHECK_LAUNCH(ctx);
+    return GK_OK;
+}
+
 extern "C" int gk_sbm_sweep_end(gk_ctx *ctx, gk_net *net, int32_t *c_out, double *out_lp, int64_t *out_nchanged) {
     if (!ctx || !ctx->sweep) return GK_EINVAL;
     gk_sweep *sw = ctx->sweep;
@@ -350,12 +365,58 @@ extern "C" int gk_sbm_sweep_end(gk_ctx *ctx, gk_net *net, int32_t *c_out, double
     return GK_OK;
 }
 
+// The row-sharded sweep with the engine's own communicator (gk_comm_init): per node block, partial statistics over this
+// rank's rows -> NCCL all-reduce -> the rank that owns the block's rows draws it -> NCCL broadcast of the block's labels.
+// Everything is enqueued on the context stream; the host does not wait inside the sweep.
+static int sbm_sweep_sharded(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, const double *log_m, const double *p,
+                             const double *mu, const double *sigma, int self_mode, int sampler, double beta,
+                             const double *uniforms, int block_nodes, double *out_lp, int64_t *out_nchanged) {
+    if (!ctx->comm)
+        return gk_fail(ctx, GK_EINVAL, "gk_sbm_sweep on a row-sharded network needs gk_comm_init (or use the begin/partials/sample/end form)");
+    if (out_lp) return gk_fail(ctx, GK_EUNSUPPORTED, "per-node log conditionals are available on single-rank networks only");
+    const int world = gk_comm_world(ctx), rank = gk_comm_rank(ctx), N = net->N;
+    int r0, r1;
+    gk_comm_row_range(N, rank, world, &r0, &r1);
+    if (r0 != net->row0 || r1 != net->row0 + net->nrows)
+        return gk_fail(ctx, GK_EINVAL, "rank %d of %d must hold rows [%d, %d), the network holds [%d, %d)", rank, world, r0, r1, net->row0, net->row0 + net->nrows);
+    int rc = gk_sbm_sweep_begin(ctx, net, c_inout, K, log_m, p, mu, sigma, self_mode, sampler, beta, uniforms);
+    if (rc) return rc;
+    gk_sweep *sw = ctx->sweep;
+    int bn = block_nodes > 0 ? block_nodes : 1024;
+    bn = std::max(128, bn / 128 * 128);
+    double *stats = (double *)gk_scratch(ctx, 10, gk_sbm_partial_len(ctx, bn) * 8);
+    int32_t *lab = (int32_t *)gk_scratch(ctx, 11, (size_t)bn * 4);
+    if (!stats || !lab) return GK_ENOMEM;
+    ctx->last_cells.valid = false;
+    for (int rk = 0; rk < world; ++rk) {
+        int s0, s1;
+        gk_comm_row_range(N, rk, world, &s0, &s1);
+        for (int n0 = s0; n0 < s1; n0 += bn) {
+            const int nb = std::min(bn, s1 - n0);
+            if ((rc = gk_sbm_block_partials(ctx, net, n0, nb, stats))) return rc;
+            if ((rc = gk_comm_allreduce_f64(ctx, stats, gk_sbm_partial_len(ctx, nb)))) return rc;
+            if (rank == rk) {
+                if ((rc = gk_sbm_block_sample(ctx, net, n0, nb, stats))) return rc;
+                GK_CUDA(ctx, cudaMemcpyAsync(lab, sw->c + n0, (size_t)nb * 4, cudaMemcpyDeviceToDevice, ctx->stream));
+            }
+            if ((rc = gk_comm_broadcast(ctx, lab, (size_t)nb * 4, rk))) return rc;
+            if (rank != rk) {
+                k_set_block<<<(nb + 255) / 256, 256, 0, ctx->stream>>>(sw->c, sw->c8, sw->sizes, lab, n0, nb);
+                GK_CHECK_LAUNCH(ctx);
+            }
+        }
+    }
+    if ((rc = gk_comm_allreduce_i64(ctx, (long long *)sw->nchanged, 1))) return rc;     // every block was counted by its owner
+    return gk_sbm_sweep_end(ctx, net, c_inout, nullptr, out_nchanged);
+}
+
 extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, const double *log_m, const double *p,
                             const double *mu, const double *sigma, int self_mode, int sampler, double beta,
                             const double *uniforms, int block_nodes, double *out_lp, int64_t *out_nchanged) {
     if (!ctx || !net || !c_inout) return GK_EINVAL;
-    if (net->row0 != 0 || net->nrows != net->N) return gk_fail(ctx, GK_EINVAL, "gk_sbm_sweep needs an unsharded network; use the begin/partials/sample/end form");
     if (K == 1) { if (out_nchanged) *out_nchanged = 0; return GK_OK; }      // C == 1: no-op (adjacency.py:657-658)
+    if (net->row0 != 0 || net->nrows != net->N)
+        return sbm_sweep_sharded(ctx, net, c_inout, K, log_m, p, mu, sigma, self_mode, sampler, beta, uniforms, block_nodes, out_lp, out_nchanged);
     int rc = gk_sbm_sweep_begin(ctx, net, c_inout, K, log_m, p, mu, sigma, self_mode, sampler, beta, uniforms);
     if (rc) return rc;
     gk_sweep *sw = ctx->sweep;

@@ -280,7 +280,9 @@ class DeviceEigenmodel:
         D = self.D
         if self.comm is not None:
             assert not want_conditionals, "per-node conditionals are available on single-rank networks only"
-            return self._resample_F_sharded(sigma_F, z)
+            if not self.net.native():
+                return self._resample_F_sharded(sigma_F, z)
+            # the engine's own communicator: one C call, collectives in-stream; the statistics come back already summed
         F = np.empty((self.N, D))
         prec = np.empty((self.N, D, D)) if want_conditionals else None
         h = np.empty((self.N, D)) if want_conditionals else None
@@ -391,7 +393,7 @@ class DeviceLatent:
         ``allreduce`` (row-sharded form) is called between every pair pass and the update that consumes it and
         must sum the accumulator at ``acc_ptr`` over the ranks.  Returns (accepted, log_ratio)."""
         p = np.ascontiguousarray(np.atleast_1d(p0), dtype=np.float64)
-        if allreduce is None and self.comm is not None:
+        if allreduce is None and self.comm is not None and not self.net.native():
             allreduce, acc_ptr = (lambda: self.comm.allreduce_(self._acc)), ctypes.c_void_p(self._acc.data_ptr())
         acc, ratio = ctypes.c_int(0), ctypes.c_double(0.0)
         lib, c, h = self.ctx.lib, self.ctx.h, self.h

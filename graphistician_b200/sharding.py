@@ -140,6 +140,13 @@ class DeviceEngine(object):
         lab = np.ascontiguousarray(lab, dtype=np.int32)
         self.ctx.check(self.lib.gk_sbm_set_block(self.ctx.h, int(n0), int(nb), ptr(lab)))
 
+    def export_block_dev(self, n0, nb, lab_t):
+        """labels of the block -> the device tensor ``lab_t`` (int32), in-stream, no host synchronisation"""
+        self.ctx.check(self.lib.gk_sbm_export_block_dev(self.ctx.h, int(n0), int(nb), _ptr(lab_t)))
+
+    def import_block_dev(self, n0, nb, lab_t):
+        self.ctx.check(self.lib.gk_sbm_import_block_dev(self.ctx.h, int(n0), int(nb), _ptr(lab_t)))
+
     def sweep_end(self):
         from ._lib import ptr
         c = np.empty(self.N, np.int32)
@@ -160,6 +167,10 @@ class ShardedDeviceNetwork(object):
         self.diagA, self.diagW = diagA, diagW
         self.local = getattr(engine, "net", None)    # the DeviceNetwork shard (None for the CPU test engine)
         self.ctx = getattr(engine, "ctx", None)
+
+    def native(self):
+        """True when this rank's libgk context holds the engine's own communicator over the same ranks."""
+        return self.ctx is not None and getattr(self.ctx, "native_world", 1) == self.comm.world and self.comm.world > 1
 
     def block_stats(self, c, K):
         n, sw, sww = self.engine.block_stats(c, K)
@@ -190,13 +201,36 @@ class ShardedDeviceNetwork(object):
         the owner of the block's rows draws it -> label broadcast."""
         assert not want_lp, "per-node log conditionals are available on single-rank networks only"
         eng, comm, N = self.engine, self.comm, self.N
+        if self.native():                            # one C call: block loop and NCCL collectives inside libgk, in-stream
+            return self.local.sbm_sweep(c, log_m, p, mu, sigma, uniforms, self_mode=self_mode, sampler=sampler, beta=beta,
+                                        block_nodes=block_nodes)
         eng.sweep_begin(c, log_m, p, mu, sigma, uniforms, self_mode, sampler, beta)
         bn = block_nodes if block_nodes > 0 else 1024
         bn = max(ALIGN, bn // ALIGN * ALIGN)
+        on_device = comm.device == "cuda" and hasattr(eng, "export_block_dev")
+        if on_device:                                # exchange buffers live on the device and are reused for every block
+            import torch
+            if getattr(self, "_xbuf", None) is None or self._xbuf.numel() < eng.partial_len(bn):
+                self._xbuf = comm.buffer(eng.partial_len(bn))
+                self._xlab = torch.zeros(bn, dtype=torch.int32, device=self._xbuf.device)
         for rk in range(comm.world):
             s0, s1 = row_range(N, rk, comm.world)
             for n0 in range(s0, s1, bn):
                 nb = min(bn, s1 - n0)
+                if on_device:
+                    # partial statistics -> NCCL all-reduce -> owner draws -> NCCL broadcast of the labels: every step is
+                    # enqueued on the one stream libgk and NCCL share; the host never waits inside the sweep
+                    buf = self._xbuf[:eng.partial_len(nb)]
+                    lab = self._xlab[:nb]
+                    eng.block_partials(n0, nb, buf)
+                    comm.allreduce_(buf)
+                    if comm.rank == rk:
+                        eng.block_sample(n0, nb, buf)
+                        eng.export_block_dev(n0, nb, lab)
+                    comm.dist.broadcast(lab, src=comm._global(rk), group=comm.group)
+                    if comm.rank != rk:
+                        eng.import_block_dev(n0, nb, lab)
+                    continue
                 buf = comm.buffer(eng.partial_len(nb))
                 eng.block_partials(n0, nb, buf)
                 comm.allreduce_(buf)
@@ -229,8 +263,11 @@ def sharded_device_network(A, W, comm, dtype="f32", ctx=None, engine_factory=Non
         from . import _lib
         ctx = ctx or _lib.default_context()
         if comm.device == "cuda":
+            import os
             import torch
             ctx.set_stream(torch.cuda.current_stream().cuda_stream)
+            if comm.world > 1 and not os.environ.get("GK_NO_NATIVE_COMM"):
+                ctx.init_comm(comm)                  # libgk issues the sweeps' collectives itself from here on
         engine = DeviceEngine(A, W, r0, r1, dtype=dtype, ctx=ctx)
     else:
         engine = engine_factory(A, W, r0, r1)

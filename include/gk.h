@@ -105,6 +105,11 @@ int gk_sbm_block_sample(gk_ctx *ctx, gk_net *net, int n0, int nb, const double *
 /* labels of a node block: read after the owner sampled / overwrite on the other ranks (host arrays) */
 int gk_sbm_get_block(gk_ctx *ctx, int n0, int nb, int32_t *c_out);
 int gk_sbm_set_block(gk_ctx *ctx, int n0, int nb, const int32_t *c_in);
+/* The same exchange through DEVICE buffers, enqueued on the ctx stream without host synchronisation: the owner exports the
+ * block's labels, NCCL broadcasts the buffer in-stream, the other ranks import it (labels must lie in [0, K): they come
+ * from gk_sbm_block_sample on the owner).  stochastic_block_model.py:252-302 keeps c replicated on every rank this way. */
+int gk_sbm_export_block_dev(gk_ctx *ctx, int n0, int nb, int32_t *labels_dev);
+int gk_sbm_import_block_dev(gk_ctx *ctx, int n0, int nb, const int32_t *labels_dev);
 int gk_sbm_sweep_end(gk_ctx *ctx, gk_net *net, int32_t *c_out, double *out_lp, int64_t *out_nchanged);
 
 /* ---- eigenmodel (logistic / probit), K3-K6 ---------------------------------------------------------
@@ -319,6 +324,21 @@ int gk_ais_sweep(gk_ctx *ctx, gk_ais *ais, const double *log_pi, const double *B
  * seeded by `seed` (the Python shell draws the seed from np.random); the caller forms log Z = -log(P) + logsumexp. */
 int gk_ais_run(gk_ctx *ctx, gk_ais *ais, int model, double b0, double b1, const double *alpha0, int n_temps,
                int steps_per_temp, const int32_t *f0, uint64_t seed, double *log_weights);
+
+/* ---- the engine's own communicator (no counterpart in the reference, which is single-process) ---------
+ * One process per GPU.  Rank 0 asks for an id (128 bytes, NCCL's ncclUniqueId), the host passes it to the other ranks by
+ * any channel it has (torch.distributed, MPI, a file), every rank calls gk_comm_init.  From then on the calls that take a
+ * ROW-SHARDED network -- gk_sbm_sweep, gk_eig_resample_F, gk_latent_hmc -- run their collectives themselves, in-stream
+ * between their kernels: per node block the partial statistics are all-reduced, the owner of the block's rows draws it and
+ * its labels / features are broadcast (rows of rank r: whole blocks of 128 rows, spread evenly: [128*(nblk*r/world),
+ * 128*(nblk*(r+1)/world)) with nblk = ceil(N/128)).  libnccl.so.2 is opened at run time (dlopen). */
+int gk_comm_unique_id(gk_ctx *ctx, uint8_t *id128);
+int gk_comm_init(gk_ctx *ctx, const uint8_t *id128, int rank, int world);
+int gk_comm_destroy(gk_ctx *ctx);
+int gk_comm_rank(gk_ctx *ctx);
+int gk_comm_world(gk_ctx *ctx);
+/* in-stream SUM over the ranks of n doubles at a device address (for the host-driven block forms) */
+int gk_comm_allreduce(gk_ctx *ctx, double *buf_dev, size_t n);
 
 #ifdef __cplusplus
 }

@@ -1,6 +1,6 @@
-"""Two-GPU (NCCL) run of the row-sharded paths against the single-GPU path of the same model classes.
+"""Multi-GPU (NCCL; 2, 4 and 8 ranks) run of the row-sharded paths against the single-GPU path of the same model classes.
 
-Needs two CUDA devices (``gpurun --gpus 2``); skipped otherwise.  One process per GPU; every rank seeds ``np.random``
+Needs as many CUDA devices as ranks (``gpurun --gpus N``); skipped otherwise.  One process per GPU; every rank seeds ``np.random``
 identically, so the replicated host state must stay identical and equal to the unsharded run: block labels and
 integer counts bit-exact, fp parameters to round-off (different summation order across shards)."""
 import os
@@ -17,7 +17,7 @@ def _free_port():
     return port
 
 
-def _run_models(comm):
+def _run_models(comm, world=2):
     """The three model families on a (possibly sharded) network; returns the sampled state."""
     from graphistician_b200.stochastic_block_model import GaussianStochasticBlockModel
     from graphistician_b200.eigenmodel import LogisticEigenmodel
@@ -25,7 +25,7 @@ def _run_models(comm):
     from graphistician_b200.old_abstractions import FixedGaussianNetwork, network_for
     out = {}
     # --- Gaussian SBM, shared c (config 2 model)
-    N, C, B = 640, 6, 2
+    N, C, B = max(640, 128 * world + 128), 6, 2
     np.random.seed(3)
     truth = GaussianStochasticBlockModel(N, B, C=C, dtype="f64")
     net = truth.rvs()
@@ -39,7 +39,7 @@ def _run_models(comm):
     out["sbm_c"], out["sbm_p"], out["sbm_mu"] = model.c.copy(), model.p.copy(), model.mus.copy()
     out["sbm_ll"] = model.log_likelihood(network)
     # --- logistic eigenmodel, injected omega / normals, then the device PG path
-    N, D = 512, 4
+    N, D = max(512, 128 * world), 4
     np.random.seed(5)
     rng = np.random.RandomState(9)
     eg = LogisticEigenmodel(N, D, p=0.1, sigma_F=1.0, lmbda=np.ones(D), dtype="f64")
@@ -57,7 +57,7 @@ def _run_models(comm):
     eg2.resample(network)                                   # device Polya-gamma draw (counter-based: shard invariant)
     out["eig_F_pg"], out["eig_ll"] = eg2.F.copy(), eg2.log_likelihood(network)
     # --- latent distance, injected HMC draws
-    N, dim = 384, 2
+    N, dim = max(384, 128 * world), 2
     np.random.seed(7)
     lat = LatentDistanceAdjacencyDistribution(N, dim=dim, dtype="f64")
     A = lat.rvs().astype(np.uint8)
@@ -88,10 +88,10 @@ def _worker(rank, world, port, q):
         from graphistician_b200.sharding import Comm
         comm = Comm()
         assert comm.device == "cuda" and comm.world == world
-        sharded = _run_models(comm)
+        sharded = _run_models(comm, world)
         dist.barrier()
         if rank == 0:
-            single = _run_models(None)
+            single = _run_models(None, world)
             res = {}
             for k in single:
                 a, b = np.asarray(sharded[k]), np.asarray(single[k])
@@ -102,15 +102,16 @@ def _worker(rank, world, port, q):
         dist.destroy_process_group()
 
 
-def test_two_rank_sharded_models_match_single_gpu():
+@pytest.mark.parametrize("world", [2, 4, 8])
+def test_sharded_models_match_single_gpu(world):
     import torch
-    if torch.cuda.device_count() < 2:
-        pytest.skip("needs two GPUs (gpurun --gpus 2)")
+    if torch.cuda.device_count() < world:
+        pytest.skip("needs %d GPUs (gpurun --gpus %d)" % (world, world))
     import torch.multiprocessing as mp
     ctx = mp.get_context("spawn")
     q = ctx.Queue()
     port = _free_port()
-    procs = [ctx.Process(target=_worker, args=(r, 2, port, q)) for r in range(2)]
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
     for p in procs:
         p.start()
     res = q.get(timeout=600)
