@@ -394,7 +394,7 @@ class Runner:
 def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, first_sweep=False, e2e=True):
     """One workload record: value (resident), e2e (host buffers), roofline of the dominant kernel family,
     launches, clocks, and (rank 0, one GPU) the CPU baseline."""
-    wl = setup_workload(name, args, 0 if rows else R.rank, dtype)
+    wl = setup_workload(name, args, 0, dtype)      # every rank: the same data and chain seed, so the per-GPU work is identical
     model, network, d = wl["model"], wl["network"], wl["data"]
     if rows:                                                   # one chain, rows of A / W sharded over the ranks
         from graphistician_b200.sharding import Comm
@@ -519,8 +519,8 @@ def run_ours(args):
            "warmup": args.warmup, "ms_per_step": rec["ms_per_step"], "higher_is_better": True,
            "scaling": "strong" if rows else "weak", "vs_baseline": None, "dtype": args.dtype, "data": "synthetic",
            "config": rec["config"],
-           "parallelism": ("one chain, rows sharded x%d" if rows else "independent chains x%d") % R.world}
-    for k in ("l2", "gpu_launches", "clocks", "e2e", "roofline", "n_changed_last_sweep", "regime", "cpu_baseline"):
+           "parallelism": ("one chain, rows sharded x%d" if rows else "replica chains x%d (same data and seed on every GPU: identical work per GPU, no data-path collective)") % R.world}
+    for k in ("l2", "gpu_launches", "clocks", "e2e", "roofline", "n_changed_last_sweep", "extra_warmup_sweeps", "regime", "cpu_baseline"):
         if k in rec:
             out[k] = rec[k]
     if primary == "sbm" and extras:
