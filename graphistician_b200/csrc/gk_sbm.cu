@@ -278,9 +278,15 @@ extern "C" int gk_sbm_block_partials(gk_ctx *ctx, gk_net *net, int n0, int nb, d
 
 template <typename T, int B>
 static int launch_sample(gk_ctx *ctx, gk_net *net, gk_sweep *sw, int n0, int nb, const double *stats_dev) {
-    int wpb = 8, grid = std::min((nb + wpb - 1) / wpb, ctx->num_sms * 4);
-    k_lp_from_stats<B><<<grid, wpb * 32, 0, ctx->stream>>>(stats_dev, sw->T, net->diagA, net->diagW, n0, nb, sw->N, sw->K, sw->lp);
-    GK_CHECK_LAUNCH(ctx);
+    {
+        const int KP = gk_lp_kp(sw->K), npc = GK_LP_THREADS / KP;
+        const size_t sm = gk_lp_smem(sw->K, sw->S);
+        if (sm > 48 * 1024 && gk_attr_needed(ctx, (const void *)k_lp_from_stats<B>))
+            GK_CUDA(ctx, cudaFuncSetAttribute(k_lp_from_stats<B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
+        k_lp_from_stats<B><<<(nb + npc - 1) / npc, GK_LP_THREADS, sm, ctx->stream>>>(stats_dev, sw->T, net->diagA, net->diagW, n0, nb,
+                                                                                   sw->N, sw->K, KP, sw->lp);
+        GK_CHECK_LAUNCH(ctx);
+    }
     gk_seq_params P;
     P.n0 = n0; P.nb = nb; P.K = sw->K; P.N = sw->N; P.ld = net->ld; P.row0 = net->row0; P.sampler = sw->sampler;
     P.c = sw->c; P.c8 = sw->c8; P.sizes = sw->sizes; P.lp = sw->lp; P.u = sw->u; P.T = sw->T;

@@ -12,39 +12,45 @@ struct gk_tables {
 };
 
 // lp_base[n][k] = log m[k] + sum_{k',s} out[k'][s] COt + in[k'][s] CIt + self term   (no block-size term)
-// stats: [nb_pad][2][K*S] doubles.  One warp per node, lane = candidate block k.
+// stats: [nb_pad][2][K*S] doubles.  A CTA takes 256 / KP nodes (KP = K rounded up to 8, 16 or 32); the two coefficient
+// tables and the nodes' statistics are staged in shared memory with coalesced loads, then thread (node, k) runs the sum in
+// the order of the plain loop.  (The earlier one-warp-per-node form fetched every term from L2 just before its use: 37 us
+// per 1024-node block for 0.4 MFLOP.)
+#define GK_LP_THREADS 256
+static inline int gk_lp_kp(int K) { return K > 16 ? 32 : (K > 8 ? 16 : 8); }
+static inline size_t gk_lp_smem(int K, int S) { return ((size_t)2 * K * S * K + (size_t)(GK_LP_THREADS / gk_lp_kp(K)) * 2 * K * S) * 8; }
+
 template <int B>
-__global__ void k_lp_from_stats(const double *__restrict__ stats, gk_tables Tb, const uint8_t *__restrict__ diagA,
-                                const double *__restrict__ diagW, int n0, int nb, int N, int K, double *__restrict__ lp) {
+__global__ void __launch_bounds__(GK_LP_THREADS)
+k_lp_from_stats(const double *__restrict__ stats, gk_tables Tb, const uint8_t *__restrict__ diagA,
+                const double *__restrict__ diagW, int n0, int nb, int N, int K, int KP, double *__restrict__ lp) {
     constexpr int S = gk_sdim<B>::S;
-    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, wpb = blockDim.x >> 5;
-    const int KS = K * S;
-    for (int i = blockIdx.x * wpb + warp; i < nb; i += gridDim.x * wpb) {
-        const int n = n0 + i;
-        if (n >= N) continue;
-        const double *so = stats + ((size_t)i * 2 + 0) * KS, *si = stats + ((size_t)i * 2 + 1) * KS;
-        double v = 0.0;
-        if (lane < K) {
-            v = Tb.logm[lane] + Tb.selfc[lane];
-            // same summation order as the plain loop; unrolled so that the 4 loads of 8 terms are in flight together
-            // (the un-unrolled loop was one L1 round trip per term: 35 us per block, 3.6 % issue-active)
-            const double *co = Tb.COt + lane, *ci = Tb.CIt + lane;
+    extern __shared__ double s_lp[];
+    const int KS = K * S, NPC = GK_LP_THREADS / KP;
+    double *s_co = s_lp, *s_ci = s_lp + (size_t)KS * K, *s_st = s_ci + (size_t)KS * K;   // [KS][K], [KS][K], [NPC][2][KS]
+    const int tid = threadIdx.x, i0 = blockIdx.x * NPC;
+    for (int t = tid; t < KS * K; t += GK_LP_THREADS) { s_co[t] = Tb.COt[t]; s_ci[t] = Tb.CIt[t]; }
+    const int nn = min(NPC, nb - i0);
+    for (int t = tid; t < nn * 2 * KS; t += GK_LP_THREADS) s_st[t] = stats[(size_t)i0 * 2 * KS + t];
+    __syncthreads();
+    const int il = tid / KP, k = tid % KP, i = i0 + il, n = n0 + i;
+    if (il >= nn || k >= K || n >= N) return;
+    const double *so = s_st + (size_t)il * 2 * KS, *si = so + KS;
+    double v = Tb.logm[k] + Tb.selfc[k];
 #pragma unroll 8
-            for (int j = 0; j < KS; ++j) v += __ldg(so + j) * __ldg(co + (size_t)j * K) + __ldg(si + j) * __ldg(ci + (size_t)j * K);
-            if (diagA[n]) {
-                double x[S]; x[0] = 1.0;
+    for (int j = 0; j < KS; ++j) v += so[j] * s_co[j * K + k] + si[j] * s_ci[j * K + k];
+    if (diagA[n]) {
+        double x[S]; x[0] = 1.0;
 #pragma unroll
-                for (int b = 0; b < B; ++b) x[1 + b] = diagW[(size_t)n * B + b];
+        for (int b = 0; b < B; ++b) x[1 + b] = diagW[(size_t)n * B + b];
 #pragma unroll
-                for (int b = 0; b < B; ++b)
+        for (int b = 0; b < B; ++b)
 #pragma unroll
-                    for (int b2 = b; b2 < B; ++b2) x[gk_sym_idx(B, b, b2)] = x[1 + b] * x[1 + b2];
+            for (int b2 = b; b2 < B; ++b2) x[gk_sym_idx(B, b, b2)] = x[1 + b] * x[1 + b2];
 #pragma unroll
-                for (int s = 0; s < S; ++s) v += x[s] * Tb.selfa[(size_t)s * K + lane];
-            }
-            lp[(size_t)i * K + lane] = v;
-        }
+        for (int s = 0; s < S; ++s) v += x[s] * Tb.selfa[(size_t)s * K + k];
     }
+    lp[(size_t)i * K + k] = v;
 }
 
 __device__ __forceinline__ long long gk_sbm_clock() { long long t; asm volatile("mov.u64 %0, %%clock64;" : "=l"(t) :: "memory"); return t; }

@@ -203,6 +203,41 @@ class StochasticBlockModel(AldousHooverNetwork):
         u = np.full(len(z), 0.5); u[n] = np.random.rand()
         return int(self._sweep(theta, A, z, beta, u, only=n)[n])
 
+    def collapsed_sample_f(self, theta, n, A, f, uniform=None, return_lp=False):
+        """internals/graph_models.py:299-335 (unused by the reference's own drivers): Gibbs update of z[n] with the block
+        probabilities B integrated out, ln p(z_n = r) = ln pi[r] + sum_{r1, r2} [betaln(m + b1, mhat + b0) - betaln(b1, b0)]
+        with m / mhat the edges / non-edges of A[np.ix_(z == r1, z == r2)] under z_n = r.  The reference rebuilds every one of
+        the R^2 sub-matrices for every candidate (O(R^3 N^2) per node); here the R x R table comes from ONE device pass
+        (gk_block_stats, cached per labelling by the caller through ``table``) and is moved between candidates by node n's own
+        row and column counts.  The reference draws inside its r loop (:331-333, an indentation slip that costs R - 1
+        uniforms); the label returned is the draw from the complete vector, as there."""
+        (B, pi) = theta
+        z = np.array(f, dtype=np.int64)
+        R = self.R
+        Ab = np.asarray(A) != 0
+        m, _ = _total_edge_stats(A, z, R)
+        m = m.astype(np.float64)
+        sz = np.bincount(z, minlength=R).astype(np.float64)
+        a = int(z[n]); s = float(Ab[n, n])
+        oth = np.ones(len(z), bool); oth[n] = False
+        co = np.bincount(z[Ab[n, :] & oth], minlength=R).astype(np.float64)      # n -> class r
+        ci = np.bincount(z[Ab[:, n] & oth], minlength=R).astype(np.float64)      # class r -> n
+        m0 = m.copy(); m0[a, :] -= co; m0[:, a] -= ci; m0[a, a] -= s
+        sz0 = sz.copy(); sz0[a] -= 1
+        lp = np.log(np.asarray(pi, dtype=np.float64)).copy()
+        for r in range(R):
+            mr = m0.copy(); mr[r, :] += co; mr[:, r] += ci; mr[r, r] += s
+            szr = sz0.copy(); szr[r] += 1
+            pairs = np.outer(szr, szr)
+            lp[r] += np.sum(betaln(mr + self.b1, pairs - mr + self.b0) - betaln(self.b1, self.b0))
+        if uniform is None:
+            for _ in range(R - 1):                   # the draws the reference makes (and discards) inside its loop
+                np.random.rand()
+            uniform = np.random.rand()
+        mx = lp.max(); p = np.exp(lp - mx); p /= p.sum()
+        zn = int(min(np.searchsorted(np.cumsum(p), uniform, side="left"), R - 1))
+        return (zn, lp) if return_lp else zn
+
     def _sweep(self, theta, A, z, beta, u, only=None):
         (B, pi) = theta
         dev = _device(A)

@@ -61,6 +61,25 @@ class GaussianWeights(Gaussian):
     def resample_from_mf(self):
         self._resample_from_mf()
 
+    def expected_log_likelihood(self, network):
+        """internals/weights.py:174-198: sum over ALL N^2 ordered pairs (no A mask, as the reference writes it) of
+        Gaussian().negentropy(E_x = E_W[n1, n2], E_xxT = E_WWT[n1, n2], ...).sum().  The per-pair term is linear in
+        (1, E_W, E_WWT), so the N^2 Python loop becomes three sums over the network's arrays (chunked NumPy: a host
+        diagnostic, not a sweep)."""
+        E_W = getattr(network, "E_W", None)
+        E_W = np.asarray(network.W if E_W is None else E_W)
+        N = E_W.shape[0]
+        assert E_W.shape == (N, N, self.B)
+        E_WWT = getattr(network, "E_WWT", None)
+        c0, c1, C2 = self.expected_log_likelihood_coefficients()
+        s1 = np.zeros(self.B); s2 = np.zeros((self.B, self.B))
+        for r0 in range(0, N, 256):
+            w = E_W[r0:r0 + 256].astype(np.float64)
+            s1 += w.sum(axis=(0, 1))
+            s2 += (np.einsum("ijb,ijc->bc", w, w) if E_WWT is None
+                   else np.asarray(E_WWT[r0:r0 + 256], dtype=np.float64).sum(axis=(0, 1)))
+        return float(N * N * c0 + c1.dot(s1) + np.sum(C2 * s2))
+
     def expected_log_likelihood_coefficients(self):
         """Coefficients (c0, c1[B], C2[B,B]) of E_q[ln N(w | mu, Sigma)] = c0 + c1.w + w^T C2 w as the reference's
         Gaussian.negentropy writes it (internals/distributions.py:278-308; its -0.5*log(2*pi) constant kept)."""

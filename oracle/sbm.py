@@ -305,6 +305,25 @@ def ais_naive_sample_f_loops(A, z, B, pi, beta, u):
     return z, lps
 
 
+def ais_collapsed_ln_post_loops(A, z, n, pi, b0, b1):
+    """internals/graph_models.py:299-335, the log posterior vector of collapsed_sample_f literally: for every candidate r
+    and every (r1, r2), the edges / non-edges of A[np.ix_(zother == r1, zother == r2)]."""
+    from scipy.special import betaln
+    R = len(pi)
+    Ab = A.astype(bool)
+    zother = np.array(z).astype(int)
+    ln_pi_post = np.log(pi).astype(np.float64)
+    for r in range(R):
+        zother[n] = r
+        for r1 in range(R):
+            for r2 in range(R):
+                Ar1r2 = Ab[np.ix_(zother == r1, zother == r2)]
+                mr1r2 = np.sum(Ar1r2)
+                hat_mr1r2 = Ar1r2.size - mr1r2
+                ln_pi_post[r] += betaln(mr1r2 + b1, hat_mr1r2 + b0) - betaln(b1, b0)
+    return ln_pi_post
+
+
 def log_sum_exp_sample(lnp, u):
     """hips.inference.log_sum_exp_sample (recollection): p = exp(lnp - logsumexp); first index with cumsum >= u."""
     lnp = np.asarray(lnp, dtype=np.float64)

@@ -55,3 +55,23 @@ def test_mf_expectations_after_an_update():
     E_mu = w.mf_expected_mu()
     assert np.allclose(w.mf_expected_mumuT(), w.mf_expected_Sigma() + np.outer(E_mu, E_mu))
     _check("E[mu mu^T], exact", w.mf_expected_Sigma() / w.kappa_mf + np.outer(E_mu, E_mu), mumuT)
+
+
+def test_expected_log_likelihood_sums_the_per_pair_negentropy():
+    """internals/weights.py:174-198: the N^2 loop of Gaussian().negentropy(...).sum() over every ordered pair, against the
+    three-sums form of GaussianWeights.expected_log_likelihood."""
+    import types
+    from graphistician_b200.internals.weights import GaussianWeights
+    rng = np.random.RandomState(4)
+    N, B = 9, 2
+    gw = GaussianWeights(B)
+    W = rng.randn(N, N, B)
+    c0, c1, C2 = gw.expected_log_likelihood_coefficients()
+    ell = 0.0
+    for i in range(N):
+        for j in range(N):
+            w = W[i, j]
+            ell += c0 + c1.dot(w) + w.dot(C2).dot(w)
+    net = types.SimpleNamespace(W=W, E_W=W, E_WWT=W[:, :, :, None] * W[:, :, None, :])
+    assert np.isclose(gw.expected_log_likelihood(net), ell, rtol=1e-12)
+    assert np.isclose(gw.expected_log_likelihood(types.SimpleNamespace(W=W)), ell, rtol=1e-12)

@@ -125,3 +125,18 @@ def test_sbm_ais_prefers_the_block_model_on_block_data():
     z_sbm = estimate_marginal_likelihood(A, np.array(f0), t0, sbm_model, N_samples=4, B=60, steps_per_B=2)
     assert np.isfinite(z_er) and np.isfinite(z_sbm)
     assert z_sbm > z_er + 50.0
+
+
+def test_collapsed_sample_f_matches_reference_loop():
+    """internals/graph_models.py:299-335 (B integrated out): the count-table form against the literal np.ix_ loops."""
+    N, R = 60, 3
+    model, A, f, theta = _sbm_data(N, R, 31)
+    rng = np.random.RandomState(2)
+    z = rng.randint(0, R, N)
+    for n in (0, 7, N - 1):
+        u = rng.rand()
+        zn, lp = model.collapsed_sample_f(theta, n, A, z, uniform=u, return_lp=True)
+        lp_ref = sbm.ais_collapsed_ln_post_loops(A, z, n, theta[1], model.b0, model.b1)
+        assert np.allclose(lp, lp_ref, rtol=1e-10, atol=1e-9)
+        assert zn == sbm.log_sum_exp_sample(lp_ref, u)
+        z[n] = zn
