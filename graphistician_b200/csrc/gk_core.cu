@@ -50,6 +50,7 @@ extern "C" int gk_ctx_create(int device, gk_ctx **out) {
     if (cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking) != cudaSuccess) { delete ctx; return GK_ECUDA; }
     ctx->own_stream = true;
     ctx->sbm_prof = getenv("GK_SBM_PROF") != nullptr;
+    ctx->sbm_overlap = getenv("GK_SBM_NO_OVERLAP") == nullptr;
     *out = ctx;
     return GK_OK;
 }
@@ -59,6 +60,9 @@ extern "C" void gk_ctx_destroy(gk_ctx *ctx) {
     cudaSetDevice(ctx->device);
     cudaStreamSynchronize(ctx->stream);
     gk_comm_release(ctx);
+    if (ctx->aux) { cudaStreamSynchronize(ctx->aux); cudaStreamDestroy(ctx->aux); }
+    if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
+    if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
     for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (auto &f : ctx->fam) for (auto &p : f.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);

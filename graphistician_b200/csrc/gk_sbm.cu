@@ -450,11 +450,56 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
     uint8_t *c_old8 = (uint8_t *)(cb + o_cold);
     GK_CUDA(ctx, cudaMemcpyAsync(c_old8, sw->c8, (size_t)N, cudaMemcpyDeviceToDevice, ctx->stream));
     ctx->last_cells.valid = false;
+    // The strip pass of block b+1 runs on a second stream beside the serial kernel of block b, on a snapshot of the labels
+    // taken before block b is drawn; k_stats_fix then moves the terms of block b's movers to their new class (nothing to do
+    // in the stationary regime).  The serial CTA is enqueued first and the strip grid leaves four SMs free, so the two run
+    // side by side.
+    const bool overlap = ctx->sbm_overlap && !ctx->sbm_prof && bn <= 2048 && N > bn;
+    uint8_t *c_spec = nullptr;
+    if (overlap) {
+        if (!ctx->aux) {
+            GK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking));
+            GK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
+            GK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
+        }
+        c_spec = (uint8_t *)gk_scratch(ctx, 10, (size_t)N);
+        if (!c_spec) return GK_ENOMEM;
+    }
     for (int n0 = 0; n0 < N; n0 += bn) {
         int nb = std::min(bn, N - n0);
         double *stats = stats_all + (size_t)n0 * 2 * KS;
-        if ((rc = gk_sbm_block_partials(ctx, net, n0, nb, stats))) return rc;
-        if ((rc = gk_sbm_block_sample(ctx, net, n0, nb, stats))) return rc;
+        if (!overlap) {
+            if ((rc = gk_sbm_block_partials(ctx, net, n0, nb, stats))) return rc;
+            if ((rc = gk_sbm_block_sample(ctx, net, n0, nb, stats))) return rc;
+            continue;
+        }
+        if (n0 == 0) {
+            if ((rc = gk_sbm_block_partials(ctx, net, n0, nb, stats))) return rc;
+        } else {                                   // statistics came from the second stream, on the labels of before block b-1
+            GK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
+            const int p0 = n0 - bn;
+#define CALL_FIX(T, BB) (k_stats_fix<T, BB><<<(nb + 127) / 128, 128, 0, ctx->stream>>>(net->A, net->At, net->W, net->Wt, net->ld, c_spec, sw->c8, p0, bn, n0, nb, K, stats), GK_OK)
+            rc = GK_DISPATCH_TB(net, CALL_FIX);
+            GK_CHECK_LAUNCH(ctx);
+        }
+        const int n1 = n0 + bn;
+        if (n1 < N) {
+            GK_CUDA(ctx, cudaMemcpyAsync(c_spec, sw->c8, (size_t)N, cudaMemcpyDeviceToDevice, ctx->stream));
+            GK_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+        }
+        if ((rc = gk_sbm_block_sample(ctx, net, n0, nb, stats))) return rc;          // lp + the serial CTA, enqueued first
+        if (n1 < N) {
+            GK_CUDA(ctx, cudaStreamWaitEvent(ctx->aux, ctx->ev_fork, 0));
+            cudaStream_t keep = ctx->stream;
+            ctx->stream = ctx->aux;
+            const int nb1 = std::min(bn, N - n1), nb1_pad = (nb1 + GK_STRIP_COLS - 1) / GK_STRIP_COLS * GK_STRIP_COLS;
+            double *stats1 = stats_all + (size_t)n1 * 2 * KS;
+#define CALL_K2S(T, BB) strip_to_stats<T, BB>(ctx, net, c_spec, K, n1, nb1_pad, 0, 2, stats1)
+            rc = GK_DISPATCH_TB(net, CALL_K2S);
+            ctx->stream = keep;
+            if (rc) return rc;
+            GK_CUDA(ctx, cudaEventRecord(ctx->ev_join, ctx->aux));
+        }
     }
     // K1 of the final labels: fold, then move the movers' out-edges from their old source class to the new one
     GK_CUDA(ctx, cudaMemsetAsync(cell, 0, (size_t)K * KS * 8, ctx->stream));

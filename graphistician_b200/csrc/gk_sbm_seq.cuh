@@ -432,6 +432,77 @@ __global__ void __launch_bounds__(64) k_cell_movers(const uint8_t *__restrict__ 
     }
 }
 
+// Speculative strip statistics (gk_sbm_sweep overlaps the strip pass of node block b+1 with the serial kernel of block b):
+// the statistics of the nodes [n0, n0+nb) were taken with the labels `c_spec` that block [p0, p0+pn) carried BEFORE it was
+// drawn; every node m of that block whose label changed a -> b' moves its edge terms x(n -> m) (out half) and x(m -> n)
+// (in half) from class a to class b'.  Counts stay exact integers; the fp sums change by round-off only.  One thread per
+// node n (it owns its two statistics rows: no atomics); the mover list is rebuilt per CTA in shared memory, in index order.
+template <typename T, int B>
+__global__ void __launch_bounds__(128) k_stats_fix(const uint8_t *__restrict__ A, const uint8_t *__restrict__ At, const void *__restrict__ Wv,
+                                                   const void *__restrict__ Wtv, int ld, const uint8_t *__restrict__ c_spec,
+                                                   const uint8_t *__restrict__ c8, int p0, int pn, int n0, int nb, int K,
+                                                   double *__restrict__ stats) {
+    constexpr int S = gk_sdim<B>::S;
+    __shared__ int s_cnt;
+    __shared__ unsigned short s_m[2048];
+    __shared__ unsigned char s_a[2048], s_b[2048];
+    const int tid = threadIdx.x;
+    if (tid == 0) s_cnt = 0;
+    __syncthreads();
+    for (int base = 0; base < pn; base += 128) {                    // ordered compaction: the list is the same in every CTA
+        const int i = base + tid;
+        const bool mv = i < pn && c_spec[p0 + i] != c8[p0 + i];
+        const unsigned bal = __ballot_sync(0xffffffffu, mv);
+        __shared__ int s_w[4];
+        if ((tid & 31) == 0) s_w[tid >> 5] = __popc(bal);
+        __syncthreads();
+        int off = s_cnt;
+        for (int w = 0; w < (tid >> 5); ++w) off += s_w[w];
+        if (mv) {
+            const int pos = off + __popc(bal & ((1u << (tid & 31)) - 1));
+            s_m[pos] = (unsigned short)i; s_a[pos] = c_spec[p0 + i]; s_b[pos] = c8[p0 + i];
+        }
+        __syncthreads();
+        if (tid == 0) s_cnt += s_w[0] + s_w[1] + s_w[2] + s_w[3];
+        __syncthreads();
+    }
+    const int nm = s_cnt;
+    const int i = blockIdx.x * 128 + tid;
+    if (nm == 0 || i >= nb) return;
+    const int n = n0 + i, KS = K * S;
+    const T *W = (const T *)Wv, *Wt = (const T *)Wtv;
+    double *so = stats + ((size_t)i * 2 + 0) * KS, *si = so + KS;
+    for (int q = 0; q < nm; ++q) {
+        const int m = p0 + s_m[q], a = s_a[q], b = s_b[q];
+        if (At[(size_t)m * ld + n]) {                               // edge n -> m: out half of node n
+            double x[S]; x[0] = 1.0;
+            if constexpr (B > 0) {
+#pragma unroll
+                for (int d = 0; d < B; ++d) x[1 + d] = (double)Wt[((size_t)m * ld + n) * B + d];
+#pragma unroll
+                for (int d = 0; d < B; ++d)
+#pragma unroll
+                    for (int d2 = d; d2 < B; ++d2) x[gk_sym_idx(B, d, d2)] = x[1 + d] * x[1 + d2];
+            }
+#pragma unroll
+            for (int t = 0; t < S; ++t) { so[a * S + t] -= x[t]; so[b * S + t] += x[t]; }
+        }
+        if (A[(size_t)m * ld + n]) {                                // edge m -> n: in half of node n
+            double x[S]; x[0] = 1.0;
+            if constexpr (B > 0) {
+#pragma unroll
+                for (int d = 0; d < B; ++d) x[1 + d] = (double)W[((size_t)m * ld + n) * B + d];
+#pragma unroll
+                for (int d = 0; d < B; ++d)
+#pragma unroll
+                    for (int d2 = d; d2 < B; ++d2) x[gk_sym_idx(B, d, d2)] = x[1 + d] * x[1 + d2];
+            }
+#pragma unroll
+            for (int t = 0; t < S; ++t) { si[a * S + t] -= x[t]; si[b * S + t] += x[t]; }
+        }
+    }
+}
+
 // c (int32) -> c8 and block sizes are prepared on the host; this just narrows the labels on the device
 __global__ void k_narrow_labels(const int32_t *__restrict__ c, uint8_t *__restrict__ c8, int N) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) c8[i] = (uint8_t)c[i];
