@@ -645,6 +645,7 @@ def bench_ais(args, R, steps, warmup, cpu=True, scan=(8, 32, 512)):
     collective), so the N-GPU value is the sum of the ranks' particle-sweeps."""
     N, Rk, P = args.ais_n, 3, args.ais_particles
     dev, t_up, chunk_bytes = _ais_device(args, R, P)
+    z_true = ais_truth(N, Rk)[0]
     rng = np.random.RandomState(5678 + R.rank)
     dev.set_labels(rng.randint(0, Rk, N))
     model_b0 = model_b1 = 1.0; alpha0 = 10 * np.ones(Rk)
@@ -721,8 +722,26 @@ def bench_ais(args, R, steps, warmup, cpu=True, scan=(8, 32, 512)):
     }
     if cpu and R.rank == 0 and R.world == 1 and not args.no_cpu_baseline:
         rec["cpu_baseline"] = cpu_baseline_ais(args, N, Rk)
+
+    def stationary(dv, Ps):
+        """The other end of the ladder: labels at the planted blocks, theta from their tempered posterior; (almost) no node moves."""
+        dv.set_labels(z_true)
+        n_e, szs = dv.counts()
+        lp_s = np.log(np.stack([rng.dirichlet(alpha0 + szs[k]) for k in range(Ps)]))
+        n_p = szs[:, :, None] * szs[:, None, :]
+        B_s = np.clip(rng.beta(1.0 + 0.5 * n_e, 1.0 + 0.5 * (n_p - n_e)), 1e-6, 1 - 1e-6).astype(np.float32).astype(np.float64)
+        moved = []
+        st = lambda: moved.append(float(dv.sweep(lp_s, B_s, 0.5, seed=11)[0].mean()))
+        R.timed(st, 2)
+        ms_s = R.timed(st, 5)
+        return {"value": R.world * Ps * 5 / (ms_s * 1e-3), "unit": AIS_UNIT, "ms_per_step": ms_s / 5, "n_changed_mean_last_sweep": moved[-1]}
+
+    rec["regime"] = "labels drawn uniformly and theta from their tempered posterior: about two thirds of the nodes move per sweep " \
+                    "(the start of an AIS ladder, the per-node path of k_ais_seq); `stationary` is the other end"
+    rec["n_changed_mean_last_sweep"] = float(dev.sweep(lpi, Bm, beta, seed=7)[0].mean())
+    rec["stationary"] = stationary(dev, P)
     dev.close()
-    rec["particle_scan"] = {str(P): {"value": rec["value"], "ms_per_step": rec["ms_per_step"]}}
+    rec["particle_scan"] = {str(P): {"value": rec["value"], "ms_per_step": rec["ms_per_step"], "stationary": rec["stationary"]["value"]}}
     for Ps in scan:                                            # SURVEY.md 8d config 5: P swept per GPU (resident sweeps only)
         if Ps == P or R.world > 1:
             continue
@@ -735,7 +754,7 @@ def bench_ais(args, R, steps, warmup, cpu=True, scan=(8, 32, 512)):
         st = lambda: dv.sweep(lp_s, B_s, beta, seed=7)
         R.timed(st, 2)
         ms_s = R.timed(st, 3)
-        rec["particle_scan"][str(Ps)] = {"value": Ps * 3 / (ms_s * 1e-3), "ms_per_step": ms_s / 3}
+        rec["particle_scan"][str(Ps)] = {"value": Ps * 3 / (ms_s * 1e-3), "ms_per_step": ms_s / 3, "stationary": stationary(dv, Ps)["value"]}
         dv.close()
     return rec
 

@@ -243,7 +243,8 @@ struct AisSeqParams {
     int N, Npad, nw, n0, p0;
 };
 
-#define AIS_RING 8                // nodes of read-ahead of the serial kernel (cp.async ring in shared memory)
+#define AIS_RING 64               // nodes held by the cp.async ring of the serial kernel: two windows of 32 nodes
+#define AIS_HOT 6                 // a window with at least this many movers sends the next window down the per-node path
 
 __device__ __forceinline__ void ais_cp4(uint32_t *smem, const uint32_t *g) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g) : "memory");
@@ -255,9 +256,62 @@ template <int R> static constexpr size_t ais_seq_smem() {
     return (size_t)AIS_NB * (2 * (R - 1) * 4 + 8 + 8) + (size_t)AIS_RING * 2 * 32 * 4;
 }
 
-// One warp per particle.  The block's small per-node records (entry counts, degrees, uniforms) are staged in shared memory
-// once; the node's words of A / A^T (one per lane) come through an AIS_RING-deep cp.async ring, so that no register
-// scoreboard ties a node's arithmetic to loads issued for later nodes.
+// ln_pi_post of one node and its draw (internals/graph_models.py:261-297).  co / ci: the node's out- / in-neighbours per
+// class under the current labels, the node itself included under its current label a; it is excluded here and re-added, as
+// candidate k, in both directions (:275-293).  hips log_sum_exp_sample: first index whose normalised cdf reaches u -- decided
+// in fp32 when u is clearly inside a cell of the cdf (error of the fp32 cdf < 1e-5 of its total, margin 1e-4), else by the
+// fp64 arithmetic of the reference.
+template <int R>
+__device__ __forceinline__ int ais_decide(const int (&co)[R], const int (&ci)[R], const int (&sz)[R], int a, int self, double u,
+                                          double beta, const double *lpi, const double *lB, const double *l1B, double (&lp)[R]) {
+    double dco[R], dci[R], dsz[R];
+#pragma unroll
+    for (int r = 0; r < R; ++r) {
+        const int me = (r == a);
+        dco[r] = (double)(co[r] - (me & self)); dci[r] = (double)(ci[r] - (me & self)); dsz[r] = (double)(sz[r] - me);
+    }
+    double mx = -1.7976931348623157e308;
+#pragma unroll
+    for (int k = 0; k < R; ++k) {
+        double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+#pragma unroll
+        for (int r = 0; r < R; ++r) {
+            s0 = fma(dco[r], lB[k * R + r], s0);  s1 = fma(dsz[r] - dco[r], l1B[k * R + r], s1);
+            s2 = fma(dci[r], lB[r * R + k], s2);  s3 = fma(dsz[r] - dci[r], l1B[r * R + k], s3);
+        }
+        const double sf = 2.0 * (self ? lB[k * R + k] : l1B[k * R + k]);
+        lp[k] = lpi[k] + beta * (((s0 + s1) + (s2 + s3)) + sf);
+        mx = fmax(mx, lp[k]);
+    }
+    int b = 0;
+    float ef[R], totf = 0.f;
+#pragma unroll
+    for (int k = 0; k < R; ++k) { ef[k] = __expf((float)(lp[k] - mx)); totf += ef[k]; }
+    const float thr = (float)u * totf, band = 1e-4f * totf;
+    float cumf = 0.f; bool sure = true;
+#pragma unroll
+    for (int k = 0; k < R - 1; ++k) { cumf += ef[k]; b += (cumf < thr); sure = sure && (fabsf(cumf - thr) > band); }
+    if (!sure) {
+        double e[R], tot = 0.0, cum = 0.0;
+#pragma unroll
+        for (int k = 0; k < R; ++k) { e[k] = exp(lp[k] - mx); tot += e[k]; }
+        b = 0;
+#pragma unroll
+        for (int k = 0; k < R; ++k) { cum += e[k] / tot; b += (cum < u); }
+        b = min(b, R - 1);
+    }
+    return b;
+}
+
+// One warp per particle walks the block's 1024 nodes in index order, a window of 32 nodes at a time.  The block's small
+// per-node records (entry counts, degrees, uniforms) are staged in shared memory once; the nodes' words of A / A^T (lane =
+// word of the block's node bits) come through a cp.async ring of two windows.
+//   * per-node path (windows after a window with many movers): every lane works on the same node; the block-entry counts
+//     are corrected by popc(row & current mask) - popc(row & entry mask) over the block's own words.
+//   * window path (few movers): lane j owns node 32 w + j; its counts are corrected once per window, all 32 conditionals
+//     and draws are formed side by side, everything up to the first mover commits (those nodes saw exactly the state the
+//     serial loop would have shown them), the mover's bit goes from class a to class b in the later lanes' counts, and the
+//     remaining lanes draw again.  Same arithmetic per node on both paths (ais_decide), so the path taken never shows.
 template <int R>
 __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
     const int p = P.p0 + blockIdx.x, lane = threadIdx.x;
@@ -269,14 +323,21 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
     uint32_t *s_ring = reinterpret_cast<uint32_t *>(s_u + AIS_NB);        // [AIS_RING][2][32]
     __shared__ double s_tab[TS];
     __shared__ int s_cell[R * R];                    // change of the cell table over this block
-    const int nb = min(AIS_NB, P.N - P.n0);
+    const int nb = min(AIS_NB, P.N - P.n0), nwin = (nb + 31) >> 5;
     const uint32_t *gAo = P.Ab + (size_t)P.n0 * P.nw + (P.n0 >> 5) + lane;
     const uint32_t *gAi = P.Atb + (size_t)P.n0 * P.nw + (P.n0 >> 5) + lane;
-#pragma unroll
-    for (int k = 0; k < AIS_RING - 1; ++k) {         // read-ahead of the first nodes' words
-        if (k < nb) { ais_cp4(s_ring + (k * 2) * 32 + lane, gAo + (size_t)k * P.nw); ais_cp4(s_ring + (k * 2 + 1) * 32 + lane, gAi + (size_t)k * P.nw); }
+    auto issue_window = [&](int w) {
+        for (int j = 0; j < 32; ++j) {
+            const int k = 32 * w + j;
+            if (k < nb) {
+                uint32_t *slot = s_ring + (size_t)(k & (AIS_RING - 1)) * 64;
+                ais_cp4(slot + lane, gAo + (size_t)k * P.nw);
+                ais_cp4(slot + 32 + lane, gAi + (size_t)k * P.nw);
+            }
+        }
         ais_cp_commit();
-    }
+    };
+    issue_window(0);
     {
         const uint4 *g = reinterpret_cast<const uint4 *>(P.cnt + (size_t)p * AIS_NB * CE);
         uint4 *d = reinterpret_cast<uint4 *>(s_ce);
@@ -302,121 +363,152 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
         sz[r] = (int)P.sz[p * R + r];
     }
     int nchg = 0;
-    for (int i = 0; i < nb; ++i) {
-        {
-            const int k = i + AIS_RING - 1;
-            if (k < nb) {
-                const int slot = k & (AIS_RING - 1);
-                ais_cp4(s_ring + (slot * 2) * 32 + lane, gAo + (size_t)k * P.nw);
-                ais_cp4(s_ring + (slot * 2 + 1) * 32 + lane, gAi + (size_t)k * P.nw);
-            }
-            ais_cp_commit();
-            ais_cp_wait<AIS_RING - 1>();
-        }
-        struct { uint32_t ao, ai, ce[CE]; uint2 dg; int a; double u; } cur;
-        cur.ao = s_ring[((i & (AIS_RING - 1)) * 2) * 32 + lane];
-        cur.ai = s_ring[((i & (AIS_RING - 1)) * 2 + 1) * 32 + lane];
-#pragma unroll
-        for (int r = 0; r < CE; ++r) cur.ce[r] = s_ce[i * CE + r];
-        cur.dg = s_dg[i];
-        cur.u = s_u[i];
-        {   // the node's current label: the class whose mask holds bit i (the node has not been drawn yet in this sweep)
-            int al = 0;
-#pragma unroll
-            for (int r = 1; r < R; ++r) al += r * (int)((C[r] >> (i & 31)) & 1u);
-            cur.a = __shfl_sync(0xffffffffu, al, i >> 5);
-        }
-        // counts of node n's out- and in-neighbours per class under the CURRENT labels: block-entry counts plus what the
-        // nodes of this block that already moved changed (nothing while no node of the block has moved: C == E)
-        int co[R], ci[R];
-        {
-            int so = 0, si = 0;
-#pragma unroll
-            for (int r = 0; r < R - 1; ++r) { co[r] = (int)cur.ce[r]; ci[r] = (int)cur.ce[R - 1 + r]; }
-            if (nchg) {
-#pragma unroll
-                for (int r = 0; r < R - 1; ++r) {
-                    const int d_o = __popc(cur.ao & C[r]) - __popc(cur.ao & E[r]) + 32;
-                    const int d_i = __popc(cur.ai & C[r]) - __popc(cur.ai & E[r]) + 32;
-                    const unsigned red = __reduce_add_sync(0xffffffffu, (unsigned)d_o | ((unsigned)d_i << 16));
-                    co[r] += (int)(red & 0xffffu) - 1024;
-                    ci[r] += (int)(red >> 16) - 1024;
-                }
-            }
-#pragma unroll
-            for (int r = 0; r < R - 1; ++r) { so += co[r]; si += ci[r]; }
-            co[R - 1] = (int)cur.dg.x - so;
-            ci[R - 1] = (int)cur.dg.y - si;
-        }
-        const int a = cur.a;
-        const int self = (__shfl_sync(0xffffffffu, cur.ao, i >> 5) >> (i & 31)) & 1;      // A[n, n]
-        // the node itself is excluded here and re-added, as candidate k, in both directions (internals/graph_models.py:275-293)
-        double dco[R], dci[R], dsz[R];
+    // the path of the block's first window follows the move rate of this particle's sweep so far
+    bool hot = P.n0 > 0 && P.nchg[p] * 32 >= (long long)AIS_HOT * P.n0;
+    // one committed move a -> b of node i (uniform arguments): masks, sizes, labels, the particle's cell table
+    auto commit_move = [&](int i, int a, int b, const int (&cox)[R], const int (&cix)[R], int self) {
+        ++nchg;
+        const uint32_t bit = (lane == (i >> 5)) ? (1u << (i & 31)) : 0u;
 #pragma unroll
         for (int r = 0; r < R; ++r) {
-            const int me = (r == a);
-            co[r] -= me & self; ci[r] -= me & self;
-            dco[r] = (double)co[r]; dci[r] = (double)ci[r]; dsz[r] = (double)(sz[r] - me);
+            if (r == a) { C[r] &= ~bit; sz[r] -= 1; }
+            if (r == b) { C[r] |= bit; sz[r] += 1; }
         }
-        double lp[R];
-        double mx = -1.7976931348623157e308;
-#pragma unroll
-        for (int k = 0; k < R; ++k) {
-            double s0 = 0.0, s1 = 0.0, s2 = 0.0, s3 = 0.0;
+        if (lane == 0) {
+            P.z[(size_t)p * P.Npad + P.n0 + i] = (uint8_t)b;
 #pragma unroll
             for (int r = 0; r < R; ++r) {
-                s0 = fma(dco[r], lB[k * R + r], s0);  s1 = fma(dsz[r] - dco[r], l1B[k * R + r], s1);
-                s2 = fma(dci[r], lB[r * R + k], s2);  s3 = fma(dsz[r] - dci[r], l1B[r * R + k], s3);
+                s_cell[a * R + r] -= cox[r]; s_cell[b * R + r] += cox[r];          // edges n -> class r change their source class
+                s_cell[r * R + a] -= cix[r]; s_cell[r * R + b] += cix[r];          // edges class r -> n change their target class
             }
-            const double sf = 2.0 * (self ? lB[k * R + k] : l1B[k * R + k]);
-            lp[k] = lpi[k] + beta * (((s0 + s1) + (s2 + s3)) + sf);
-            mx = fmax(mx, lp[k]);
+            s_cell[a * R + a] -= self; s_cell[b * R + b] += self;
         }
-        // hips log_sum_exp_sample: first index whose normalised cdf reaches u.  Decided in fp32 when u is clearly inside
-        // a cell of the cdf (error of the fp32 cdf < 1e-5 of its total), else by the fp64 arithmetic of the reference.
-        int b = 0;
-        {
-            float ef[R], totf = 0.f;
+    };
+    for (int w = 0; w < nwin; ++w) {
+        if (w + 1 < nwin) issue_window(w + 1); else ais_cp_commit();
+        ais_cp_wait<1>();
+        __syncwarp();                                 // the window path reads words other lanes copied
+        const int i0 = 32 * w, cnt = min(32, nb - i0);
+        int moved = 0;
+        if (hot) {
+            for (int jj = 0; jj < cnt; ++jj) {
+                const int i = i0 + jj;
+                const uint32_t *slot = s_ring + (size_t)(i & (AIS_RING - 1)) * 64;
+                const uint32_t ao = slot[lane], ai = slot[32 + lane];
+                int co[R], ci[R];
+                {
+                    int so = 0, si = 0;
 #pragma unroll
-            for (int k = 0; k < R; ++k) { ef[k] = __expf((float)(lp[k] - mx)); totf += ef[k]; }
-            const float thr = (float)cur.u * totf, band = 1e-4f * totf;
-            float cumf = 0.f; bool sure = true;
+                    for (int r = 0; r < R - 1; ++r) { co[r] = (int)s_ce[i * CE + r]; ci[r] = (int)s_ce[i * CE + R - 1 + r]; }
+                    if (nchg) {
 #pragma unroll
-            for (int k = 0; k < R - 1; ++k) { cumf += ef[k]; b += (cumf < thr); sure = sure && (fabsf(cumf - thr) > band); }
-            if (!sure) {
-                double e[R], tot = 0.0, cum = 0.0;
+                        for (int r = 0; r < R - 1; ++r) {
+                            const int d_o = __popc(ao & C[r]) - __popc(ao & E[r]) + 32;
+                            const int d_i = __popc(ai & C[r]) - __popc(ai & E[r]) + 32;
+                            const unsigned red = __reduce_add_sync(0xffffffffu, (unsigned)d_o | ((unsigned)d_i << 16));
+                            co[r] += (int)(red & 0xffffu) - 1024;
+                            ci[r] += (int)(red >> 16) - 1024;
+                        }
+                    }
 #pragma unroll
-                for (int k = 0; k < R; ++k) { e[k] = exp(lp[k] - mx); tot += e[k]; }
-                b = 0;
+                    for (int r = 0; r < R - 1; ++r) { so += co[r]; si += ci[r]; }
+                    const uint2 dg = s_dg[i];
+                    co[R - 1] = (int)dg.x - so;
+                    ci[R - 1] = (int)dg.y - si;
+                }
+                int al = 0;
 #pragma unroll
-                for (int k = 0; k < R; ++k) { cum += e[k] / tot; b += (cum < cur.u); }
-                b = min(b, R - 1);
+                for (int r = 1; r < R; ++r) al += r * (int)((C[r] >> (i & 31)) & 1u);
+                const int a = __shfl_sync(0xffffffffu, al, i >> 5);
+                const int self = (__shfl_sync(0xffffffffu, ao, i >> 5) >> (i & 31)) & 1;      // A[n, n]
+                double lp[R];
+                const int b = ais_decide<R>(co, ci, sz, a, self, s_u[i], beta, lpi, lB, l1B, lp);
+                if (P.lp && lane < R) {
+                    double v = lp[0];
+#pragma unroll
+                    for (int k = 1; k < R; ++k) if (lane == k) v = lp[k];
+                    P.lp[((size_t)p * P.N + P.n0 + i) * R + lane] = v;
+                }
+                if (b != a) {
+                    int cox[R], cix[R];
+#pragma unroll
+                    for (int r = 0; r < R; ++r) { cox[r] = co[r] - ((r == a) & self); cix[r] = ci[r] - ((r == a) & self); }
+                    commit_move(i, a, b, cox, cix, self);
+                    ++moved;
+                }
             }
-        }
-        if (P.lp && lane < R) {
-            double v = lp[0];
+        } else {
+            // lane j owns node i0 + j
+            const int i = i0 + lane;
+            const bool mine = lane < cnt;
+            int co[R], ci[R];
 #pragma unroll
-            for (int k = 1; k < R; ++k) if (lane == k) v = lp[k];
-            P.lp[((size_t)p * P.N + P.n0 + i) * R + lane] = v;
-        }
-        if (b != a) {
-            ++nchg;
-            const uint32_t bit = (lane == (i >> 5)) ? (1u << (i & 31)) : 0u;
+            for (int r = 0; r < R - 1; ++r) { co[r] = mine ? (int)s_ce[i * CE + r] : 0; ci[r] = mine ? (int)s_ce[i * CE + R - 1 + r] : 0; }
+            if (nchg) {
+                for (int jj = 0; jj < cnt; ++jj) {
+                    const uint32_t *slot = s_ring + (size_t)((i0 + jj) & (AIS_RING - 1)) * 64;
+                    const uint32_t ao = slot[lane], ai = slot[32 + lane];
 #pragma unroll
-            for (int r = 0; r < R; ++r) {
-                if (r == a) { C[r] &= ~bit; sz[r] -= 1; }
-                if (r == b) { C[r] |= bit; sz[r] += 1; }
+                    for (int r = 0; r < R - 1; ++r) {
+                        const int d_o = __popc(ao & C[r]) - __popc(ao & E[r]) + 32;
+                        const int d_i = __popc(ai & C[r]) - __popc(ai & E[r]) + 32;
+                        const unsigned red = __reduce_add_sync(0xffffffffu, (unsigned)d_o | ((unsigned)d_i << 16));
+                        if (lane == jj) { co[r] += (int)(red & 0xffffu) - 1024; ci[r] += (int)(red >> 16) - 1024; }
+                    }
+                }
             }
-            if (lane == 0) {
-                P.z[(size_t)p * P.Npad + P.n0 + i] = (uint8_t)b;
+            {
+                int so = 0, si = 0;
+#pragma unroll
+                for (int r = 0; r < R - 1; ++r) { so += co[r]; si += ci[r]; }
+                const uint2 dg = mine ? s_dg[i] : make_uint2(0, 0);
+                co[R - 1] = (int)dg.x - so;
+                ci[R - 1] = (int)dg.y - si;
+            }
+            const uint32_t *myslot = s_ring + (size_t)(i & (AIS_RING - 1)) * 64;
+            const uint32_t my_o = mine ? myslot[w] : 0u, my_i = mine ? myslot[32 + w] : 0u;   // my row / column over this window's nodes
+            const int self = (my_o >> lane) & 1;
+            int a = 0;
+#pragma unroll
+            for (int r = 1; r < R; ++r) a += r * (int)((__shfl_sync(0xffffffffu, C[r], w) >> lane) & 1u);
+            const double u = mine ? s_u[i] : 0.5;
+            unsigned pending = cnt == 32 ? 0xffffffffu : ((1u << cnt) - 1u);
+            while (pending) {
+                double lp[R];
+                const int b = ais_decide<R>(co, ci, sz, a, self, u, beta, lpi, lB, l1B, lp);
+                const unsigned mv = __ballot_sync(0xffffffffu, b != a) & pending;
+                const int jstar = mv ? (__ffs(mv) - 1) : 32;
+                const unsigned done = jstar >= 31 ? pending : (pending & ((2u << jstar) - 1u));     // committed by this round
+                if (P.lp && ((done >> lane) & 1u)) {
+#pragma unroll
+                    for (int k = 0; k < R; ++k) P.lp[((size_t)p * P.N + P.n0 + i) * R + k] = lp[k];
+                }
+                pending &= ~done;
+                if (!mv) break;
+                const int ma = __shfl_sync(0xffffffffu, a, jstar), mb = __shfl_sync(0xffffffffu, b, jstar);
+                const int mself = __shfl_sync(0xffffffffu, self, jstar);
+                int cox[R], cix[R];
 #pragma unroll
                 for (int r = 0; r < R; ++r) {
-                    s_cell[a * R + r] -= co[r]; s_cell[b * R + r] += co[r];          // edges n -> class r change their source class
-                    s_cell[r * R + a] -= ci[r]; s_cell[r * R + b] += ci[r];          // edges class r -> n change their target class
+                    cox[r] = __shfl_sync(0xffffffffu, co[r], jstar) - ((r == ma) & mself);
+                    cix[r] = __shfl_sync(0xffffffffu, ci[r], jstar) - ((r == ma) & mself);
                 }
-                s_cell[a * R + a] -= self; s_cell[b * R + b] += self;
+                commit_move(i0 + jstar, ma, mb, cox, cix, mself);
+                ++moved;
+                if (lane == jstar) a = mb;
+                // the later nodes of the window: their edge to / from the mover changes class
+                const int x_o = (int)((my_o >> jstar) & 1u), x_i = (int)((my_i >> jstar) & 1u);
+                if (lane != jstar) {
+#pragma unroll
+                    for (int r = 0; r < R; ++r) {
+                        if (r == ma) { co[r] -= x_o; ci[r] -= x_i; }
+                        if (r == mb) { co[r] += x_o; ci[r] += x_i; }
+                    }
+                }
             }
         }
+        hot = moved >= AIS_HOT;
+        __syncwarp();                                 // ring slots of this window are free for the window after next
     }
     __syncwarp();
 #pragma unroll
