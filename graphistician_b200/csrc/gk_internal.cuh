@@ -38,7 +38,8 @@ struct gk_ctx {
     std::vector<const void *> attr_funcs;     // kernels whose attributes this context has set
     bool sbm_prof = false;                    // env GK_SBM_PROF, read once at context creation
     bool sbm_overlap = true;                  // env GK_SBM_NO_OVERLAP clears it: strip pass of block b+1 beside the serial kernel of block b
-    cudaStream_t aux = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // second stream of that overlap (created on first use)
+    cudaStream_t aux = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // second (low-priority) stream of that overlap, created on first use
+    bool fork_after_lp = false;               // launch_sample records ev_fork between k_lp_from_stats and the serial kernel
 };
 
 struct gk_net {

@@ -286,6 +286,10 @@ static int launch_sample(gk_ctx *ctx, gk_net *net, gk_sweep *sw, int n0, int nb,
         k_lp_from_stats<B><<<(nb + npc - 1) / npc, GK_LP_THREADS, sm, ctx->stream>>>(stats_dev, sw->T, net->diagA, net->diagW, n0, nb,
                                                                                    sw->N, sw->K, KP, sw->lp);
         GK_CHECK_LAUNCH(ctx);
+        if (ctx->fork_after_lp) {                  // the other stream's strip pass may start once the serial CTA can too
+            ctx->fork_after_lp = false;
+            GK_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+        }
     }
     gk_seq_params P;
     P.n0 = n0; P.nb = nb; P.K = sw->K; P.N = sw->N; P.ld = net->ld; P.row0 = net->row0; P.sampler = sw->sampler;
@@ -458,7 +462,9 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
     uint8_t *c_spec = nullptr;
     if (overlap) {
         if (!ctx->aux) {
-            GK_CUDA(ctx, cudaStreamCreateWithFlags(&ctx->aux, cudaStreamNonBlocking));
+            int lo = 0, hi = 0;                    // lowest priority: when both become runnable the serial CTA is placed first
+            GK_CUDA(ctx, cudaDeviceGetStreamPriorityRange(&lo, &hi));
+            GK_CUDA(ctx, cudaStreamCreateWithPriority(&ctx->aux, cudaStreamNonBlocking, lo));
             GK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_fork, cudaEventDisableTiming));
             GK_CUDA(ctx, cudaEventCreateWithFlags(&ctx->ev_join, cudaEventDisableTiming));
         }
@@ -485,7 +491,7 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
         const int n1 = n0 + bn;
         if (n1 < N) {
             GK_CUDA(ctx, cudaMemcpyAsync(c_spec, sw->c8, (size_t)N, cudaMemcpyDeviceToDevice, ctx->stream));
-            GK_CUDA(ctx, cudaEventRecord(ctx->ev_fork, ctx->stream));
+            ctx->fork_after_lp = true;
         }
         if ((rc = gk_sbm_block_sample(ctx, net, n0, nb, stats))) return rc;          // lp + the serial CTA, enqueued first
         if (n1 < N) {
