@@ -512,7 +512,7 @@ def run_ours(args):
     if names == ["ais"]:
         return run_ais(args, R)
     primary = names[0]
-    extras = args.workload == "all" and not args.no_extras and not rows
+    extras = args.workload in ("all", "sbm") and not args.no_extras and not rows
     rec, wl = bench_workload(primary, args, R, args.dtype, args.steps, args.warmup, rows=rows,
                              first_sweep=(primary == "sbm" and extras))
     out = {"metric": METRIC, "value": rec["value"], "unit": UNIT, "n_gpus": R.world, "steps": args.steps,

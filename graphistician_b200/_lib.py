@@ -11,6 +11,7 @@ LIB_PATH = os.path.join(HERE, "libgk.so")
 GK_F32, GK_F64 = 0, 1
 SELF_SKIP, SELF_ONCE, SELF_TWICE = 0, 1, 2
 SAMPLER_CUMSUM, SAMPLER_LSE = 0, 1
+CTX_OPT_SBM_OVERLAP = 1
 
 c_int, c_i64, c_dbl, c_vp, c_sz = ctypes.c_int, ctypes.c_int64, ctypes.c_double, ctypes.c_void_p, ctypes.c_size_t
 PI64 = ctypes.POINTER(ctypes.c_int64)
@@ -22,6 +23,7 @@ SIGNATURES = {
     "gk_last_error": (ctypes.c_char_p, [c_vp]),
     "gk_ctx_set_stream": (c_int, [c_vp, c_vp]),
     "gk_ctx_synchronize": (c_int, [c_vp]),
+    "gk_ctx_set_option": (c_int, [c_vp, c_int, c_int]),
     "gk_ctx_launch_count": (c_i64, [c_vp]),
     "gk_ctx_kernel_timing": (c_int, [c_vp, c_int]),
     "gk_ctx_kernel_timing_read": (c_int, [c_vp, c_int, ctypes.POINTER(c_dbl), PI64, ctypes.POINTER(c_dbl)]),
@@ -161,6 +163,9 @@ class Context:
 
     def synchronize(self):
         self.check(self.lib.gk_ctx_synchronize(self.h))
+
+    def set_option(self, option, value):
+        self.check(self.lib.gk_ctx_set_option(self.h, int(option), int(value)))
 
     def launch_count(self):
         return int(self.lib.gk_ctx_launch_count(self.h))

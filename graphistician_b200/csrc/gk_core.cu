@@ -51,6 +51,7 @@ extern "C" int gk_ctx_create(int device, gk_ctx **out) {
     ctx->own_stream = true;
     ctx->sbm_prof = getenv("GK_SBM_PROF") != nullptr;
     ctx->sbm_overlap = getenv("GK_SBM_NO_OVERLAP") == nullptr;
+    if (!ctx->sbm_overlap) ctx->sbm_overlap_mode = 0;
     *out = ctx;
     return GK_OK;
 }
@@ -67,6 +68,12 @@ extern "C" void gk_ctx_destroy(gk_ctx *ctx) {
     for (auto &f : ctx->fam) for (auto &p : f.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
     delete ctx;
+}
+
+extern "C" int gk_ctx_set_option(gk_ctx *ctx, int option, int value) {
+    if (!ctx) return GK_EINVAL;
+    if (option == GK_CTX_OPT_SBM_OVERLAP && value >= 0 && value <= 2) { ctx->sbm_overlap_mode = value; return GK_OK; }
+    return gk_fail(ctx, GK_EINVAL, "gk_ctx_set_option: unknown option %d or value %d", option, value);
 }
 
 extern "C" const char *gk_last_error(gk_ctx *ctx) { return ctx ? ctx->err.c_str() : "null ctx"; }
@@ -206,6 +213,7 @@ static int upload_w(gk_ctx *ctx, gk_net *net, void *dst, const void *src, int w_
 extern "C" int gk_network_upload(gk_ctx *ctx, gk_net *net, const uint8_t *A_rows, const void *W_rows, int w_dtype,
                                  const uint8_t *At_rows, const void *Wt_rows) {
     if (ctx && ctx->last_cells.net == net) ctx->last_cells.valid = false;      // statistics of the previous data
+    if (ctx && ctx->last_sweep_net == (const void *)net) ctx->last_sweep_moves = -1;
     if (!ctx || !net || !A_rows) return GK_EINVAL;
     if (net->B && !W_rows) return gk_fail(ctx, GK_EINVAL, "W required when B > 0");
     bool whole = net->row0 == 0 && net->nrows == net->N;

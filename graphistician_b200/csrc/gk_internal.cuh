@@ -37,8 +37,10 @@ struct gk_ctx {
     bool attr_done[64] = {false};
     std::vector<const void *> attr_funcs;     // kernels whose attributes this context has set
     bool sbm_prof = false;                    // env GK_SBM_PROF, read once at context creation
+    int sbm_overlap_mode = 1;                 // gk_ctx_set_option(GK_CTX_OPT_SBM_OVERLAP): 0 never, 1 when the last sweep moved few nodes, 2 always
     bool sbm_overlap = true;                  // env GK_SBM_NO_OVERLAP clears it: strip pass of block b+1 beside the serial kernel of block b
     cudaStream_t aux = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // second (low-priority) stream of that overlap, created on first use
+    long long last_sweep_moves = -1; const void *last_sweep_net = nullptr;   // moves of the last unsharded gk_sbm_sweep (and on which network)
     bool fork_after_lp = false;               // launch_sample records ev_fork between k_lp_from_stats and the serial kernel
 };
 

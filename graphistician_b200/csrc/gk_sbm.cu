@@ -458,7 +458,10 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
     // taken before block b is drawn; k_stats_fix then moves the terms of block b's movers to their new class (nothing to do
     // in the stationary regime).  The serial CTA is enqueued first and the strip grid leaves four SMs free, so the two run
     // side by side.
-    const bool overlap = ctx->sbm_overlap && !ctx->sbm_prof && bn <= 2048 && N > bn;
+    // ... which pays while few nodes move (the correction costs ~2 us per mover and block): taken when the previous sweep on
+    // this network moved at most 256 nodes, i.e. not during burn-in or on weakly structured data
+    const bool few = ctx->last_sweep_net == (const void *)net && ctx->last_sweep_moves >= 0 && ctx->last_sweep_moves <= 256;
+    const bool overlap = !ctx->sbm_prof && bn <= 2048 && N > bn && (ctx->sbm_overlap_mode == 2 || (ctx->sbm_overlap_mode == 1 && few));
     uint8_t *c_spec = nullptr;
     if (overlap) {
         if (!ctx->aux) {
@@ -484,7 +487,7 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
         } else {                                   // statistics came from the second stream, on the labels of before block b-1
             GK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, ctx->ev_join, 0));
             const int p0 = n0 - bn;
-#define CALL_FIX(T, BB) (k_stats_fix<T, BB><<<(nb + 127) / 128, 128, 0, ctx->stream>>>(net->A, net->At, net->W, net->Wt, net->ld, c_spec, sw->c8, p0, bn, n0, nb, K, stats), GK_OK)
+#define CALL_FIX(T, BB) (k_stats_fix<T, BB><<<(nb + 63) / 64, 128, 0, ctx->stream>>>(net->A, net->At, net->W, net->Wt, net->ld, c_spec, sw->c8, p0, bn, n0, nb, K, stats), GK_OK)
             rc = GK_DISPATCH_TB(net, CALL_FIX);
             GK_CHECK_LAUNCH(ctx);
         }
@@ -530,8 +533,11 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
         GK_CUDA(ctx, cudaMemcpyAsync(hc.data(), cell, (size_t)K * KS * 8, cudaMemcpyDeviceToHost, ctx->stream));
         GK_CUDA(ctx, cudaMemcpyAsync(&nmov, mcnt, 4, cudaMemcpyDeviceToHost, ctx->stream));
         const int S_ = sw->S;
-        rc = gk_sbm_sweep_end(ctx, net, c_inout, out_lp, out_nchanged);      // synchronises the stream
+        int64_t moves = 0;
+        rc = gk_sbm_sweep_end(ctx, net, c_inout, out_lp, &moves);      // synchronises the stream
         if (rc) return rc;
+        if (out_nchanged) *out_nchanged = moves;
+        ctx->last_sweep_moves = moves; ctx->last_sweep_net = net;
         ctx->last_cells.net = net; ctx->last_cells.K = K; ctx->last_cells.S = S_;
         ctx->last_cells.valid = nmov <= CAP;
         return GK_OK;

@@ -446,6 +446,7 @@ __global__ void __launch_bounds__(128) k_stats_fix(const uint8_t *__restrict__ A
     __shared__ int s_cnt;
     __shared__ unsigned short s_m[2048];
     __shared__ unsigned char s_a[2048], s_b[2048];
+    __shared__ int s_w[4];
     const int tid = threadIdx.x;
     if (tid == 0) s_cnt = 0;
     __syncthreads();
@@ -453,7 +454,6 @@ __global__ void __launch_bounds__(128) k_stats_fix(const uint8_t *__restrict__ A
         const int i = base + tid;
         const bool mv = i < pn && c_spec[p0 + i] != c8[p0 + i];
         const unsigned bal = __ballot_sync(0xffffffffu, mv);
-        __shared__ int s_w[4];
         if ((tid & 31) == 0) s_w[tid >> 5] = __popc(bal);
         __syncthreads();
         int off = s_cnt;
@@ -467,38 +467,32 @@ __global__ void __launch_bounds__(128) k_stats_fix(const uint8_t *__restrict__ A
         __syncthreads();
     }
     const int nm = s_cnt;
-    const int i = blockIdx.x * 128 + tid;
+    // thread = (node, direction): 64 nodes per CTA, each thread owns one statistics row (no atomics, fixed order)
+    const int dir = tid >> 6, i = blockIdx.x * 64 + (tid & 63);
     if (nm == 0 || i >= nb) return;
     const int n = n0 + i, KS = K * S;
-    const T *W = (const T *)Wv, *Wt = (const T *)Wtv;
-    double *so = stats + ((size_t)i * 2 + 0) * KS, *si = so + KS;
-    for (int q = 0; q < nm; ++q) {
-        const int m = p0 + s_m[q], a = s_a[q], b = s_b[q];
-        if (At[(size_t)m * ld + n]) {                               // edge n -> m: out half of node n
+    const uint8_t *E = dir ? A : At;                                // dir 0: edge n -> m (out half), dir 1: edge m -> n (in half)
+    const T *X = (const T *)(dir ? Wv : Wtv);
+    double *row = stats + ((size_t)i * 2 + dir) * KS;
+    for (int q0 = 0; q0 < nm; q0 += 8) {
+        unsigned char e[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) e[t] = (q0 + t < nm) ? E[(size_t)(p0 + s_m[q0 + t]) * ld + n] : 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            if (!e[t]) continue;
+            const int m = p0 + s_m[q0 + t], a = s_a[q0 + t], b = s_b[q0 + t];
             double x[S]; x[0] = 1.0;
             if constexpr (B > 0) {
 #pragma unroll
-                for (int d = 0; d < B; ++d) x[1 + d] = (double)Wt[((size_t)m * ld + n) * B + d];
+                for (int d = 0; d < B; ++d) x[1 + d] = (double)X[((size_t)m * ld + n) * B + d];
 #pragma unroll
                 for (int d = 0; d < B; ++d)
 #pragma unroll
                     for (int d2 = d; d2 < B; ++d2) x[gk_sym_idx(B, d, d2)] = x[1 + d] * x[1 + d2];
             }
 #pragma unroll
-            for (int t = 0; t < S; ++t) { so[a * S + t] -= x[t]; so[b * S + t] += x[t]; }
-        }
-        if (A[(size_t)m * ld + n]) {                                // edge m -> n: in half of node n
-            double x[S]; x[0] = 1.0;
-            if constexpr (B > 0) {
-#pragma unroll
-                for (int d = 0; d < B; ++d) x[1 + d] = (double)W[((size_t)m * ld + n) * B + d];
-#pragma unroll
-                for (int d = 0; d < B; ++d)
-#pragma unroll
-                    for (int d2 = d; d2 < B; ++d2) x[gk_sym_idx(B, d, d2)] = x[1 + d] * x[1 + d2];
-            }
-#pragma unroll
-            for (int t = 0; t < S; ++t) { si[a * S + t] -= x[t]; si[b * S + t] += x[t]; }
+            for (int u = 0; u < S; ++u) { row[a * S + u] -= x[u]; row[b * S + u] += x[u]; }
         }
     }
 }

@@ -42,6 +42,11 @@ void gk_ctx_destroy(gk_ctx *ctx);
 const char *gk_last_error(gk_ctx *ctx);
 int gk_ctx_set_stream(gk_ctx *ctx, void *cuda_stream);      /* e.g. torch's current stream handle */
 int gk_ctx_synchronize(gk_ctx *ctx);
+/* engine options.  GK_CTX_OPT_SBM_OVERLAP: gk_sbm_sweep runs the strip pass of node block b+1 beside the serial kernel of
+ * block b (same results) -- 0 never, 1 (default) when the previous sweep on the network moved <= 256 nodes,
+ * 2 always. */
+enum { GK_CTX_OPT_SBM_OVERLAP = 1 };
+int gk_ctx_set_option(gk_ctx *ctx, int option, int value);
 int64_t gk_ctx_launch_count(gk_ctx *ctx);                   /* kernels launched so far by this ctx */
 /* per-kernel CUDA-event timing (bench.py roofline); family: 0 = strip statistics kernel,
  * 1 = sequential sampler, 2 = Polya-gamma draw, 3 = eigen slab contraction, 4 = latent pairwise,

@@ -152,6 +152,42 @@ def test_sweep_leaves_the_next_k1_table(N, K, B, dtype, bn):
     assert net.sbm_sweep_stats(K + 1) is None                            # another K: nothing to offer
 
 
+@pytest.mark.parametrize("N,K,B,dtype,bn", [(1500, 4, 2, "f64", 256), (2600, 8, 2, "f64", 0), (900, 16, 1, "f32", 128), (640, 7, 0, "f32", 64)])
+def test_overlapped_sweep_equals_the_serial_order(N, K, B, dtype, bn):
+    """GK_CTX_OPT_SBM_OVERLAP = 2: the strip pass of node block b+1 runs beside the serial kernel of block b on a label
+    snapshot and k_stats_fix moves the terms of block b's movers.  From random labels (hundreds of movers per block), the
+    sweep after it and a third one: labels identical to the serial order (mode 0) and to the oracle, conditionals to
+    round-off, and the K1 table the sweep leaves behind equal to a fresh pass (counts bit-exact)."""
+    from graphistician_b200 import _lib
+    A, W, c_true, m, p, mus, sig, u = _problem(5 * N + K, N, K, B)
+    net, Wd = _net(A, W, dtype)
+    rng = np.random.RandomState(N + 1)
+    c0 = rng.randint(0, K, N)                       # not the generating labels: most nodes move in the first sweep
+    us = [rng.rand(N) for _ in range(3)]
+    out = {}
+    try:
+        for mode in (0, 2):
+            net.ctx.set_option(_lib.CTX_OPT_SBM_OVERLAP, mode)
+            c, res = c0.copy(), []
+            for it in range(3):
+                c, lp, nch = net.sbm_sweep(c, np.log(m), p, mus if B else None, sig if B else None, us[it], block_nodes=bn, want_lp=True)
+                res.append((c.copy(), lp.copy(), nch, net.sbm_sweep_stats(K)))
+            out[mode] = res
+    finally:
+        net.ctx.set_option(_lib.CTX_OPT_SBM_OVERLAP, 1)
+    tol = 1e-9 if dtype == "f64" else 1e-3
+    for it in range(3):
+        (ca, lpa, na, sa), (cb, lpb, nb_, sb) = out[0][it], out[2][it]
+        assert np.array_equal(ca, cb) and na == nb_
+        assert np.allclose(lpa, lpb, rtol=tol, atol=tol * 1e-2 * np.abs(lpa).max())
+        if sb is not None:
+            n_edge, sw, sww = net.block_stats(cb, K)
+            assert np.array_equal(sb[0], n_edge)
+    c_ref, _ = sbm.sbm_assign_sweep(A.astype(float), Wd, c0, m, p, mus if B else None, sig if B else None, us[0], sbm.SELF_OLD)
+    assert np.array_equal(out[2][0][0], c_ref)
+    assert out[2][0][2] > N // 4, "the first sweep must exercise the correction (many movers)"
+
+
 def test_sweep_with_exact_zero_and_one_probabilities():
     """p == 0 / p == 1 are legal (stochastic_block_model.py:58-60).  The reference's Bernoulli.log_probability turns an
     impossible event into a hard exclusion (nan_to_num(-inf) = -1.8e308) and 0 * log 0 into 0 (internals/distributions.py:59-67):
