@@ -19,7 +19,7 @@
 #define AIS_MAXR 8
 #define AIS_CW 512               // words of a row per column chunk of k_ais_rowcnt (16 per lane)
 #define AIS_QG 32                // mask rows (particle, class) per CTA of k_ais_rowcnt: lane q owns count q
-#define AIS_RW 4                 // rows per warp
+#define AIS_RW 4                 // rows per warp (2 when the grid would not fill the machine three CTAs deep)
 #define AIS_WARPS 8
 #define AIS_LOG0 (-1e10)         // log 0 of the conditional tables (as gk_sbm.cu: exp underflows to 0, 0 * finite = 0)
 
@@ -138,6 +138,7 @@ __device__ __forceinline__ unsigned ais_popc16(const uint32_t *a, const uint4 m0
 }
 
 // grid (row tiles of AIS_WARPS*AIS_RW rows, mask groups of AIS_QG, 2 directions); dynamic shared memory AIS_QG*AIS_CW words
+template <int RW>
 __global__ void __launch_bounds__(AIS_WARPS * 32)
 k_ais_rowcnt(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, const uint32_t *__restrict__ mask, int nw, int R,
              int n0, int qbeg, int Q, uint32_t *__restrict__ cnt) {
@@ -145,10 +146,10 @@ k_ais_rowcnt(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int q0 = qbeg + blockIdx.y * AIS_QG;
     const uint32_t *bits = blockIdx.z ? Atb : Ab;
-    const int row_base = blockIdx.x * (AIS_WARPS * AIS_RW) + warp * AIS_RW;
-    unsigned acc[AIS_RW];
+    const int row_base = blockIdx.x * (AIS_WARPS * RW) + warp * RW;
+    unsigned acc[RW];
 #pragma unroll
-    for (int r = 0; r < AIS_RW; ++r) acc[r] = 0;
+    for (int r = 0; r < RW; ++r) acc[r] = 0;
     const int nq = min(AIS_QG, Q - q0);
     for (int c0 = 0; c0 < nw; c0 += AIS_CW) {
         __syncthreads();
@@ -164,7 +165,7 @@ k_ais_rowcnt(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, 
         }
         __syncthreads();
 #pragma unroll
-        for (int rr = 0; rr < AIS_RW; ++rr) {
+        for (int rr = 0; rr < RW; ++rr) {
             const int i = row_base + rr;
             uint32_t a[16];
 #pragma unroll
@@ -183,7 +184,7 @@ k_ais_rowcnt(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, 
         }
     }
 #pragma unroll
-    for (int rr = 0; rr < AIS_RW; ++rr) {
+    for (int rr = 0; rr < RW; ++rr) {
         const int i = row_base + rr;
         if (i < AIS_NB && lane < nq) {          // cnt[particle][node][direction][class]: one contiguous record per (particle, node)
             const int qq = q0 + lane, p = qq / (R - 1), r = qq % (R - 1);
@@ -636,12 +637,17 @@ static int ais_rowcnt(gk_ctx *ctx, gk_ais *a, int n0, int p0, int p1, cudaStream
     const int qbeg = p0 * (a->R - 1), Q = p1 * (a->R - 1);
     if (Q == qbeg) return GK_OK;
     const size_t sm = (size_t)AIS_QG * AIS_CW * 4;
-    if (gk_attr_needed(ctx, (const void *)k_ais_rowcnt))
-        GK_CUDA(ctx, cudaFuncSetAttribute(k_ais_rowcnt, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
-    dim3 g(AIS_NB / (AIS_WARPS * AIS_RW), (Q - qbeg + AIS_QG - 1) / AIS_QG, 2);
+    if (gk_attr_needed(ctx, (const void *)k_ais_rowcnt<AIS_RW>)) {
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_ais_rowcnt<AIS_RW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+        GK_CUDA(ctx, cudaFuncSetAttribute(k_ais_rowcnt<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm));
+    }
+    const int qgroups = (Q - qbeg + AIS_QG - 1) / AIS_QG;
+    const bool fine = (AIS_NB / (AIS_WARPS * AIS_RW)) * qgroups * 2 < 3 * ctx->num_sms;     // three CTAs fit an SM
+    dim3 g(AIS_NB / (AIS_WARPS * (fine ? 2 : AIS_RW)), qgroups, 2);
     const bool timed = st == ctx->stream;
     if (timed) gk_time_begin(ctx, 0, 2.0 * AIS_NB * a->nw * 4.0);
-    k_ais_rowcnt<<<g, AIS_WARPS * 32, sm, st>>>(a->Ab, a->Atb, a->mask, a->nw, a->R, n0, qbeg, Q, a->cnt);
+    if (fine) k_ais_rowcnt<2><<<g, AIS_WARPS * 32, sm, st>>>(a->Ab, a->Atb, a->mask, a->nw, a->R, n0, qbeg, Q, a->cnt);
+    else k_ais_rowcnt<AIS_RW><<<g, AIS_WARPS * 32, sm, st>>>(a->Ab, a->Atb, a->mask, a->nw, a->R, n0, qbeg, Q, a->cnt);
     if (timed) gk_time_end(ctx, 0);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
