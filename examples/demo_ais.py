@@ -5,11 +5,14 @@ import _common
 import numpy as np
 
 from graphistician_b200.internals.graph_models import ErdosRenyiNetwork, StochasticBlockModel, sample_network, \
-    invariant_sbm_order, estimate_marginal_likelihood
+    invariant_sbm_order, estimate_marginal_likelihood, estimate_marginal_likelihood_batched
 
 
-def demo(seed=None, N_samples=5, N=16, R=3, B=100, steps_per_B=2, verbose=True):
+def demo(seed=None, N_samples=5, N=16, R=3, B=100, steps_per_B=2, verbose=True, batched=False):
+    """``batched``: the particles run co-resident on the device over the bit-packed matrix (gk_ais_*, configs[4]'s form)
+    instead of one after another."""
     _common.seed_everything(seed)
+    estimate = estimate_marginal_likelihood_batched if batched else estimate_marginal_likelihood
     er_model = ErdosRenyiNetwork(x=(1.0, 1.0))
     sbm_model = StochasticBlockModel(R=R, b0=1.0, b1=1.0, alpha0=10 * np.ones(R))
     (A_true, f_true, theta_true) = sample_network(sbm_model, N)
@@ -21,10 +24,10 @@ def demo(seed=None, N_samples=5, N=16, R=3, B=100, steps_per_B=2, verbose=True):
     eb_rho = nnz_A / N_conns
     eb_er_marg_lkhd = nnz_A * np.log(eb_rho) + (N_conns - nnz_A) * np.log(1 - eb_rho)
     _, f0, theta0 = sample_network(er_model, N)
-    est_er, w_er = estimate_marginal_likelihood(A_true, f0, theta0, er_model, N_samples=N_samples, B=B,
+    est_er, w_er = estimate(A_true, f0, theta0, er_model, N_samples=N_samples, B=B,
                                                 steps_per_B=steps_per_B, return_weights=True)
     _, f0, theta0 = sample_network(sbm_model, N)
-    est_sbm, w_sbm = estimate_marginal_likelihood(A_true, f0, theta0, sbm_model, N_samples=N_samples, B=B,
+    est_sbm, w_sbm = estimate(A_true, f0, theta0, sbm_model, N_samples=N_samples, B=B,
                                                   steps_per_B=steps_per_B, return_weights=True)
     if verbose:
         print("Empirical Bayes ER Marg Lkhd: ", eb_er_marg_lkhd)

@@ -85,6 +85,19 @@ def test_demo_ais():
     assert t["ais_er"] <= t["empirical_bayes_er"] + 1.0
 
 
+def test_demo_ais_batched():
+    """the same demo with the particles co-resident on the device (gk_ais_*): the two drivers estimate the same evidence"""
+    mod = _load("demo_ais")
+    a = mod.demo(seed=6, N_samples=24, N=32, B=40, steps_per_B=2, verbose=False, batched=True)
+    b = mod.demo(seed=6, N_samples=24, N=32, B=40, steps_per_B=2, verbose=False, batched=False)
+    for k in ("ais_er", "ais_sbm"):
+        assert np.isfinite(a[k]) and np.isfinite(b[k])
+    assert a["ais_er"] <= a["empirical_bayes_er"] + 1.0
+    se = np.sqrt(a["log_weights_sbm"].var(ddof=1) / 24 + b["log_weights_sbm"].var(ddof=1) / 24)
+    assert abs(a["log_weights_sbm"].mean() - b["log_weights_sbm"].mean()) < 4 * se + 1.0
+    assert abs(a["ais_er"] - b["ais_er"]) < 3.0
+
+
 def test_demo_walkthrough():
     t = _load("demo").demo(seed=7, N_iter=30, verbose=False, geweke_iter=400)
     assert np.all(np.isfinite(t["lp_trace"])) and t["lp_trace"][-1] > t["lp_trace"][0]
