@@ -159,7 +159,7 @@ extern "C" int gk_network_create(gk_ctx *ctx, int N, int B, int dev_dtype, int r
     *out = nullptr;
     if (N <= 0 || B < 0 || row0 < 0 || nrows <= 0 || row0 + nrows > N) return gk_fail(ctx, GK_EINVAL, "bad network shape");
     if (dev_dtype != GK_F32 && dev_dtype != GK_F64) return gk_fail(ctx, GK_EINVAL, "bad dtype");
-    if (B > 2) return gk_fail(ctx, GK_EUNSUPPORTED, "B=%d: this build compiles weight dimensions B in {0,1,2}", B);
+    if (B > 4) return gk_fail(ctx, GK_EUNSUPPORTED, "B=%d: this build compiles weight dimensions B in {0,...,4}", B);
     GK_CUDA(ctx, cudaSetDevice(ctx->device));
     gk_net *net = new gk_net();
     net->N = N; net->B = B; net->dtype = dev_dtype; net->row0 = row0; net->nrows = nrows; net->ld = gk_pad(N);

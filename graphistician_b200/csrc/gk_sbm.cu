@@ -17,21 +17,43 @@ struct gk_sweep {
 #define GK_CELL_MOVER_CAP 1024            // sweeps that moved more nodes than this leave no K1 table behind (a full pass is cheaper)
 static inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
 
-// sum_edges log N(w; mu, Sigma) = n*c0 + c1.sum_w + sum_{b<=b'} C2s[b,b'] sum_ww[b,b']   (B <= 2, closed form)
+// sum_edges log N(w; mu, Sigma) = n*c0 + c1.sum_w + sum_{b<=b'} C2s[b,b'] sum_ww[b,b']   (Cholesky of the symmetrised Sigma, B <= 4)
 static bool gauss_coef(int B, const double *mu, const double *sg, double *c0, double *c1, double *C2s) {
     const double LOG2PI = 1.8378770664093453;
-    if (B == 1) {
-        if (!(sg[0] > 0)) return false;
-        double iv = 1.0 / sg[0];
-        c1[0] = iv * mu[0]; *c0 = -0.5 * (LOG2PI + log(sg[0]) + mu[0] * c1[0]); C2s[0] = -0.5 * iv;
-        return true;
+    double L[16] = {0}, Li[16] = {0}, P[16];
+    for (int i = 0; i < B; ++i)
+        for (int j = 0; j <= i; ++j) {
+            double v = 0.5 * (sg[i * B + j] + sg[j * B + i]);
+            for (int k = 0; k < j; ++k) v -= L[i * B + k] * L[j * B + k];
+            if (i == j) { if (!(v > 0)) return false; L[i * B + i] = sqrt(v); }
+            else L[i * B + j] = v / L[j * B + j];
+        }
+    double logdet = 0.0;
+    for (int i = 0; i < B; ++i) logdet += 2.0 * log(L[i * B + i]);
+    for (int i = 0; i < B; ++i) {                       // Li = L^-1 (lower)
+        Li[i * B + i] = 1.0 / L[i * B + i];
+        for (int j = 0; j < i; ++j) {
+            double v = 0.0;
+            for (int k = j; k < i; ++k) v -= L[i * B + k] * Li[k * B + j];
+            Li[i * B + j] = v / L[i * B + i];
+        }
     }
-    double a = sg[0], b = 0.5 * (sg[1] + sg[2]), d = sg[3], det = a * d - b * b;
-    if (!(det > 0) || !(a > 0)) return false;
-    double i00 = d / det, i01 = -b / det, i11 = a / det;
-    c1[0] = i00 * mu[0] + i01 * mu[1]; c1[1] = i01 * mu[0] + i11 * mu[1];
-    *c0 = -0.5 * (2 * LOG2PI + log(det) + mu[0] * c1[0] + mu[1] * c1[1]);
-    C2s[0] = -0.5 * i00; C2s[1] = -i01; C2s[2] = -0.5 * i11;     // packed (0,0),(0,1)x2,(1,1)
+    for (int i = 0; i < B; ++i)                         // P = Sigma^-1 = Li^T Li
+        for (int j = 0; j < B; ++j) {
+            double v = 0.0;
+            for (int k = (i > j ? i : j); k < B; ++k) v += Li[k * B + i] * Li[k * B + j];
+            P[i * B + j] = v;
+        }
+    double quad = 0.0;
+    for (int i = 0; i < B; ++i) {
+        c1[i] = 0.0;
+        for (int j = 0; j < B; ++j) c1[i] += P[i * B + j] * mu[j];
+        quad += mu[i] * c1[i];
+    }
+    *c0 = -0.5 * (B * LOG2PI + logdet + quad);
+    int t = 0;                                          // packed (b, b') for b <= b', in gk_sym_idx order
+    for (int i = 0; i < B; ++i)
+        for (int j = i; j < B; ++j) C2s[t++] = (i == j ? -0.5 : -1.0) * P[i * B + j];
     return true;
 }
 
@@ -59,7 +81,7 @@ static int build_tables(gk_ctx *ctx, int K, int B, const double *log_m, const do
                 l1m[(size_t)k * K + k2] = beta * l1;
             }
             if (mu && B > 0) {
-                double c0, c1[2], C2s[3];
+                double c0, c1[4], C2s[10];
                 if (!gauss_coef(B, mu + ((size_t)k * K + k2) * B, sigma + ((size_t)k * K + k2) * B * B, &c0, c1, C2s))
                     return gk_fail(ctx, GK_EINVAL, "Sigma[%d,%d] is not positive definite", k, k2);
                 cs[0] += beta * c0;
@@ -118,6 +140,7 @@ static int launch_strip(gk_ctx *ctx, gk_net *net, const uint8_t *c8, int K, int 
     P.c8 = c8; P.K = K; P.chunk_rows = chunk_rows; P.nchunks = nchunks; P.partial = partial;
     int U = std::max(K, GK_STRIP_WARPS);
     size_t smem = (size_t)U * S * GK_SLOT_PITCH * sizeof(ACC) + (size_t)chunk_rows * 3 + 16;
+    if (smem > 160 * 1024) return gk_fail(ctx, GK_EUNSUPPORTED, "K=%d with B=%d in %s storage: the strip kernel needs %zu bytes of shared memory per CTA (limit 160 KB)", K, B, sizeof(T) == 8 ? "fp64" : "fp32", smem);
     if (gk_attr_needed(ctx, (const void *)k_strip_stats<T, B>))     // per context (= per device), not per process
         GK_CUDA(ctx, cudaFuncSetAttribute(k_strip_stats<T, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024));
     double bytes = (double)net->nrows * (double)std::min(nb_pad, net->N - n0) * (1.0 + B * sizeof(T)) * ndirs;
@@ -143,10 +166,9 @@ static int strip_to_stats(gk_ctx *ctx, gk_net *net, const uint8_t *c8, int K, in
     return GK_OK;
 }
 
-#define GK_DISPATCH_TB(net, CALL)                                                      \
-    ((net)->dtype == GK_F32                                                            \
-         ? ((net)->B == 0 ? CALL(float, 0) : (net)->B == 1 ? CALL(float, 1) : CALL(float, 2))   \
-         : ((net)->B == 0 ? CALL(double, 0) : (net)->B == 1 ? CALL(double, 1) : CALL(double, 2)))
+#define GK_DISPATCH_B(net, T, CALL)                                                     \
+    ((net)->B == 0 ? CALL(T, 0) : (net)->B == 1 ? CALL(T, 1) : (net)->B == 2 ? CALL(T, 2) : (net)->B == 3 ? CALL(T, 3) : CALL(T, 4))
+#define GK_DISPATCH_TB(net, CALL) ((net)->dtype == GK_F32 ? GK_DISPATCH_B(net, float, CALL) : GK_DISPATCH_B(net, double, CALL))
 
 // ---------------------------------------------------------------------------------------------
 // K1
@@ -281,6 +303,7 @@ static int launch_sample(gk_ctx *ctx, gk_net *net, gk_sweep *sw, int n0, int nb,
     {
         const int KP = gk_lp_kp(sw->K), npc = GK_LP_THREADS / KP;
         const size_t sm = gk_lp_smem(sw->K, sw->S);
+        if (sm > 200 * 1024) return gk_fail(ctx, GK_EUNSUPPORTED, "K=%d with B=%d: the conditional tables need %zu bytes of shared memory (limit 200 KB)", sw->K, B, sm);
         if (sm > 48 * 1024 && gk_attr_needed(ctx, (const void *)k_lp_from_stats<B>))
             GK_CUDA(ctx, cudaFuncSetAttribute(k_lp_from_stats<B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024));
         k_lp_from_stats<B><<<(nb + npc - 1) / npc, GK_LP_THREADS, sm, ctx->stream>>>(stats_dev, sw->T, net->diagA, net->diagW, n0, nb,
@@ -299,8 +322,18 @@ static int launch_sample(gk_ctx *ctx, gk_net *net, gk_sweep *sw, int n0, int nb,
     P.prof = ctx->sbm_prof;
     gk_time_begin(ctx, 1, 0.0);
     const size_t dyn = ((size_t)sw->K * (nb | 1) + nb) * 8 + (size_t)(nb + 15) / 16 * 16;
-    if (nb <= GK_SEQ_THREADS && dyn <= 208 * 1024) {          // conditionals of the block fit in shared memory
-        GK_CUDA(ctx, cudaFuncSetAttribute(k_sbm_seq2<T, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, 208 * 1024));
+    // dynamic shared memory the kernel may have: 227 KB per CTA minus its static arrays (they grow with the S = 1 + B + B(B+1)/2
+    // statistics per class), at most 208 KB
+    static size_t dyn_max_memo[2][5] = {{0}};
+    size_t &dyn_max = dyn_max_memo[sizeof(T) == 8][B];
+    if (!dyn_max) {
+        cudaFuncAttributes fa;
+        GK_CUDA(ctx, cudaFuncGetAttributes(&fa, k_sbm_seq2<T, B>));
+        dyn_max = std::min<size_t>(208 * 1024, (size_t)227 * 1024 - fa.sharedSizeBytes - 1024);
+    }
+    if (nb <= GK_SEQ_THREADS && dyn <= dyn_max) {          // conditionals of the block fit in shared memory
+        if (gk_attr_needed(ctx, (const void *)k_sbm_seq2<T, B>))
+            GK_CUDA(ctx, cudaFuncSetAttribute(k_sbm_seq2<T, B>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn_max));
         k_sbm_seq2<T, B><<<1, GK_SEQ_THREADS, dyn, ctx->stream>>>(P);
     } else {
         k_sbm_seq<T, B><<<1, GK_SEQ_THREADS, 0, ctx->stream>>>(P);
@@ -520,10 +553,9 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
     k_find_movers<<<std::min((N + 255) / 256, ctx->num_sms * 4), 256, 0, ctx->stream>>>(c_old8, sw->c8, N, CAP, mcnt, mlist);
     GK_CHECK_LAUNCH(ctx);
 #define CALL_MOV(T, BB) (k_cell_movers<T, BB><<<std::min(CAP, ctx->num_sms * 4), 64, (size_t)KS * 64 * 8, ctx->stream>>>(net->A, net->W, net->ld, sw->c8, mcnt, mlist, CAP, bn, N, K, cell), GK_OK)
-    if ((size_t)KS * 64 * 8 > 48 * 1024) {
-        if (net->dtype == GK_F32) { if (net->B == 2) cudaFuncSetAttribute(k_cell_movers<float, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); else if (net->B == 1) cudaFuncSetAttribute(k_cell_movers<float, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); else cudaFuncSetAttribute(k_cell_movers<float, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); }
-        else { if (net->B == 2) cudaFuncSetAttribute(k_cell_movers<double, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); else if (net->B == 1) cudaFuncSetAttribute(k_cell_movers<double, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); else cudaFuncSetAttribute(k_cell_movers<double, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, 160 * 1024); }
-    }
+#define CALL_MOVATTR(T, BB) (cudaFuncSetAttribute(k_cell_movers<T, BB>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024) == cudaSuccess ? GK_OK : GK_ECUDA)
+    if ((size_t)KS * 64 * 8 > 200 * 1024) return gk_fail(ctx, GK_EUNSUPPORTED, "K=%d with B=%d: the mover correction needs %zu bytes of shared memory", K, net->B, (size_t)KS * 64 * 8);
+    if ((size_t)KS * 64 * 8 > 48 * 1024 && (rc = GK_DISPATCH_TB(net, CALL_MOVATTR))) return gk_fail(ctx, rc, "cudaFuncSetAttribute(k_cell_movers)");
     rc = GK_DISPATCH_TB(net, CALL_MOV);
     GK_CHECK_LAUNCH(ctx);
     {

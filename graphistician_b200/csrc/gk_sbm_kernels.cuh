@@ -30,7 +30,14 @@ __device__ __forceinline__ void gk_load_w2(const T *__restrict__ p, T (&w)[2 * B
     else if constexpr (sizeof(T) == 4 && B == 1) { float2 v = __ldg((const float2 *)p); w[0] = v.x; w[1] = v.y; }
     else if constexpr (sizeof(T) == 4 && B == 2) { float4 v = __ldg((const float4 *)p); w[0] = v.x; w[1] = v.y; w[2] = v.z; w[3] = v.w; }
     else if constexpr (sizeof(T) == 8 && B == 1) { double2 v = __ldg((const double2 *)p); w[0] = v.x; w[1] = v.y; }
-    else { double2 v0 = __ldg((const double2 *)p), v1 = __ldg((const double2 *)p + 1); w[0] = v0.x; w[1] = v0.y; w[2] = v1.x; w[3] = v1.y; }
+    else if constexpr (sizeof(T) == 8 && B == 2) { double2 v0 = __ldg((const double2 *)p), v1 = __ldg((const double2 *)p + 1); w[0] = v0.x; w[1] = v0.y; w[2] = v1.x; w[3] = v1.y; }
+    else if constexpr (sizeof(T) == 4) {          // B = 3, 4: two nodes = 2 B floats, 8-byte aligned (the node pair starts on an even column)
+#pragma unroll
+        for (int k = 0; k < B; ++k) { float2 v = __ldg((const float2 *)p + k); w[2 * k] = v.x; w[2 * k + 1] = v.y; }
+    } else {
+#pragma unroll
+        for (int k = 0; k < B; ++k) { double2 v = __ldg((const double2 *)p + k); w[2 * k] = v.x; w[2 * k + 1] = v.y; }
+    }
 }
 
 struct gk_strip_params {

@@ -24,7 +24,7 @@ def _oracle_niw_cells(n_edge, sw, sww, niw):
     return mus, sigmas
 
 
-@pytest.mark.parametrize("N,C,B,dtype", [(50, 5, 2, "f64"), (160, 4, 1, "f64"), (300, 16, 2, "f32")])
+@pytest.mark.parametrize("N,C,B,dtype", [(50, 5, 2, "f64"), (160, 4, 1, "f64"), (300, 16, 2, "f32"), (120, 4, 3, "f64"), (200, 6, 4, "f64")])
 def test_resample_matches_oracle(N, C, B, dtype):
     from graphistician_b200.stochastic_block_model import GaussianStochasticBlockModel
     np.random.seed(3)

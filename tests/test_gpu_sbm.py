@@ -33,7 +33,7 @@ def _net(A, W, dtype):
     return DeviceNetwork(A, Wd, dtype=dtype), Wd
 
 
-@pytest.mark.parametrize("N,K,B,dtype", [(50, 5, 2, "f64"), (200, 16, 2, "f32"), (333, 7, 1, "f64"),
+@pytest.mark.parametrize("N,K,B,dtype", [(50, 5, 2, "f64"), (200, 16, 2, "f32"), (333, 7, 1, "f64"), (210, 6, 3, "f64"), (300, 16, 4, "f32"), (190, 9, 4, "f64"),
                                          (129, 1, 2, "f32"), (64, 32, 0, "f32"), (700, 20, 2, "f64")])
 def test_block_stats(N, K, B, dtype):
     A, W, c, m, p, mus, sig, u = _problem(N + K, N, K, B)
@@ -81,7 +81,8 @@ def _count_changes(A, W, c, m, p, mus, sig, u, mode, beta, sampler):
 
 @pytest.mark.parametrize("N,K,B,dtype,bn", [(50, 5, 2, "f64", 0), (200, 16, 2, "f64", 64), (333, 7, 1, "f64", 128),
                                             (200, 16, 2, "f32", 0), (130, 3, 2, "f64", 64), (257, 32, 2, "f64", 0),
-                                            (300, 4, 1, "f32", 64), (500, 16, 2, "f32", 128), (512, 8, 1, "f64", 64)])
+                                            (300, 4, 1, "f32", 64), (500, 16, 2, "f32", 128), (512, 8, 1, "f64", 64),
+                                            (260, 6, 3, "f64", 64), (400, 16, 4, "f32", 128), (330, 5, 4, "f64", 0), (1300, 8, 3, "f32", 0)])
 def test_sweep_old_api_shared_c(N, K, B, dtype, bn):
     from graphistician_b200 import _lib
     A, W, c, m, p, mus, sig, u = _problem(7 * N + K, N, K, B)
@@ -123,7 +124,7 @@ def test_peaked_posterior_stationary():
     assert np.array_equal(c2, ref) and nch < 50
 
 
-@pytest.mark.parametrize("N,K,B,dtype,bn", [(700, 5, 2, "f64", 128), (1500, 4, 2, "f64", 0), (900, 16, 1, "f32", 256),
+@pytest.mark.parametrize("N,K,B,dtype,bn", [(700, 5, 2, "f64", 128), (1500, 4, 2, "f64", 0), (900, 16, 1, "f32", 256), (800, 6, 4, "f64", 128), (1200, 5, 3, "f32", 0),
                                             (640, 7, 0, "f32", 64), (2600, 8, 2, "f64", 0)])
 def test_sweep_leaves_the_next_k1_table(N, K, B, dtype, bn):
     """gk_sbm_sweep_stats: the K1 statistics of the labels a sweep ends on, folded from the sweep's own per-node statistics plus
@@ -152,7 +153,8 @@ def test_sweep_leaves_the_next_k1_table(N, K, B, dtype, bn):
     assert net.sbm_sweep_stats(K + 1) is None                            # another K: nothing to offer
 
 
-@pytest.mark.parametrize("N,K,B,dtype,bn", [(1500, 4, 2, "f64", 256), (2600, 8, 2, "f64", 0), (900, 16, 1, "f32", 128), (640, 7, 0, "f32", 64)])
+@pytest.mark.parametrize("N,K,B,dtype,bn", [(1500, 4, 2, "f64", 256), (2600, 8, 2, "f64", 0), (900, 16, 1, "f32", 128), (640, 7, 0, "f32", 64),
+                                            (1100, 5, 4, "f64", 256), (1400, 6, 3, "f32", 0)])
 def test_overlapped_sweep_equals_the_serial_order(N, K, B, dtype, bn):
     """GK_CTX_OPT_SBM_OVERLAP = 2: the strip pass of node block b+1 runs beside the serial kernel of block b on a label
     snapshot and k_stats_fix moves the terms of block b's movers.  From random labels (hundreds of movers per block), the
@@ -212,3 +214,18 @@ def test_sweep_with_exact_zero_and_one_probabilities():
     assert np.all(lp_gpu[excluded] < -1e9)                             # hard exclusions stay hard
     # (a label that WAS excluded and is freed by a move comes back through -1e10 + 1e10: good to the ulp of 1e10, 2e-6)
     assert np.allclose(lp_gpu[~excluded], lp_ref[~excluded], rtol=1e-9, atol=1e-4)
+
+
+def test_weight_dimension_limits_are_reported():
+    """B in {0..4} is compiled (template instantiations); beyond it, or when a (K, B, dtype) combination needs more shared
+    memory than an SM has, the C ABI says so (GK_EUNSUPPORTED) instead of launching."""
+    from graphistician_b200 import DeviceNetwork
+    from graphistician_b200._lib import GKError
+    rng = np.random.RandomState(0)
+    A = (rng.rand(64, 64) < 0.3).astype(np.uint8)
+    with pytest.raises(GKError):
+        DeviceNetwork(A, rng.randn(64, 64, 5), dtype="f32")
+    net = DeviceNetwork(np.tile(A, (4, 4)), rng.randn(256, 256, 4), dtype="f64")
+    with pytest.raises(GKError):
+        net.block_stats(rng.randint(0, 32, 256), 32)             # 32 x 15 x 65 fp64 slots: more than 160 KB
+    net.close()
