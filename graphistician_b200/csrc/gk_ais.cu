@@ -245,7 +245,6 @@ struct AisSeqParams {
 };
 
 #define AIS_RING 64               // nodes held by the cp.async ring of the serial kernel: two windows of 32 nodes
-#define AIS_HOT 6                 // a window with at least this many movers sends the next window down the per-node path
 
 __device__ __forceinline__ void ais_cp4(uint32_t *smem, const uint32_t *g) {
     asm volatile("cp.async.ca.shared.global [%0], [%1], 4;" ::"r"((unsigned)__cvta_generic_to_shared(smem)), "l"(g) : "memory");
@@ -306,13 +305,12 @@ __device__ __forceinline__ int ais_decide(const int (&co)[R], const int (&ci)[R]
 
 // One warp per particle walks the block's 1024 nodes in index order, a window of 32 nodes at a time.  The block's small
 // per-node records (entry counts, degrees, uniforms) are staged in shared memory once; the nodes' words of A / A^T (lane =
-// word of the block's node bits) come through a cp.async ring of two windows.
-//   * per-node path (windows after a window with many movers): every lane works on the same node; the block-entry counts
-//     are corrected by popc(row & current mask) - popc(row & entry mask) over the block's own words.
-//   * window path (few movers): lane j owns node 32 w + j; its counts are corrected once per window, all 32 conditionals
-//     and draws are formed side by side, everything up to the first mover commits (those nodes saw exactly the state the
-//     serial loop would have shown them), the mover's bit goes from class a to class b in the later lanes' counts, and the
-//     remaining lanes draw again.  Same arithmetic per node on both paths (ais_decide), so the path taken never shows.
+// word of the block's node bits) come through a cp.async ring of two windows.  Per window: the block-entry counts of its 32
+// nodes are corrected by popc(row & current mask) - popc(row & entry mask) over the block's own words (lane = word, one
+// redux per node and class; skipped while no node of the block has moved); then lane j owns node 32 w + j, all 32
+// conditionals and draws are formed side by side, everything up to the first mover commits (those nodes saw exactly the
+// state the serial loop would have shown them), the mover's bit goes from class a to class b in the later lanes' counts,
+// and the remaining lanes draw again: (movers + 1) rounds per window, never more than the 32 of a node-by-node walk.
 template <int R>
 __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
     const int p = P.p0 + blockIdx.x, lane = threadIdx.x;
@@ -364,8 +362,6 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
         sz[r] = (int)P.sz[p * R + r];
     }
     int nchg = 0;
-    // the path of the block's first window follows the move rate of this particle's sweep so far
-    bool hot = P.n0 > 0 && P.nchg[p] * 32 >= (long long)AIS_HOT * P.n0;
     // one committed move a -> b of node i (uniform arguments): masks, sizes, labels, the particle's cell table
     auto commit_move = [&](int i, int a, int b, const int (&cox)[R], const int (&cix)[R], int self) {
         ++nchg;
@@ -390,55 +386,7 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
         ais_cp_wait<1>();
         __syncwarp();                                 // the window path reads words other lanes copied
         const int i0 = 32 * w, cnt = min(32, nb - i0);
-        int moved = 0;
-        if (hot) {
-            for (int jj = 0; jj < cnt; ++jj) {
-                const int i = i0 + jj;
-                const uint32_t *slot = s_ring + (size_t)(i & (AIS_RING - 1)) * 64;
-                const uint32_t ao = slot[lane], ai = slot[32 + lane];
-                int co[R], ci[R];
-                {
-                    int so = 0, si = 0;
-#pragma unroll
-                    for (int r = 0; r < R - 1; ++r) { co[r] = (int)s_ce[i * CE + r]; ci[r] = (int)s_ce[i * CE + R - 1 + r]; }
-                    if (nchg) {
-#pragma unroll
-                        for (int r = 0; r < R - 1; ++r) {
-                            const int d_o = __popc(ao & C[r]) - __popc(ao & E[r]) + 32;
-                            const int d_i = __popc(ai & C[r]) - __popc(ai & E[r]) + 32;
-                            const unsigned red = __reduce_add_sync(0xffffffffu, (unsigned)d_o | ((unsigned)d_i << 16));
-                            co[r] += (int)(red & 0xffffu) - 1024;
-                            ci[r] += (int)(red >> 16) - 1024;
-                        }
-                    }
-#pragma unroll
-                    for (int r = 0; r < R - 1; ++r) { so += co[r]; si += ci[r]; }
-                    const uint2 dg = s_dg[i];
-                    co[R - 1] = (int)dg.x - so;
-                    ci[R - 1] = (int)dg.y - si;
-                }
-                int al = 0;
-#pragma unroll
-                for (int r = 1; r < R; ++r) al += r * (int)((C[r] >> (i & 31)) & 1u);
-                const int a = __shfl_sync(0xffffffffu, al, i >> 5);
-                const int self = (__shfl_sync(0xffffffffu, ao, i >> 5) >> (i & 31)) & 1;      // A[n, n]
-                double lp[R];
-                const int b = ais_decide<R>(co, ci, sz, a, self, s_u[i], beta, lpi, lB, l1B, lp);
-                if (P.lp && lane < R) {
-                    double v = lp[0];
-#pragma unroll
-                    for (int k = 1; k < R; ++k) if (lane == k) v = lp[k];
-                    P.lp[((size_t)p * P.N + P.n0 + i) * R + lane] = v;
-                }
-                if (b != a) {
-                    int cox[R], cix[R];
-#pragma unroll
-                    for (int r = 0; r < R; ++r) { cox[r] = co[r] - ((r == a) & self); cix[r] = ci[r] - ((r == a) & self); }
-                    commit_move(i, a, b, cox, cix, self);
-                    ++moved;
-                }
-            }
-        } else {
+        {
             // lane j owns node i0 + j
             const int i = i0 + lane;
             const bool mine = lane < cnt;
@@ -495,7 +443,6 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
                     cix[r] = __shfl_sync(0xffffffffu, ci[r], jstar) - ((r == ma) & mself);
                 }
                 commit_move(i0 + jstar, ma, mb, cox, cix, mself);
-                ++moved;
                 if (lane == jstar) a = mb;
                 // the later nodes of the window: their edge to / from the mover changes class
                 const int x_o = (int)((my_o >> jstar) & 1u), x_i = (int)((my_i >> jstar) & 1u);
@@ -508,7 +455,6 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
                 }
             }
         }
-        hot = moved >= AIS_HOT;
         __syncwarp();                                 // ring slots of this window are free for the window after next
     }
     __syncwarp();
