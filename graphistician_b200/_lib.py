@@ -12,6 +12,7 @@ GK_F32, GK_F64 = 0, 1
 SELF_SKIP, SELF_ONCE, SELF_TWICE = 0, 1, 2
 SAMPLER_CUMSUM, SAMPLER_LSE = 0, 1
 CTX_OPT_SBM_OVERLAP = 1
+AIS_OPT_INCREMENTAL = 1
 
 c_int, c_i64, c_dbl, c_vp, c_sz = ctypes.c_int, ctypes.c_int64, ctypes.c_double, ctypes.c_void_p, ctypes.c_size_t
 PI64 = ctypes.POINTER(ctypes.c_int64)
@@ -95,6 +96,7 @@ SIGNATURES = {
     "gk_ais_create": (c_int, [c_vp, c_int, c_int, c_int, ctypes.POINTER(c_vp)]),
     "gk_ais_destroy": (c_int, [c_vp, c_vp]),
     "gk_ais_device_bytes": (c_sz, [c_vp]),
+    "gk_ais_set_option": (c_int, [c_vp, c_vp, c_int, c_int]),
     "gk_ais_upload_rows": (c_int, [c_vp, c_vp, c_vp, c_int, c_int, c_int]),
     "gk_ais_upload_network": (c_int, [c_vp, c_vp, c_vp]),
     "gk_ais_nnz": (c_int, [c_vp, c_vp, PI64]),

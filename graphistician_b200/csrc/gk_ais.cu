@@ -21,6 +21,7 @@
 #define AIS_QG 32                // mask rows (particle, class) per CTA of k_ais_rowcnt: lane q owns count q
 #define AIS_RW 4                 // rows per warp (2 when the grid would not fill the machine three CTAs deep)
 #define AIS_WARPS 8
+#define AIS_INC_MAX_MOVES 256    // a sweep in which no particle moved more nodes than this is followed by an incremental one
 #define AIS_LOG0 (-1e10)         // log 0 of the conditional tables (as gk_sbm.cu: exp underflows to 0, 0 * finite = 0)
 
 struct gk_ais {
@@ -30,6 +31,9 @@ struct gk_ais {
     uint32_t *mask = nullptr;                 // P x R x nw
     uint8_t *z = nullptr;                     // P x Npad
     uint32_t *cnt = nullptr;                  // P x AIS_NB x 2 x (R-1): block-entry class counts of the current node block
+    uint32_t *cnt_all = nullptr;              // P x Npad x 2 x (R-1): the same for EVERY node, kept current move by move (incremental mode; lazily allocated)
+    uint32_t *mv_list = nullptr; int *mv_cnt = nullptr;   // P x AIS_NB movers (i | a << 16 | b << 24) of the block just drawn, and their number
+    bool cache_valid = false; long long last_max_moves = -1; int inc_mode = 1;     // inc_mode: 0 never, 1 after a sweep with few movers, 2 always
     long long *cell = nullptr;                // P x R x R edge counts, diagonal included
     long long *sz = nullptr;                  // P x R
     long long *nchg = nullptr;                // P
@@ -141,7 +145,7 @@ __device__ __forceinline__ unsigned ais_popc16(const uint32_t *a, const uint4 m0
 template <int RW>
 __global__ void __launch_bounds__(AIS_WARPS * 32)
 k_ais_rowcnt(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, const uint32_t *__restrict__ mask, int nw, int R,
-             int n0, int qbeg, int Q, uint32_t *__restrict__ cnt) {
+             int n0, int qbeg, int Q, uint32_t *__restrict__ cnt, size_t stride, int off) {
     extern __shared__ uint4 s_m4[];                                   // [AIS_QG][AIS_CW/4]
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int q0 = qbeg + blockIdx.y * AIS_QG;
@@ -188,7 +192,7 @@ k_ais_rowcnt(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, 
         const int i = row_base + rr;
         if (i < AIS_NB && lane < nq) {          // cnt[particle][node][direction][class]: one contiguous record per (particle, node)
             const int qq = q0 + lane, p = qq / (R - 1), r = qq % (R - 1);
-            cnt[(((size_t)p * AIS_NB + i) * 2 + blockIdx.z) * (R - 1) + r] = acc[rr];
+            cnt[(((size_t)p * stride + off + i) * 2 + blockIdx.z) * (R - 1) + r] = acc[rr];
         }
     }
 }
@@ -242,6 +246,8 @@ struct AisSeqParams {
     long long *cell, *sz, *nchg;
     const double *tab, *u; double *lp;
     int N, Npad, nw, n0, p0;
+    size_t cnt_stride; int cnt_off;           // cnt holds records of cnt_stride nodes per particle; this block starts at cnt_off
+    uint32_t *mv_list; int *mv_cnt;           // movers of this block (incremental mode) or null
 };
 
 #define AIS_RING 64               // nodes held by the cp.async ring of the serial kernel: two windows of 32 nodes
@@ -338,7 +344,7 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
     };
     issue_window(0);
     {
-        const uint4 *g = reinterpret_cast<const uint4 *>(P.cnt + (size_t)p * AIS_NB * CE);
+        const uint4 *g = reinterpret_cast<const uint4 *>(P.cnt + ((size_t)p * P.cnt_stride + P.cnt_off) * CE);
         uint4 *d = reinterpret_cast<uint4 *>(s_ce);
         for (int t = lane; t < AIS_NB * CE / 4; t += 32) d[t] = g[t];
         const uint4 *g2 = reinterpret_cast<const uint4 *>(P.deg + P.n0);
@@ -373,6 +379,7 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
         }
         if (lane == 0) {
             P.z[(size_t)p * P.Npad + P.n0 + i] = (uint8_t)b;
+            if (P.mv_list) P.mv_list[(size_t)p * AIS_NB + nchg - 1] = (uint32_t)i | ((uint32_t)a << 16) | ((uint32_t)b << 24);
 #pragma unroll
             for (int r = 0; r < R; ++r) {
                 s_cell[a * R + r] -= cox[r]; s_cell[b * R + r] += cox[r];          // edges n -> class r change their source class
@@ -464,7 +471,38 @@ __global__ void __launch_bounds__(32) k_ais_seq(AisSeqParams P) {
         if (lane == 0) P.sz[p * R + r] = sz[r];
     }
     for (int t = lane; t < R * R; t += 32) P.cell[(size_t)p * R * R + t] += s_cell[t];
-    if (lane == 0) P.nchg[p] += nchg;
+    if (lane == 0) { P.nchg[p] += nchg; if (P.mv_cnt) P.mv_cnt[p] = nchg; }
+}
+
+// Incremental mode: the class counts of EVERY node are kept in cnt_all and moved along with the labels.  After a block has been
+// drawn, each of its movers m (a -> b) changes, for every node j, the out-count of j by A[j, m] and the in-count by A[m, j]:
+// one bit of row m of A^T resp. A per node.  Thread = node j (it owns its record: no atomics), the two rows are read as words
+// shared by the 32 nodes of a warp.  With no mover the kernel returns at once -- and the sweep needs no counting pass at all.
+template <int R>
+__global__ void __launch_bounds__(256) k_ais_apply(const uint32_t *__restrict__ Ab, const uint32_t *__restrict__ Atb, int nw, int Npad, int N,
+                                                   int n0, int p0, const uint32_t *__restrict__ mv_list, const int *__restrict__ mv_cnt,
+                                                   uint32_t *__restrict__ cnt_all) {
+    constexpr int CE = 2 * (R - 1);
+    const int p = p0 + blockIdx.y, nm = mv_cnt[p];
+    const int j = blockIdx.x * 256 + threadIdx.x;
+    if (nm == 0 || j >= N) return;
+    int d[CE];
+#pragma unroll
+    for (int t = 0; t < CE; ++t) d[t] = 0;
+    for (int q = 0; q < nm; ++q) {
+        const uint32_t e = mv_list[(size_t)p * AIS_NB + q];
+        const int m = n0 + (int)(e & 0xffffu), a = (int)((e >> 16) & 0xffu), b = (int)(e >> 24);
+        const int xo = (int)((Atb[(size_t)m * nw + (j >> 5)] >> (j & 31)) & 1u);      // A[j, m]
+        const int xi = (int)((Ab[(size_t)m * nw + (j >> 5)] >> (j & 31)) & 1u);       // A[m, j]
+#pragma unroll
+        for (int r = 0; r < R - 1; ++r) {
+            if (r == a) { d[r] -= xo; d[R - 1 + r] -= xi; }
+            if (r == b) { d[r] += xo; d[R - 1 + r] += xi; }
+        }
+    }
+    uint32_t *c = cnt_all + ((size_t)p * Npad + j) * CE;
+#pragma unroll
+    for (int t = 0; t < CE; ++t) if (d[t]) c[t] = (uint32_t)((int)c[t] + d[t]);
 }
 
 // ---------------------------------------------------------------------------------------------------------------
@@ -516,7 +554,7 @@ extern "C" int gk_ais_destroy(gk_ctx *ctx, gk_ais *a) {
     if (a->s2) { cudaStreamSynchronize(a->s2); cudaStreamDestroy(a->s2); }
     if (a->ev_fork) cudaEventDestroy(a->ev_fork);
     if (a->ev_join) cudaEventDestroy(a->ev_join);
-    void *ptrs[] = {a->Ab, a->Atb, a->deg, a->mask, a->z, a->cnt, a->cell, a->sz, a->nchg, a->tab, a->u, a->lp};
+    void *ptrs[] = {a->Ab, a->Atb, a->deg, a->mask, a->z, a->cnt, a->cell, a->sz, a->nchg, a->tab, a->u, a->lp, a->cnt_all, a->mv_list, a->mv_cnt};
     for (void *p : ptrs) if (p) cudaFree(p);
     delete a;
     return GK_OK;
@@ -524,13 +562,19 @@ extern "C" int gk_ais_destroy(gk_ctx *ctx, gk_ais *a) {
 
 extern "C" size_t gk_ais_device_bytes(gk_ais *a) { return a ? a->bytes : 0; }
 
+extern "C" int gk_ais_set_option(gk_ctx *ctx, gk_ais *a, int option, int value) {
+    if (!ctx || !a) return GK_EINVAL;
+    if (option == GK_AIS_OPT_INCREMENTAL && value >= 0 && value <= 2) { a->inc_mode = value; return GK_OK; }
+    return gk_fail(ctx, GK_EINVAL, "gk_ais_set_option: unknown option %d or value %d", option, value);
+}
+
 static int ais_pack(gk_ctx *ctx, gk_ais *a, const uint8_t *src, size_t lds, int row0, int nrows) {
     k_ais_pack_rows<<<ctx->num_sms * 8, 256, 0, ctx->stream>>>(src, lds, a->N, nrows, row0, a->Ab, a->nw);
     GK_CHECK_LAUNCH(ctx);
     dim3 g((a->N + 255) / 256, (nrows + 31) / 32);
     k_ais_pack_cols<<<g, 256, 0, ctx->stream>>>(src, lds, a->N, nrows, row0, a->Atb, a->nw);
     GK_CHECK_LAUNCH(ctx);
-    a->packed = true; a->degrees = false;
+    a->packed = true; a->degrees = false; a->cache_valid = false;
     return GK_OK;
 }
 
@@ -579,7 +623,7 @@ extern "C" int gk_ais_nnz(gk_ctx *ctx, gk_ais *a, int64_t *nnz) {
 }
 
 // block-entry counts of node block n0 for the particles [p0, p1), on `st`
-static int ais_rowcnt(gk_ctx *ctx, gk_ais *a, int n0, int p0, int p1, cudaStream_t st) {
+static int ais_rowcnt(gk_ctx *ctx, gk_ais *a, int n0, int p0, int p1, cudaStream_t st, bool to_all = false) {
     const int qbeg = p0 * (a->R - 1), Q = p1 * (a->R - 1);
     if (Q == qbeg) return GK_OK;
     const size_t sm = (size_t)AIS_QG * AIS_CW * 4;
@@ -592,8 +636,11 @@ static int ais_rowcnt(gk_ctx *ctx, gk_ais *a, int n0, int p0, int p1, cudaStream
     dim3 g(AIS_NB / (AIS_WARPS * (fine ? 2 : AIS_RW)), qgroups, 2);
     const bool timed = st == ctx->stream;
     if (timed) gk_time_begin(ctx, 0, 2.0 * AIS_NB * a->nw * 4.0);
-    if (fine) k_ais_rowcnt<2><<<g, AIS_WARPS * 32, sm, st>>>(a->Ab, a->Atb, a->mask, a->nw, a->R, n0, qbeg, Q, a->cnt);
-    else k_ais_rowcnt<AIS_RW><<<g, AIS_WARPS * 32, sm, st>>>(a->Ab, a->Atb, a->mask, a->nw, a->R, n0, qbeg, Q, a->cnt);
+    uint32_t *dst = to_all ? a->cnt_all : a->cnt;
+    const size_t stride = to_all ? (size_t)a->Npad : (size_t)AIS_NB;
+    const int off = to_all ? n0 : 0;
+    if (fine) k_ais_rowcnt<2><<<g, AIS_WARPS * 32, sm, st>>>(a->Ab, a->Atb, a->mask, a->nw, a->R, n0, qbeg, Q, dst, stride, off);
+    else k_ais_rowcnt<AIS_RW><<<g, AIS_WARPS * 32, sm, st>>>(a->Ab, a->Atb, a->mask, a->nw, a->R, n0, qbeg, Q, dst, stride, off);
     if (timed) gk_time_end(ctx, 0);
     GK_CHECK_LAUNCH(ctx);
     return GK_OK;
@@ -629,7 +676,7 @@ extern "C" int gk_ais_set_labels(gk_ctx *ctx, gk_ais *a, const int32_t *z, int b
     const long long warps = (long long)a->P * a->nw;
     k_ais_masks<<<(unsigned)((warps * 32 + 255) / 256), 256, 0, ctx->stream>>>(a->z, a->Npad, a->nw, a->N, a->P, a->R, a->mask);
     GK_CHECK_LAUNCH(ctx);
-    a->labelled = true;
+    a->labelled = true; a->cache_valid = false; a->last_max_moves = -1;
     return ais_recount(ctx, a);
 }
 
@@ -653,6 +700,11 @@ extern "C" int gk_ais_counts(gk_ctx *ctx, gk_ais *a, int recompute, int64_t *n_e
     return GK_OK;
 }
 
+template <int R> static void ais_launch_apply(gk_ais *a, int n0, int p0, int np, cudaStream_t st) {
+    dim3 g((a->N + 255) / 256, np);
+    k_ais_apply<R><<<g, 256, 0, st>>>(a->Ab, a->Atb, a->nw, a->Npad, a->N, n0, p0, a->mv_list, a->mv_cnt, a->cnt_all);
+}
+
 template <int R> static int ais_launch_seq(gk_ctx *ctx, int np, cudaStream_t st, const AisSeqParams &prm) {
     if (gk_attr_needed(ctx, (const void *)k_ais_seq<R>))
         GK_CUDA(ctx, cudaFuncSetAttribute(k_ais_seq<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ais_seq_smem<R>()));
@@ -666,7 +718,6 @@ static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool
     const int R = a->R;
     int rc = ais_degrees(ctx, a); if (rc) return rc;
     GK_CUDA(ctx, cudaMemcpyAsync(a->tab, tab_host, (size_t)a->P * (1 + R + 2 * R * R) * 8, cudaMemcpyHostToDevice, ctx->stream));
-    GK_CUDA(ctx, cudaMemsetAsync(a->nchg, 0, (size_t)a->P * 8, ctx->stream));
     a->sweep++;
     if (R == 1) return GK_OK;
     if (!inject) {
@@ -674,8 +725,41 @@ static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool
         k_ais_uniforms<<<(unsigned)((tot + 255) / 256), 256, 0, ctx->stream>>>(a->u, a->P, a->N, a->Npad, seed, a->sweep);
         GK_CHECK_LAUNCH(ctx);
     }
+    // Incremental mode (the previous sweep moved few nodes): the class counts of every node live in cnt_all and follow the
+    // moves (k_ais_apply), so no counting pass runs at all; entering the mode costs one counting pass over the final masks.
+    bool inc = a->inc_mode == 2;
+    if (a->inc_mode == 1 && a->sweep > 1) {
+        std::vector<long long> h(a->P);
+        GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+        if (a->last_max_moves == -2) {               // the previous sweep's move counts are still on the device
+            GK_CUDA(ctx, cudaMemcpy(h.data(), a->nchg, (size_t)a->P * 8, cudaMemcpyDeviceToHost));
+            a->last_max_moves = 0;
+            for (long long v : h) a->last_max_moves = std::max(a->last_max_moves, v);
+        }
+        inc = a->last_max_moves >= 0 && a->last_max_moves <= AIS_INC_MAX_MOVES;
+    }
+    GK_CUDA(ctx, cudaMemsetAsync(a->nchg, 0, (size_t)a->P * 8, ctx->stream));
+    if (inc) {
+        const size_t CE = 2 * (R - 1);
+        if (!a->cnt_all) {
+            GK_CUDA(ctx, cudaMalloc(&a->cnt_all, ((size_t)a->P * a->Npad + 4) * CE * 4));
+            GK_CUDA(ctx, cudaMalloc(&a->mv_list, (size_t)a->P * AIS_NB * 4));
+            GK_CUDA(ctx, cudaMalloc(&a->mv_cnt, (size_t)a->P * 4));
+            a->bytes += ((size_t)a->P * a->Npad + 4) * CE * 4 + (size_t)a->P * AIS_NB * 4 + (size_t)a->P * 4;
+            a->cache_valid = false;
+        }
+        if (!a->cache_valid) {
+            for (int n0 = 0; n0 < a->N; n0 += AIS_NB)
+                if ((rc = ais_rowcnt(ctx, a, n0, 0, a->P, ctx->stream, true))) return rc;
+            a->cache_valid = true;
+        }
+    } else {
+        a->cache_valid = false;
+    }
     AisSeqParams prm;
-    prm.Ab = a->Ab; prm.Atb = a->Atb; prm.deg = a->deg; prm.cnt = a->cnt; prm.mask = a->mask; prm.z = a->z;
+    prm.Ab = a->Ab; prm.Atb = a->Atb; prm.deg = a->deg; prm.mask = a->mask; prm.z = a->z;
+    prm.cnt = inc ? a->cnt_all : a->cnt; prm.cnt_stride = inc ? (size_t)a->Npad : (size_t)AIS_NB;
+    prm.mv_list = inc ? a->mv_list : nullptr; prm.mv_cnt = inc ? a->mv_cnt : nullptr;
     prm.cell = a->cell; prm.sz = a->sz; prm.nchg = a->nchg; prm.tab = a->tab; prm.u = a->u;
     prm.lp = want_lp ? a->lp : nullptr;
     prm.N = a->N; prm.Npad = a->Npad; prm.nw = a->nw;
@@ -686,21 +770,21 @@ static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool
         GK_CUDA(ctx, cudaStreamWaitEvent(a->s2, a->ev_fork, 0));
     }
     for (int n0 = 0; n0 < a->N; n0 += AIS_NB) {
-        prm.n0 = n0;
+        prm.n0 = n0; prm.cnt_off = inc ? n0 : 0;
         for (int g = 0; g < ngroups; ++g) {
             const int p0 = g ? split : 0, p1 = g ? a->P : split;
             cudaStream_t st = g ? a->s2 : ctx->stream;
-            if ((rc = ais_rowcnt(ctx, a, n0, p0, p1, st))) return rc;
+            if (!inc && (rc = ais_rowcnt(ctx, a, n0, p0, p1, st))) return rc;
             prm.p0 = p0;
             if (!g) gk_time_begin(ctx, 1, 0.0);
             switch (R) {
-                case 2: rc = ais_launch_seq<2>(ctx, p1 - p0, st, prm); break;
-                case 3: rc = ais_launch_seq<3>(ctx, p1 - p0, st, prm); break;
-                case 4: rc = ais_launch_seq<4>(ctx, p1 - p0, st, prm); break;
-                case 5: rc = ais_launch_seq<5>(ctx, p1 - p0, st, prm); break;
-                case 6: rc = ais_launch_seq<6>(ctx, p1 - p0, st, prm); break;
-                case 7: rc = ais_launch_seq<7>(ctx, p1 - p0, st, prm); break;
-                default: rc = ais_launch_seq<8>(ctx, p1 - p0, st, prm); break;
+                case 2: rc = ais_launch_seq<2>(ctx, p1 - p0, st, prm); if (inc) ais_launch_apply<2>(a, n0, p0, p1 - p0, st); break;
+                case 3: rc = ais_launch_seq<3>(ctx, p1 - p0, st, prm); if (inc) ais_launch_apply<3>(a, n0, p0, p1 - p0, st); break;
+                case 4: rc = ais_launch_seq<4>(ctx, p1 - p0, st, prm); if (inc) ais_launch_apply<4>(a, n0, p0, p1 - p0, st); break;
+                case 5: rc = ais_launch_seq<5>(ctx, p1 - p0, st, prm); if (inc) ais_launch_apply<5>(a, n0, p0, p1 - p0, st); break;
+                case 6: rc = ais_launch_seq<6>(ctx, p1 - p0, st, prm); if (inc) ais_launch_apply<6>(a, n0, p0, p1 - p0, st); break;
+                case 7: rc = ais_launch_seq<7>(ctx, p1 - p0, st, prm); if (inc) ais_launch_apply<7>(a, n0, p0, p1 - p0, st); break;
+                default: rc = ais_launch_seq<8>(ctx, p1 - p0, st, prm); if (inc) ais_launch_apply<8>(a, n0, p0, p1 - p0, st); break;
             }
             if (!g) gk_time_end(ctx, 1);
             if (rc) return rc;
@@ -711,6 +795,7 @@ static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool
         GK_CUDA(ctx, cudaEventRecord(a->ev_join, a->s2));
         GK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, a->ev_join, 0));
     }
+    a->last_max_moves = -2;
     return GK_OK;
 }
 

@@ -486,6 +486,9 @@ class DeviceAIS:
     def device_bytes(self):
         return int(self.ctx.lib.gk_ais_device_bytes(self.h))
 
+    def set_option(self, option, value):
+        self.ctx.check(self.ctx.lib.gk_ais_set_option(self.ctx.h, self.h, int(option), int(value)))
+
     def nnz(self):
         v = ctypes.c_int64()
         self.ctx.check(self.ctx.lib.gk_ais_nnz(self.ctx.h, self.h, ctypes.byref(v)))

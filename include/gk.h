@@ -299,6 +299,11 @@ enum { GK_AIS_ER = 0,   /* internals/graph_models.py:105-182 (ErdosRenyiNetwork)
 int gk_ais_create(gk_ctx *ctx, int N, int P, int R, gk_ais **out);
 int gk_ais_destroy(gk_ctx *ctx, gk_ais *ais);
 size_t gk_ais_device_bytes(gk_ais *ais);
+/* GK_AIS_OPT_INCREMENTAL: keep the class counts of every node on the device and move them along with the labels (no counting
+ * pass in the sweep; same results) -- 0 never, 1 (default) after a sweep in which no particle moved more than 256 nodes,
+ * 2 always.  Costs P x N x 2 (R - 1) x 4 bytes. */
+enum { GK_AIS_OPT_INCREMENTAL = 1 };
+int gk_ais_set_option(gk_ctx *ctx, gk_ais *ais, int option, int value);
 /* rows [row0, row0 + nrows) of the {0,1} uint8 matrix A (nrows x N, row0 a multiple of 32; the `A` of
  * estimate_marginal_likelihood, demo_ais.py:10) -> the bit-packed rows of A and bit columns of A^T.  src_on_device != 0:
  * A_rows is a device pointer. */

@@ -123,6 +123,44 @@ def test_row_chunk_upload_equals_whole_upload_and_exact_zero_one_probabilities()
     dev.close()
 
 
+@pytest.mark.parametrize("N,R,P", [(1500, 3, 5), (2300, 4, 18), (700, 2, 3)])
+def test_incremental_counts_equal_the_counting_pass(N, R, P):
+    """GK_AIS_OPT_INCREMENTAL: the class counts of every node are kept on the device and moved with the labels (k_ais_apply)
+    instead of being recounted per node block.  Five sweeps from random labels (many movers, then few) in mode 2 (always)
+    and in mode 1 (switches itself on once a sweep moved few nodes) against mode 0: identical labels, move counts,
+    conditionals and R x R tables; and the tables equal a fresh count."""
+    from graphistician_b200 import _lib
+    from graphistician_b200.device import DeviceAIS
+    A, zt, rng = _data(N, R, 41 + N)
+    z0 = rng.randint(0, R, (P, N))
+    pi = rng.dirichlet(5 * np.ones(R), P)
+    Bt = rng.beta(1, 1, (R, R))
+    A = (rng.rand(N, N) < Bt[np.ix_(zt, zt)]).astype(np.uint8)
+    Bm = np.tile(np.clip(Bt, 0.02, 0.98), (P, 1, 1))
+    beta = np.linspace(1.0, 0.3, P)
+    us = [rng.rand(P, N) for _ in range(5)]
+    out = {}
+    for mode in (0, 2, 1):
+        dev = DeviceAIS(A, P, R)
+        dev.set_option(_lib.AIS_OPT_INCREMENTAL, mode)
+        dev.set_labels(z0)
+        res = []
+        for it in range(5):
+            nchg, lp = dev.sweep(np.log(pi), Bm, beta, uniforms=us[it], want_lp=True)
+            res.append((dev.get_labels(), nchg.copy(), lp.copy(), dev.counts()))
+        e1, s1 = dev.counts(); e2, s2 = dev.counts(recompute=True)
+        assert np.array_equal(e1, e2) and np.array_equal(s1, s2)
+        out[mode] = res
+        dev.close()
+    for mode in (2, 1):
+        for it in range(5):
+            z_a, n_a, lp_a, (e_a, s_a) = out[0][it]
+            z_b, n_b, lp_b, (e_b, s_b) = out[mode][it]
+            assert np.array_equal(z_a, z_b) and np.array_equal(n_a, n_b), (mode, it)
+            assert np.array_equal(lp_a, lp_b) and np.array_equal(e_a, e_b) and np.array_equal(s_a, s_b), (mode, it)
+    assert out[0][0][1].min() > N // 4 and out[0][4][1].max() <= 256, "the sweeps must cover both regimes"
+
+
 def _ref_sample_theta(rs, A, z, R, b0, b1, alpha0, beta):
     """internals/graph_models.py:337-371 literally, drawing from the particle's stream."""
     alpha_post = np.array([alpha0[r] + np.sum(z == r) for r in range(R)], dtype=float)
