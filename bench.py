@@ -460,6 +460,16 @@ def bench_workload(name, args, R, dtype, steps, warmup, rows=False, cpu=True, fi
                      "sweep_frac_of_peak": algo_bytes / (ms / steps * 1e-3) / 1e9 / peak},
         "l2": "inputs (%.2f GB/sweep) exceed the 126 MB L2" % (algo_bytes / 1e9),
     })
+    if name == "latent":
+        # the pair kernel is bound by the XU (MUFU) pipe, not by HBM: ex2 + rcp per unordered pair, 16 MUFU per clock and SM
+        sm_mhz = clocks.get("sm_mhz") or 1965.0
+        pairs = 22.0 * args.n * (args.n - 1) / 2.0 / mult
+        n_sm = R.torch.cuda.get_device_properties(R.local).multi_processor_count
+        bound_ms = pairs * 2.0 / (16.0 * n_sm * sm_mhz * 1e6) * 1e3
+        rec["roofline"]["xu_pipe"] = {"mufu_per_pair": 2, "pair_evaluations_per_sweep": pairs, "bound_ms_per_sweep": bound_ms,
+                                      "frac": bound_ms / (kms / 3.0) if kms > 0 else None,
+                                      "note": "the HBM figure above is SURVEY.md 8(d)'s accounting (22 N^2 bytes); the kernel reads A + A^T "
+                                              "once per unordered pair and is bound by the two transcendental operations per pair"}
     if name == "sbm":
         rec["n_changed_last_sweep"] = int(max_over_ranks(float(getattr(model, "_n_changed", -1)), R.world, R.dev))
         rec["extra_warmup_sweeps"] = extra_warm
