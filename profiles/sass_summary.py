@@ -10,7 +10,7 @@ KERN = {"gk_sbm.o": ["k_strip_stats<float, 2>", "k_sbm_seq2<float, 2>", "k_lp_fr
         "gk_eig.o": ["k_eig_seq5<8, 0>", "k_eig_pg_tile<float>", "k_eig_push<float, 8>"],
         "gk_eig_tc.o": ["k_eig_gfull_tc"],
         "gk_latent.o": ["k_latent_pair<float, 2, 0, 1>", "k_latent_pair<float, 2, 1, 1>"],
-        "gk_ais.o": ["k_ais_rowcnt", "k_ais_seq<3>"]}
+        "gk_ais.o": ["k_ais_rowcnt<4>", "k_ais_seq<3>", "k_ais_apply<3>"]}
 KEEP = ("UTC", "UTMA", "LDTM", "STTM", "SYNCS", "REDUX", "LDGSTS", "MUFU", "POPC", "DFMA", "HMMA", "IMMA", "BAR", "SHFL")
 
 print("# cuobjdump -sass instruction histograms of the hot kernels at HEAD (sm_100a); profiles/sass_summary.py\n")
