@@ -39,7 +39,7 @@ struct gk_ais {
     long long *nchg = nullptr;                // P
     double *tab = nullptr;                    // P x (1 + R + 2 R R): beta, log pi, log B, log(1-B)
     double *u = nullptr;                      // P x Npad uniforms of the sweep: injected, or k_ais_uniforms (allocated on first use)
-    cudaStream_t s2 = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // second particle group
+    cudaStream_t sx[3] = {nullptr, nullptr, nullptr}; cudaEvent_t ev_fork = nullptr, ev_join[3] = {nullptr, nullptr, nullptr};   // particle groups 2 - 4
     double *lp = nullptr;                     // P x N x R conditionals (allocated on first use)
     bool packed = false, degrees = false, labelled = false;
     uint32_t sweep = 0;
@@ -540,9 +540,11 @@ extern "C" int gk_ais_create(gk_ctx *ctx, int N, int P, int R, gk_ais **out) {
         cudaMemsetAsync(*al.p, 0, al.n, ctx->stream);
         a->bytes += al.n;
     }
-    if (cudaStreamCreateWithFlags(&a->s2, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaEventCreateWithFlags(&a->ev_fork, cudaEventDisableTiming) != cudaSuccess ||
-        cudaEventCreateWithFlags(&a->ev_join, cudaEventDisableTiming) != cudaSuccess)
+    bool ok = cudaEventCreateWithFlags(&a->ev_fork, cudaEventDisableTiming) == cudaSuccess;
+    for (int g = 0; g < 3; ++g)
+        ok = ok && cudaStreamCreateWithFlags(&a->sx[g], cudaStreamNonBlocking) == cudaSuccess &&
+             cudaEventCreateWithFlags(&a->ev_join[g], cudaEventDisableTiming) == cudaSuccess;
+    if (!ok)
         return gk_fail(ctx, GK_ECUDA, "gk_ais_create: stream / event creation failed");
     *out = a;
     return GK_OK;
@@ -551,9 +553,11 @@ extern "C" int gk_ais_create(gk_ctx *ctx, int N, int P, int R, gk_ais **out) {
 extern "C" int gk_ais_destroy(gk_ctx *ctx, gk_ais *a) {
     if (ais_check(ctx, a)) return GK_EINVAL;
     cudaStreamSynchronize(ctx->stream);
-    if (a->s2) { cudaStreamSynchronize(a->s2); cudaStreamDestroy(a->s2); }
+    for (int g = 0; g < 3; ++g) {
+        if (a->sx[g]) { cudaStreamSynchronize(a->sx[g]); cudaStreamDestroy(a->sx[g]); }
+        if (a->ev_join[g]) cudaEventDestroy(a->ev_join[g]);
+    }
     if (a->ev_fork) cudaEventDestroy(a->ev_fork);
-    if (a->ev_join) cudaEventDestroy(a->ev_join);
     void *ptrs[] = {a->Ab, a->Atb, a->deg, a->mask, a->z, a->cnt, a->cell, a->sz, a->nchg, a->tab, a->u, a->lp, a->cnt_all, a->mv_list, a->mv_cnt};
     for (void *p : ptrs) if (p) cudaFree(p);
     delete a;
@@ -712,7 +716,7 @@ template <int R> static int ais_launch_seq(gk_ctx *ctx, int np, cudaStream_t st,
     return GK_OK;
 }
 
-// One sweep.  The particles are split in two groups on two streams so that one group's serial kernel (one warp per
+// One sweep.  The particles are split in up to four groups on as many streams so that one group's serial kernel (one warp per
 // particle) runs beside the other group's counting pass (which fills the rest of the machine).
 static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool inject, uint64_t seed, bool want_lp) {
     const int R = a->R;
@@ -763,17 +767,19 @@ static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool
     prm.cell = a->cell; prm.sz = a->sz; prm.nchg = a->nchg; prm.tab = a->tab; prm.u = a->u;
     prm.lp = want_lp ? a->lp : nullptr;
     prm.N = a->N; prm.Npad = a->Npad; prm.nw = a->nw;
-    const int ngroups = (a->P >= 16 && !ctx->timing) ? 2 : 1;          // kernel timing brackets need one stream
-    const int split = ngroups == 2 ? (a->P + 1) / 2 : a->P;
-    if (ngroups == 2) {
+    // particle groups on their own streams: a group's serial kernel runs beside the other groups' counting passes
+    const int ngroups = ctx->timing ? 1 : (a->P >= 64 ? 4 : (a->P >= 16 ? 2 : 1));      // kernel timing brackets need one stream
+    const int per = (a->P + ngroups - 1) / ngroups;
+    if (ngroups > 1) {
         GK_CUDA(ctx, cudaEventRecord(a->ev_fork, ctx->stream));
-        GK_CUDA(ctx, cudaStreamWaitEvent(a->s2, a->ev_fork, 0));
+        for (int g = 1; g < ngroups; ++g) GK_CUDA(ctx, cudaStreamWaitEvent(a->sx[g - 1], a->ev_fork, 0));
     }
     for (int n0 = 0; n0 < a->N; n0 += AIS_NB) {
         prm.n0 = n0; prm.cnt_off = inc ? n0 : 0;
         for (int g = 0; g < ngroups; ++g) {
-            const int p0 = g ? split : 0, p1 = g ? a->P : split;
-            cudaStream_t st = g ? a->s2 : ctx->stream;
+            const int p0 = std::min(a->P, g * per), p1 = std::min(a->P, (g + 1) * per);
+            if (p1 == p0) continue;
+            cudaStream_t st = g ? a->sx[g - 1] : ctx->stream;
             if (!inc && (rc = ais_rowcnt(ctx, a, n0, p0, p1, st))) return rc;
             prm.p0 = p0;
             if (!g) gk_time_begin(ctx, 1, 0.0);
@@ -791,9 +797,9 @@ static int ais_sweep_device(gk_ctx *ctx, gk_ais *a, const double *tab_host, bool
             GK_CHECK_LAUNCH(ctx);
         }
     }
-    if (ngroups == 2) {
-        GK_CUDA(ctx, cudaEventRecord(a->ev_join, a->s2));
-        GK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, a->ev_join, 0));
+    for (int g = 1; g < ngroups; ++g) {
+        GK_CUDA(ctx, cudaEventRecord(a->ev_join[g - 1], a->sx[g - 1]));
+        GK_CUDA(ctx, cudaStreamWaitEvent(ctx->stream, a->ev_join[g - 1], 0));
     }
     a->last_max_moves = -2;
     return GK_OK;
