@@ -11,7 +11,15 @@ int gk_fail(gk_ctx *ctx, int code, const char *fmt, ...) {
     return code;
 }
 
+void gk_spec_cancel(gk_ctx *ctx) {
+    if (!ctx || !ctx->spec.active) return;
+    if (ctx->aux) cudaStreamSynchronize(ctx->aux);
+    ctx->spec.active = false;
+}
+
 void *gk_scratch(gk_ctx *ctx, int slot, size_t bytes) {
+    // slots 2, 3, 10, 11 may be in use by the background strip passes of a speculated sweep: any other user ends the speculation
+    if (ctx->spec.active && !ctx->spec.self && (slot == 2 || slot == 3 || slot == 10 || slot == 11)) gk_spec_cancel(ctx);
     if (ctx->scratch_bytes[slot] >= bytes && ctx->scratch[slot]) return ctx->scratch[slot];
     if (ctx->scratch[slot]) { cudaStreamSynchronize(ctx->stream); cudaFree(ctx->scratch[slot]); ctx->scratch[slot] = nullptr; }
     size_t want = bytes + bytes / 4 + 256;
@@ -52,6 +60,7 @@ extern "C" int gk_ctx_create(int device, gk_ctx **out) {
     ctx->sbm_prof = getenv("GK_SBM_PROF") != nullptr;
     ctx->sbm_overlap = getenv("GK_SBM_NO_OVERLAP") == nullptr;
     if (!ctx->sbm_overlap) ctx->sbm_overlap_mode = 0;
+    if (const char *mo = getenv("GK_SBM_OVERLAP_MODE")) { const int v = atoi(mo); if (v >= 0 && v <= 3) ctx->sbm_overlap_mode = v; }
     *out = ctx;
     return GK_OK;
 }
@@ -64,6 +73,7 @@ extern "C" void gk_ctx_destroy(gk_ctx *ctx) {
     if (ctx->aux) { cudaStreamSynchronize(ctx->aux); cudaStreamDestroy(ctx->aux); }
     if (ctx->ev_fork) cudaEventDestroy(ctx->ev_fork);
     if (ctx->ev_join) cudaEventDestroy(ctx->ev_join);
+    for (cudaEvent_t e : ctx->spec.ev) cudaEventDestroy(e);
     for (int i = 0; i < 12; ++i) if (ctx->scratch[i]) cudaFree(ctx->scratch[i]);
     for (auto &f : ctx->fam) for (auto &p : f.pending) { cudaEventDestroy(p.first); cudaEventDestroy(p.second); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->stream);
@@ -72,7 +82,7 @@ extern "C" void gk_ctx_destroy(gk_ctx *ctx) {
 
 extern "C" int gk_ctx_set_option(gk_ctx *ctx, int option, int value) {
     if (!ctx) return GK_EINVAL;
-    if (option == GK_CTX_OPT_SBM_OVERLAP && value >= 0 && value <= 2) { ctx->sbm_overlap_mode = value; return GK_OK; }
+    if (option == GK_CTX_OPT_SBM_OVERLAP && value >= 0 && value <= 3) { if (value != 3) gk_spec_cancel(ctx); ctx->sbm_overlap_mode = value; return GK_OK; }
     return gk_fail(ctx, GK_EINVAL, "gk_ctx_set_option: unknown option %d or value %d", option, value);
 }
 
@@ -103,6 +113,7 @@ extern "C" int gk_ctx_kernel_timing(gk_ctx *ctx, int enable) {
 extern "C" int gk_ctx_kernel_timing_read(gk_ctx *ctx, int family, double *ms, int64_t *launches, double *bytes) {
     if (!ctx || family < 0 || family >= GK_NFAMILY) return GK_EINVAL;
     GK_CUDA(ctx, cudaStreamSynchronize(ctx->stream));
+    if (ctx->aux) GK_CUDA(ctx, cudaStreamSynchronize(ctx->aux));      // kernels of the overlapped / speculated strip passes
     gk_timing &f = ctx->fam[family];
     for (size_t i = 0; i < f.pending.size(); ++i) {
         float t = 0.f;
@@ -180,6 +191,7 @@ extern "C" int gk_network_create(gk_ctx *ctx, int N, int B, int dev_dtype, int r
 
 extern "C" int gk_network_destroy(gk_ctx *ctx, gk_net *net) {
     if (ctx && ctx->last_cells.net == net) { ctx->last_cells.valid = false; ctx->last_cells.net = nullptr; }
+    if (ctx && ctx->spec.net == (const void *)net) { gk_spec_cancel(ctx); ctx->spec.net = nullptr; }
     if (!net) return GK_OK;
     if (ctx) { cudaSetDevice(ctx->device); cudaStreamSynchronize(ctx->stream); }
     cudaFree(net->A); cudaFree(net->At); cudaFree(net->W); cudaFree(net->Wt);
@@ -214,6 +226,7 @@ extern "C" int gk_network_upload(gk_ctx *ctx, gk_net *net, const uint8_t *A_rows
                                  const uint8_t *At_rows, const void *Wt_rows) {
     if (ctx && ctx->last_cells.net == net) ctx->last_cells.valid = false;      // statistics of the previous data
     if (ctx && ctx->last_sweep_net == (const void *)net) ctx->last_sweep_moves = -1;
+    if (ctx && ctx->spec.net == (const void *)net) gk_spec_cancel(ctx);
     if (!ctx || !net || !A_rows) return GK_EINVAL;
     if (net->B && !W_rows) return gk_fail(ctx, GK_EINVAL, "W required when B > 0");
     bool whole = net->row0 == 0 && net->nrows == net->N;

@@ -37,10 +37,13 @@ struct gk_ctx {
     bool attr_done[64] = {false};
     std::vector<const void *> attr_funcs;     // kernels whose attributes this context has set
     bool sbm_prof = false;                    // env GK_SBM_PROF, read once at context creation
-    int sbm_overlap_mode = 1;                 // gk_ctx_set_option(GK_CTX_OPT_SBM_OVERLAP): 0 never, 1 when the last sweep moved few nodes, 2 always
+    int sbm_overlap_mode = 3;                 // gk_ctx_set_option(GK_CTX_OPT_SBM_OVERLAP): 0 never, 1 block b+1 beside block b after a sweep with few movers, 2 the same always, 3 (default) = 1 + the next sweep's strip passes speculated in the background
     bool sbm_overlap = true;                  // env GK_SBM_NO_OVERLAP clears it: strip pass of block b+1 beside the serial kernel of block b
     cudaStream_t aux = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // second (low-priority) stream of that overlap, created on first use
     long long last_sweep_moves = -1; const void *last_sweep_net = nullptr;   // moves of the last unsharded gk_sbm_sweep (and on which network)
+    // whole-sweep speculation of gk_sbm_sweep: strip passes of the next sweep running on `aux` from the labels in spec_labels
+    struct { bool active = false, self = false; const void *net = nullptr; int K = 0, bn = 0, N = 0, nblk = 0;
+             std::vector<int32_t> labels; std::vector<cudaEvent_t> ev; } spec;
     bool fork_after_lp = false;               // launch_sample records ev_fork between k_lp_from_stats and the serial kernel
 };
 
@@ -75,6 +78,7 @@ static inline bool gk_attr_needed(gk_ctx *ctx, const void *f) {
 int gk_net_refresh_asym(gk_ctx *ctx, gk_net *net);  // recomputes an existing net->Asym after a re-upload; gk_eig.cu
 int gk_net_ensure_asym(gk_ctx *ctx, gk_net *net);   // builds net->Asym = A + A^T (zero diagonal) once; gk_eig.cu
 void *gk_scratch(gk_ctx *ctx, int slot, size_t bytes);
+void gk_spec_cancel(gk_ctx *ctx);                  // waits for and discards background strip passes (gk_sbm.cu speculation)
 // gk_eig_tc.cu: the full Omega . (F (x) F) contraction on tcgen05 tensor cores fed by TMA (fp32 storage, D = 8)
 size_t gk_tc_work_bytes(int npad);
 int gk_tc_gfull(gk_ctx *ctx, const float *S, const uint8_t *Asym, int ld, int N, const double *F, void *work, float *partial,

@@ -497,6 +497,70 @@ __global__ void __launch_bounds__(128) k_stats_fix(const uint8_t *__restrict__ A
     }
 }
 
+// Whole-sweep speculation (gk_sbm_sweep, GK_CTX_OPT_SBM_OVERLAP = 3): the strip passes of ALL node blocks of the next sweep run
+// in the background from the labels the previous sweep ended on.  k_append_movers lists, block after block, the nodes whose label
+// differs from that snapshot (index order; a node moves at most once per sweep, so N entries suffice); k_stats_fix_list moves the
+// terms of every listed mover in the rows of the block about to be drawn -- the list then holds exactly the movers of the earlier
+// blocks of this sweep.
+__global__ void __launch_bounds__(1024) k_append_movers(const uint8_t *__restrict__ c_spec, const uint8_t *__restrict__ c8, int p0, int pn,
+                                                        int *__restrict__ cnt, int *__restrict__ list) {
+    __shared__ int s_w[32], s_base;
+    const int tid = threadIdx.x;
+    if (tid == 0) s_base = *cnt;
+    for (int base = 0; base < pn; base += 1024) {
+        const int i = base + tid;
+        const bool mv = i < pn && c_spec[p0 + i] != c8[p0 + i];
+        const unsigned bal = __ballot_sync(0xffffffffu, mv);
+        if ((tid & 31) == 0) s_w[tid >> 5] = __popc(bal);
+        __syncthreads();
+        int off = s_base;
+        for (int w = 0; w < (tid >> 5); ++w) off += s_w[w];
+        if (mv) {
+            const int pos = off + __popc(bal & ((1u << (tid & 31)) - 1));
+            list[3 * pos] = p0 + i; list[3 * pos + 1] = c_spec[p0 + i]; list[3 * pos + 2] = c8[p0 + i];
+        }
+        __syncthreads();
+        if (tid == 0) { int t = 0; for (int w = 0; w < 32; ++w) t += s_w[w]; s_base += t; }
+        __syncthreads();
+    }
+    if (tid == 0) *cnt = s_base;
+}
+
+template <typename T, int B>
+__global__ void __launch_bounds__(128) k_stats_fix_list(const uint8_t *__restrict__ A, const uint8_t *__restrict__ At, const void *__restrict__ Wv,
+                                                        const void *__restrict__ Wtv, int ld, const int *__restrict__ cnt,
+                                                        const int *__restrict__ list, int n0, int nb, int K, double *__restrict__ stats) {
+    constexpr int S = gk_sdim<B>::S;
+    const int nm = *cnt, tid = threadIdx.x;
+    const int dir = tid >> 6, i = blockIdx.x * 64 + (tid & 63);
+    if (nm == 0 || i >= nb) return;
+    const int n = n0 + i, KS = K * S;
+    const uint8_t *E = dir ? A : At;                                // dir 0: edge n -> m (out half), dir 1: edge m -> n (in half)
+    const T *X = (const T *)(dir ? Wv : Wtv);
+    double *row = stats + ((size_t)i * 2 + dir) * KS;
+    for (int q0 = 0; q0 < nm; q0 += 8) {
+        unsigned char e[8];
+#pragma unroll
+        for (int t = 0; t < 8; ++t) e[t] = (q0 + t < nm) ? E[(size_t)list[3 * (q0 + t)] * ld + n] : 0;
+#pragma unroll
+        for (int t = 0; t < 8; ++t) {
+            if (!e[t]) continue;
+            const int m = list[3 * (q0 + t)], a = list[3 * (q0 + t) + 1], b = list[3 * (q0 + t) + 2];
+            double x[S]; x[0] = 1.0;
+            if constexpr (B > 0) {
+#pragma unroll
+                for (int d = 0; d < B; ++d) x[1 + d] = (double)X[((size_t)m * ld + n) * B + d];
+#pragma unroll
+                for (int d = 0; d < B; ++d)
+#pragma unroll
+                    for (int d2 = d; d2 < B; ++d2) x[gk_sym_idx(B, d, d2)] = x[1 + d] * x[1 + d2];
+            }
+#pragma unroll
+            for (int u = 0; u < S; ++u) { row[a * S + u] -= x[u]; row[b * S + u] += x[u]; }
+        }
+    }
+}
+
 // c (int32) -> c8 and block sizes are prepared on the host; this just narrows the labels on the device
 __global__ void k_narrow_labels(const int32_t *__restrict__ c, uint8_t *__restrict__ c8, int N) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < N; i += gridDim.x * blockDim.x) c8[i] = (uint8_t)c[i];

@@ -42,9 +42,12 @@ void gk_ctx_destroy(gk_ctx *ctx);
 const char *gk_last_error(gk_ctx *ctx);
 int gk_ctx_set_stream(gk_ctx *ctx, void *cuda_stream);      /* e.g. torch's current stream handle */
 int gk_ctx_synchronize(gk_ctx *ctx);
-/* engine options.  GK_CTX_OPT_SBM_OVERLAP: gk_sbm_sweep runs the strip pass of node block b+1 beside the serial kernel of
- * block b (same results) -- 0 never, 1 (default) when the previous sweep on the network moved <= 256 nodes,
- * 2 always. */
+/* engine options.  GK_CTX_OPT_SBM_OVERLAP: how gk_sbm_sweep schedules its strip passes (same results in every mode):
+ * 0 each block's strip pass, then its serial kernel; 1 the strip pass of node block b+1 beside the serial kernel of block b when
+ * the previous sweep on the network moved <= 256 nodes; 2 the same always; 3 (default) as 1, and a sweep that moved <= 256 nodes
+ * leaves the strip passes of EVERY block of the next sweep running in the background from its final labels -- they overlap the
+ * caller's host work; the next sweep uses them if it is called with those labels on that network and corrects them for the
+ * nodes that move meanwhile; any other use of the engine's scratch buffers or a re-upload cancels them. */
 enum { GK_CTX_OPT_SBM_OVERLAP = 1 };
 int gk_ctx_set_option(gk_ctx *ctx, int option, int value);
 int64_t gk_ctx_launch_count(gk_ctx *ctx);                   /* kernels launched so far by this ctx */

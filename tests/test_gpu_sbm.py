@@ -176,7 +176,7 @@ def test_overlapped_sweep_equals_the_serial_order(N, K, B, dtype, bn):
                 res.append((c.copy(), lp.copy(), nch, net.sbm_sweep_stats(K)))
             out[mode] = res
     finally:
-        net.ctx.set_option(_lib.CTX_OPT_SBM_OVERLAP, 1)
+        net.ctx.set_option(_lib.CTX_OPT_SBM_OVERLAP, 3)
     tol = 1e-9 if dtype == "f64" else 1e-3
     for it in range(3):
         (ca, lpa, na, sa), (cb, lpb, nb_, sb) = out[0][it], out[2][it]
@@ -188,6 +188,61 @@ def test_overlapped_sweep_equals_the_serial_order(N, K, B, dtype, bn):
     c_ref, _ = sbm.sbm_assign_sweep(A.astype(float), Wd, c0, m, p, mus if B else None, sig if B else None, us[0], sbm.SELF_OLD)
     assert np.array_equal(out[2][0][0], c_ref)
     assert out[2][0][2] > N // 4, "the first sweep must exercise the correction (many movers)"
+
+
+@pytest.mark.parametrize("N,K,B,dtype,bn", [(2300, 4, 2, "f64", 256), (1500, 6, 1, "f32", 128), (1200, 5, 0, "f32", 64), (1100, 4, 3, "f64", 256)])
+def test_speculated_sweep_equals_the_serial_order(N, K, B, dtype, bn):
+    """GK_CTX_OPT_SBM_OVERLAP = 3: a sweep that moved few nodes leaves the strip passes of every block of the NEXT sweep running in
+    the background from its final labels; the next sweep corrects them block by block for the nodes that move meanwhile
+    (k_append_movers / k_stats_fix_list).  Six sweeps from lightly perturbed labels with the block probabilities shaken every
+    sweep (so that nodes keep moving while the speculation is in use), a call in between that claims the scratch buffers, and a
+    re-upload: labels, move counts, conditionals and the K1 table equal the serial order (mode 0) throughout."""
+    from graphistician_b200 import _lib
+    A, W, c_true, m, p, mus, sig, u = _problem(9 * N + K, N, K, B)
+    net, Wd = _net(A, W, dtype)
+    rng = np.random.RandomState(N + 2)
+    c0 = c_true.copy()
+    flip = rng.choice(N, 40, replace=False)
+    c0[flip] = rng.randint(0, K, 40)
+    us = [rng.rand(N) for _ in range(6)]
+
+    def run(mode, beta):
+        net.ctx.set_option(_lib.CTX_OPT_SBM_OVERLAP, mode)
+        c, res = c0.copy(), []
+        for it in range(6):
+            c, lp, nch = net.sbm_sweep(c, np.log(m), p, mus if B else None, sig if B else None, us[it], block_nodes=bn, want_lp=True, beta=beta)
+            res.append((c.copy(), lp.copy(), nch, net.sbm_sweep_stats(K)))
+            if it == 2:
+                net.block_stats(c, K)                      # another user of the scratch buffers: the speculation must give way
+            if it == 4:
+                net.upload(A, Wd)                          # new data behind the same handle: the speculation must be dropped
+        return res
+
+    out = {}
+    try:
+        # a temperature at which a few nodes (but never more than 256, the regime that arms the speculation) move in every sweep
+        for beta in (0.05, 0.02, 0.01, 0.006, 0.004, 0.003, 0.002, 0.0015, 0.001, 0.0007, 0.0005):
+            out[0] = run(0, beta)
+            if all(1 <= r[2] <= 256 for r in out[0]):
+                break
+        else:
+            pytest.skip("no temperature with 1..256 movers per sweep for this problem")
+        out[3] = run(3, beta)
+    finally:
+        net.ctx.set_option(_lib.CTX_OPT_SBM_OVERLAP, 3)
+    tol = 1e-9 if dtype == "f64" else 1e-3
+    moved_under_speculation = 0
+    for it in range(6):
+        (ca, lpa, na, sa), (cb, lpb, nb_, sb) = out[0][it], out[3][it]
+        assert np.array_equal(ca, cb) and na == nb_, it
+        assert np.allclose(lpa, lpb, rtol=tol, atol=tol * 1e-2 * np.abs(lpa).max()), it
+        if sb is not None:
+            n_edge, sw, sww = net.block_stats(cb, K)
+            assert np.array_equal(sb[0], n_edge), it
+        if it in (1, 2, 4):
+            moved_under_speculation += nb_
+    assert moved_under_speculation > 0, "nodes must move while a speculation is in use"
+    assert max(r[2] for r in out[0]) <= 256, "every sweep must stay in the regime that arms the speculation"
 
 
 def test_sweep_with_exact_zero_and_one_probabilities():
