@@ -472,6 +472,13 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
     }
     int bn = block_nodes > 0 ? block_nodes : 1024;
     bn = std::max(GK_STRIP_COLS, bn / GK_STRIP_COLS * GK_STRIP_COLS);
+    // background strip passes left by the previous sweep (mode 3, below): matched -- or waited for and dropped -- BEFORE any
+    // scratch buffer they use can be resized
+    const int nblk = (N + bn - 1) / bn;
+    bool spec = ctx->spec.active && ctx->spec.net == (const void *)net && ctx->spec.K == K && ctx->spec.bn == bn && ctx->spec.N == N &&
+                !ctx->sbm_prof && memcmp(ctx->spec.labels.data(), c_inout, (size_t)N * 4) == 0;
+    if (ctx->spec.active && !spec) gk_spec_cancel(ctx);
+    ctx->spec.active = false;                     // consumed (or cancelled); re-armed at the end of this sweep
     // per-node statistics of the whole sweep stay resident ([N_pad][2][K*S] doubles): their in-edge half, folded with the labels
     // the sweep ends on, IS the K1 table of the next resample() -- no third pass over A / W (gk_sbm_sweep_stats)
     const int KS = K * sw->S;
@@ -497,11 +504,6 @@ extern "C" int gk_sbm_sweep(gk_ctx *ctx, gk_net *net, int32_t *c_inout, int K, c
     const bool few = ctx->last_sweep_net == (const void *)net && ctx->last_sweep_moves >= 0 && ctx->last_sweep_moves <= 256;
     // Whole-sweep speculation (mode 3): the previous sweep left the strip passes of ALL blocks of this one running on the second
     // stream, from the labels it ended on.  They are this sweep's statistics if the caller comes back with those labels.
-    const int nblk = (N + bn - 1) / bn;
-    bool spec = ctx->spec.active && ctx->spec.net == (const void *)net && ctx->spec.K == K && ctx->spec.bn == bn && ctx->spec.N == N &&
-                !ctx->sbm_prof && memcmp(ctx->spec.labels.data(), c_inout, (size_t)N * 4) == 0;
-    if (ctx->spec.active && !spec) gk_spec_cancel(ctx);
-    ctx->spec.active = false;                     // consumed (or cancelled); re-armed at the end of this sweep
     const bool overlap = !spec && !ctx->sbm_prof && bn <= 2048 && N > bn &&
                          (ctx->sbm_overlap_mode == 2 || (ctx->sbm_overlap_mode == 1 && few) || (ctx->sbm_overlap_mode == 3 && few));
     int *spec_cnt = nullptr, *spec_list = nullptr;
