@@ -320,6 +320,16 @@ def make_ref_ais(R):
         out["rho_new_%d" % bi] = er.sample_theta((A, None), beta=beta)
         out["sbm_logpr_%d" % bi] = sbm.logpr(A, list(z), (Bm, pi), beta=beta)
         out["er_logpr_%d" % bi] = er.logpr(A, [None] * N, 0.31, beta=beta)
+    # collapsed_sample_f (:299-335; unused by the reference's drivers): it draws inside its r loop, so the recorder sees R
+    # vectors per call -- the last one is the complete ln_pi_post, and the label returned is the draw made from it
+    cn = np.array([0, 5, N - 1])
+    uc = rng.rand(len(cn), Rb)
+    out["coll_nodes"], out["coll_u"] = cn, uc
+    for k, n in enumerate(cn):
+        REC.reset(); REC.uniforms = list(uc[k])
+        zn = sbm.collapsed_sample_f((Bm, pi), int(n), A, list(z))
+        out["coll_lp_%d" % k] = np.array(REC.lp[-1]); out["coll_z_%d" % k] = int(zn)
+        assert len(REC.lp) == Rb
     _save("ref_ais.npz", out)
 
 

@@ -274,6 +274,17 @@ def test_ais_tempered_steps_are_the_references():
         assert np.isclose(rs.beta(1.0 + beta * A.sum(), 1.0 + beta * (N * N - A.sum())), g["rho_new_%d" % bi], rtol=1e-13)
 
 
+def test_ais_collapsed_sampler_is_the_references():
+    """internals/graph_models.py:299-335 (collapsed_sample_f) executed on the reference's own class: the complete log
+    posterior vector and the label drawn from it (the R-th uniform: the reference draws once per candidate, :331-333)."""
+    g = load("ref_ais.npz")
+    A, z, pi = g["A"].astype(float), g["z"], g["pi"]
+    for k, n in enumerate(g["coll_nodes"]):
+        lp = sbm.ais_collapsed_ln_post_loops(A, z, int(n), pi, 1.0, 1.0)
+        assert np.allclose(lp, g["coll_lp_%d" % k], rtol=1e-12, atol=1e-10)
+        assert sbm.log_sum_exp_sample(lp, g["coll_u"][k][-1]) == int(g["coll_z_%d" % k])
+
+
 # ---------------------------------------------------------------------------------------------- mean-field SBM
 def _wexp_from(niw_arr, B):
     C = niw_arr.shape[0]
