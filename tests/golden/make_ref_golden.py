@@ -632,8 +632,33 @@ def make_ref_shared_cov(R):
     _save("ref_shared_cov.npz", out)
 
 
+# --------------------------------------------------------------------------------------------------
+# internals/weights.py:174-198: GaussianWeights.expected_log_likelihood, the N^2 negentropy loop, on the reference's class
+# --------------------------------------------------------------------------------------------------
+def make_ref_gw_ell(R):
+    rng = np.random.RandomState(20251)
+    N, B = 6, 2
+    A = (rng.rand(N, N) < 0.5).astype(np.float64)
+    W = rng.randn(N, N, B)
+    net = R.Network(A, W)
+    out = dict(A=A.astype(np.uint8), W=W)
+    X = rng.randn(B, B)
+    hyp = [dict(), dict(mu_0=np.array([0.4, -1.1]), Sigma_0=X.dot(X.T) + 0.7 * np.eye(B), nu_0=6.5, kappa_0=2.5)]
+    for k, h in enumerate(hyp):
+        np.random.seed(70 + k)                 # pybasicbayes' Gaussian draws its state (and the shim's stand-in its q) at construction
+        gw = R.iweights.GaussianWeights(B, **h)
+        if k == 1:                             # a q away from the prior: one mean-field update on the network
+            gw.meanfieldupdate(net, np.ones((N, N)))
+        out["ell_%d" % k] = float(gw.expected_log_likelihood(net))
+        out["q_%d_mu" % k], out["q_%d_sigma" % k] = np.array(gw.mu_mf), np.array(gw.sigma_mf)
+        out["q_%d_kappa" % k], out["q_%d_nu" % k] = float(gw.kappa_mf), float(gw.nu_mf)
+        for name, v in h.items():
+            out["hyp_%d_%s" % (k, name)] = np.asarray(v)
+    _save("ref_gw_ell.npz", out)
+
+
 if __name__ == "__main__":
     R = ref_shim.load_reference()
-    which = sys.argv[1:] or ["sbm", "adjacency", "latent", "weights", "eigen", "ais", "mf_sbm", "mf_eigen", "predictive", "latent_weights", "shared_cov"]
+    which = sys.argv[1:] or ["sbm", "adjacency", "latent", "weights", "eigen", "ais", "mf_sbm", "mf_eigen", "predictive", "latent_weights", "shared_cov", "gw_ell"]
     for w in which:
         globals()["make_ref_" + w](R)

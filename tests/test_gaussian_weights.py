@@ -75,3 +75,17 @@ def test_expected_log_likelihood_sums_the_per_pair_negentropy():
     net = types.SimpleNamespace(W=W, E_W=W, E_WWT=W[:, :, :, None] * W[:, :, None, :])
     assert np.isclose(gw.expected_log_likelihood(net), ell, rtol=1e-12)
     assert np.isclose(gw.expected_log_likelihood(types.SimpleNamespace(W=W)), ell, rtol=1e-12)
+
+
+def test_expected_log_likelihood_is_the_references():
+    """internals/weights.py:174-198 executed on the reference's own GaussianWeights (tests/golden/make_ref_golden.py gw_ell)
+    against the three-sums form: at the q the reference object was constructed with, and after one of its mean-field updates."""
+    import os
+    import types
+    from graphistician_b200.internals.weights import GaussianWeights
+    g = np.load(os.path.join(os.path.dirname(__file__), "golden", "ref_gw_ell.npz"))
+    net = types.SimpleNamespace(W=g["W"], E_W=g["W"], E_WWT=g["W"][:, :, :, None] * g["W"][:, :, None, :])
+    for k in (0, 1):
+        gw = GaussianWeights(2)
+        gw.mf_natural_hypparam = gw._standard_to_natural(g["q_%d_mu" % k], g["q_%d_sigma" % k], float(g["q_%d_kappa" % k]), float(g["q_%d_nu" % k]))
+        assert np.isclose(gw.expected_log_likelihood(net), float(g["ell_%d" % k]), rtol=1e-10), k
