@@ -750,6 +750,15 @@ def bench_ais(args, R, steps, warmup, cpu=True, scan=(8, 32, 512)):
                     "(the start of an AIS ladder, the per-node path of k_ais_seq); `stationary` is the other end"
     rec["n_changed_mean_last_sweep"] = float(dev.sweep(lpi, Bm, beta, seed=7)[0].mean())
     rec["stationary"] = stationary(dev, P)
+    # the whole of estimate_marginal_likelihood (examples/demo_ais.py:10-62) for these P particles in one C call (gk_ais_run):
+    # 100 temperatures x 2 Gibbs steps from uniformly drawn labels, conjugate draws on the host, wall clock
+    t0 = time.perf_counter()
+    w = dev.run(1, 1.0, 1.0, alpha0, 100, 2, f0=rng.randint(0, Rk, N), seed=1234 + R.rank)
+    t_ladder = time.perf_counter() - t0
+    from scipy.special import logsumexp
+    rec["ladder"] = {"n_temps": 100, "steps_per_temp": 2, "particles": P, "seconds": t_ladder,
+                     "particle_sweeps_per_s": P * 198 / t_ladder, "log_Z": float(-np.log(P) + logsumexp(w)),
+                     "log_weight_std": float(np.std(w))}
     dev.close()
     rec["particle_scan"] = {str(P): {"value": rec["value"], "ms_per_step": rec["ms_per_step"], "stationary": rec["stationary"]["value"]}}
     for Ps in scan:                                            # P swept per GPU (resident sweeps only)
