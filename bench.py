@@ -162,7 +162,8 @@ def make_eigen_data(N, D, seed=1234, rank=0, p=0.01, pin=True):
         g = _chunk_rng(seed, rank, i)
         eta = F[r0:r1] @ F.T + mu0
         eta[np.arange(r1 - r0), np.arange(r0, r1)] = mu0
-        A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < 1.0 / (1.0 + np.exp(-eta))
+        with np.errstate(over="ignore"):           # eta <= 0: exp(-eta) may reach inf, and 1 / (1 + inf) = 0 is the value wanted
+            A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < 1.0 / (1.0 + np.exp(-eta))
     _fill_rows(N, fill)
     return dict(A=A, W=None, F=F, mu0=float(mu0), _keep=(keepA,))
 
@@ -179,7 +180,8 @@ def make_latent_data(N, dim, B=1, seed=1234, rank=0, sigma=2.0, pin=True):
     def fill(i, r0, r1):
         g = _chunk_rng(seed, rank, i)
         eta = -(sq[r0:r1, None] + sq[None, :] - 2.0 * (L[r0:r1] @ L.T))
-        A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < 1.0 / (1.0 + np.exp(-eta))
+        with np.errstate(over="ignore"):           # eta <= 0: exp(-eta) may reach inf, and 1 / (1 + inf) = 0 is the value wanted
+            A[r0:r1] = g.random((r1 - r0, N), dtype=np.float32) < 1.0 / (1.0 + np.exp(-eta))
         W[r0:r1] = g.standard_normal((r1 - r0, N, B), dtype=np.float32)
     _fill_rows(N, fill)
     return dict(A=A, W=W, L=L, _keep=(keepA, keepW))
@@ -603,7 +605,7 @@ def _ais_cpu_nodes(N, R, z_true, Bt, z, Bm, pi, beta, lo, hi, seed=3):
 
 
 def cpu_baseline_ais(args, N, R, nodes=None):
-    nodes = nodes or args.cpu_nodes or 4096
+    nodes = min(N, nodes or args.cpu_nodes or 4096)
     z_true, Bt, pi = ais_truth(N, R)
     z = np.random.RandomState(1).randint(0, R, N)
     t0 = time.perf_counter()
@@ -983,8 +985,9 @@ def reference_ais(args, procs):
     forked worker per usable core, scaled to full feature sweeps (a particle's sweep is serial; particles are independent,
     so `procs` cores run `procs` particles side by side)."""
     import multiprocessing as mp
-    N, R, per = args.ais_n, 3, 1024
-    tasks = [(k * per, (k + 1) * per, N, R) for k in range(procs)]
+    N, R = args.ais_n, 3
+    per = min(1024, N)
+    tasks = [((k * per) % (N - per + 1), (k * per) % (N - per + 1) + per, N, R) for k in range(procs)]
     t0 = time.perf_counter()
     with mp.get_context("fork").Pool(procs) as pool:
         secs = pool.map(_ais_ref_task, tasks, chunksize=1)
@@ -997,7 +1000,7 @@ def reference_ais(args, procs):
             "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": cfg,
             "cpu_baseline": {"value": value, "unit": AIS_UNIT, "cores": procs, "kind": "port",
                              "sample": "%d nodes of one particle's feature sweep per core on %d cores (oracle count form, NumPy), "
-                                       "%.1f s wall; scaled x%d to full sweeps, %d particles side by side" % (per, procs, wall, N // per, procs)},
+                                       "%.1f s wall; scaled x%.1f to full sweeps, %d particles side by side" % (per, procs, wall, N / float(per), procs)},
             "e2e": {"value": value, "unit": AIS_UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}, "host": host_info()}
 
 
