@@ -51,7 +51,7 @@ int gk_ctx_synchronize(gk_ctx *ctx);
 enum { GK_CTX_OPT_SBM_OVERLAP = 1 };
 int gk_ctx_set_option(gk_ctx *ctx, int option, int value);
 int64_t gk_ctx_launch_count(gk_ctx *ctx);                   /* kernels launched so far by this ctx */
-/* per-kernel CUDA-event timing (bench.py roofline); family: 0 = strip statistics kernel,
+/* per-kernel CUDA-event timing (bench.py roofline; measurement only, no counterpart in the reference); family: 0 = strip statistics kernel,
  * 1 = sequential sampler, 2 = Polya-gamma draw, 3 = eigen slab contraction, 4 = latent pairwise,
  * 5 = eigen sequential feature draw, 6 = mean-field soft strip statistics, 7 = mean-field sequential update */
 int gk_ctx_kernel_timing(gk_ctx *ctx, int enable);
@@ -142,6 +142,8 @@ enum { GK_EIG_OPT_CHOL_F64 = 0,
        /* 1 (default): with fp32 storage, D = 8 and the logistic link the once-per-sweep contraction G = S . Phi runs on the
         * tcgen05 tensor cores fed by TMA (tf32 operands, fp32 accumulation in tensor memory); 0: the FMA kernel k_eig_gfull */
        GK_EIG_OPT_TC = 4 };
+/* scheduling / kernel choices of the engine, for A/B measurements and the parity tests; every setting draws from the same
+ * conditionals (eigenmodel.py:871-943) -- the reference has no such switch */
 int gk_eig_set_option(gk_ctx *ctx, gk_eig *eig, int option, int value);
 /* upload the model attributes F (N x D), mu_0, lmbda (D)  (eigenmodel.py:41-73 state) */
 int gk_eig_set_params(gk_ctx *ctx, gk_eig *eig, const double *F, double mu0, const double *lmbda);
